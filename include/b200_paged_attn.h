@@ -1,0 +1,165 @@
+/*
+ * b200_paged_attn.h -- C ABI of the B200-native paged-decode hot path.
+ *
+ * This is the drop-in boundary: plain pointers, sizes and enums, no torch types.
+ * Each entry point replaces one launcher of the reference (paths relative to the
+ * reference repository root):
+ *
+ *   b200pa_paged_attention_v1       csrc/attention/paged_attention_v1.cu:160-182
+ *                                   (launcher :46-125; schema csrc/torch_bindings.cpp:52-62)
+ *   b200pa_paged_attention_v2       csrc/attention/paged_attention_v2.cu:167-192
+ *                                   (launcher :47-126; schema csrc/torch_bindings.cpp:66-76)
+ *   b200pa_reshape_and_cache        csrc/cache_kernels.cu:416-442
+ *                                   (schema csrc/torch_bindings.cpp:667-673)
+ *   b200pa_reshape_and_cache_flash  csrc/cache_kernels.cu:459-497
+ *                                   (schema csrc/torch_bindings.cpp:676-682)
+ *   b200pa_convert_fp8              csrc/cache_kernels.cu:573-623
+ *                                   (schema csrc/torch_bindings.cpp:696-699)
+ *   b200pa_get_max_shared_memory_per_block_device_attribute
+ *                                   csrc/cuda_utils_kernels.cu (schema
+ *                                   csrc/torch_bindings.cpp:718-730)
+ *
+ * Conventions
+ *   - All data pointers are DEVICE pointers on the current CUDA device; strides
+ *     are in ELEMENTS of the pointed-to type, exactly the values the reference
+ *     launchers read from the tensors (query.stride(0), key_cache.stride(0), ...).
+ *   - k_scale / v_scale are DEVICE pointers to one fp32 (read in-kernel; no host
+ *     sync, CUDA-graph capturable), as in the reference kernels.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *   - Every launcher is asynchronous, allocates nothing, keeps no state, and
+ *     mutates only the buffers documented as outputs.
+ *   - Return 0 on success.  Non-zero = the configuration is outside the supported
+ *     domain or the launch failed; b200pa_last_error() then returns a message
+ *     (thread-local, valid until the next call on the same thread).  The torch
+ *     shim turns that into TORCH_CHECK(false, msg) -> Python RuntimeError, which
+ *     is the reference's error convention (paged_attention_v1.cu:122,156).
+ *   - There is NO CPU fallback: without a CUDA device every compute entry point
+ *     fails with B200PA_ERR_CUDA.
+ */
+#ifndef B200_PAGED_ATTN_H_
+#define B200_PAGED_ATTN_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200PA_ABI_VERSION 1
+
+/* scalar_t of query / out / key / value (reference: VLLM_DISPATCH_FLOATING_TYPES) */
+enum { B200PA_F32 = 0, B200PA_F16 = 1, B200PA_BF16 = 2 };
+/* vllm::Fp8KVCacheDataType (csrc/attention/dtype_fp8.cuh:15-19) */
+enum { B200PA_KV_AUTO = 0, B200PA_KV_FP8_E4M3 = 1, B200PA_KV_FP8_E5M2 = 2 };
+
+enum {
+  B200PA_OK = 0,
+  B200PA_ERR_UNSUPPORTED = 1, /* head size / block size / dtype outside the domain */
+  B200PA_ERR_INVALID = 2,     /* inconsistent arguments */
+  B200PA_ERR_CUDA = 3         /* CUDA runtime error (no device, launch failure) */
+};
+
+/* which kernel family b200pa_paged_attention_v1/v2 may use (tests, A/B runs) */
+enum {
+  B200PA_IMPL_AUTO = 0,    /* fast path when the shape is covered, else generic */
+  B200PA_IMPL_GENERIC = 1, /* SIMT kernel, whole reference domain */
+  B200PA_IMPL_FAST = 2     /* TMA-staged tensor-core kernel; error if not covered */
+};
+
+int b200pa_abi_version(void);
+const char* b200pa_last_error(void);
+
+/* "auto" | "fp8" | "fp8_e4m3" | "fp8_e5m2" -> B200PA_KV_*; -1 if unknown
+ * (DISPATCH_BY_KV_CACHE_DTYPE, quant_utils.cuh:545-582). */
+int b200pa_kv_dtype_from_string(const char* kv_cache_dtype);
+
+/* Process-wide override of the kernel family (default B200PA_IMPL_AUTO). */
+void b200pa_set_impl(int impl);
+int b200pa_get_impl(void);
+/* Number of kernels launched by this library so far in this process. */
+uint64_t b200pa_launch_count(void);
+
+/*
+ * out[num_seqs, num_heads, head_size]                      (written)
+ * query[num_seqs, num_heads, head_size], row stride q_stride
+ * key_cache[num_blocks, num_kv_heads, head_size/x, block_size, x]
+ * value_cache[num_blocks, num_kv_heads, head_size, block_size]
+ *   x = 16 / sizeof(cache element); strides kv_block_stride, kv_head_stride
+ * block_tables[num_seqs, max_num_blocks_per_seq] int32, seq_lens[num_seqs] int32
+ * alibi_slopes[num_heads] fp32 or NULL
+ */
+int b200pa_paged_attention_v1(
+    void* out, const void* query, const void* key_cache, const void* value_cache,
+    int num_seqs, int num_heads, int num_kv_heads, int head_size, int block_size,
+    float scale, const int32_t* block_tables, int max_num_blocks_per_seq,
+    const int32_t* seq_lens, int max_seq_len, const float* alibi_slopes,
+    int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
+    int scalar_type, int kv_dtype, const float* k_scale, const float* v_scale,
+    int tp_rank, int blocksparse_local_blocks, int blocksparse_vert_stride,
+    int blocksparse_block_size, int blocksparse_head_sliding_step, void* stream);
+
+/*
+ * Split-K variant.  Caller-provided scratch, reference shapes:
+ *   exp_sums, max_logits [num_seqs, num_heads, max_num_partitions] fp32
+ *   tmp_out              [num_seqs, num_heads, max_num_partitions, head_size] scalar_t
+ * with max_num_partitions >= ceil(max_seq_len / 512)  (_PARTITION_SIZE,
+ * vllm/attention/ops/paged_attn.py:21).  Scratch contents after the call: every
+ * slot j < ceil(seq_len/512) of a (seq, head) holds a valid partial
+ * (normalised partial output, its exp-sum and max logit) over a contiguous token
+ * range or has exp_sum == 0 ("merged into an earlier slot"); `out` is the
+ * contract.
+ */
+int b200pa_paged_attention_v2(
+    void* out, float* exp_sums, float* max_logits, void* tmp_out,
+    const void* query, const void* key_cache, const void* value_cache,
+    int num_seqs, int num_heads, int num_kv_heads, int head_size, int block_size,
+    float scale, const int32_t* block_tables, int max_num_blocks_per_seq,
+    const int32_t* seq_lens, int max_seq_len, int max_num_partitions,
+    const float* alibi_slopes, int64_t q_stride, int64_t kv_block_stride,
+    int64_t kv_head_stride, int scalar_type, int kv_dtype, const float* k_scale,
+    const float* v_scale, int tp_rank, int blocksparse_local_blocks,
+    int blocksparse_vert_stride, int blocksparse_block_size,
+    int blocksparse_head_sliding_step, void* stream);
+
+/*
+ * key, value [num_tokens, num_heads, head_size] scalar_t, row strides key_stride /
+ * value_stride; slot_mapping[num_tokens] int64 (slot < 0: token skipped);
+ * caches in the x-packed layout above (dense, as the reference indexes them).
+ */
+int b200pa_reshape_and_cache(
+    const void* key, const void* value, void* key_cache, void* value_cache,
+    const int64_t* slot_mapping, int num_tokens, int64_t key_stride,
+    int64_t value_stride, int num_heads, int head_size, int block_size, int x,
+    int scalar_type, int kv_dtype, const float* k_scale, const float* v_scale,
+    void* stream);
+
+/*
+ * Flash layout, addressed by strides only: NHD [num_blocks, block_size, num_heads,
+ * head_size] (head_stride == head_size) or HND [num_blocks, num_heads, block_size,
+ * head_size].  block_stride is shared by key_cache and value_cache.
+ */
+int b200pa_reshape_and_cache_flash(
+    const void* key, const void* value, void* key_cache, void* value_cache,
+    const int64_t* slot_mapping, int num_tokens, int64_t key_stride,
+    int64_t value_stride, int64_t block_stride, int64_t page_stride,
+    int64_t head_stride, int num_heads, int head_size, int block_size,
+    int scalar_type, int kv_dtype, const float* k_scale, const float* v_scale,
+    void* stream);
+
+/*
+ * Whole-tensor fp8 <-> scalar_t conversion with a HOST scale (test utility).
+ * to_fp8 != 0: src scalar_t -> dst uint8 codes; else src uint8 -> dst scalar_t.
+ * kv_dtype must be B200PA_KV_FP8_E4M3 or B200PA_KV_FP8_E5M2.
+ */
+int b200pa_convert_fp8(void* dst, const void* src, int64_t num_elements,
+                       float scale, int scalar_type, int kv_dtype, int to_fp8,
+                       void* stream);
+
+/* cudaDevAttrMaxSharedMemoryPerBlockOptin of `device_id`. */
+int b200pa_get_max_shared_memory_per_block_device_attribute(int device_id,
+                                                            int64_t* value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_PAGED_ATTN_H_ */

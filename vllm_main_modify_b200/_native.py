@@ -1,0 +1,88 @@
+"""Loader of the native libraries.  No fallback: a missing library is an error."""
+from __future__ import annotations
+
+import ctypes
+import os
+import threading
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200pa.so")
+SHIM_PATH = os.path.join(_HERE, "_b200pa_torch.so")
+
+# every symbol include/b200_paged_attn.h declares
+C_ABI_SYMBOLS = (
+    "b200pa_abi_version", "b200pa_last_error", "b200pa_kv_dtype_from_string",
+    "b200pa_set_impl", "b200pa_get_impl", "b200pa_launch_count",
+    "b200pa_paged_attention_v1", "b200pa_paged_attention_v2",
+    "b200pa_reshape_and_cache", "b200pa_reshape_and_cache_flash",
+    "b200pa_convert_fp8",
+    "b200pa_get_max_shared_memory_per_block_device_attribute",
+)
+
+IMPL_AUTO, IMPL_GENERIC, IMPL_FAST = 0, 1, 2
+
+_lock = threading.Lock()
+_clib = None
+_shim_loaded = False
+_vllm_ns = False
+
+
+def native_lib_paths():
+    return LIB_PATH, SHIM_PATH
+
+
+def c_lib() -> ctypes.CDLL:
+    """dlopen libb200pa.so (the C ABI).  Works without a GPU; compute calls don't."""
+    global _clib
+    with _lock:
+        if _clib is None:
+            if not os.path.exists(LIB_PATH):
+                raise ImportError(
+                    f"{LIB_PATH} is missing: build it with "
+                    "`python -m vllm_main_modify_b200.build` (there is no fallback path)")
+            lib = ctypes.CDLL(LIB_PATH, mode=ctypes.RTLD_GLOBAL)
+            lib.b200pa_last_error.restype = ctypes.c_char_p
+            lib.b200pa_launch_count.restype = ctypes.c_uint64
+            lib.b200pa_kv_dtype_from_string.argtypes = [ctypes.c_char_p]
+            _clib = lib
+        return _clib
+
+
+def load(register_vllm_namespaces: bool = True):
+    """Load the C ABI and the torch shim; returns ``torch.ops.b200pa``.
+
+    With ``register_vllm_namespaces`` the ops are also defined as
+    ``torch.ops._C.paged_attention_v1/v2``, ``torch.ops._C_cache_ops.*`` and
+    ``torch.ops._C_cuda_utils.*`` unless another extension (the reference's own
+    ``vllm._C``) already defined them in this process.
+    """
+    global _shim_loaded, _vllm_ns
+    import torch
+    c_lib()
+    with _lock:
+        if not _shim_loaded:
+            if not os.path.exists(SHIM_PATH):
+                raise ImportError(
+                    f"{SHIM_PATH} is missing: build it with "
+                    "`python -m vllm_main_modify_b200.build` (there is no fallback path)")
+            torch.ops.load_library(SHIM_PATH)
+            _shim_loaded = True
+        if register_vllm_namespaces and not _vllm_ns:
+            already = hasattr(torch.ops._C, "paged_attention_v1") if hasattr(torch.ops, "_C") else False
+            if not already:
+                shim = ctypes.CDLL(SHIM_PATH)
+                shim.b200pa_register_vllm_namespaces()
+            _vllm_ns = True
+    return torch.ops.b200pa
+
+
+def set_impl(impl: int) -> None:
+    c_lib().b200pa_set_impl(int(impl))
+
+
+def get_impl() -> int:
+    return int(c_lib().b200pa_get_impl())
+
+
+def launch_count() -> int:
+    return int(c_lib().b200pa_launch_count())

@@ -1,0 +1,240 @@
+"""Attention backend for the decode hot path -- the model-facing contract.
+
+Mirrors the reference's ``AttentionBackend`` / ``AttentionImpl`` /
+``AttentionLayer`` contract (``vllm/attention/backends/abstract.py:27-181``) and
+the metadata-builder shape of its V1 backends (``vllm/v1/attention/backends/
+cpu_attn.py:324-440``, ``rocm_attn.py:279-426``): same method names, argument
+meaning and error behaviour, so that registering this class as
+``Attention(..., attn_backend=B200PagedAttentionBackend)``
+(``vllm/attention/layer.py:101,184-192``) or through a platform plugin's
+``get_attn_backend_cls`` is a pure wiring change.
+
+It is deliberately free of ``import vllm``: the classes below are structural
+twins of the ABCs, not subclasses, so the package works (and is tested) without
+the reference installed.  Scope: decode (one query token per sequence).  Prefill /
+chunked prefill are delegated by the caller, as the reference's paged-attention
+backends do (``cpu_attn.py:584-612``) -- see SURVEY.md section 8(f) row 1.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Any, List, Optional, Tuple, Type
+
+import torch
+
+from .paged_attn import PagedAttention
+
+
+class AttentionType:
+    """``abstract.py:12-24`` of the reference."""
+    DECODER = "decoder"
+    ENCODER = "encoder"
+    ENCODER_ONLY = "encoder_only"
+    ENCODER_DECODER = "encoder_decoder"
+
+
+@dataclass
+class B200PagedAttentionMetadata:
+    """Per-step tensors the runner hands to ``AttentionImpl.forward``.
+
+    Field meaning follows the reference's V1 metadata classes
+    (``cpu_attn.py:268-322``): everything lives on the device already.
+    """
+    num_actual_tokens: int            # tokens in the batch, excluding CUDA-graph padding
+    max_query_len: int                # 1 for a pure decode batch
+    seq_lens: torch.Tensor            # [num_seqs] int32, tokens seen so far (incl. the new one)
+    max_seq_len: int                  # host copy of seq_lens.max()
+    block_table: torch.Tensor         # [num_seqs, max_blocks_per_seq] int32
+    slot_mapping: torch.Tensor        # [num_actual_tokens] int64, <0 = skip
+    query_start_loc: Optional[torch.Tensor] = None  # [num_seqs + 1] int32
+
+    @property
+    def num_decode_tokens(self) -> int:
+        return self.num_actual_tokens if self.max_query_len <= 1 else 0
+
+
+class B200PagedAttentionMetadataBuilder:
+    """Builds :class:`B200PagedAttentionMetadata` from the runner's
+    ``CommonAttentionMetadata`` (``vllm/v1/attention/backends/utils.py``), which is
+    duck-typed here: ``num_actual_tokens, max_query_len, seq_lens, max_seq_len,
+    block_table_tensor, slot_mapping, query_start_loc``."""
+
+    # decode-only batches can be captured in a full CUDA graph: every op of the
+    # path is asynchronous on the current stream and allocation-free.
+    cudagraph_support = "UNIFORM_SINGLE_TOKEN_DECODE"
+    reorder_batch_threshold = 1
+
+    def __init__(self, kv_cache_spec: Any = None, layer_names: Optional[List[str]] = None,
+                 vllm_config: Any = None, device: Optional[torch.device] = None) -> None:
+        self.kv_cache_spec = kv_cache_spec
+        self.layer_names = layer_names
+        self.vllm_config = vllm_config
+        self.device = device
+
+    def build(self, common_prefix_len: int, common_attn_metadata: Any,
+              fast_build: bool = False) -> B200PagedAttentionMetadata:
+        m = common_attn_metadata
+        max_seq_len = getattr(m, "max_seq_len", None)
+        if max_seq_len is None:
+            cpu = getattr(m, "seq_lens_cpu", None)
+            max_seq_len = int(cpu.max()) if cpu is not None else int(m.seq_lens.max())
+        return B200PagedAttentionMetadata(
+            num_actual_tokens=int(m.num_actual_tokens),
+            max_query_len=int(m.max_query_len),
+            seq_lens=m.seq_lens,
+            max_seq_len=int(max_seq_len),
+            block_table=m.block_table_tensor,
+            slot_mapping=m.slot_mapping,
+            query_start_loc=getattr(m, "query_start_loc", None),
+        )
+
+    def build_for_cudagraph_capture(self, common_attn_metadata: Any) -> B200PagedAttentionMetadata:
+        return self.build(0, common_attn_metadata)
+
+
+class B200PagedAttentionImpl:
+    """``AttentionImpl`` (``abstract.py:113-181``) for paged decode on B200."""
+
+    can_return_lse_for_decode: bool = False
+    need_to_return_lse_for_decode: bool = False
+    dcp_world_size: int = 1
+    dcp_rank: int = 0
+
+    def __init__(
+        self,
+        num_heads: int,
+        head_size: int,
+        scale: float,
+        num_kv_heads: Optional[int] = None,
+        alibi_slopes: Optional[List[float]] = None,
+        sliding_window: Optional[int] = None,
+        kv_cache_dtype: str = "auto",
+        logits_soft_cap: Optional[float] = None,
+        attn_type: str = AttentionType.DECODER,
+        kv_sharing_target_layer_name: Optional[str] = None,
+        **extra: Any,
+    ) -> None:
+        if kv_sharing_target_layer_name is not None:
+            raise NotImplementedError("KV sharing is not supported by B200PagedAttentionImpl")
+        if logits_soft_cap is not None:
+            raise NotImplementedError("logits_soft_cap is not supported by the paged_attention ops")
+        if sliding_window is not None:
+            raise NotImplementedError("sliding_window is not supported by the paged_attention ops")
+        if attn_type != AttentionType.DECODER:
+            raise NotImplementedError("Encoder self-attention and encoder/decoder cross-attention "
+                                      "are not implemented for B200PagedAttentionImpl")
+        self.num_heads = num_heads
+        self.head_size = head_size
+        self.scale = float(scale)
+        self.num_kv_heads = num_heads if num_kv_heads is None else num_kv_heads
+        if alibi_slopes is not None:
+            alibi_slopes = torch.tensor(alibi_slopes, dtype=torch.float32)
+        self.alibi_slopes = alibi_slopes
+        self.kv_cache_dtype = kv_cache_dtype
+        assert self.num_heads % self.num_kv_heads == 0
+        self.num_queries_per_kv = self.num_heads // self.num_kv_heads
+        B200PagedAttentionBackend.validate_head_size(head_size)
+
+    def forward(
+        self,
+        layer: Any,                      # AttentionLayer: supplies _k_scale / _v_scale
+        query: torch.Tensor,             # [num_tokens, num_heads * head_size] or [T, H, D]
+        key: Optional[torch.Tensor],     # [num_tokens, num_kv_heads * head_size] or [T, Hkv, D]
+        value: Optional[torch.Tensor],
+        kv_cache: torch.Tensor,          # get_kv_cache_shape(...): [2, num_blocks, BS*Hkv*D]
+        attn_metadata: Optional[B200PagedAttentionMetadata],
+        output: Optional[torch.Tensor] = None,
+        output_scale: Optional[torch.Tensor] = None,
+        output_block_scale: Optional[torch.Tensor] = None,
+    ) -> torch.Tensor:
+        if output_scale is not None or output_block_scale is not None:
+            raise NotImplementedError("fused output quantization is not yet supported "
+                                      "for B200PagedAttentionImpl")
+        if output is None:
+            output = torch.empty_like(query)
+        if attn_metadata is None:        # profiling run
+            return output
+        if attn_metadata.max_query_len > 1:
+            raise NotImplementedError(
+                "B200PagedAttentionImpl implements the decode path; prefill / chunked prefill "
+                "batches must be routed to a prefill backend by the caller")
+        n = attn_metadata.num_actual_tokens
+        q = query.view(-1, self.num_heads, self.head_size)
+        out = output.view(-1, self.num_heads, self.head_size)
+        key_cache, value_cache = PagedAttention.split_kv_cache(kv_cache, self.num_kv_heads,
+                                                               self.head_size)
+        if key is not None and value is not None:
+            k = key.view(-1, self.num_kv_heads, self.head_size)
+            v = value.view(-1, self.num_kv_heads, self.head_size)
+            PagedAttention.write_to_paged_cache(k, v, key_cache, value_cache,
+                                                attn_metadata.slot_mapping, self.kv_cache_dtype,
+                                                layer._k_scale, layer._v_scale)
+        if self.alibi_slopes is not None and self.alibi_slopes.device != q.device:
+            self.alibi_slopes = self.alibi_slopes.to(q.device)
+        PagedAttention.forward_decode(
+            q[:n], key_cache, value_cache, attn_metadata.block_table, attn_metadata.seq_lens,
+            attn_metadata.max_seq_len, self.kv_cache_dtype, self.num_kv_heads, self.scale,
+            self.alibi_slopes, layer._k_scale, layer._v_scale, output=out[:n])
+        return output
+
+    def fused_output_quant_supported(self, quant_key: Any) -> bool:
+        return False
+
+
+class B200PagedAttentionBackend:
+    """``AttentionBackend`` (``abstract.py:27-82``) twin."""
+
+    accept_output_buffer: bool = True
+    supports_quant_query_input: bool = False
+
+    @staticmethod
+    def get_name() -> str:
+        return "B200_PAGED_ATTN"
+
+    @staticmethod
+    def get_impl_cls() -> Type[B200PagedAttentionImpl]:
+        return B200PagedAttentionImpl
+
+    @staticmethod
+    def get_metadata_cls() -> Type[B200PagedAttentionMetadata]:
+        return B200PagedAttentionMetadata
+
+    @classmethod
+    def make_metadata(cls, *args, **kwargs) -> B200PagedAttentionMetadata:
+        return cls.get_metadata_cls()(*args, **kwargs)
+
+    @staticmethod
+    def get_builder_cls() -> Type[B200PagedAttentionMetadataBuilder]:
+        return B200PagedAttentionMetadataBuilder
+
+    @staticmethod
+    def get_kv_cache_shape(num_blocks: int, block_size: int, num_kv_heads: int,
+                           head_size: int) -> Tuple[int, ...]:
+        return PagedAttention.get_kv_cache_shape(num_blocks, block_size, num_kv_heads, head_size)
+
+    @staticmethod
+    def get_kv_cache_stride_order() -> Tuple[int, ...]:
+        raise NotImplementedError
+
+    @classmethod
+    def full_cls_name(cls) -> Tuple[str, str]:
+        return (cls.__module__, cls.__qualname__)
+
+    @classmethod
+    def get_supported_dtypes(cls) -> List[torch.dtype]:
+        return [torch.float16, torch.bfloat16, torch.float32]
+
+    @staticmethod
+    def get_supported_head_sizes() -> List[int]:
+        return PagedAttention.get_supported_head_sizes()
+
+    @classmethod
+    def validate_head_size(cls, head_size: int) -> None:
+        supported = cls.get_supported_head_sizes()
+        if head_size not in supported:
+            raise ValueError(f"Head size {head_size} is not supported by {cls.get_name()}. "
+                             f"Supported head sizes are: {supported}.")
+
+    @staticmethod
+    def use_cascade_attention(*args, **kwargs) -> bool:
+        return False

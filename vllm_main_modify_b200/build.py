@@ -1,0 +1,125 @@
+"""In-tree build of the native libraries (sm_100a only).
+
+  libb200pa.so        CUDA kernels + the C ABI of include/b200_paged_attn.h
+                      (no torch, no python; cudart linked statically)
+  _b200pa_torch.so    thin TORCH_LIBRARY shim over the C ABI (csrc/torch_shim.cpp)
+
+Both are built next to this file so they travel with the repository snapshot.
+`python -m vllm_main_modify_b200.build` builds both; `build_all()` is what
+`__graft_entry__.build()` calls.
+"""
+from __future__ import annotations
+
+import hashlib
+import os
+import subprocess
+import sys
+from concurrent.futures import ThreadPoolExecutor
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+ROOT = os.path.dirname(HERE)
+BUILD = os.path.join(HERE, "_build")
+LIB = os.path.join(HERE, "libb200pa.so")
+SHIM = os.path.join(HERE, "_b200pa_torch.so")
+
+CUDA_HOME = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+NVCC = os.path.join(CUDA_HOME, "bin", "nvcc")
+# The image exports CC/CXX=/opt/gcc/bin/*, a wrapper without libgomp; pin the system one.
+HOST_CXX = "/usr/bin/g++"
+
+CU_SOURCES = ["c_abi.cu", "cache_kernels.cu", "paged_attention_generic.cu",
+              "paged_attention_fast.cu"]
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
+              "-Xcompiler", "-fPIC", "-ccbin", HOST_CXX, "--expt-relaxed-constexpr",
+              "-Xptxas", "-v", "-Wno-deprecated-gpu-targets"]
+
+
+def _digest(paths, extra=""):
+    h = hashlib.sha1(extra.encode())
+    for p in sorted(paths):
+        with open(p, "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()
+
+
+def _headers():
+    hs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
+    hs.append(os.path.join(ROOT, "include", "b200_paged_attn.h"))
+    return hs
+
+
+def _compile_cu(src: str, verbose: bool) -> str:
+    os.makedirs(BUILD, exist_ok=True)
+    obj = os.path.join(BUILD, src.replace(".cu", ".o"))
+    stamp = obj + ".sha1"
+    key = _digest([os.path.join(CSRC, src)] + _headers(), " ".join(NVCC_FLAGS))
+    if os.path.exists(obj) and os.path.exists(stamp) and open(stamp).read() == key:
+        return obj
+    cmd = [NVCC] + NVCC_FLAGS + ["-c", os.path.join(CSRC, src), "-o", obj]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    log = os.path.join(BUILD, src + ".log")
+    with open(log, "w") as f:
+        f.write(" ".join(cmd) + "\n" + res.stdout + res.stderr)
+    if res.returncode != 0:
+        sys.stderr.write(res.stdout + res.stderr)
+        raise RuntimeError(f"nvcc failed on {src}")
+    if verbose:
+        sys.stderr.write(f"[build] {src} ok (ptxas log: {log})\n")
+    with open(stamp, "w") as f:
+        f.write(key)
+    return obj
+
+
+def build_lib(verbose: bool = False) -> str:
+    with ThreadPoolExecutor(max_workers=len(CU_SOURCES)) as ex:
+        objs = list(ex.map(lambda s: _compile_cu(s, verbose), CU_SOURCES))
+    key = _digest(objs)
+    stamp = os.path.join(BUILD, "libb200pa.sha1")
+    if os.path.exists(LIB) and os.path.exists(stamp) and open(stamp).read() == key:
+        return LIB
+    cmd = [NVCC, "-shared", "-o", LIB] + objs + ["-cudart", "static", "-ccbin", HOST_CXX,
+                                                 "-gencode", "arch=compute_100a,code=sm_100a"]
+    subprocess.check_call(cmd)
+    with open(stamp, "w") as f:
+        f.write(key)
+    if verbose:
+        sys.stderr.write(f"[build] linked {LIB}\n")
+    return LIB
+
+
+def build_shim(verbose: bool = False) -> str:
+    import sysconfig
+
+    import torch
+    tdir = os.path.dirname(torch.__file__)
+    src = os.path.join(CSRC, "torch_shim.cpp")
+    os.makedirs(BUILD, exist_ok=True)
+    key = _digest([src] + _headers(), torch.__version__)
+    stamp = os.path.join(BUILD, "shim.sha1")
+    if os.path.exists(SHIM) and os.path.exists(stamp) and open(stamp).read() == key:
+        return SHIM
+    abi = int(torch._C._GLIBCXX_USE_CXX11_ABI)
+    cmd = [HOST_CXX, "-O2", "-std=c++17", "-fPIC", "-shared", "-w",
+           f"-D_GLIBCXX_USE_CXX11_ABI={abi}",
+           f"-I{tdir}/include", f"-I{tdir}/include/torch/csrc/api/include",
+           f"-I{sysconfig.get_paths()['include']}", f"-I{CUDA_HOME}/include",
+           f"-I{os.path.join(ROOT, 'include')}", src, "-o", SHIM,
+           f"-L{HERE}", "-lb200pa", "-Wl,-rpath,$ORIGIN",
+           f"-L{tdir}/lib", f"-Wl,-rpath,{tdir}/lib",
+           "-ltorch", "-ltorch_cpu", "-lc10", "-ltorch_cuda", "-lc10_cuda"]
+    subprocess.check_call(cmd)
+    with open(stamp, "w") as f:
+        f.write(key)
+    if verbose:
+        sys.stderr.write(f"[build] built {SHIM}\n")
+    return SHIM
+
+
+def build_all(verbose: bool = False) -> None:
+    build_lib(verbose)
+    build_shim(verbose)
+
+
+if __name__ == "__main__":
+    build_all(verbose=True)

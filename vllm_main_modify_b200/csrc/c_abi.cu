@@ -1,0 +1,286 @@
+// extern "C" entry points of libb200pa.so (see include/b200_paged_attn.h).
+//
+// Argument validation mirrors the host-side checks of the reference launchers
+// (unsupported head size / block size / dtype -> error before launch:
+// paged_attention_v1.cu:122,156, quant_utils.cuh:554,580 of the reference); the
+// kernels never report errors from the device and never synchronise the host.
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "common.cuh"
+
+namespace b200pa {
+
+// kernels (other translation units)
+int launch_reshape_and_cache(const void*, const void*, void*, void*, const int64_t*, int, int64_t,
+                             int64_t, int, int, int, int, int, int, const float*, const float*,
+                             cudaStream_t);
+int launch_reshape_and_cache_flash(const void*, const void*, void*, void*, const int64_t*, int,
+                                   int64_t, int64_t, int64_t, int64_t, int64_t, int, int, int, int,
+                                   int, const float*, const float*, cudaStream_t);
+int launch_convert_fp8(void*, const void*, int64_t, float, int, int, int, cudaStream_t);
+int launch_reduce(void*, const float*, const float*, const void*, const int32_t*, int, int, int,
+                  int, int, cudaStream_t);
+int launch_generic(void*, float*, float*, void*, const void*, const void*, const void*, int, int,
+                   int, int, int, float, const int32_t*, int, const int32_t*, int, int,
+                   const float*, int64_t, int64_t, int64_t, int, int, const float*, const float*,
+                   BlockSparse, bool, cudaStream_t);
+bool fast_supported(const void*, const void*, const void*, int, int, int, int, int64_t, int64_t,
+                    int64_t, int, int, int);
+int launch_fast(void*, float*, float*, void*, const void*, const void*, const void*, int, int, int,
+                int, float, const int32_t*, int, const int32_t*, int, int, const float*, int64_t,
+                int64_t, int64_t, int, int, const float*, const float*, bool, int, cudaStream_t);
+
+static thread_local char g_err[512] = "";
+static std::atomic<int> g_impl{B200PA_IMPL_AUTO};
+static std::atomic<uint64_t> g_launches{0};
+
+int set_error(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+int check_launch(const char* what) {
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess)
+    return set_error(B200PA_ERR_CUDA, "%s: CUDA error: %s", what, cudaGetErrorString(e));
+  return B200PA_OK;
+}
+
+void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+
+static int num_sms() {
+  static int cached = 0;
+  if (cached == 0) {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess &&
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
+      cached = n;
+    else
+      return 148;
+  }
+  return cached;
+}
+
+static bool head_size_ok(int h) {
+  switch (h) {  // paged_attention_v1.cu:90-124 of the reference
+    case 32: case 64: case 80: case 96: case 112: case 120: case 128: case 192: case 256: return true;
+    default: return false;
+  }
+}
+
+static int paged_attention_common(
+    bool partitioned, void* out, float* exp_sums, float* max_logits, void* tmp_out,
+    const void* query, const void* key_cache, const void* value_cache, int num_seqs,
+    int num_heads, int num_kv_heads, int head_size, int block_size, float scale,
+    const int32_t* block_tables, int max_num_blocks_per_seq, const int32_t* seq_lens,
+    int max_seq_len, int max_num_partitions, const float* alibi_slopes, int64_t q_stride,
+    int64_t kv_block_stride, int64_t kv_head_stride, int scalar_type, int kv_dtype,
+    const float* k_scale, const float* v_scale, int tp_rank, int bs_local_blocks,
+    int bs_vert_stride, int bs_block_size, int bs_head_sliding_step, void* stream_v) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
+  if (!head_size_ok(head_size))
+    return set_error(B200PA_ERR_UNSUPPORTED, "Unsupported head size: %d", head_size);
+  if (block_size != 8 && block_size != 16 && block_size != 32)
+    return set_error(B200PA_ERR_UNSUPPORTED, "Unsupported block size: %d", block_size);
+  if (scalar_type != B200PA_F32 && scalar_type != B200PA_F16 && scalar_type != B200PA_BF16)
+    return set_error(B200PA_ERR_UNSUPPORTED, "Unsupported input type of kv cache: %d", scalar_type);
+  if (kv_dtype != B200PA_KV_AUTO && kv_dtype != B200PA_KV_FP8_E4M3 && kv_dtype != B200PA_KV_FP8_E5M2)
+    return set_error(B200PA_ERR_UNSUPPORTED, "Unsupported data type of kv cache: %d", kv_dtype);
+  if (num_seqs < 0 || num_heads <= 0 || num_kv_heads <= 0 || num_heads % num_kv_heads != 0)
+    return set_error(B200PA_ERR_INVALID, "num_heads %d must be a positive multiple of num_kv_heads %d",
+                     num_heads, num_kv_heads);
+  if (!out || !query || !key_cache || !value_cache || !block_tables || !seq_lens)
+    return set_error(B200PA_ERR_INVALID, "null tensor pointer");
+  if (kv_dtype != B200PA_KV_AUTO && (!k_scale || !v_scale))
+    return set_error(B200PA_ERR_INVALID, "fp8 kv cache needs k_scale and v_scale");
+  const int ces = kv_dtype == B200PA_KV_AUTO ? (scalar_type == B200PA_F32 ? 4 : 2) : 1;
+  const int x = 16 / ces;
+  if (head_size % x != 0)
+    return set_error(B200PA_ERR_UNSUPPORTED, "Unsupported head size: %d with %d-byte cache elements",
+                     head_size, ces);
+  if ((reinterpret_cast<uintptr_t>(key_cache) | reinterpret_cast<uintptr_t>(value_cache)) & 15u ||
+      (kv_block_stride * ces) % 16 != 0 || (kv_head_stride * ces) % 16 != 0)
+    return set_error(B200PA_ERR_INVALID, "kv cache must be 16-byte aligned (base and strides)");
+  if (partitioned) {
+    if (!exp_sums || !max_logits || !tmp_out)
+      return set_error(B200PA_ERR_INVALID, "paged_attention_v2 needs exp_sums, max_logits, tmp_out");
+    const int parts = (max_seq_len + kPartitionSize - 1) / kPartitionSize;
+    if (max_num_partitions < parts)
+      return set_error(B200PA_ERR_INVALID, "max_num_partitions %d < ceil(max_seq_len %d / 512)",
+                       max_num_partitions, max_seq_len);
+  }
+  if (num_seqs == 0) return B200PA_OK;
+
+  BlockSparse bsp;
+  bsp.enabled = bs_vert_stride > 1;  // paged_attention_v1.cu:175 of the reference
+  bsp.local_blocks = bs_local_blocks;
+  bsp.vert_stride = bs_vert_stride;
+  bsp.block_size = bs_block_size;
+  bsp.head_sliding_step = bs_head_sliding_step;
+  bsp.tp_rank = tp_rank;
+  if (bsp.enabled && bs_block_size <= 0)
+    return set_error(B200PA_ERR_INVALID, "blocksparse_block_size must be positive");
+
+  const int impl = g_impl.load();
+  const bool fast_ok = fast_supported(query, key_cache, value_cache, num_heads, num_kv_heads,
+                                      head_size, block_size, q_stride, kv_block_stride,
+                                      kv_head_stride, scalar_type, kv_dtype, bs_vert_stride);
+  if (impl == B200PA_IMPL_FAST && !fast_ok)
+    return set_error(B200PA_ERR_UNSUPPORTED, "configuration not covered by the fast kernel");
+  int rc;
+  if (fast_ok && impl != B200PA_IMPL_GENERIC) {
+    rc = launch_fast(out, exp_sums, max_logits, tmp_out, query, key_cache, value_cache, num_seqs,
+                     num_heads, num_kv_heads, head_size, scale, block_tables,
+                     max_num_blocks_per_seq, seq_lens, max_seq_len, max_num_partitions,
+                     alibi_slopes, q_stride, kv_block_stride, kv_head_stride, scalar_type,
+                     kv_dtype, k_scale, v_scale, partitioned, num_sms(), stream);
+  } else {
+    rc = launch_generic(out, exp_sums, max_logits, tmp_out, query, key_cache, value_cache,
+                        num_seqs, num_heads, num_kv_heads, head_size, block_size, scale,
+                        block_tables, max_num_blocks_per_seq, seq_lens, max_seq_len,
+                        max_num_partitions, alibi_slopes, q_stride, kv_block_stride,
+                        kv_head_stride, scalar_type, kv_dtype, k_scale, v_scale, bsp, partitioned,
+                        stream);
+  }
+  if (rc) return rc;
+  if (partitioned)
+    rc = launch_reduce(out, exp_sums, max_logits, tmp_out, seq_lens, num_seqs, num_heads,
+                       head_size, max_num_partitions, scalar_type, stream);
+  return rc;
+}
+
+}  // namespace b200pa
+
+using namespace b200pa;
+
+extern "C" {
+
+int b200pa_abi_version(void) { return B200PA_ABI_VERSION; }
+const char* b200pa_last_error(void) { return g_err; }
+
+int b200pa_kv_dtype_from_string(const char* s) {
+  if (!s) return -1;
+  if (!strcmp(s, "auto")) return B200PA_KV_AUTO;
+  if (!strcmp(s, "fp8") || !strcmp(s, "fp8_e4m3")) return B200PA_KV_FP8_E4M3;
+  if (!strcmp(s, "fp8_e5m2")) return B200PA_KV_FP8_E5M2;
+  return -1;
+}
+
+void b200pa_set_impl(int impl) { g_impl.store(impl); }
+int b200pa_get_impl(void) { return g_impl.load(); }
+uint64_t b200pa_launch_count(void) { return g_launches.load(); }
+
+int b200pa_paged_attention_v1(
+    void* out, const void* query, const void* key_cache, const void* value_cache, int num_seqs,
+    int num_heads, int num_kv_heads, int head_size, int block_size, float scale,
+    const int32_t* block_tables, int max_num_blocks_per_seq, const int32_t* seq_lens,
+    int max_seq_len, const float* alibi_slopes, int64_t q_stride, int64_t kv_block_stride,
+    int64_t kv_head_stride, int scalar_type, int kv_dtype, const float* k_scale,
+    const float* v_scale, int tp_rank, int blocksparse_local_blocks, int blocksparse_vert_stride,
+    int blocksparse_block_size, int blocksparse_head_sliding_step, void* stream) {
+  return paged_attention_common(false, out, nullptr, nullptr, nullptr, query, key_cache,
+                                value_cache, num_seqs, num_heads, num_kv_heads, head_size,
+                                block_size, scale, block_tables, max_num_blocks_per_seq, seq_lens,
+                                max_seq_len, 1, alibi_slopes, q_stride, kv_block_stride,
+                                kv_head_stride, scalar_type, kv_dtype, k_scale, v_scale, tp_rank,
+                                blocksparse_local_blocks, blocksparse_vert_stride,
+                                blocksparse_block_size, blocksparse_head_sliding_step, stream);
+}
+
+int b200pa_paged_attention_v2(
+    void* out, float* exp_sums, float* max_logits, void* tmp_out, const void* query,
+    const void* key_cache, const void* value_cache, int num_seqs, int num_heads, int num_kv_heads,
+    int head_size, int block_size, float scale, const int32_t* block_tables,
+    int max_num_blocks_per_seq, const int32_t* seq_lens, int max_seq_len, int max_num_partitions,
+    const float* alibi_slopes, int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
+    int scalar_type, int kv_dtype, const float* k_scale, const float* v_scale, int tp_rank,
+    int blocksparse_local_blocks, int blocksparse_vert_stride, int blocksparse_block_size,
+    int blocksparse_head_sliding_step, void* stream) {
+  return paged_attention_common(true, out, exp_sums, max_logits, tmp_out, query, key_cache,
+                                value_cache, num_seqs, num_heads, num_kv_heads, head_size,
+                                block_size, scale, block_tables, max_num_blocks_per_seq, seq_lens,
+                                max_seq_len, max_num_partitions, alibi_slopes, q_stride,
+                                kv_block_stride, kv_head_stride, scalar_type, kv_dtype, k_scale,
+                                v_scale, tp_rank, blocksparse_local_blocks,
+                                blocksparse_vert_stride, blocksparse_block_size,
+                                blocksparse_head_sliding_step, stream);
+}
+
+static int check_cache_args(const char* op, const void* key, const void* value, void* kc, void* vc,
+                            const int64_t* slots, int num_tokens, int scalar_type, int kv_dtype,
+                            const float* ks, const float* vs) {
+  if (num_tokens < 0) return set_error(B200PA_ERR_INVALID, "%s: negative num_tokens", op);
+  if (num_tokens > 0 && (!key || !value || !kc || !vc || !slots))
+    return set_error(B200PA_ERR_INVALID, "%s: null tensor pointer", op);
+  if (scalar_type != B200PA_F32 && scalar_type != B200PA_F16 && scalar_type != B200PA_BF16)
+    return set_error(B200PA_ERR_UNSUPPORTED, "Unsupported input type of kv cache: %d", scalar_type);
+  if (kv_dtype != B200PA_KV_AUTO && kv_dtype != B200PA_KV_FP8_E4M3 && kv_dtype != B200PA_KV_FP8_E5M2)
+    return set_error(B200PA_ERR_UNSUPPORTED, "Unsupported data type of kv cache: %d", kv_dtype);
+  if (kv_dtype != B200PA_KV_AUTO && (!ks || !vs))
+    return set_error(B200PA_ERR_INVALID, "%s: fp8 kv cache needs k_scale and v_scale", op);
+  return B200PA_OK;
+}
+
+int b200pa_reshape_and_cache(const void* key, const void* value, void* key_cache,
+                             void* value_cache, const int64_t* slot_mapping, int num_tokens,
+                             int64_t key_stride, int64_t value_stride, int num_heads,
+                             int head_size, int block_size, int x, int scalar_type, int kv_dtype,
+                             const float* k_scale, const float* v_scale, void* stream) {
+  int rc = check_cache_args("reshape_and_cache", key, value, key_cache, value_cache, slot_mapping,
+                            num_tokens, scalar_type, kv_dtype, k_scale, v_scale);
+  if (rc) return rc;
+  if (num_heads <= 0 || head_size <= 0 || block_size <= 0)
+    return set_error(B200PA_ERR_INVALID, "reshape_and_cache: bad shape");
+  return launch_reshape_and_cache(key, value, key_cache, value_cache, slot_mapping, num_tokens,
+                                  key_stride, value_stride, num_heads, head_size, block_size, x,
+                                  scalar_type, kv_dtype, k_scale, v_scale,
+                                  reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200pa_reshape_and_cache_flash(const void* key, const void* value, void* key_cache,
+                                   void* value_cache, const int64_t* slot_mapping, int num_tokens,
+                                   int64_t key_stride, int64_t value_stride, int64_t block_stride,
+                                   int64_t page_stride, int64_t head_stride, int num_heads,
+                                   int head_size, int block_size, int scalar_type, int kv_dtype,
+                                   const float* k_scale, const float* v_scale, void* stream) {
+  int rc = check_cache_args("reshape_and_cache_flash", key, value, key_cache, value_cache,
+                            slot_mapping, num_tokens, scalar_type, kv_dtype, k_scale, v_scale);
+  if (rc) return rc;
+  if (num_heads <= 0 || head_size <= 0 || block_size <= 0)
+    return set_error(B200PA_ERR_INVALID, "reshape_and_cache_flash: bad shape");
+  return launch_reshape_and_cache_flash(key, value, key_cache, value_cache, slot_mapping,
+                                        num_tokens, key_stride, value_stride, block_stride,
+                                        page_stride, head_stride, num_heads, head_size, block_size,
+                                        scalar_type, kv_dtype, k_scale, v_scale,
+                                        reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200pa_convert_fp8(void* dst, const void* src, int64_t num_elements, float scale,
+                       int scalar_type, int kv_dtype, int to_fp8, void* stream) {
+  if (num_elements < 0) return set_error(B200PA_ERR_INVALID, "convert_fp8: negative size");
+  if (num_elements > 0 && (!dst || !src)) return set_error(B200PA_ERR_INVALID, "convert_fp8: null pointer");
+  if (scalar_type != B200PA_F32 && scalar_type != B200PA_F16 && scalar_type != B200PA_BF16)
+    return set_error(B200PA_ERR_UNSUPPORTED, "Unsupported input type of kv cache: %d", scalar_type);
+  return launch_convert_fp8(dst, src, num_elements, scale, scalar_type, kv_dtype, to_fp8,
+                            reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200pa_get_max_shared_memory_per_block_device_attribute(int device_id, int64_t* value) {
+  if (!value) return set_error(B200PA_ERR_INVALID, "null output pointer");
+  int v = 0;
+  const cudaError_t e = cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, device_id);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    return set_error(B200PA_ERR_CUDA, "cudaDeviceGetAttribute: %s", cudaGetErrorString(e));
+  }
+  *value = v;
+  return B200PA_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,296 @@
+// Thin TORCH_LIBRARY shim over the C ABI (include/b200_paged_attn.h).
+//
+// Exports, VERBATIM, the op schemas of the reference
+// (csrc/torch_bindings.cpp:52-76 `_C`, :667-699 `_C_cache_ops`, :718-730
+// `_C_cuda_utils`) with the C++ signatures of csrc/ops.h:30-52 and
+// csrc/cache.h:20-41.  Each op only extracts pointers / sizes / strides from the
+// tensors -- exactly the values the reference launchers read
+// (paged_attention_v1.cu:54-75, cache_kernels.cu:426-433, :478-488) -- calls the
+// C ABI on at::cuda::getCurrentCUDAStream() under an OptionalCUDAGuard, and turns
+// a non-zero status into TORCH_CHECK(false, msg).
+//
+// The ops are always registered under the private namespace `b200pa`;
+// b200pa_register_vllm_namespaces() additionally defines them as `_C::*`,
+// `_C_cache_ops::*`, `_C_cuda_utils::*` (when the reference's own extension is
+// not loaded in the process) so that an unmodified `vllm/_custom_ops.py` resolves
+// `torch.ops._C.paged_attention_v1` etc. to this library.
+#include <ATen/cuda/CUDAContext.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <torch/all.h>
+#include <torch/library.h>
+
+#include <memory>
+#include <optional>
+#include <string>
+#include <vector>
+
+#include "b200_paged_attn.h"
+
+namespace {
+
+int scalar_code(at::ScalarType t) {
+  switch (t) {
+    case at::ScalarType::Float: return B200PA_F32;
+    case at::ScalarType::Half: return B200PA_F16;
+    case at::ScalarType::BFloat16: return B200PA_BF16;
+    default: TORCH_CHECK(false, "Unsupported input type of kv cache: ", t);
+  }
+}
+
+int kv_code(const std::string& s) {
+  const int k = b200pa_kv_dtype_from_string(s.c_str());
+  TORCH_CHECK(k >= 0, "Unsupported data type of kv cache: ", s);
+  return k;
+}
+
+void check_status(int rc) { TORCH_CHECK(rc == 0, b200pa_last_error()); }
+
+void check_cuda(const torch::Tensor& t, const char* name) {
+  TORCH_CHECK(t.is_cuda(), name, " must be a CUDA tensor (this library has no CPU path)");
+}
+
+void check_cache_dtype(const torch::Tensor& cache, const torch::Tensor& ref, int kv,
+                       const char* name) {
+  if (kv == B200PA_KV_AUTO) {
+    TORCH_CHECK(cache.scalar_type() == ref.scalar_type(), name,
+                " dtype must match the query/key dtype when kv_cache_dtype is auto");
+  } else {
+    TORCH_CHECK(cache.element_size() == 1, name, " must be a 1-byte tensor for an fp8 kv cache");
+  }
+}
+
+void paged_attention_v1(torch::Tensor& out, torch::Tensor& query, torch::Tensor& key_cache,
+                        torch::Tensor& value_cache, int64_t num_kv_heads, double scale,
+                        torch::Tensor& block_tables, torch::Tensor& seq_lens, int64_t block_size,
+                        int64_t max_seq_len, const std::optional<torch::Tensor>& alibi_slopes,
+                        const std::string& kv_cache_dtype, torch::Tensor& k_scale,
+                        torch::Tensor& v_scale, const int64_t tp_rank,
+                        const int64_t blocksparse_local_blocks,
+                        const int64_t blocksparse_vert_stride,
+                        const int64_t blocksparse_block_size,
+                        const int64_t blocksparse_head_sliding_step) {
+  check_cuda(query, "query");
+  const int kv = kv_code(kv_cache_dtype);
+  const int st = scalar_code(query.scalar_type());
+  check_cache_dtype(key_cache, query, kv, "key_cache");
+  TORCH_CHECK(block_tables.scalar_type() == at::ScalarType::Int, "block_tables must be int32");
+  TORCH_CHECK(seq_lens.scalar_type() == at::ScalarType::Int, "seq_lens must be int32");
+  TORCH_CHECK(out.is_contiguous(), "out must be contiguous");
+  TORCH_CHECK(query.stride(2) == 1 && query.stride(1) == query.size(2),
+              "query heads must be densely packed");
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(query));
+  const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  const float* alibi = alibi_slopes ? reinterpret_cast<const float*>(alibi_slopes->data_ptr()) : nullptr;
+  check_status(b200pa_paged_attention_v1(
+      out.data_ptr(), query.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(),
+      (int)query.size(0), (int)query.size(1), (int)num_kv_heads, (int)query.size(2),
+      (int)block_size, (float)scale, block_tables.data_ptr<int>(), (int)block_tables.size(1),
+      seq_lens.data_ptr<int>(), (int)max_seq_len, alibi, query.stride(0), key_cache.stride(0),
+      key_cache.stride(1), st, kv, reinterpret_cast<const float*>(k_scale.data_ptr()),
+      reinterpret_cast<const float*>(v_scale.data_ptr()), (int)tp_rank,
+      (int)blocksparse_local_blocks, (int)blocksparse_vert_stride, (int)blocksparse_block_size,
+      (int)blocksparse_head_sliding_step, stream));
+}
+
+void paged_attention_v2(torch::Tensor& out, torch::Tensor& exp_sums, torch::Tensor& max_logits,
+                        torch::Tensor& tmp_out, torch::Tensor& query, torch::Tensor& key_cache,
+                        torch::Tensor& value_cache, int64_t num_kv_heads, double scale,
+                        torch::Tensor& block_tables, torch::Tensor& seq_lens, int64_t block_size,
+                        int64_t max_seq_len, const std::optional<torch::Tensor>& alibi_slopes,
+                        const std::string& kv_cache_dtype, torch::Tensor& k_scale,
+                        torch::Tensor& v_scale, const int64_t tp_rank,
+                        const int64_t blocksparse_local_blocks,
+                        const int64_t blocksparse_vert_stride,
+                        const int64_t blocksparse_block_size,
+                        const int64_t blocksparse_head_sliding_step) {
+  check_cuda(query, "query");
+  const int kv = kv_code(kv_cache_dtype);
+  const int st = scalar_code(query.scalar_type());
+  check_cache_dtype(key_cache, query, kv, "key_cache");
+  TORCH_CHECK(block_tables.scalar_type() == at::ScalarType::Int, "block_tables must be int32");
+  TORCH_CHECK(seq_lens.scalar_type() == at::ScalarType::Int, "seq_lens must be int32");
+  TORCH_CHECK(exp_sums.scalar_type() == at::ScalarType::Float &&
+                  max_logits.scalar_type() == at::ScalarType::Float,
+              "exp_sums / max_logits must be float32");
+  TORCH_CHECK(out.is_contiguous() && exp_sums.is_contiguous() && max_logits.is_contiguous() &&
+                  tmp_out.is_contiguous(),
+              "out / exp_sums / max_logits / tmp_out must be contiguous");
+  TORCH_CHECK(query.stride(2) == 1 && query.stride(1) == query.size(2),
+              "query heads must be densely packed");
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(query));
+  const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  const float* alibi = alibi_slopes ? reinterpret_cast<const float*>(alibi_slopes->data_ptr()) : nullptr;
+  check_status(b200pa_paged_attention_v2(
+      out.data_ptr(), exp_sums.data_ptr<float>(), max_logits.data_ptr<float>(), tmp_out.data_ptr(),
+      query.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(), (int)query.size(0),
+      (int)query.size(1), (int)num_kv_heads, (int)query.size(2), (int)block_size, (float)scale,
+      block_tables.data_ptr<int>(), (int)block_tables.size(1), seq_lens.data_ptr<int>(),
+      (int)max_seq_len, (int)exp_sums.size(-1), alibi, query.stride(0), key_cache.stride(0),
+      key_cache.stride(1), st, kv, reinterpret_cast<const float*>(k_scale.data_ptr()),
+      reinterpret_cast<const float*>(v_scale.data_ptr()), (int)tp_rank,
+      (int)blocksparse_local_blocks, (int)blocksparse_vert_stride, (int)blocksparse_block_size,
+      (int)blocksparse_head_sliding_step, stream));
+}
+
+void reshape_and_cache(torch::Tensor& key, torch::Tensor& value, torch::Tensor& key_cache,
+                       torch::Tensor& value_cache, torch::Tensor& slot_mapping,
+                       const std::string& kv_cache_dtype, torch::Tensor& k_scale,
+                       torch::Tensor& v_scale) {
+  check_cuda(key, "key");
+  const int kv = kv_code(kv_cache_dtype);
+  const int st = scalar_code(key.scalar_type());
+  check_cache_dtype(key_cache, key, kv, "key_cache");
+  TORCH_CHECK(slot_mapping.scalar_type() == at::ScalarType::Long, "slot_mapping must be int64");
+  TORCH_CHECK(key_cache.is_contiguous() && value_cache.is_contiguous(),
+              "reshape_and_cache indexes the caches densely (as the reference kernel does)");
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(key));
+  const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  check_status(b200pa_reshape_and_cache(
+      key.data_ptr(), value.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(),
+      slot_mapping.data_ptr<int64_t>(), (int)slot_mapping.size(0), key.stride(0), value.stride(0),
+      (int)key.size(1), (int)key.size(2), (int)key_cache.size(3), (int)key_cache.size(4), st, kv,
+      reinterpret_cast<const float*>(k_scale.data_ptr()),
+      reinterpret_cast<const float*>(v_scale.data_ptr()), stream));
+}
+
+void reshape_and_cache_flash(torch::Tensor& key, torch::Tensor& value, torch::Tensor& key_cache,
+                             torch::Tensor& value_cache, torch::Tensor& slot_mapping,
+                             const std::string& kv_cache_dtype, torch::Tensor& k_scale,
+                             torch::Tensor& v_scale) {
+  check_cuda(key, "key");
+  const int kv = kv_code(kv_cache_dtype);
+  const int st = scalar_code(key.scalar_type());
+  check_cache_dtype(key_cache, key, kv, "key_cache");
+  TORCH_CHECK(slot_mapping.scalar_type() == at::ScalarType::Long, "slot_mapping must be int64");
+  TORCH_CHECK(key_cache.stride(0) == value_cache.stride(0));  // cache_kernels.cu:488
+  TORCH_CHECK(key_cache.stride(3) == 1, "head elements must be contiguous in the cache");
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(key));
+  const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  check_status(b200pa_reshape_and_cache_flash(
+      key.data_ptr(), value.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(),
+      slot_mapping.data_ptr<int64_t>(), (int)slot_mapping.size(0), key.stride(0), value.stride(0),
+      key_cache.stride(0), key_cache.stride(1), key_cache.stride(2), (int)key.size(1),
+      (int)key.size(2), (int)key_cache.size(1), st, kv,
+      reinterpret_cast<const float*>(k_scale.data_ptr()),
+      reinterpret_cast<const float*>(v_scale.data_ptr()), stream));
+}
+
+void convert_fp8(torch::Tensor& dst_cache, torch::Tensor& src_cache, const double scale,
+                 const std::string& kv_cache_dtype) {
+  TORCH_CHECK(src_cache.is_cuda(), "src must be on a GPU");
+  TORCH_CHECK(dst_cache.is_cuda(), "dst must be on a GPU");
+  TORCH_CHECK(src_cache.device().index() == dst_cache.device().index(),
+              "src and dst must be on the same GPU");
+  TORCH_CHECK(src_cache.is_contiguous() && dst_cache.is_contiguous(),
+              "convert_fp8 works on contiguous caches");
+  TORCH_CHECK(src_cache.numel() == dst_cache.numel(), "src and dst must have the same size");
+  // the reference only ever instantiates the fp8 conversions (its "auto" branch
+  // reaches an assert(false) in scaled_convert, quant_utils.cuh:528-539)
+  TORCH_CHECK(kv_cache_dtype == "fp8" || kv_cache_dtype == "fp8_e4m3" || kv_cache_dtype == "fp8_e5m2",
+              "Unsupported data type: ", kv_cache_dtype);
+  const int kv = kv_code(kv_cache_dtype);
+  const bool to_fp8 = dst_cache.element_size() == 1;
+  TORCH_CHECK(to_fp8 || src_cache.element_size() == 1, "one side of convert_fp8 must be uint8");
+  const int st = scalar_code(to_fp8 ? src_cache.scalar_type() : dst_cache.scalar_type());
+  at::cuda::OptionalCUDAGuard device_guard(src_cache.device());
+  const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  check_status(b200pa_convert_fp8(dst_cache.data_ptr(), src_cache.data_ptr(), src_cache.numel(),
+                                  (float)scale, st, kv, to_fp8 ? 1 : 0, stream));
+}
+
+int64_t get_max_shared_memory_per_block_device_attribute(int64_t device_id) {
+  int64_t v = 0;
+  check_status(b200pa_get_max_shared_memory_per_block_device_attribute((int)device_id, &v));
+  return v;
+}
+
+constexpr const char* kSchemaV1 =
+    "paged_attention_v1("
+    "    Tensor! out, Tensor query, Tensor key_cache,"
+    "    Tensor value_cache, int num_kv_heads, float scale,"
+    "    Tensor block_tables, Tensor seq_lens, int block_size,"
+    "    int max_seq_len, Tensor? alibi_slopes,"
+    "    str kv_cache_dtype, Tensor k_scale, Tensor v_scale,"
+    "    int tp_rank, int blocksparse_local_blocks,"
+    "    int blocksparse_vert_stride, int blocksparse_block_size,"
+    "    int blocksparse_head_sliding_step) -> ()";
+constexpr const char* kSchemaV2 =
+    "paged_attention_v2("
+    "    Tensor! out, Tensor! exp_sums, Tensor! max_logits,"
+    "    Tensor! tmp_out, Tensor query, Tensor key_cache,"
+    "    Tensor value_cache, int num_kv_heads, float scale,"
+    "    Tensor block_tables, Tensor seq_lens, int block_size,"
+    "    int max_seq_len, Tensor? alibi_slopes,"
+    "    str kv_cache_dtype, Tensor k_scale, Tensor v_scale,"
+    "    int tp_rank, int blocksparse_local_blocks,"
+    "    int blocksparse_vert_stride, int blocksparse_block_size,"
+    "    int blocksparse_head_sliding_step) -> ()";
+constexpr const char* kSchemaReshape =
+    "reshape_and_cache(Tensor key, Tensor value,"
+    "                  Tensor! key_cache, Tensor! value_cache,"
+    "                  Tensor slot_mapping,"
+    "                  str kv_cache_dtype,"
+    "                  Tensor k_scale, Tensor v_scale) -> ()";
+constexpr const char* kSchemaReshapeFlash =
+    "reshape_and_cache_flash(Tensor key, Tensor value,"
+    "                        Tensor! key_cache,"
+    "                        Tensor! value_cache,"
+    "                        Tensor slot_mapping,"
+    "                        str kv_cache_dtype,"
+    "                        Tensor k_scale, Tensor v_scale) -> ()";
+constexpr const char* kSchemaConvert =
+    "convert_fp8(Tensor! dst_cache, Tensor src_cache, float scale, str kv_cache_dtype) -> ()";
+constexpr const char* kSchemaSmem =
+    "get_max_shared_memory_per_block_device_attribute(int device_id) -> int";
+
+void define_attention(torch::Library& ops) {
+  ops.def(kSchemaV1);
+  ops.impl("paged_attention_v1", torch::kCUDA, &paged_attention_v1);
+  ops.def(kSchemaV2);
+  ops.impl("paged_attention_v2", torch::kCUDA, &paged_attention_v2);
+}
+void define_cache(torch::Library& ops) {
+  ops.def(kSchemaReshape);
+  ops.impl("reshape_and_cache", torch::kCUDA, &reshape_and_cache);
+  ops.def(kSchemaReshapeFlash);
+  ops.impl("reshape_and_cache_flash", torch::kCUDA, &reshape_and_cache_flash);
+  ops.def(kSchemaConvert);
+  ops.impl("convert_fp8", torch::kCUDA, &convert_fp8);
+}
+void define_utils(torch::Library& ops) {
+  ops.def(kSchemaSmem);
+  // no tensor argument -> no dispatch key to infer: register as a catch-all like the reference
+  ops.impl("get_max_shared_memory_per_block_device_attribute",
+           &get_max_shared_memory_per_block_device_attribute);
+}
+
+std::vector<std::unique_ptr<torch::Library>> g_vllm_libs;
+
+}  // namespace
+
+TORCH_LIBRARY(b200pa, ops) {
+  define_attention(ops);
+  define_cache(ops);
+  define_utils(ops);
+}
+
+// Register the same ops under the reference's namespaces.  Returns 0 on success,
+// 1 if they were already registered by this call earlier.  Throws (c10::Error)
+// if another extension already defined the schemas in this process.
+extern "C" int b200pa_register_vllm_namespaces(void) {
+  if (!g_vllm_libs.empty()) return 1;
+  auto mk = [](const char* ns) {
+    return std::make_unique<torch::Library>(torch::Library::FRAGMENT, ns, std::nullopt, __FILE__,
+                                            __LINE__);
+  };
+  auto c = mk("_C");
+  define_attention(*c);
+  auto cache = mk("_C_cache_ops");
+  define_cache(*cache);
+  auto utils = mk("_C_cuda_utils");
+  define_utils(*utils);
+  g_vllm_libs.push_back(std::move(c));
+  g_vllm_libs.push_back(std::move(cache));
+  g_vllm_libs.push_back(std::move(utils));
+  return 0;
+}

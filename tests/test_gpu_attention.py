@@ -1,0 +1,624 @@
+"""GPU parity of paged_attention_v1 / v2 against the CPU oracle.
+
+Mirrors the reference's tests/kernels/attention/test_attention.py (:121-345):
+same parameter sweep (version, heads, head size, block size, ALiBi, kv dtype),
+same input distributions (U(-1/sqrt(D), 1/sqrt(D)), block tables with repeats),
+but compares with the oracle (oracle/paged_attn_oracle.c, pinned in
+tests/test_oracle.py) within BASELINE.json's gate: 1e-2 abs + 1e-2 rel, and with
+an fp64 restatement at the reference test's own tolerance (atol 1e-3 for 16-bit
+KV, 1e-2 for fp8).  All calls go through the torch shim -> C ABI.
+"""
+import random
+
+import pytest
+import torch
+
+from tests import helpers as hp
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+ATOL, RTOL = 1e-2, 1e-2           # BASELINE.json north_star gate vs the reference kernels
+GENERIC, FAST = 1, 2
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from vllm_main_modify_b200 import _custom_ops
+    return _custom_ops
+
+
+@pytest.fixture(scope="module")
+def native():
+    from vllm_main_modify_b200 import _native
+    yield _native
+    _native.set_impl(_native.IMPL_AUTO)
+
+
+@pytest.fixture(scope="module")
+def ora():
+    from oracle import oracle
+    return oracle
+
+
+def _run_gpu(ops, version, q, kc, vc, Hkv, scale, bt, sl, BS, max_len, alibi, kv, ks, vs,
+             extra=(0, 0, 0, 64, 0), parts=None):
+    """Upload, run, return (out, exp_sums, max_logits, tmp_out) on the CPU."""
+    qd, kcd, vcd = q.to(DEV), kc.to(DEV), vc.to(DEV)
+    btd, sld = bt.to(DEV), sl.to(DEV)
+    ald = None if alibi is None else alibi.to(DEV)
+    ksd = torch.as_tensor(ks, dtype=torch.float32).reshape(()).to(DEV)
+    vsd = torch.as_tensor(vs, dtype=torch.float32).reshape(()).to(DEV)
+    out = torch.full_like(qd, float("nan"))
+    B, H, D = q.shape
+    if version == "v1":
+        ops.paged_attention_v1(out, qd, kcd, vcd, Hkv, scale, btd, sld, BS, max_len, ald, kv,
+                               ksd, vsd, *extra)
+        torch.cuda.synchronize()
+        return out.cpu(), None, None, None
+    P = parts if parts is not None else (max_len + 511) // 512
+    es = torch.full((B, H, P), float("nan"), dtype=torch.float32, device=DEV)
+    ml = torch.full((B, H, P), float("nan"), dtype=torch.float32, device=DEV)
+    tmp = torch.full((B, H, P, D), float("nan"), dtype=q.dtype, device=DEV)
+    ops.paged_attention_v2(out, es, ml, tmp, qd, kcd, vcd, Hkv, scale, btd, sld, BS, max_len,
+                           ald, kv, ksd, vsd, *extra)
+    torch.cuda.synchronize()
+    return out.cpu(), es.cpu(), ml.cpu(), tmp.cpu()
+
+
+def _run_oracle(ora, version, q, kc, vc, Hkv, scale, bt, sl, BS, max_len, alibi, kv, ks, vs,
+                extra=(0, 0, 0, 64, 0)):
+    out = torch.empty_like(q)
+    ks_t, vs_t = torch.tensor(float(ks)), torch.tensor(float(vs))
+    if version == "v1":
+        ora.paged_attention_v1(out, q, kc, vc, Hkv, scale, bt, sl, BS, max_len, alibi, kv,
+                               ks_t, vs_t, *extra)
+    else:
+        B, H, D = q.shape
+        P = (max_len + 511) // 512
+        es, ml = torch.zeros(B, H, P), torch.zeros(B, H, P)
+        tmp = torch.zeros(B, H, P, D, dtype=q.dtype)
+        ora.paged_attention_v2(out, es, ml, tmp, q, kc, vc, Hkv, scale, bt, sl, BS, max_len,
+                               alibi, kv, ks_t, vs_t, *extra)
+    return out
+
+
+def _close(got, want, atol=ATOL, rtol=RTOL):
+    assert not torch.isnan(got.float()).any(), "NaN in the GPU output"
+    torch.testing.assert_close(got.float(), want.float(), atol=atol, rtol=rtol)
+
+
+def _alibi(H):
+    g = torch.Generator().manual_seed(11)
+    return torch.randn(H, generator=g, dtype=torch.float32)
+
+
+# ------------------------------------------------------------ reference sweep
+
+@pytest.mark.parametrize("version", ["v1", "v2"])
+@pytest.mark.parametrize("impl", [GENERIC, FAST])
+@pytest.mark.parametrize("heads", [(40, 40), (64, 8)])
+@pytest.mark.parametrize("head_size", [32, 64, 80, 128, 256])
+@pytest.mark.parametrize("block_size", [16, 32])
+@pytest.mark.parametrize("use_alibi", [False, True])
+@pytest.mark.parametrize("kv", ["auto", "fp8"])
+def test_paged_attention_sweep(ops, native, ora, version, impl, heads, head_size, block_size,
+                               use_alibi, kv):
+    H, Hkv = heads
+    dtype = torch.bfloat16
+    fast_ok = block_size == 16 and head_size in (64, 128)
+    if impl == FAST and not fast_ok:
+        pytest.skip("shape served by the generic kernel")
+    if kv == "fp8" and head_size % 16:
+        pytest.skip("x = 16 does not divide the head size")
+    B, NB, MAX = 7, 4321, 2048
+    rnd = random.Random(0)
+    lens = [rnd.randint(1, MAX) for _ in range(B)]
+    lens[-1] = MAX
+    s = head_size ** -0.5
+    q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, head_size, block_size, NB, lens, dtype,
+                                             seed=0, kv=kv, lo=-s, hi=s)
+    alibi = _alibi(H) if use_alibi else None
+    ks, vs = (1.0, 1.0) if kv == "auto" else (s / 2.0, s / 3.0)
+    native.set_impl(impl)
+    try:
+        got, *_ = _run_gpu(ops, version, q, kc, vc, Hkv, s, bt, sl, block_size, MAX, alibi, kv,
+                           ks, vs)
+    finally:
+        native.set_impl(native.IMPL_AUTO)
+    want = _run_oracle(ora, version, q, kc, vc, Hkv, s, bt, sl, block_size, MAX, alibi, kv,
+                       ks, vs)
+    _close(got, want)
+    if head_size == 128:
+        # the reference test's own check: fp64 math on the (dequantised) cache
+        kd = vd = None
+        if kv == "fp8":
+            kd, vd = hp.e4m3_to_float(kc) * ks, hp.e4m3_to_float(vc) * vs
+        ref64 = hp.torch_reference_attention(q, kc, vc, bt, sl, s, Hkv, alibi, kd, vd)
+        atol = 1e-3 if kv == "auto" else 1e-2
+        torch.testing.assert_close(got.double(), ref64, atol=atol, rtol=1e-2)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.float32])
+@pytest.mark.parametrize("version", ["v1", "v2"])
+@pytest.mark.parametrize("kv", ["auto", "fp8", "fp8_e5m2"])
+@pytest.mark.parametrize("block_size", [8, 16, 32])
+def test_other_dtypes_and_block_sizes(ops, native, ora, dtype, version, kv, block_size):
+    B, H, Hkv, D, NB = 5, 16, 4, 128, 300
+    lens = [1, 17, 512, 513, 1500]
+    s = D ** -0.5
+    q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, block_size, NB, lens, dtype, seed=3,
+                                             kv="auto" if kv == "auto" else "fp8", lo=-s, hi=s)
+    if kv == "fp8_e5m2":
+        # e5m2 codes: keep exponents moderate and avoid inf/nan (exp field 31)
+        kc, vc = kc & 0xBB, vc & 0xBB
+    ks, vs = (1.0, 1.0) if kv == "auto" else (0.01, 0.02)
+    got, *_ = _run_gpu(ops, version, q, kc, vc, Hkv, s, bt, sl, block_size, 1500, None, kv, ks, vs)
+    want = _run_oracle(ora, version, q, kc, vc, Hkv, s, bt, sl, block_size, 1500, None, kv, ks, vs)
+    tol = (1e-4, 1e-3) if (dtype == torch.float32 and kv == "auto") else (ATOL, RTOL)
+    _close(got, want, *tol)
+
+
+# ------------------------------------------------------------ golden fixtures
+
+ATTN_GOLDEN = ["attn_gqa_bf16_d128.npz", "attn_mha_bf16_d64_alibi.npz",
+               "attn_gqa_f16_d80.npz", "attn_gqa_bf16_d128_bs32.npz",
+               "attn_mha_f32_d32.npz"]
+
+
+@pytest.mark.parametrize("name", ATTN_GOLDEN)
+@pytest.mark.parametrize("version", ["v1", "v2"])
+@pytest.mark.parametrize("impl", [0, GENERIC])
+def test_against_reference_golden_outputs(ops, native, name, version, impl):
+    """Outputs recorded from the reference's own test oracle and CPU kernels
+    (tests/golden/make_golden.py)."""
+    g = hp.load_golden(name)
+    dt = hp.golden_dtype(g)
+    q = hp.from_bits(g["q"], dt)
+    kc, vc = hp.from_bits(g["key_cache"], dt), hp.from_bits(g["value_cache"], dt)
+    bt = torch.from_numpy(g["block_tables"].copy())
+    sl = torch.from_numpy(g["seq_lens"].copy())
+    alibi = torch.from_numpy(g["alibi_slopes"].copy()) if "alibi_slopes" in g else None
+    Hkv, BS, scale = int(g["num_kv_heads"]), int(g["block_size"]), float(g["scale"])
+    native.set_impl(impl)
+    try:
+        got, *_ = _run_gpu(ops, version, q, kc, vc, Hkv, scale, bt, sl, BS, int(sl.max()), alibi,
+                           "auto", 1.0, 1.0)
+    finally:
+        native.set_impl(native.IMPL_AUTO)
+    tol = (1e-4, 1e-4) if dt == torch.float32 else (ATOL, RTOL)
+    _close(got, hp.from_bits(g["out_test_ref"], dt), *tol)
+    for key in ("out_cpu_v1", "out_cpu_v2"):
+        if key in g:
+            _close(got, hp.from_bits(g[key], dt), *tol)
+
+
+# ------------------------------------------------- BASELINE configs (reduced)
+
+def _config_inputs(name):
+    """The five BASELINE.json configs at a batch the oracle finishes in seconds
+    (same per-sequence shape)."""
+    D, BS = 128, 16
+    s = D ** -0.5
+    if name == "cfg1":    # Llama-2-7B MHA, ctx 1024, bf16
+        B, H, Hkv, lens, kv = 8, 32, 32, [1024] * 8, "auto"
+    elif name == "cfg2":  # Llama-3-8B GQA 32/8, ctx 4096, bf16
+        B, H, Hkv, lens, kv = 4, 32, 8, [4096] * 4, "auto"
+    elif name == "cfg3":  # Llama-3-8B, fp8, ctx 8192
+        B, H, Hkv, lens, kv = 4, 32, 8, [8192] * 4, "fp8"
+    elif name == "cfg4":  # Llama-3-70B 64/8 sharded 8 ways -> 8 q heads, 1 kv head; ctx 32768
+        B, H, Hkv, lens, kv = 3, 8, 1, [32768] * 3, "fp8"
+    elif name == "cfg4_tp1":
+        B, H, Hkv, lens, kv = 1, 64, 8, [32768], "fp8"
+    else:                 # cfg5: ragged 128..131072, permuted tables, Qwen2-72B shard
+        B, H, Hkv, kv = 6, 8, 1, "fp8"
+        lens = [128, 131072, 5000, 777, 65536 + 3, 20001]
+    NB = sum((L + BS - 1) // BS for L in lens) + 7
+    q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, NB, lens, torch.bfloat16, seed=1,
+                                             kv=kv, lo=-s, hi=s, permute=True)
+    ks, vs = (1.0, 1.0) if kv == "auto" else (s / 1.7, s / 2.9)
+    return q, kc, vc, bt, sl, H, Hkv, D, BS, s, kv, ks, vs, max(lens)
+
+
+@pytest.mark.parametrize("name", ["cfg1", "cfg2", "cfg3", "cfg4", "cfg4_tp1", "cfg5"])
+@pytest.mark.parametrize("version", ["v1", "v2"])
+@pytest.mark.parametrize("impl", [FAST, GENERIC])
+def test_baseline_configs_reduced_batch(ops, native, ora, name, version, impl):
+    q, kc, vc, bt, sl, H, Hkv, D, BS, s, kv, ks, vs, max_len = _config_inputs(name)
+    native.set_impl(impl)
+    try:
+        got, *_ = _run_gpu(ops, version, q, kc, vc, Hkv, s, bt, sl, BS, max_len, None, kv, ks, vs)
+    finally:
+        native.set_impl(native.IMPL_AUTO)
+    want = _run_oracle(ora, version, q, kc, vc, Hkv, s, bt, sl, BS, max_len, None, kv, ks, vs)
+    _close(got, want)
+
+
+# ---------------------------------------------------- full-size property tests
+
+def _full_size(ops, B, H, Hkv, ctx, kv, seed=0):
+    """Inputs generated ON the device at BASELINE's full size."""
+    D, BS = 128, 16
+    s = D ** -0.5
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    nblk = ctx // BS
+    NB = B * nblk
+    q = ((torch.rand(B, H, D, generator=g, device=DEV) * 2 - 1) * s).to(torch.bfloat16)
+    if kv == "auto":
+        kc = ((torch.rand(NB, Hkv, D // 8, BS, 8, generator=g, device=DEV) * 2 - 1) * s).to(torch.bfloat16)
+        vc = ((torch.rand(NB, Hkv, D, BS, generator=g, device=DEV) * 2 - 1) * s).to(torch.bfloat16)
+    else:
+        kc = torch.randint(0, 0x48, (NB, Hkv, D // 16, BS, 16), generator=g, device=DEV, dtype=torch.uint8)
+        kc |= (torch.randint(0, 2, kc.shape, generator=g, device=DEV, dtype=torch.uint8) << 7)
+        vc = torch.randint(0, 0x48, (NB, Hkv, D, BS), generator=g, device=DEV, dtype=torch.uint8)
+        vc |= (torch.randint(0, 2, vc.shape, generator=g, device=DEV, dtype=torch.uint8) << 7)
+    perm = torch.randperm(NB, generator=g, device=DEV).to(torch.int32)
+    bt = perm.view(B, nblk).contiguous()
+    sl = torch.full((B,), ctx, dtype=torch.int32, device=DEV)
+    return q, kc, vc, bt, sl, s
+
+
+def _call(ops, version, q, kc, vc, Hkv, s, bt, sl, max_len, kv, ks, vs):
+    out = torch.empty_like(q)
+    B, H, D = q.shape
+    if version == "v1":
+        ops.paged_attention_v1(out, q, kc, vc, Hkv, s, bt, sl, 16, max_len, None, kv, ks, vs)
+    else:
+        P = (max_len + 511) // 512
+        es = torch.empty(B, H, P, dtype=torch.float32, device=DEV)
+        ml = torch.empty_like(es)
+        tmp = torch.empty(B, H, P, D, dtype=q.dtype, device=DEV)
+        ops.paged_attention_v2(out, es, ml, tmp, q, kc, vc, Hkv, s, bt, sl, 16, max_len, None,
+                               kv, ks, vs)
+    return out
+
+
+@pytest.mark.parametrize("cfg", [("cfg2", 64, 32, 8, 4096, "auto"),
+                                 ("cfg3", 256, 32, 8, 8192, "fp8"),
+                                 ("cfg4_tp8", 128, 8, 1, 32768, "fp8")])
+def test_full_size_properties(ops, native, ora, cfg):
+    name, B, H, Hkv, ctx, kv = cfg
+    q, kc, vc, bt, sl, s = _full_size(ops, B, H, Hkv, ctx, kv)
+    ks = torch.tensor(1.0 if kv == "auto" else s / 1.7, device=DEV)
+    vs = torch.tensor(1.0 if kv == "auto" else s / 2.9, device=DEV)
+    native.set_impl(FAST)
+    try:
+        o1 = _call(ops, "v1", q, kc, vc, Hkv, s, bt, sl, ctx, kv, ks, vs)
+        o2 = _call(ops, "v2", q, kc, vc, Hkv, s, bt, sl, ctx, kv, ks, vs)
+        # (i) determinism
+        o1b = _call(ops, "v1", q, kc, vc, Hkv, s, bt, sl, ctx, kv, ks, vs)
+        assert torch.equal(o1, o1b)
+        # (ii) v1 and v2 agree
+        _close(o2.cpu(), o1.cpu())
+        # (iii) block-table permutation invariance: move the pages, permute the table
+        #       consistently -> identical results (bitwise: the page walk order is unchanged)
+        g = torch.Generator(device=DEV).manual_seed(99)
+        NB = kc.shape[0]
+        sigma = torch.randperm(NB, generator=g, device=DEV)
+        kc2 = torch.empty_like(kc)
+        vc2 = torch.empty_like(vc)
+        kc2[sigma] = kc
+        vc2[sigma] = vc
+        bt2 = sigma.to(torch.int32)[bt.long()]
+        o3 = _call(ops, "v2", q, kc2, vc2, Hkv, s, bt2, sl, ctx, kv, ks, vs)
+        assert torch.equal(o3, o2)
+        del kc2, vc2
+        # (iv) linearity in v_scale (fp8): doubling v_scale doubles the output exactly
+        if kv != "auto":
+            o4 = _call(ops, "v2", q, kc, vc, Hkv, s, bt, sl, ctx, kv, ks, vs * 2)
+            assert torch.equal(o4.float(), o2.float() * 2)
+    finally:
+        native.set_impl(native.IMPL_AUTO)
+    # (v) the generic kernel (different algorithm) agrees on the whole batch
+    native.set_impl(GENERIC)
+    try:
+        og = _call(ops, "v2", q, kc, vc, Hkv, s, bt, sl, ctx, kv, ks, vs)
+    finally:
+        native.set_impl(native.IMPL_AUTO)
+    _close(o2.cpu(), og.cpu())
+    # (vi) the oracle on a sample of sequences (first, middle, last)
+    idx = [0, B // 2, B - 1]
+    sel = torch.tensor(idx, device=DEV)
+    qs, bts, sls = q[sel].cpu(), bt[sel].cpu(), sl[sel].cpu()
+    # compact the touched pages so the CPU copy stays small
+    used = torch.unique(bts.flatten().long())
+    remap = torch.zeros(kc.shape[0], dtype=torch.int32)
+    remap[used] = torch.arange(used.numel(), dtype=torch.int32)
+    kcs, vcs = kc[used.to(DEV)].cpu(), vc[used.to(DEV)].cpu()
+    bts = remap[bts.long()]
+    want = _run_oracle(ora, "v2", qs, kcs, vcs, Hkv, s, bts, sls, 16, ctx, None, kv,
+                       float(ks), float(vs))
+    _close(o2[sel].cpu(), want)
+    _close(o1[sel].cpu(), want)
+
+
+# ------------------------------------------------------------- layout details
+
+@pytest.mark.parametrize("version", ["v1", "v2"])
+@pytest.mark.parametrize("kv", ["auto", "fp8"])
+def test_strided_query_and_padded_cache(ops, ora, version, kv):
+    """query is a slice of a fused qkv tensor (q_stride != H*D, paged_attention_v1.cu:172)
+    and the cache has a padded block stride (kv_block_stride from stride(0))."""
+    B, H, Hkv, D, BS, NB = 5, 32, 8, 128, 16, 200
+    lens = [700, 16, 15, 1025, 333]
+    s = D ** -0.5
+    q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, NB, lens, torch.bfloat16, seed=4,
+                                             kv=kv, lo=-s, hi=s)
+    ks, vs = (1.0, 1.0) if kv == "auto" else (0.02, 0.03)
+    want = _run_oracle(ora, version, q, kc, vc, Hkv, s, bt, sl, BS, 1025, None, kv, ks, vs)
+    qkv = torch.zeros(B, H + 2 * Hkv, D, dtype=q.dtype, device=DEV)
+    qkv[:, :H] = q.to(DEV)
+    qd = qkv[:, :H]
+    assert qd.stride(0) != H * D
+    x = kc.shape[-1]
+    pad = 3
+    kbig = torch.zeros(NB, Hkv + pad, D // x, BS, x, dtype=kc.dtype, device=DEV)
+    vbig = torch.zeros(NB, Hkv + pad, D, BS, dtype=vc.dtype, device=DEV)
+    kbig[:, :Hkv] = kc.to(DEV)
+    vbig[:, :Hkv] = vc.to(DEV)
+    kcd, vcd = kbig[:, :Hkv], vbig[:, :Hkv]
+    out = torch.empty(B, H, D, dtype=q.dtype, device=DEV)
+    ksd, vsd = torch.tensor(ks, device=DEV), torch.tensor(vs, device=DEV)
+    if version == "v1":
+        ops.paged_attention_v1(out, qd, kcd, vcd, Hkv, s, bt.to(DEV), sl.to(DEV), BS, 1025, None,
+                               kv, ksd, vsd)
+    else:
+        P = 3
+        es = torch.empty(B, H, P, dtype=torch.float32, device=DEV)
+        ml = torch.empty_like(es)
+        tmp = torch.empty(B, H, P, D, dtype=q.dtype, device=DEV)
+        ops.paged_attention_v2(out, es, ml, tmp, qd, kcd, vcd, Hkv, s, bt.to(DEV), sl.to(DEV),
+                               BS, 1025, None, kv, ksd, vsd)
+    _close(out.cpu(), want)
+
+
+@pytest.mark.parametrize("impl", [FAST, GENERIC])
+def test_v2_scratch_contract(ops, native, impl):
+    """After paged_attention_v2 the scratch buffers hold valid partials: merging
+    them with the reference's reduce formula (attention_kernels.cuh:560-664)
+    reproduces `out`."""
+    B, H, Hkv, D, BS, NB = 4, 16, 4, 128, 16, 600
+    lens = [4096, 513, 100, 2049]
+    s = D ** -0.5
+    q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, NB, lens, torch.bfloat16, seed=6,
+                                             lo=-s, hi=s)
+    native.set_impl(impl)
+    try:
+        out, es, ml, tmp = _run_gpu(ops, "v2", q, kc, vc, Hkv, s, bt, sl, BS, 4096, None, "auto",
+                                    1.0, 1.0)
+    finally:
+        native.set_impl(native.IMPL_AUTO)
+    for b in range(B):
+        npart = (lens[b] + 511) // 512
+        e, m, t = es[b, :, :npart], ml[b, :, :npart], tmp[b, :, :npart].float()
+        assert not torch.isnan(e).any() and not torch.isnan(m).any()
+        live = e > 0
+        mm = torch.where(live, m, torch.full_like(m, -float("inf")))
+        gmax = mm.max(dim=1, keepdim=True).values
+        w = torch.where(live, e * torch.exp(mm - gmax), torch.zeros_like(e))
+        t = torch.where(live.unsqueeze(-1), t, torch.zeros_like(t))
+        merged = (t * w.unsqueeze(-1)).sum(1) / (w.sum(1, keepdim=True) + 1e-6)
+        torch.testing.assert_close(out[b].float(), merged, atol=2e-3, rtol=2e-2)
+
+
+def test_zero_length_sequence_v1_gives_zeros(ops, native):
+    B, H, Hkv, D, BS, NB = 3, 8, 2, 128, 16, 20
+    lens = [40, 0, 7]
+    s = D ** -0.5
+    q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, NB, lens, torch.bfloat16, seed=8,
+                                             lo=-s, hi=s)
+    for impl in (FAST, GENERIC):
+        native.set_impl(impl)
+        try:
+            out, *_ = _run_gpu(ops, "v1", q, kc, vc, Hkv, s, bt, sl, BS, 40, None, "auto", 1.0, 1.0)
+        finally:
+            native.set_impl(native.IMPL_AUTO)
+        assert float(out[1].float().abs().sum()) == 0.0
+        assert float(out[0].float().abs().sum()) > 0.0
+
+
+def test_tail_page_garbage_is_ignored(ops, native, ora):
+    """Slots past seq_len in the last page may hold anything, including NaN codes
+    (attention_kernels.cuh:415-425 zeroes them)."""
+    B, H, Hkv, D, BS, NB = 2, 8, 2, 128, 16, 12
+    lens = [21, 35]
+    s = D ** -0.5
+    for kv in ("auto", "fp8"):
+        q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, NB, lens, torch.bfloat16,
+                                                 seed=9, kv=kv, lo=-s, hi=s, permute=True)
+        want = _run_oracle(ora, "v1", q, kc, vc, Hkv, s, bt, sl, BS, 35, None, kv, 0.5, 0.25)
+        kc2, vc2 = kc.clone(), vc.clone()
+        for b, L in enumerate(lens):
+            blk, off = int(bt[b, (L - 1) // BS]), L % BS
+            if kv == "auto":
+                kc2[blk, :, :, off:, :] = float("nan")
+                vc2[blk, :, :, off:] = float("nan")
+            else:
+                kc2[blk, :, :, off:, :] = 0x7F
+                vc2[blk, :, :, off:] = 0x7F
+        for impl in (FAST, GENERIC):
+            native.set_impl(impl)
+            try:
+                for version in ("v1", "v2"):
+                    got, *_ = _run_gpu(ops, version, q, kc2, vc2, Hkv, s, bt, sl, BS, 35, None, kv,
+                                       0.5, 0.25)
+                    _close(got, want)
+            finally:
+                native.set_impl(native.IMPL_AUTO)
+
+
+def test_blocksparse_matches_oracle(ops, ora):
+    B, H, Hkv, D, BS, NB = 3, 8, 2, 64, 16, 120
+    lens = [300, 513, 1200]
+    s = D ** -0.5
+    q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, NB, lens, torch.bfloat16, seed=7,
+                                             lo=-s, hi=s)
+    extra = (1, 2, 3, 32, 1)   # tp_rank, local_blocks, vert_stride, block_size, sliding_step
+    for version in ("v1", "v2"):
+        got, *_ = _run_gpu(ops, version, q, kc, vc, Hkv, s, bt, sl, BS, 1200, None, "auto", 1.0,
+                           1.0, extra=extra)
+        want = _run_oracle(ora, version, q, kc, vc, Hkv, s, bt, sl, BS, 1200, None, "auto", 1.0,
+                           1.0, extra=extra)
+        _close(got, want)
+
+
+# ----------------------------------------------------------- boundary contract
+
+def _small_device_case(kv="fp8"):
+    B, H, Hkv, D, BS, NB = 4, 32, 8, 128, 16, 300
+    lens = [1000, 37, 512, 640]
+    s = D ** -0.5
+    q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, NB, lens, torch.bfloat16, seed=12,
+                                             kv=kv, lo=-s, hi=s)
+    return [t.to(DEV) for t in (q, kc, vc, bt, sl)] + [Hkv, s, BS, 1000]
+
+
+def test_opcheck_schemas(ops):
+    """tests/kernels/utils.py:1247-1261 of the reference: torch.library.opcheck on the
+    registered ops with the positional tail (..., 0, 0, 0, 64, 0)."""
+    q, kc, vc, bt, sl, Hkv, s, BS, max_len = _small_device_case()
+    one = torch.tensor(0.02, device=DEV)
+    out = torch.empty_like(q)
+    utils = ("test_schema", "test_faketensor")
+    for ns in (torch.ops.b200pa, torch.ops._C):
+        torch.library.opcheck(ns.paged_attention_v1,
+                              (out, q, kc, vc, Hkv, s, bt, sl, BS, max_len, None, "fp8", one, one,
+                               0, 0, 0, 64, 0), test_utils=utils)
+        B, H, D = q.shape
+        P = 2
+        es = torch.empty(B, H, P, dtype=torch.float32, device=DEV)
+        ml = torch.empty_like(es)
+        tmp = torch.empty(B, H, P, D, dtype=q.dtype, device=DEV)
+        torch.library.opcheck(ns.paged_attention_v2,
+                              (out, es, ml, tmp, q, kc, vc, Hkv, s, bt, sl, BS, max_len, None,
+                               "fp8", one, one, 0, 0, 0, 64, 0), test_utils=utils)
+    key = torch.randn(4, Hkv, 128, dtype=torch.bfloat16, device=DEV)
+    slots = torch.tensor([3, 99, -1, 1000], dtype=torch.int64, device=DEV)
+    for ns in (torch.ops.b200pa, torch.ops._C_cache_ops):
+        torch.library.opcheck(ns.reshape_and_cache, (key, key, kc, vc, slots, "fp8", one, one),
+                              test_utils=utils)
+        kf = torch.zeros(10, BS, Hkv, 128, dtype=torch.uint8, device=DEV)
+        torch.library.opcheck(ns.reshape_and_cache_flash,
+                              (key, key, kf, kf.clone(), slots[:3], "fp8", one, one),
+                              test_utils=utils)
+    assert torch.ops._C_cuda_utils.get_max_shared_memory_per_block_device_attribute(0) >= 227 * 1024
+
+
+def test_cuda_graph_capture_and_replay(ops):
+    """The ops are asynchronous on the current stream, allocation-free and read
+    k_scale / v_scale on the device: a decode step captures into a CUDA graph."""
+    q, kc, vc, bt, sl, Hkv, s, BS, max_len = _small_device_case()
+    ks, vs = torch.tensor(0.02, device=DEV), torch.tensor(0.03, device=DEV)
+    B, H, D = q.shape
+    key = torch.randn(B, Hkv, D, dtype=torch.bfloat16, device=DEV) * 0.05
+    slots = (bt[torch.arange(B, device=DEV), ((sl - 1) // BS).long()].long() * BS
+             + ((sl - 1) % BS).long())
+    P = 2
+    es = torch.empty(B, H, P, dtype=torch.float32, device=DEV)
+    ml = torch.empty_like(es)
+    tmp = torch.empty(B, H, P, D, dtype=q.dtype, device=DEV)
+    out_g = torch.empty_like(q)
+
+    def step(out):
+        ops.reshape_and_cache(key, key, kc, vc, slots, "fp8", ks, vs)
+        ops.paged_attention_v2(out, es, ml, tmp, q, kc, vc, Hkv, s, bt, sl, BS, max_len, None,
+                               "fp8", ks, vs)
+
+    stream = torch.cuda.Stream()
+    with torch.cuda.stream(stream):
+        step(out_g)                      # warm-up on the side stream
+        stream.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=stream):
+            step(out_g)
+    out_g.zero_()
+    graph.replay()
+    torch.cuda.synchronize()
+    out_e = torch.empty_like(q)
+    step(out_e)
+    torch.cuda.synchronize()
+    assert torch.equal(out_g, out_e)
+    # the scale is read on the device at replay time
+    vs.mul_(2)
+    graph.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out_g.float(), out_e.float() * 2)
+
+
+def test_error_convention(ops):
+    q, kc, vc, bt, sl, Hkv, s, BS, max_len = _small_device_case("auto")
+    one = torch.tensor(1.0, device=DEV)
+    out = torch.empty_like(q)
+    q48 = torch.zeros(4, 32, 48, dtype=torch.bfloat16, device=DEV)
+    with pytest.raises(RuntimeError, match="Unsupported head size"):
+        ops.paged_attention_v1(torch.empty_like(q48), q48, kc, vc, Hkv, s, bt, sl, BS, max_len,
+                               None, "auto", one, one)
+    with pytest.raises(RuntimeError, match="Unsupported block size"):
+        ops.paged_attention_v1(out, q, kc, vc, Hkv, s, bt, sl, 4, max_len, None, "auto", one, one)
+    with pytest.raises(RuntimeError, match="Unsupported data type of kv cache"):
+        ops.paged_attention_v1(out, q, kc, vc, Hkv, s, bt, sl, BS, max_len, None, "int4", one, one)
+    with pytest.raises(RuntimeError):   # CPU tensors: there is no CPU path
+        ops.paged_attention_v1(out.cpu(), q.cpu(), kc.cpu(), vc.cpu(), Hkv, s, bt.cpu(), sl.cpu(),
+                               BS, max_len, None, "auto", one.cpu(), one.cpu())
+
+
+def test_launch_counter_counts_native_launches(ops, native):
+    q, kc, vc, bt, sl, Hkv, s, BS, max_len = _small_device_case()
+    one = torch.tensor(0.02, device=DEV)
+    n0 = native.launch_count()
+    ops.paged_attention_v1(torch.empty_like(q), q, kc, vc, Hkv, s, bt, sl, BS, max_len, None,
+                           "fp8", one, one)
+    assert native.launch_count() == n0 + 1
+
+
+# ------------------------------------------------------ backend (AttentionImpl)
+
+class _Layer:
+    """AttentionLayer protocol (abstract.py:92-110): carries the scale tensors."""
+
+    def __init__(self, ks, vs):
+        self._k_scale = torch.tensor(ks, device=DEV)
+        self._v_scale = torch.tensor(vs, device=DEV)
+        self._q_scale = torch.tensor(1.0, device=DEV)
+
+
+@pytest.mark.parametrize("kv", ["auto", "fp8"])
+def test_backend_decode_step_matches_oracle(ora, kv):
+    """AttentionImpl.forward: write the new token's K/V, then attend -- against the
+    oracle doing the same two steps on the CPU."""
+    from vllm_main_modify_b200.backend import (B200PagedAttentionBackend,
+                                               B200PagedAttentionMetadata)
+    B, H, Hkv, D, BS, NB = 6, 32, 8, 128, 16, 400
+    lens = [1, 16, 17, 900, 512, 513]            # seq_lens INCLUDING the new token
+    dt = torch.bfloat16
+    s = D ** -0.5
+    cdt = dt if kv == "auto" else torch.uint8
+    q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, NB, lens, dt, seed=21, kv=kv,
+                                             lo=-s, hi=s, permute=True)
+    g = torch.Generator().manual_seed(22)
+    key = ((torch.rand(B, Hkv, D, generator=g) * 2 - 1) * s).to(dt)
+    value = ((torch.rand(B, Hkv, D, generator=g) * 2 - 1) * s).to(dt)
+    slots = torch.tensor([int(bt[b, (L - 1) // BS]) * BS + (L - 1) % BS
+                          for b, L in enumerate(lens)], dtype=torch.int64)
+    ks, vs = (1.0, 1.0) if kv == "auto" else (s / 100, s / 90)
+    # oracle: write, then attend
+    kc_o, vc_o = kc.clone(), vc.clone()
+    ora.reshape_and_cache(key, value, kc_o, vc_o, slots, kv, torch.tensor(ks), torch.tensor(vs))
+    want = _run_oracle(ora, "v1", q, kc_o, vc_o, Hkv, s, bt, sl, BS, max(lens), None, kv, ks, vs)
+    # product: the backend object model
+    backend = B200PagedAttentionBackend
+    shape = backend.get_kv_cache_shape(NB, BS, Hkv, D)
+    kv_cache = torch.empty(shape, dtype=cdt, device=DEV)
+    kv_cache[0] = kc.reshape(NB, -1).to(DEV)
+    kv_cache[1] = vc.reshape(NB, -1).to(DEV)
+    impl = backend.get_impl_cls()(H, D, s, Hkv, None, None, kv)
+    meta = B200PagedAttentionMetadata(num_actual_tokens=B, max_query_len=1, seq_lens=sl.to(DEV),
+                                      max_seq_len=max(lens), block_table=bt.to(DEV),
+                                      slot_mapping=slots.to(DEV))
+    out = impl.forward(_Layer(ks, vs), q.to(DEV).view(B, H * D), key.to(DEV).view(B, Hkv * D),
+                       value.to(DEV).view(B, Hkv * D), kv_cache, meta)
+    torch.cuda.synchronize()
+    _close(out.view(B, H, D).cpu(), want)
+    # and the cache bytes are the oracle's
+    assert torch.equal(kv_cache[0].cpu().view(torch.uint8), kc_o.reshape(NB, -1).view(torch.uint8))
+    assert torch.equal(kv_cache[1].cpu().view(torch.uint8), vc_o.reshape(NB, -1).view(torch.uint8))

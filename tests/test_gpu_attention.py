@@ -539,10 +539,16 @@ def test_cuda_graph_capture_and_replay(ops):
     torch.cuda.synchronize()
     assert torch.equal(out_g, out_e)
     # the scale is read on the device at replay time
+    # (the step also re-quantises the new token's V with the new scale, so the
+    # comparison is against an eager step under the same scale, not "old * 2")
+    prev = out_g.clone()
     vs.mul_(2)
     graph.replay()
     torch.cuda.synchronize()
-    assert torch.equal(out_g.float(), out_e.float() * 2)
+    step(out_e)
+    torch.cuda.synchronize()
+    assert torch.equal(out_g, out_e)
+    assert not torch.equal(out_g, prev)
 
 
 def test_error_convention(ops):

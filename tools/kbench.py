@@ -1,0 +1,98 @@
+#!/usr/bin/env python
+"""Kernel-level sweep over the five BASELINE configs (development tool).
+
+Times ops.paged_attention_v1 / _v2 and ops.reshape_and_cache directly with CUDA
+events on the current stream (KV per call >> L2 for cfg2-5; cfg1 gets an L2 flush
+between calls) and prints one JSON line per (config, op).
+
+  python tools/kbench.py [--configs cfg1,cfg2,...] [--iters 20] [--tp 1]
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import bench  # noqa: E402
+
+
+def time_op(fn, iters, flush=None):
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    evs = []
+    for _ in range(iters):
+        if flush is not None:
+            flush.add_(1)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        evs.append((a, b))
+    torch.cuda.synchronize()
+    ts = sorted(a.elapsed_time(b) for a, b in evs)
+    return ts[len(ts) // 2], ts[0]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--configs", default="cfg1,cfg2,cfg3,cfg4,cfg5")
+    ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--tp", type=int, default=1, help="emulate rank 0 of a tp-way KV-head shard")
+    args = ap.parse_args()
+    from vllm_main_modify_b200 import _custom_ops as ops
+    from vllm_main_modify_b200.paged_attn import PagedAttention
+
+    dev = torch.device("cuda", 0)
+    peak = 6524.6
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peak = float(json.load(f)["hbm_gbs"])
+    except OSError:
+        pass
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    for cfg in args.configs.split(","):
+        desc, B, H, Hkv, ctx, kv, ragged = bench.CONFIGS[cfg]
+        w = bench.make_shard(cfg, 0, args.tp, dev)
+        kc, vc = PagedAttention.split_kv_cache(w["kv_cache"], w["Hkv"], bench.D)
+        nbytes = bench.kv_bytes(w["lens"], w["Hkv"], kv)
+        out = torch.empty_like(w["q"])
+        P = (w["max_len"] + 511) // 512
+        es = torch.empty(B, w["H"], P, dtype=torch.float32, device=dev)
+        ml = torch.empty_like(es)
+        tmp = torch.empty(B, w["H"], P, bench.D, dtype=out.dtype, device=dev)
+        fl = flush if nbytes < (512 << 20) else None
+
+        def v1():
+            ops.paged_attention_v1(out, w["q"], kc, vc, w["Hkv"], w["scale"], w["bt"], w["sl"],
+                                   bench.BS, w["max_len"], None, kv, w["ks"], w["vs"])
+
+        def v2():
+            ops.paged_attention_v2(out, es, ml, tmp, w["q"], kc, vc, w["Hkv"], w["scale"], w["bt"],
+                                   w["sl"], bench.BS, w["max_len"], None, kv, w["ks"], w["vs"])
+
+        def wr():
+            ops.reshape_and_cache(w["k_new"], w["v_new"], kc, vc, w["slots"], kv, w["ks"], w["vs"])
+
+        for name, fn in (("v1", v1), ("v2", v2), ("reshape_and_cache", wr)):
+            med, best = time_op(fn, args.iters, fl)
+            line = {"config": cfg, "tp": args.tp, "op": name, "ms_median": round(med, 4),
+                    "ms_best": round(best, 4)}
+            if name != "reshape_and_cache":
+                gbs = nbytes / (med * 1e-3) / 1e9
+                line.update(kv_gib=round(nbytes / 2**30, 3), gbs=round(gbs, 1),
+                            frac_measured=round(gbs / peak, 4), pct_8tb=round(gbs / 80.0, 2),
+                            heuristic_v1=PagedAttention.use_v1(w["max_len"], B, w["H"]))
+            print(json.dumps(line), flush=True)
+        del w, kc, vc, tmp, es, ml, out
+        torch.cuda.empty_cache()
+
+
+if __name__ == "__main__":
+    main()

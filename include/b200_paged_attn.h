@@ -63,7 +63,10 @@ enum {
 enum {
   B200PA_IMPL_AUTO = 0,    /* fast path when the shape is covered, else generic */
   B200PA_IMPL_GENERIC = 1, /* SIMT kernel, whole reference domain */
-  B200PA_IMPL_FAST = 2     /* TMA-staged tensor-core kernel; error if not covered */
+  B200PA_IMPL_FAST = 2,    /* TMA-staged tensor-core kernel, one CTA per (chunk, kv head,
+                              sequence); error if not covered */
+  B200PA_IMPL_STREAM = 3   /* v2 only: persistent stream-K kernel (the default for covered
+                              shapes); error if not covered */
 };
 
 int b200pa_abi_version(void);

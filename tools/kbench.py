@@ -45,8 +45,12 @@ def main():
     ap.add_argument("--configs", default="cfg1,cfg2,cfg3,cfg4,cfg5")
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--tp", type=int, default=1, help="emulate rank 0 of a tp-way KV-head shard")
+    ap.add_argument("--impl", type=int, default=0, help="b200pa_set_impl value (0 auto)")
+    ap.add_argument("--ops", default="v1,v2,reshape_and_cache")
     args = ap.parse_args()
     from vllm_main_modify_b200 import _custom_ops as ops
+    from vllm_main_modify_b200 import _native
+    _native.set_impl(args.impl)
     from vllm_main_modify_b200.paged_attn import PagedAttention
 
     dev = torch.device("cuda", 0)
@@ -81,8 +85,12 @@ def main():
             ops.reshape_and_cache(w["k_new"], w["v_new"], kc, vc, w["slots"], kv, w["ks"], w["vs"])
 
         for name, fn in (("v1", v1), ("v2", v2), ("reshape_and_cache", wr)):
+            if name not in args.ops.split(","):
+                continue
             med, best = time_op(fn, args.iters, fl)
-            line = {"config": cfg, "tp": args.tp, "op": name, "ms_median": round(med, 4),
+            line = {"config": cfg, "tp": args.tp, "impl": args.impl,
+                    "tune": os.environ.get("B200PA_STREAM_TUNE", "0"), "op": name,
+                    "ms_median": round(med, 4),
                     "ms_best": round(best, 4)}
             if name != "reshape_and_cache":
                 gbs = nbytes / (med * 1e-3) / 1e9

@@ -19,7 +19,7 @@ C_ABI_SYMBOLS = (
     "b200pa_get_max_shared_memory_per_block_device_attribute",
 )
 
-IMPL_AUTO, IMPL_GENERIC, IMPL_FAST = 0, 1, 2
+IMPL_AUTO, IMPL_GENERIC, IMPL_FAST, IMPL_STREAM = 0, 1, 2, 3
 
 _lock = threading.Lock()
 _clib = None

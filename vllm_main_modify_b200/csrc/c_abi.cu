@@ -7,6 +7,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -32,6 +33,13 @@ bool fast_supported(const void*, const void*, const void*, int, int, int, int, i
 int launch_fast(void*, float*, float*, void*, const void*, const void*, const void*, int, int, int,
                 int, float, const int32_t*, int, const int32_t*, int, int, const float*, int64_t,
                 int64_t, int64_t, int, int, const float*, const float*, bool, int, cudaStream_t);
+bool stream_supported(const void*, const void*, const void*, int, int, int, int, int64_t, int64_t,
+                      int64_t, int, int, int);
+int launch_stream(float*, float*, void*, const void*, const void*, const void*, int, int, int, int,
+                  float, const int32_t*, int, const int32_t*, int, const float*, int64_t, int64_t,
+                  int64_t, int, int, const float*, const float*, int, int, cudaStream_t);
+int launch_reduce_warp(void*, const float*, const float*, const void*, const int32_t*, int, int,
+                       int, int, int, cudaStream_t);
 
 static thread_local char g_err[512] = "";
 static std::atomic<int> g_impl{B200PA_IMPL_AUTO};
@@ -63,6 +71,18 @@ static int num_sms() {
       cached = n;
     else
       return 148;
+  }
+  return cached;
+}
+
+// development knob: B200PA_STREAM_TUNE=<n> selects an alternative (stages, pages/stage,
+// CTAs/SM) instantiation of the stream kernel (see launch_stream)
+static int stream_tune() {
+  static int cached = -1;
+  if (cached < 0) {
+    const char* e = getenv("B200PA_STREAM_TUNE");
+    cached = e ? atoi(e) : 0;
+    if (cached < 0) cached = 0;
   }
   return cached;
 }
@@ -133,7 +153,24 @@ static int paged_attention_common(
                                       kv_head_stride, scalar_type, kv_dtype, bs_vert_stride);
   if (impl == B200PA_IMPL_FAST && !fast_ok)
     return set_error(B200PA_ERR_UNSUPPORTED, "configuration not covered by the fast kernel");
+  const bool stream_ok =
+      partitioned && stream_supported(query, key_cache, value_cache, num_heads, num_kv_heads,
+                                      head_size, block_size, q_stride, kv_block_stride,
+                                      kv_head_stride, scalar_type, kv_dtype, bs_vert_stride);
+  if (impl == B200PA_IMPL_STREAM && !stream_ok)
+    return set_error(B200PA_ERR_UNSUPPORTED, "configuration not covered by the stream kernel");
   int rc;
+  if (stream_ok && (impl == B200PA_IMPL_AUTO || impl == B200PA_IMPL_STREAM)) {
+    // persistent stream-K kernel + warp-per-row merge
+    rc = launch_stream(exp_sums, max_logits, tmp_out, query, key_cache, value_cache, num_seqs,
+                       num_heads, num_kv_heads, head_size, scale, block_tables,
+                       max_num_blocks_per_seq, seq_lens, max_num_partitions, alibi_slopes,
+                       q_stride, kv_block_stride, kv_head_stride, scalar_type, kv_dtype, k_scale,
+                       v_scale, num_sms(), stream_tune(), stream);
+    if (rc) return rc;
+    return launch_reduce_warp(out, exp_sums, max_logits, tmp_out, seq_lens, num_seqs, num_heads,
+                              head_size, max_num_partitions, scalar_type, stream);
+  }
   if (fast_ok && impl != B200PA_IMPL_GENERIC) {
     rc = launch_fast(out, exp_sums, max_logits, tmp_out, query, key_cache, value_cache, num_seqs,
                      num_heads, num_kv_heads, head_size, scale, block_tables,

@@ -1,0 +1,801 @@
+// Persistent, warp-specialised-free "stream-K" paged-decode attention for sm_100a.
+//
+// Replaces the split-K decode kernel of the reference
+// (csrc/attention/attention_kernels.cuh:85-491 through paged_attention_v2_kernel
+// :525-557, launched from paged_attention_v2.cu:47-126) for head_size 64/128,
+// block_size 16, bf16/fp16 query and a 16-bit or fp8-e4m3 KV cache.
+//
+//  * WORK DECOMPOSITION.  The unit of work is one 512-token partition
+//    (_PARTITION_SIZE, paged_attn.py:21) of one (sequence, kv head).  Units are
+//    flattened in (sequence, kv head, partition) order and cut into
+//    gridDim.x * NW equal contiguous spans, one per WARP.  The grid is sized to
+//    exactly fill the machine (SMs x resident CTAs), every warp streams its span
+//    from start to end, so all warps finish together whatever the mix of
+//    sequence lengths (ragged batches need no host-side knowledge of seq_lens:
+//    each warp derives its span from seq_lens on the device).
+//  * Each warp is an independent worker: its own TMA ring, mbarriers, query
+//    fragments and accumulators.  There is no CTA-wide barrier in the kernel.
+//    When a span crosses into another (sequence, kv head) the warp writes the
+//    partial (normalised output, exp-sum, max-logit) of the segment it just
+//    finished to the scratch slot of the segment's first partition (the other
+//    slots of the segment get exp_sum = 0) and carries on; the TMA producer side
+//    runs STAGES ahead across such boundaries, so the pipe never drains.
+//    paged_attention_reduce_kernel merges the partials.
+//  * LOADS.  For one (page, kv head) the x-packed K sub-block [D/x][16][x] and
+//    the V sub-block [D][16] are each one contiguous run (2 KiB fp8 / 4 KiB
+//    16-bit at D=128): one 1-D TMA bulk copy each, PPS pages per pipeline stage,
+//    completing on the stage's mbarrier.  Block-table entries are fetched 32 at
+//    a time (one partition) per warp.
+//  * MATH.  Tokens sit on the M axis of mma.sync.m16n8k16 and the (<= 8) query
+//    heads of the GQA group on the N axis: S^T = K Q^T and O^T = V^T P^T.  One
+//    page is exactly one M tile, so there is no padding of the query group to 16
+//    rows; P^T reaches the B-operand layout with one movmatrix per 8x8 block.
+//    fp8 pages are converted in registers (cvt.rn.f16x2.e4m3x2, exact) and
+//    multiplied in f16, k_scale folded into the softmax scale, v_scale into the
+//    output scale.  Online softmax in the log2 domain with a lazily moved
+//    reference: the steady state has no shuffles, only a warp vote.
+#include "common.cuh"
+
+namespace b200pa {
+
+namespace {
+
+constexpr int kBS = 16;                      // tokens per page (block_size)
+constexpr int kPagesPerPart = kPartitionSize / kBS;
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+constexpr uint32_t kFull = 0xffffffffu;
+
+// ------------------------------------------------------------------ PTX bits
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "LAB_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra DONE;\n"
+      "bra LAB_WAIT;\n"
+      "DONE:\n"
+      "}\n" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ uint64_t l2_evict_first_policy() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void tma_load_1d(uint32_t dst, const void* src, uint32_t bytes,
+                                            uint32_t bar, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
+      "[%0], [%1], %2, [%3], %4;" ::"r"(dst),
+      "l"(src), "r"(bytes), "r"(bar), "l"(policy)
+      : "memory");
+}
+__device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
+__device__ __forceinline__ uint32_t movmatrix_trans(uint32_t a) {
+  uint32_t d;
+  asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(d) : "r"(a));
+  return d;
+}
+template <bool BF16>
+__device__ __forceinline__ void mma16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0,
+                                         uint32_t b1) {
+  if constexpr (BF16) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, "
+        "{%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  } else {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, "
+        "{%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  }
+}
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+template <bool BF16>
+__device__ __forceinline__ uint32_t pack2(float lo, float hi) {
+  uint32_t r;
+  if constexpr (BF16) {
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  } else {
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  }
+  return r;
+}
+// e4m3 x4 (one 32-bit word) -> two f16x2 words: lo = bytes 0,1 ; hi = bytes 2,3
+__device__ __forceinline__ void e4m3x4_to_f16x2x2(uint32_t w, uint32_t& lo, uint32_t& hi) {
+  asm("{\n"
+      ".reg .b16 l, h;\n"
+      "mov.b32 {l, h}, %2;\n"
+      "cvt.rn.f16x2.e4m3x2 %0, l;\n"
+      "cvt.rn.f16x2.e4m3x2 %1, h;\n"
+      "}\n"
+      : "=r"(lo), "=r"(hi)
+      : "r"(w));
+}
+
+struct StreamParams {
+  void* tmp_out;       // [S,H,P,D] scalar_t
+  float* exp_sums;     // [S,H,P]
+  float* max_logits;   // [S,H,P]
+  const void* q;
+  const void* k_cache;
+  const void* v_cache;
+  const int32_t* block_tables;
+  const int32_t* seq_lens;
+  const float* alibi_slopes;
+  const float* k_scale;
+  const float* v_scale;
+  int64_t q_stride, kv_block_stride, kv_head_stride;  // elements
+  int num_seqs, num_heads, num_kv_heads, group;       // group = num_heads / num_kv_heads
+  int h_tiles;                                         // ceil(group / 8)
+  int max_num_blocks_per_seq, max_num_partitions;
+  float scale;
+};
+
+// Where a worker is in its span of units.  A "segment" is the run of consecutive
+// partitions of one (sequence, virtual kv head) inside the span.
+struct Cursor {
+  int b, vh;        // sequence, virtual kv head (kv head x query-head tile)
+  int len, np;      // seq_lens[b], its partitions
+  int page;         // next page (absolute within the sequence)
+  int page_end;     // end of the current segment (exclusive)
+  int part0;        // first partition of the current segment
+  int nparts;       // partitions in the current segment
+  int units_left;   // units of the span beyond the current segment
+};
+
+__device__ __forceinline__ int parts_of(int len) {
+  return (len + kPartitionSize - 1) / kPartitionSize;
+}
+__device__ __forceinline__ void cursor_open(Cursor& c, int j) {
+  const int n = min(c.units_left, c.np - j);
+  c.part0 = j;
+  c.nparts = n;
+  c.units_left -= n;
+  c.page = j * kPagesPerPart;
+  c.page_end = min((j + n) * kPagesPerPart, (c.len + kBS - 1) / kBS);
+}
+// precondition: c.units_left > 0 (so another non-empty sequence / head exists)
+__device__ __forceinline__ void cursor_next_segment(Cursor& c, const int32_t* seq_lens, int vheads) {
+  if (++c.vh == vheads) {
+    c.vh = 0;
+    do {
+      ++c.b;
+      c.len = seq_lens[c.b];
+      c.np = parts_of(c.len);
+    } while (c.np == 0);
+  }
+  cursor_open(c, 0);
+}
+
+// ST: B200PA_F16 | B200PA_BF16 (query/out type).  FP8: kv cache is e4m3 bytes.
+// PPS: pages per pipeline stage.
+template <int ST, bool FP8, int D, int NW, int STAGES, int PPS, int MINB>
+__global__ void __launch_bounds__(NW * 32, MINB)
+paged_attention_stream_kernel(const StreamParams p) {
+  using T = typename Scalar<ST>::type;
+  constexpr bool MMA_BF16 = (!FP8) && (ST == B200PA_BF16);  // fp8 pages compute in f16
+  constexpr int CES = FP8 ? 1 : 2;                           // cache element bytes
+  constexpr int PAGE_BYTES = D * kBS * CES;                  // one K (or V) page of one kv head
+  constexpr int STAGE_BYTES = PPS * 2 * PAGE_BYTES;
+  constexpr int KSTEPS = D / 16;                             // QK k-steps
+  constexpr int MT = D / 16;                                 // PV m-tiles (16 head elements each)
+  constexpr int RING_BYTES = STAGES * STAGE_BYTES;
+  // probabilities are exp2(t - msub) with t - msub <= CAP; msub trails the max by OFF
+  constexpr float OFF = MMA_BF16 ? 0.f : 6.f;
+  constexpr float CAP = MMA_BF16 ? 8.f : 14.f;
+
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ __align__(8) uint64_t bars[NW * STAGES];
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int r = lane >> 2, q4 = lane & 3;
+  const int vheads = p.num_kv_heads * p.h_tiles;
+
+  // ---------------------------------------------------------------- my span
+  // units = partitions x virtual heads, flattened (seq, vhead, partition)
+  int tot = 0;
+  for (int b = lane; b < p.num_seqs; b += 32) tot += parts_of(p.seq_lens[b]);
+#pragma unroll
+  for (int m = 16; m >= 1; m >>= 1) tot += __shfl_xor_sync(kFull, tot, m);
+  const long long U = (long long)tot * vheads;
+  const long long W = (long long)gridDim.x * NW;
+  const long long w = (long long)blockIdx.x * NW + warp;
+  const long long u0 = (w * U) / W, u1 = ((w + 1) * U) / W;
+  if (u1 == u0) return;  // nothing for this warp (no CTA-wide sync anywhere below)
+
+  Cursor pc;  // producer cursor; the consumer gets a copy
+  {
+    int base = 0;
+    pc.b = 0; pc.vh = 0; pc.len = 0; pc.np = 1;
+    int j0 = 0;
+    for (int c = 0; c < p.num_seqs; c += 32) {
+      const int len = (c + lane < p.num_seqs) ? p.seq_lens[c + lane] : 0;
+      const int n = parts_of(len);
+      int incl = n;
+#pragma unroll
+      for (int m = 1; m < 32; m <<= 1) {
+        const int v = __shfl_up_sync(kFull, incl, m);
+        if (lane >= m) incl += v;
+      }
+      const int chunk_total = __shfl_sync(kFull, incl, 31);
+      if ((long long)(base + chunk_total) * vheads > u0) {
+        const unsigned mask = __ballot_sync(kFull, (long long)(base + incl) * vheads > u0);
+        const int l = __ffs(mask) - 1;
+        const int excl = __shfl_sync(kFull, incl - n, l);
+        pc.b = c + l;
+        pc.len = __shfl_sync(kFull, len, l);
+        pc.np = __shfl_sync(kFull, n, l);
+        const long long rem = u0 - (long long)(base + excl) * vheads;
+        pc.vh = (int)(rem / pc.np);
+        j0 = (int)(rem - (long long)pc.vh * pc.np);
+        break;
+      }
+      base += chunk_total;
+    }
+    pc.units_left = (int)(u1 - u0);
+    cursor_open(pc, j0);
+  }
+  Cursor cc = pc;
+
+  // ---------------------------------------------------------------- ring + barriers
+  uint8_t* ring = smem + (size_t)warp * RING_BYTES;
+  const uint32_t ring_u32 = smem_u32(ring);
+  const uint32_t bar0 = smem_u32(&bars[warp * STAGES]);
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) mbar_init(bar0 + 8 * s, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncwarp();
+
+  const int64_t blk_stride_bytes = p.kv_block_stride * CES;
+  const int64_t head_stride_bytes = p.kv_head_stride * CES;
+  const uint64_t policy = l2_evict_first_policy();
+
+  // ---------------------------------------------------------------- producer
+  int bt_reg = 0, bt_b = -1, bt_win = -1;  // 32 block-table entries of (bt_b, window bt_win)
+  bool producing = true;
+  int ip = 0;                               // stages issued
+  auto produce = [&]() {
+    if (pc.page == pc.page_end) {
+      if (pc.units_left == 0) { producing = false; return; }
+      cursor_next_segment(pc, p.seq_lens, vheads);
+    }
+    const int page0 = pc.page;
+    const int npg = min(PPS, pc.page_end - page0);
+    pc.page += npg;
+    const int win = page0 >> 5;
+    if (pc.b != bt_b || win != bt_win) {
+      const int idx = (win << 5) + lane;
+      bt_reg = (idx < p.max_num_blocks_per_seq)
+                   ? p.block_tables[(int64_t)pc.b * p.max_num_blocks_per_seq + idx] : 0;
+      bt_b = pc.b;
+      bt_win = win;
+    }
+    int phys[PPS];
+#pragma unroll
+    for (int g = 0; g < PPS; ++g) phys[g] = __shfl_sync(kFull, bt_reg, (page0 + g) & 31);
+    if (lane == 0) {
+      const int s = ip % STAGES;
+      const uint32_t bar = bar0 + 8 * s;
+      const uint32_t dst = ring_u32 + s * STAGE_BYTES;
+      const int kvh = pc.vh / p.h_tiles;
+      const uint8_t* kc = reinterpret_cast<const uint8_t*>(p.k_cache) + kvh * head_stride_bytes;
+      const uint8_t* vc = reinterpret_cast<const uint8_t*>(p.v_cache) + kvh * head_stride_bytes;
+      mbar_expect_tx(bar, npg * 2 * PAGE_BYTES);
+#pragma unroll
+      for (int g = 0; g < PPS; ++g) {
+        if (g < npg) {
+          tma_load_1d(dst + g * 2 * PAGE_BYTES, kc + (int64_t)phys[g] * blk_stride_bytes,
+                      PAGE_BYTES, bar, policy);
+          tma_load_1d(dst + g * 2 * PAGE_BYTES + PAGE_BYTES,
+                      vc + (int64_t)phys[g] * blk_stride_bytes, PAGE_BYTES, bar, policy);
+        }
+      }
+    }
+    ++ip;
+  };
+#pragma unroll 1
+  for (int i = 0; i < STAGES && producing; ++i) produce();
+
+  // ---------------------------------------------------------------- consumer state
+  uint32_t qb[KSTEPS][2];       // Q^T B-fragments: head r, k-step ks
+  float o[MT][4];               // O^T: (d = 16mt + r | + 8, heads 2q4, 2q4+1)
+  float msub[2], lsum[2];       // per head 2q4 + h: subtracted reference (log2), partial sum
+  float slope_l2[2];
+  int head0 = 0, heads_valid = 0;
+  const bool has_alibi = p.alibi_slopes != nullptr;
+  float sl2 = p.scale * kLog2e;
+  float out_scale = 1.f;
+  if constexpr (FP8) {
+    sl2 *= *p.k_scale;
+    out_scale = *p.v_scale;
+  }
+
+  // ldmatrix lane addressing
+  const int mat = lane >> 3, mi = lane & 7;
+  uint32_t k_lane_off, v_lane_off;
+  int tokA, tokB;  // tokens (within the page) of accumulator rows r and r + 8
+  if constexpr (FP8) {
+    // K x4 = {chunk c, slots 0-7 | chunk c, slots 8-15 | chunk c+1, slots 0-7 | chunk c+1, 8-15}
+    // (chunk = 16 head elements).  Slot i < 8 is token sig0(i) = 4(i/2) + (i%2) + (i >= 4 ? 2 : 0)
+    // and slot 8 + i is token sig0(i) ^ 2: both halves touch 8 distinct 16-byte bank groups, and
+    // after the movmatrix transpose quad-lane q holds P for tokens 4q..4q+3 -- the 4 bytes it
+    // gets from a V row (b0/b1 swapped for q >= 2).
+    const int sig0 = 4 * (mi >> 1) + (mi & 1) + ((mi >= 4) ? 2 : 0);
+    const int tok = (mat & 1) ? (sig0 ^ 2) : sig0;
+    k_lane_off = ((mat >> 1) * kBS + tok) * 16;
+    v_lane_off = lane * 16;  // 32 consecutive V rows (head elements) per x4
+    tokA = 4 * (r >> 1) + (r & 1) + ((r >= 4) ? 2 : 0);
+    tokB = tokA ^ 2;
+  } else {
+    // K x4 = {chunk 2ks, tok 0-7 | chunk 2ks, tok 8-15 | chunk 2ks+1, tok 0-7 | chunk 2ks+1, tok 8-15}
+    // (chunk = 8 head elements)
+    k_lane_off = ((mat >> 1) * kBS + (mat & 1) * 8 + mi) * 16;
+    // V x4 = {d 0-7, tok 0-7 | d 8-15, tok 0-7 | d 0-7, tok 8-15 | d 8-15, tok 8-15}
+    v_lane_off = ((mat & 1) * 8 + mi) * 32 + (mat >> 1) * 16;
+    tokA = r;
+    tokB = r + 8;
+  }
+
+  auto begin_segment = [&]() {
+    const int kvh = cc.vh / p.h_tiles;
+    const int tile = cc.vh - kvh * p.h_tiles;
+    head0 = kvh * p.group + tile * 8;
+    heads_valid = min(8, p.group - tile * 8);
+    const T* qrow = reinterpret_cast<const T*>(p.q) + (int64_t)cc.b * p.q_stride +
+                    (int64_t)(head0 + r) * D;
+#pragma unroll
+    for (int ks = 0; ks < KSTEPS; ++ks) {
+      uint32_t v0 = 0, v1 = 0;
+      if (r < heads_valid) {
+        if constexpr (FP8) {
+          // k-slots (2q,2q+1 | 2q+8,2q+9) of k-step ks hold head elements 16ks + (4q,4q+1 |
+          // 4q+2,4q+3): the 4 consecutive bytes a lane gets from an fp8 K row via ldmatrix
+          const uint2 raw = *reinterpret_cast<const uint2*>(qrow + 16 * ks + 4 * q4);
+          if constexpr (ST == B200PA_BF16) {
+            const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&raw.x);
+            const __nv_bfloat162 b = *reinterpret_cast<const __nv_bfloat162*>(&raw.y);
+            v0 = pack2<false>(__bfloat162float(a.x), __bfloat162float(a.y));
+            v1 = pack2<false>(__bfloat162float(b.x), __bfloat162float(b.y));
+          } else {
+            v0 = raw.x;
+            v1 = raw.y;
+          }
+        } else {
+          v0 = *reinterpret_cast<const uint32_t*>(qrow + 16 * ks + 2 * q4);
+          v1 = *reinterpret_cast<const uint32_t*>(qrow + 16 * ks + 8 + 2 * q4);
+        }
+      }
+      qb[ks][0] = v0;
+      qb[ks][1] = v1;
+    }
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      slope_l2[h] = 0.f;
+      if (has_alibi && 2 * q4 + h < heads_valid)
+        slope_l2[h] = p.alibi_slopes[head0 + 2 * q4 + h] * kLog2e;
+      msub[h] = -INFINITY;
+      lsum[h] = 0.f;
+    }
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt) o[mt][0] = o[mt][1] = o[mt][2] = o[mt][3] = 0.f;
+  };
+
+  auto end_segment = [&]() {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      lsum[h] += __shfl_xor_sync(kFull, lsum[h], 4);
+      lsum[h] += __shfl_xor_sync(kFull, lsum[h], 8);
+      lsum[h] += __shfl_xor_sync(kFull, lsum[h], 16);
+    }
+    T* tmp = reinterpret_cast<T*>(p.tmp_out);
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int hd = 2 * q4 + h;
+      if (hd < heads_valid) {
+        const int64_t idx =
+            ((int64_t)cc.b * p.num_heads + head0 + hd) * p.max_num_partitions + cc.part0;
+        const float inv = out_scale * __fdividef(1.f, lsum[h] + 1e-6f);
+        T* dst = tmp + idx * D + r;
+#pragma unroll
+        for (int mt = 0; mt < MT; ++mt) {
+          dst[16 * mt] = Scalar<ST>::from_float(o[mt][h] * inv);
+          dst[16 * mt + 8] = Scalar<ST>::from_float(o[mt][2 + h] * inv);
+        }
+        // lane r of the quad column: slot part0 + r, + 8, ... of this segment
+        for (int j = r; j < cc.nparts; j += 8) {
+          p.exp_sums[idx + j] = (j == 0) ? lsum[h] : 0.f;
+          p.max_logits[idx + j] = (j == 0) ? msub[h] * kLn2 : -FLT_MAX;
+        }
+      }
+    }
+  };
+
+  begin_segment();
+
+  // ---------------------------------------------------------------- main loop
+#pragma unroll 1
+  for (int i = 0;; ++i) {
+    if (cc.page == cc.page_end) {
+      end_segment();
+      if (cc.units_left == 0) break;
+      cursor_next_segment(cc, p.seq_lens, vheads);
+      begin_segment();
+    }
+    const int page0 = cc.page;
+    const int npg = min(PPS, cc.page_end - page0);
+    cc.page += npg;
+    const int s = i % STAGES;
+    const uint32_t sbase = ring_u32 + s * STAGE_BYTES;
+    mbar_wait(bar0 + 8 * s, (i / STAGES) & 1);
+
+    // ---- S^T = K Q^T : per page one 16(token) x 8(head) tile, two k chains
+    float sc[PPS][4];
+#pragma unroll
+    for (int g = 0; g < PPS; ++g) {
+      sc[g][0] = sc[g][1] = sc[g][2] = sc[g][3] = 0.f;
+      if (g < npg) {
+        const uint32_t kbase = sbase + g * 2 * PAGE_BYTES;
+        float sb[4] = {0.f, 0.f, 0.f, 0.f};
+        if constexpr (FP8) {
+#pragma unroll
+          for (int c = 0; c < KSTEPS; c += 2) {
+            uint32_t w4[4], a[4];
+            ldmatrix_x4(w4, kbase + c * (kBS * 16) + k_lane_off);
+            e4m3x4_to_f16x2x2(w4[0], a[0], a[2]);
+            e4m3x4_to_f16x2x2(w4[1], a[1], a[3]);
+            mma16816<false>(sc[g], a, qb[c][0], qb[c][1]);
+            e4m3x4_to_f16x2x2(w4[2], a[0], a[2]);
+            e4m3x4_to_f16x2x2(w4[3], a[1], a[3]);
+            mma16816<false>(sb, a, qb[c + 1][0], qb[c + 1][1]);
+          }
+        } else {
+#pragma unroll
+          for (int ks = 0; ks < KSTEPS; ++ks) {
+            uint32_t a[4];
+            ldmatrix_x4(a, kbase + ks * (2 * kBS * 16) + k_lane_off);
+            if (ks & 1) mma16816<MMA_BF16>(sb, a, qb[ks][0], qb[ks][1]);
+            else mma16816<MMA_BF16>(sc[g], a, qb[ks][0], qb[ks][1]);
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) sc[g][j] += sb[j];
+      }
+    }
+
+    // ---- online softmax.  d[g][j]: j = 0,1 token tokA heads 2q,2q+1 ; j = 2,3 token tokB
+    const int tok0 = page0 * kBS;
+    float d[PPS][4];
+    auto logits = [&](float neg0, float neg1) {
+#pragma unroll
+      for (int g = 0; g < PPS; ++g) {
+        const int nv = min(kBS, cc.len - (tok0 + g * kBS));  // <= 0 for an absent page
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int tk = (j & 2) ? tokB : tokA;
+          float t = fmaf(sc[g][j], sl2, (j & 1) ? neg1 : neg0);
+          if (has_alibi) t += slope_l2[j & 1] * (float)(tok0 + g * kBS + tk - cc.len + 1);
+          d[g][j] = (g < npg && tk < nv) ? t : -INFINITY;
+        }
+      }
+    };
+    logits(-msub[0], -msub[1]);
+    bool over = false;
+#pragma unroll
+    for (int g = 0; g < PPS; ++g)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) over |= d[g][j] > CAP;
+    if (__any_sync(kFull, over)) {
+      // the running max of some head outgrew its reference: exact maxima, move, rescale
+      logits(0.f, 0.f);
+      float alpha[2];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        float mx = -INFINITY;
+#pragma unroll
+        for (int g = 0; g < PPS; ++g) mx = fmaxf(mx, fmaxf(d[g][h], d[g][2 + h]));
+        mx = fmaxf(mx, __shfl_xor_sync(kFull, mx, 4));
+        mx = fmaxf(mx, __shfl_xor_sync(kFull, mx, 8));
+        mx = fmaxf(mx, __shfl_xor_sync(kFull, mx, 16));
+        alpha[h] = 1.f;
+        if (mx > msub[h] + CAP) {
+          const float nm = mx - OFF;
+          alpha[h] = ex2(msub[h] - nm);  // ex2(-inf) = 0 on the first stage
+          msub[h] = nm;
+        }
+        lsum[h] *= alpha[h];
+      }
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt) {
+        o[mt][0] *= alpha[0]; o[mt][1] *= alpha[1];
+        o[mt][2] *= alpha[0]; o[mt][3] *= alpha[1];
+      }
+      logits(-msub[0], -msub[1]);
+    }
+    uint32_t pb[PPS][2];
+#pragma unroll
+    for (int g = 0; g < PPS; ++g) {
+      float pr[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) pr[j] = ex2(d[g][j]);
+      lsum[0] += pr[0] + pr[2];
+      lsum[1] += pr[1] + pr[3];
+      // 8x8 blocks (token slot x head) -> transpose -> B fragments (k = token, n = head)
+      const uint32_t ta = movmatrix_trans(pack2<MMA_BF16>(pr[0], pr[1]));
+      const uint32_t tb = movmatrix_trans(pack2<MMA_BF16>(pr[2], pr[3]));
+      if constexpr (FP8) {
+        pb[g][0] = (q4 >= 2) ? tb : ta;
+        pb[g][1] = (q4 >= 2) ? ta : tb;
+      } else {
+        pb[g][0] = ta;
+        pb[g][1] = tb;
+      }
+    }
+
+    // ---- O^T += V^T P^T
+    auto pv = [&](int g, auto masked) {
+      constexpr bool MASKED = decltype(masked)::value;
+      const uint32_t vbase = sbase + g * 2 * PAGE_BYTES + PAGE_BYTES;
+      // tail page: V columns past the context may hold NaN bit patterns; the reference
+      // zeroes them (attention_kernels.cuh:415-425).  m01 masks a[0], a[1]; m23 a[2], a[3].
+      uint32_t m01 = 0xffffffffu, m23 = 0xffffffffu;
+      if constexpr (MASKED) {
+        const int nv = cc.len - (tok0 + g * kBS);
+        const int t01 = FP8 ? 4 * q4 : 2 * q4;
+        const int t23 = FP8 ? 4 * q4 + 2 : 2 * q4 + 8;
+        m01 = (t01 < nv ? 0x0000ffffu : 0u) | (t01 + 1 < nv ? 0xffff0000u : 0u);
+        m23 = (t23 < nv ? 0x0000ffffu : 0u) | (t23 + 1 < nv ? 0xffff0000u : 0u);
+      }
+      if constexpr (FP8) {
+#pragma unroll
+        for (int gg = 0; gg < D / 32; ++gg) {
+          uint32_t w4[4], a[4];
+          ldmatrix_x4(w4, vbase + gg * (32 * 16) + v_lane_off);
+          e4m3x4_to_f16x2x2(w4[0], a[0], a[2]);
+          e4m3x4_to_f16x2x2(w4[1], a[1], a[3]);
+          if constexpr (MASKED) { a[0] &= m01; a[1] &= m01; a[2] &= m23; a[3] &= m23; }
+          mma16816<false>(o[2 * gg], a, pb[g][0], pb[g][1]);
+          e4m3x4_to_f16x2x2(w4[2], a[0], a[2]);
+          e4m3x4_to_f16x2x2(w4[3], a[1], a[3]);
+          if constexpr (MASKED) { a[0] &= m01; a[1] &= m01; a[2] &= m23; a[3] &= m23; }
+          mma16816<false>(o[2 * gg + 1], a, pb[g][0], pb[g][1]);
+        }
+      } else {
+#pragma unroll
+        for (int mt = 0; mt < MT; ++mt) {
+          uint32_t a[4];
+          ldmatrix_x4(a, vbase + mt * (16 * 32) + v_lane_off);
+          if constexpr (MASKED) { a[0] &= m01; a[1] &= m01; a[2] &= m23; a[3] &= m23; }
+          mma16816<MMA_BF16>(o[mt], a, pb[g][0], pb[g][1]);
+        }
+      }
+    };
+    if (tok0 + npg * kBS <= cc.len) {   // every page of the stage is full
+#pragma unroll
+      for (int g = 0; g < PPS; ++g)
+        if (g < npg) pv(g, std::false_type{});
+    } else {
+#pragma unroll
+      for (int g = 0; g < PPS; ++g)
+        if (g < npg) pv(g, std::true_type{});
+    }
+
+    // ---- refill this stage (all lanes are past their last read of it)
+    __syncwarp();
+    if (producing) produce();
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// Merge of the split-K partials (reference: paged_attention_v2_reduce_kernel,
+// attention_kernels.cuh:560-664): w_j = exp_sum_j * exp(max_j - max), out = sum_j tmp_j w_j /
+// (sum_j w_j + 1e-6).  One WARP per (sequence, head); slots with exp_sum == 0 were merged into
+// an earlier slot by the producer kernel and are skipped without touching tmp_out.
+template <int ST, int D>
+__global__ void __launch_bounds__(256)
+paged_attention_reduce_warp_kernel(typename Scalar<ST>::type* __restrict__ out,
+                                   const float* __restrict__ exp_sums,
+                                   const float* __restrict__ max_logits,
+                                   const typename Scalar<ST>::type* __restrict__ tmp_out,
+                                   const int32_t* __restrict__ seq_lens, int num_rows,
+                                   int num_heads, int max_num_partitions) {
+  using T = typename Scalar<ST>::type;
+  constexpr int VEC = D / 32;  // head elements per lane
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);  // seq * num_heads + head
+  if (row >= num_rows) return;
+  const int seq = row / num_heads;
+  const int np = parts_of(seq_lens[seq]);
+  const int64_t base = (int64_t)row * max_num_partitions;
+  const T* tmp = tmp_out + base * D + lane * VEC;
+  T* dst = out + (int64_t)row * D + lane * VEC;
+  if (np <= 0) return;
+  if (np == 1) {  // reference shortcut :577-589
+#pragma unroll
+    for (int v = 0; v < VEC; ++v) dst[v] = tmp[v];
+    return;
+  }
+  float mx = -FLT_MAX;
+  for (int j = lane; j < np; j += 32)
+    if (exp_sums[base + j] != 0.f) mx = fmaxf(mx, max_logits[base + j]);
+  mx = warp_max(mx);
+  float acc[VEC];
+#pragma unroll
+  for (int v = 0; v < VEC; ++v) acc[v] = 0.f;
+  float wsum = 0.f;
+  for (int c = 0; c < np; c += 32) {
+    const int j = c + lane;
+    float wj = 0.f;
+    if (j < np) {
+      const float l = exp_sums[base + j];
+      if (l != 0.f) wj = l * __expf(max_logits[base + j] - mx);
+    }
+    wsum += wj;
+    unsigned live = __ballot_sync(kFull, wj != 0.f);
+    while (live) {
+      const int l = __ffs(live) - 1;
+      live &= live - 1;
+      const float wl = __shfl_sync(kFull, wj, l);
+      const T* src = tmp + (int64_t)(c + l) * D;
+      if constexpr (ST != B200PA_F32 && VEC == 4) {
+        const uint2 raw = *reinterpret_cast<const uint2*>(src);
+        const T* e = reinterpret_cast<const T*>(&raw);
+#pragma unroll
+        for (int v = 0; v < 4; ++v) acc[v] += Scalar<ST>::to_float(e[v]) * wl;
+      } else {
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) acc[v] += Scalar<ST>::to_float(src[v]) * wl;
+      }
+    }
+  }
+  wsum = warp_sum(wsum);
+  const float inv = __fdividef(1.f, wsum + 1e-6f);
+#pragma unroll
+  for (int v = 0; v < VEC; ++v) dst[v] = Scalar<ST>::from_float(acc[v] * inv);
+}
+
+// ---------------------------------------------------------------------------------------
+struct StreamCfgChoice { int stages, pps, minb; };
+
+template <int ST, bool FP8, int D, int STAGES, int PPS, int MINB>
+int launch_stream_t(const StreamParams& p, int num_sms, cudaStream_t stream) {
+  constexpr int NW = 4;
+  constexpr int SMEM = NW * STAGES * PPS * 2 * D * kBS * (FP8 ? 1 : 2);
+  auto kern = paged_attention_stream_kernel<ST, FP8, D, NW, STAGES, PPS, MINB>;
+  static int ctas_per_sm = 0;  // per instantiation
+  if (ctas_per_sm == 0) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+    if (e != cudaSuccess)
+      return set_error(B200PA_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    int n = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, NW * 32, SMEM);
+    if (e != cudaSuccess || n <= 0)
+      return set_error(B200PA_ERR_CUDA, "occupancy query failed: %s", cudaGetErrorString(e));
+    ctas_per_sm = n;
+  }
+  dim3 grid(num_sms * ctas_per_sm), block(NW * 32);
+  kern<<<grid, block, SMEM, stream>>>(p);
+  count_launch();
+  return check_launch("paged_attention_v2 (stream)");
+}
+
+}  // namespace
+
+bool stream_supported(const void* query, const void* key_cache, const void* value_cache,
+                      int num_heads, int num_kv_heads, int head_size, int block_size,
+                      int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
+                      int scalar_type, int kv_dtype, int blocksparse_vert_stride) {
+  if (blocksparse_vert_stride > 1) return false;
+  if (block_size != kBS) return false;
+  if (head_size != 64 && head_size != 128) return false;
+  if (scalar_type != B200PA_BF16 && scalar_type != B200PA_F16) return false;
+  if (kv_dtype != B200PA_KV_AUTO && kv_dtype != B200PA_KV_FP8_E4M3) return false;
+  if (num_kv_heads <= 0 || num_heads % num_kv_heads != 0) return false;
+  const int ces = kv_dtype == B200PA_KV_AUTO ? 2 : 1;
+  auto aligned = [](const void* p, uintptr_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; };
+  // TMA bulk copies need 16-byte aligned sources; Q rows are read as 8-byte vectors
+  if (!aligned(key_cache, 16) || !aligned(value_cache, 16) || !aligned(query, 8)) return false;
+  if ((kv_block_stride * ces) % 16 != 0 || (kv_head_stride * ces) % 16 != 0) return false;
+  if (kv_head_stride < (int64_t)head_size * block_size) return false;
+  if (q_stride % 4 != 0) return false;
+  return true;
+}
+
+int launch_stream(float* exp_sums, float* max_logits, void* tmp_out, const void* query,
+                  const void* key_cache, const void* value_cache, int num_seqs, int num_heads,
+                  int num_kv_heads, int head_size, float scale, const int32_t* block_tables,
+                  int max_num_blocks_per_seq, const int32_t* seq_lens, int max_num_partitions,
+                  const float* alibi_slopes, int64_t q_stride, int64_t kv_block_stride,
+                  int64_t kv_head_stride, int scalar_type, int kv_dtype, const float* k_scale,
+                  const float* v_scale, int num_sms, int tune, cudaStream_t stream) {
+  StreamParams p;
+  p.tmp_out = tmp_out;
+  p.exp_sums = exp_sums;
+  p.max_logits = max_logits;
+  p.q = query;
+  p.k_cache = key_cache;
+  p.v_cache = value_cache;
+  p.block_tables = block_tables;
+  p.seq_lens = seq_lens;
+  p.alibi_slopes = alibi_slopes;
+  p.k_scale = k_scale;
+  p.v_scale = v_scale;
+  p.q_stride = q_stride;
+  p.kv_block_stride = kv_block_stride;
+  p.kv_head_stride = kv_head_stride;
+  p.num_seqs = num_seqs;
+  p.num_heads = num_heads;
+  p.num_kv_heads = num_kv_heads;
+  p.group = num_heads / num_kv_heads;
+  p.h_tiles = (p.group + 7) / 8;
+  p.max_num_blocks_per_seq = max_num_blocks_per_seq;
+  p.max_num_partitions = max_num_partitions;
+  p.scale = scale;
+  const bool fp8 = kv_dtype == B200PA_KV_FP8_E4M3;
+  // (STAGES, PPS, MINB): fp8 stage = PPS x 4 KiB, 16-bit stage = PPS x 8 KiB at D = 128
+#define STREAM_CALL(ST, FP8V, DV, SG, PP, MB) \
+  return launch_stream_t<ST, FP8V, DV, SG, PP, MB>(p, num_sms, stream)
+#define STREAM_TUNE(ST, FP8V, DV)                                   \
+  switch (tune) {                                                   \
+    case 1: STREAM_CALL(ST, FP8V, DV, 2, 2, 3);                     \
+    case 2: STREAM_CALL(ST, FP8V, DV, 4, 1, 3);                     \
+    case 3: STREAM_CALL(ST, FP8V, DV, 3, 1, 4);                     \
+    default: STREAM_CALL(ST, FP8V, DV, 3, 2, 2);                    \
+  }
+  if (scalar_type == B200PA_BF16) {
+    if (fp8) { if (head_size == 128) { STREAM_TUNE(B200PA_BF16, true, 128) } else { STREAM_TUNE(B200PA_BF16, true, 64) } }
+    else     { if (head_size == 128) { STREAM_CALL(B200PA_BF16, false, 128, 3, 1, 2); } else { STREAM_CALL(B200PA_BF16, false, 64, 3, 2, 2); } }
+  } else {
+    if (fp8) { if (head_size == 128) { STREAM_CALL(B200PA_F16, true, 128, 3, 2, 2); } else { STREAM_CALL(B200PA_F16, true, 64, 3, 2, 2); } }
+    else     { if (head_size == 128) { STREAM_CALL(B200PA_F16, false, 128, 3, 1, 2); } else { STREAM_CALL(B200PA_F16, false, 64, 3, 2, 2); } }
+  }
+#undef STREAM_TUNE
+#undef STREAM_CALL
+}
+
+int launch_reduce_warp(void* out, const float* exp_sums, const float* max_logits,
+                       const void* tmp_out, const int32_t* seq_lens, int num_seqs, int num_heads,
+                       int head_size, int max_num_partitions, int scalar_type,
+                       cudaStream_t stream) {
+  const int rows = num_seqs * num_heads;
+  constexpr int WPB = 8;
+  dim3 grid((rows + WPB - 1) / WPB), block(WPB * 32);
+#define RED_CALL(ST, DV)                                                                        \
+  paged_attention_reduce_warp_kernel<ST, DV><<<grid, block, 0, stream>>>(                       \
+      (typename Scalar<ST>::type*)out, exp_sums, max_logits,                                    \
+      (const typename Scalar<ST>::type*)tmp_out, seq_lens, rows, num_heads, max_num_partitions)
+  if (scalar_type == B200PA_BF16) { if (head_size == 128) RED_CALL(B200PA_BF16, 128); else RED_CALL(B200PA_BF16, 64); }
+  else if (scalar_type == B200PA_F16) { if (head_size == 128) RED_CALL(B200PA_F16, 128); else RED_CALL(B200PA_F16, 64); }
+  else return set_error(B200PA_ERR_UNSUPPORTED, "reduce (warp): unsupported scalar type %d", scalar_type);
+#undef RED_CALL
+  count_launch();
+  return check_launch("paged_attention_v2 reduce (warp)");
+}
+
+}  // namespace b200pa

@@ -312,6 +312,16 @@ def run_ours(args):
                 peaks = json.load(f)
         except OSError:
             pass
+        # DRAM traffic of the dominant kernel per launch, from the committed ncu --set full
+        # capture of this exact workload (profiles/): only quoted for the config it was taken on
+        traffic = None
+        try:
+            with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+                tr = json.load(f)
+            if tr.get("config") == cfg and tr.get("tp") == world:
+                traffic = int(tr["dram_bytes_read"]) + int(tr["dram_bytes_write"])
+        except (OSError, ValueError, KeyError):
+            pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
         ms_step = ms_total / K
@@ -341,8 +351,9 @@ def run_ours(args):
                             "paged KV cache is device-resident state, as in the reference"},
             "gpu_launches": int(total_launches),
             "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak,
-                         "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": None,
-                         "kernel": "paged_attention_v2 (main + reduce launches, events around the op)",
+                         "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic,
+                         "kernel": "paged_attention_stream_kernel (+ its merge launch; CUDA "
+                                   "events around the paged_attention_v2 op, in-loop)",
                          "kernel_ms": round(attn_ms, 4), "peak_source": peak_src,
                          "bytes": "sum(seq_len) * Hkv_local * D * 2 (K,V) * sizeof(cache_t)"},
             "clocks": clocks,

@@ -27,7 +27,8 @@
  *     sync, CUDA-graph capturable), as in the reference kernels.
  *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
  *   - Every launcher is asynchronous, allocates nothing, keeps no state, and
- *     mutates only the buffers documented as outputs.
+ *     mutates only the buffers documented as outputs (and the caller-provided
+ *     `workspace` of the attention entry points).
  *   - Return 0 on success.  Non-zero = the configuration is outside the supported
  *     domain or the launch failed; b200pa_last_error() then returns a message
  *     (thread-local, valid until the next call on the same thread).  The torch
@@ -45,7 +46,7 @@
 extern "C" {
 #endif
 
-#define B200PA_ABI_VERSION 1
+#define B200PA_ABI_VERSION 2
 
 /* scalar_t of query / out / key / value (reference: VLLM_DISPATCH_FLOATING_TYPES) */
 enum { B200PA_F32 = 0, B200PA_F16 = 1, B200PA_BF16 = 2 };
@@ -61,12 +62,11 @@ enum {
 
 /* which kernel family b200pa_paged_attention_v1/v2 may use (tests, A/B runs) */
 enum {
-  B200PA_IMPL_AUTO = 0,    /* fast path when the shape is covered, else generic */
-  B200PA_IMPL_GENERIC = 1, /* SIMT kernel, whole reference domain */
-  B200PA_IMPL_FAST = 2,    /* TMA-staged tensor-core kernel, one CTA per (chunk, kv head,
-                              sequence); error if not covered */
-  B200PA_IMPL_STREAM = 3   /* v2 only: persistent stream-K kernel (the default for covered
-                              shapes); error if not covered */
+  B200PA_IMPL_AUTO = 0,    /* stream kernel when the shape is covered and a workspace is given,
+                              else generic */
+  B200PA_IMPL_GENERIC = 1, /* SIMT kernel, whole reference domain, no workspace */
+  B200PA_IMPL_STREAM = 2   /* persistent stream-K tensor-core kernel (v1 and v2); error if the
+                              shape is not covered or no workspace is given */
 };
 
 int b200pa_abi_version(void);
@@ -81,6 +81,16 @@ void b200pa_set_impl(int impl);
 int b200pa_get_impl(void);
 /* Number of kernels launched by this library so far in this process. */
 uint64_t b200pa_launch_count(void);
+
+/*
+ * Bytes of device scratch the attention entry points want in `workspace` for head size
+ * `head_size` on the current device (a function of the SM count only, about 20 MB on a B200;
+ * independent of batch and context).  The workspace needs no initialisation, may be shared by
+ * calls on ONE stream, and must be 16-byte aligned.  The torch shim takes it from torch's
+ * caching allocator per call (CUDA-graph safe).  workspace == NULL is allowed: the launchers then
+ * use the generic SIMT kernel, which needs none (and is several times slower).
+ */
+int64_t b200pa_paged_attention_workspace_bytes(int head_size);
 
 /*
  * out[num_seqs, num_heads, head_size]                      (written)
@@ -99,18 +109,19 @@ int b200pa_paged_attention_v1(
     int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
     int scalar_type, int kv_dtype, const float* k_scale, const float* v_scale,
     int tp_rank, int blocksparse_local_blocks, int blocksparse_vert_stride,
-    int blocksparse_block_size, int blocksparse_head_sliding_step, void* stream);
+    int blocksparse_block_size, int blocksparse_head_sliding_step,
+    void* workspace, int64_t workspace_bytes, void* stream);
 
 /*
  * Split-K variant.  Caller-provided scratch, reference shapes:
  *   exp_sums, max_logits [num_seqs, num_heads, max_num_partitions] fp32
  *   tmp_out              [num_seqs, num_heads, max_num_partitions, head_size] scalar_t
  * with max_num_partitions >= ceil(max_seq_len / 512)  (_PARTITION_SIZE,
- * vllm/attention/ops/paged_attn.py:21).  Scratch contents after the call: every
- * slot j < ceil(seq_len/512) of a (seq, head) holds a valid partial
- * (normalised partial output, its exp-sum and max logit) over a contiguous token
- * range or has exp_sum == 0 ("merged into an earlier slot"); `out` is the
- * contract.
+ * vllm/attention/ops/paged_attn.py:21).  `out` is the contract.  The scratch is
+ * working memory: the stream kernel splits the context by its own schedule and
+ * keeps its partials in `workspace`, leaving the three buffers untouched; the
+ * generic kernel leaves in every slot j < ceil(seq_len/512) of a (seq, head) the
+ * reference's partial (normalised partial output, its exp-sum and max logit).
  */
 int b200pa_paged_attention_v2(
     void* out, float* exp_sums, float* max_logits, void* tmp_out,
@@ -122,7 +133,8 @@ int b200pa_paged_attention_v2(
     int64_t kv_head_stride, int scalar_type, int kv_dtype, const float* k_scale,
     const float* v_scale, int tp_rank, int blocksparse_local_blocks,
     int blocksparse_vert_stride, int blocksparse_block_size,
-    int blocksparse_head_sliding_step, void* stream);
+    int blocksparse_head_sliding_step, void* workspace, int64_t workspace_bytes,
+    void* stream);
 
 /*
  * key, value [num_tokens, num_heads, head_size] scalar_t, row strides key_stride /

@@ -19,7 +19,7 @@ pytestmark = pytest.mark.gpu
 
 DEV = "cuda:0"
 ATOL, RTOL = 1e-2, 1e-2           # BASELINE.json north_star gate vs the reference kernels
-GENERIC, FAST = 1, 2
+GENERIC, STREAM = 1, 2         # b200pa_set_impl: SIMT kernel | persistent stream-K kernel
 
 
 @pytest.fixture(scope="module")
@@ -83,6 +83,17 @@ def _run_oracle(ora, version, q, kc, vc, Hkv, scale, bt, sl, BS, max_len, alibi,
     return out
 
 
+_ORACLE_CACHE = {}
+
+
+def _run_oracle_cached(key, ora, *args, **kw):
+    """The oracle result depends on the inputs only, not on which GPU kernel family is under
+    test: computed once per input set (the sweep below calls it per kernel family)."""
+    if key not in _ORACLE_CACHE:
+        _ORACLE_CACHE[key] = _run_oracle(ora, *args, **kw)
+    return _ORACLE_CACHE[key]
+
+
 def _close(got, want, atol=ATOL, rtol=RTOL):
     assert not torch.isnan(got.float()).any(), "NaN in the GPU output"
     torch.testing.assert_close(got.float(), want.float(), atol=atol, rtol=rtol)
@@ -96,7 +107,7 @@ def _alibi(H):
 # ------------------------------------------------------------ reference sweep
 
 @pytest.mark.parametrize("version", ["v1", "v2"])
-@pytest.mark.parametrize("impl", [GENERIC, FAST])
+@pytest.mark.parametrize("impl", [GENERIC, STREAM])
 @pytest.mark.parametrize("heads", [(40, 40), (64, 8)])
 @pytest.mark.parametrize("head_size", [32, 64, 80, 128, 256])
 @pytest.mark.parametrize("block_size", [16, 32])
@@ -106,8 +117,8 @@ def test_paged_attention_sweep(ops, native, ora, version, impl, heads, head_size
                                use_alibi, kv):
     H, Hkv = heads
     dtype = torch.bfloat16
-    fast_ok = block_size == 16 and head_size in (64, 128)
-    if impl == FAST and not fast_ok:
+    stream_ok = block_size == 16 and head_size in (64, 128)
+    if impl == STREAM and not stream_ok:
         pytest.skip("shape served by the generic kernel")
     if kv == "fp8" and head_size % 16:
         pytest.skip("x = 16 does not divide the head size")
@@ -126,8 +137,9 @@ def test_paged_attention_sweep(ops, native, ora, version, impl, heads, head_size
                            ks, vs)
     finally:
         native.set_impl(native.IMPL_AUTO)
-    want = _run_oracle(ora, version, q, kc, vc, Hkv, s, bt, sl, block_size, MAX, alibi, kv,
-                       ks, vs)
+    want = _run_oracle_cached(("sweep", version, heads, head_size, block_size, use_alibi, kv),
+                              ora, version, q, kc, vc, Hkv, s, bt, sl, block_size, MAX, alibi, kv,
+                              ks, vs)
     _close(got, want)
     if head_size == 128:
         # the reference test's own check: fp64 math on the (dequantised) cache
@@ -222,7 +234,7 @@ def _config_inputs(name):
 
 @pytest.mark.parametrize("name", ["cfg1", "cfg2", "cfg3", "cfg4", "cfg4_tp1", "cfg5"])
 @pytest.mark.parametrize("version", ["v1", "v2"])
-@pytest.mark.parametrize("impl", [FAST, GENERIC])
+@pytest.mark.parametrize("impl", [STREAM, GENERIC])
 def test_baseline_configs_reduced_batch(ops, native, ora, name, version, impl):
     q, kc, vc, bt, sl, H, Hkv, D, BS, s, kv, ks, vs, max_len = _config_inputs(name)
     native.set_impl(impl)
@@ -230,7 +242,8 @@ def test_baseline_configs_reduced_batch(ops, native, ora, name, version, impl):
         got, *_ = _run_gpu(ops, version, q, kc, vc, Hkv, s, bt, sl, BS, max_len, None, kv, ks, vs)
     finally:
         native.set_impl(native.IMPL_AUTO)
-    want = _run_oracle(ora, version, q, kc, vc, Hkv, s, bt, sl, BS, max_len, None, kv, ks, vs)
+    want = _run_oracle_cached(("cfg", name, version), ora, version, q, kc, vc, Hkv, s, bt, sl, BS,
+                              max_len, None, kv, ks, vs)
     _close(got, want)
 
 
@@ -281,7 +294,7 @@ def test_full_size_properties(ops, native, ora, cfg):
     q, kc, vc, bt, sl, s = _full_size(ops, B, H, Hkv, ctx, kv)
     ks = torch.tensor(1.0 if kv == "auto" else s / 1.7, device=DEV)
     vs = torch.tensor(1.0 if kv == "auto" else s / 2.9, device=DEV)
-    native.set_impl(FAST)
+    native.set_impl(STREAM)
     try:
         o1 = _call(ops, "v1", q, kc, vc, Hkv, s, bt, sl, ctx, kv, ks, vs)
         o2 = _call(ops, "v2", q, kc, vc, Hkv, s, bt, sl, ctx, kv, ks, vs)
@@ -332,6 +345,159 @@ def test_full_size_properties(ops, native, ora, cfg):
     _close(o1[sel].cpu(), want)
 
 
+# ------------------------------------------------- stream-K scheduler cases
+
+_RND = random.Random(0)
+SCHED_CASES = [
+    # name, B, H, Hkv, D, lens, dtype, kv, alibi, qmul
+    ("gqa8_fp8_ragged", 6, 8, 1, 128, [128, 40000, 5000, 777, 16384 + 3, 20001], torch.bfloat16, "fp8", False, 1.0),
+    ("gqa8_fp8_hot", 5, 64, 8, 128, [1000, 17, 512, 640, 3333], torch.bfloat16, "fp8", False, 40.0),
+    ("gqa4_bf16_hot", 5, 32, 8, 128, [1000, 17, 512, 640, 3333], torch.bfloat16, "auto", False, 40.0),
+    ("mha_f16_d64_alibi", 7, 40, 40, 64, [_RND.randint(1, 3000) for _ in range(7)], torch.float16, "auto", True, 10.0),
+    ("gqa16_fp8_d64_alibi", 7, 32, 2, 64, [_RND.randint(1, 3000) for _ in range(7)], torch.float16, "fp8", True, 10.0),
+    ("gqa5_bf16", 3, 10, 2, 128, [1, 513, 1025], torch.bfloat16, "auto", False, 5.0),
+    ("many_short_fp8", 300, 16, 2, 128, [_RND.randint(1, 700) for _ in range(300)], torch.bfloat16, "fp8", False, 20.0),
+    ("with_empties_fp8", 9, 8, 1, 128, [0, 600, 0, 0, 31, 5000, 0, 512, 0], torch.bfloat16, "fp8", False, 20.0),
+    ("one_long_bf16", 1, 8, 1, 128, [70001], torch.bfloat16, "auto", False, 20.0),
+    ("one_long_fp8", 1, 64, 8, 128, [131072], torch.bfloat16, "fp8", False, 20.0),
+    ("tiny", 2, 8, 8, 128, [1, 2], torch.bfloat16, "auto", False, 1.0),
+]
+
+
+@pytest.mark.parametrize("case", SCHED_CASES, ids=[c[0] for c in SCHED_CASES])
+def test_stream_scheduler_cases(ops, native, ora, case):
+    """Shapes that stress the stream-K decomposition (spans that cut sequences anywhere, many
+    sequences per span, one sequence over a hundred spans, empty sequences) and the lazy
+    softmax rescale ("hot" logits: q scaled up so that the running max keeps moving).
+    k_scale is a power of two so that the reference's rounding of K * k_scale to scalar_t
+    (quant_utils.cuh:362-372) is exact and peaky softmaxes can be compared tightly."""
+    name, B, H, Hkv, D, lens, dtype, kv, use_alibi, qmul = case
+    BS = 16
+    s = D ** -0.5
+    NB = sum((L + BS - 1) // BS for L in lens) + 5
+    q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, NB, lens, dtype, seed=3, kv=kv,
+                                             lo=-1.0, hi=1.0, permute=True)
+    q = (q.float() * qmul).to(dtype)
+    ks, vs = (1.0, 1.0) if kv == "auto" else (0.5, 1.3)
+    alibi = None
+    if use_alibi:
+        alibi = torch.tensor([2.0 ** (-(i + 1) * 8.0 / H) for i in range(H)], dtype=torch.float32)
+    max_len = max(max(lens), 1)
+    live = torch.tensor([L > 0 for L in lens])
+    outs = {}
+    for impl, version in ((GENERIC, "v2"), (STREAM, "v1"), (STREAM, "v2")):
+        native.set_impl(impl)
+        try:
+            outs[(impl, version)], *_ = _run_gpu(ops, version, q, kc, vc, Hkv, s, bt, sl, BS,
+                                                 max_len, alibi, kv, ks, vs)
+        finally:
+            native.set_impl(native.IMPL_AUTO)
+    ref = outs[(GENERIC, "v2")][live]
+    _close(outs[(STREAM, "v1")][live], ref)
+    _close(outs[(STREAM, "v2")][live], ref)
+    # v1 and v2 are the same kernel and schedule: bitwise equal
+    assert torch.equal(outs[(STREAM, "v1")][live], outs[(STREAM, "v2")][live])
+    # empty sequences: zeros, as the reference's v1 kernel leaves them
+    if not bool(live.all()):
+        assert float(outs[(STREAM, "v1")][~live].float().abs().sum()) == 0.0
+    if sum(lens) * H <= 64 * 140000:
+        want = _run_oracle(ora, "v1", q, kc, vc, Hkv, s, bt, sl, BS, max_len, alibi, kv, ks, vs)
+        # peaky softmaxes over V of magnitude up to 2.6: the reference's own rounding of P to
+        # scalar_t (attention_kernels.cuh:393-395) is ~1e-2 of max|V| here, so the absolute gate
+        # scales with the output range (it is 1e-2 for the unit-range cases)
+        atol = ATOL * max(1.0, float(want[live].float().abs().max()))
+        _close(outs[(STREAM, "v2")][live], want[live], atol=atol)
+
+
+def test_stream_graph_replay_follows_seq_lens(ops, native):
+    """The stream kernel derives its schedule from seq_lens ON THE DEVICE: a captured graph
+    replayed after the lengths (and block tables) changed gives the result of a fresh call."""
+    B, H, Hkv, D, BS = 12, 16, 2, 128, 16
+    s = D ** -0.5
+    lens_a = [3000, 17, 900, 4096, 1, 2222, 640, 33, 1500, 2048, 77, 4000]
+    lens_b = [5, 4096, 4096, 12, 3000, 100, 4095, 2049, 1, 700, 3333, 16]
+    NB = 12 * 256 + 3
+    q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, NB, [4096] * B, torch.bfloat16,
+                                             seed=5, kv="fp8", lo=-1.0, hi=1.0, permute=True)
+    qd, kcd, vcd, btd = q.to(DEV), kc.to(DEV), vc.to(DEV), bt.to(DEV)
+    sld = torch.tensor(lens_a, dtype=torch.int32, device=DEV)
+    ks, vs = torch.tensor(0.5, device=DEV), torch.tensor(1.5, device=DEV)
+    P = 8
+    es = torch.empty(B, H, P, dtype=torch.float32, device=DEV)
+    ml = torch.empty_like(es)
+    tmp = torch.empty(B, H, P, D, dtype=qd.dtype, device=DEV)
+    out_g = torch.empty_like(qd)
+
+    def step(out):
+        ops.paged_attention_v2(out, es, ml, tmp, qd, kcd, vcd, Hkv, s, btd, sld, BS, 4096, None,
+                               "fp8", ks, vs)
+
+    stream = torch.cuda.Stream()
+    with torch.cuda.stream(stream):
+        step(out_g)
+        stream.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=stream):
+            step(out_g)
+    for lens in (lens_a, lens_b, lens_a):
+        sld.copy_(torch.tensor(lens, dtype=torch.int32))
+        out_g.fill_(float("nan"))
+        graph.replay()
+        torch.cuda.synchronize()
+        out_e = torch.empty_like(qd)
+        step(out_e)
+        torch.cuda.synchronize()
+        assert torch.equal(out_g, out_e)
+        assert not torch.isnan(out_g.float()).any()
+
+
+def test_c_abi_without_workspace_uses_generic_and_stream_needs_one(native):
+    """Direct C-ABI calls (ctypes, raw device pointers): workspace == NULL is served by the
+    generic kernel; forcing the stream kernel without a workspace is an error, not a fallback."""
+    import ctypes
+    lib = native.c_lib()
+    B, H, Hkv, D, BS, NB = 3, 8, 2, 128, 16, 40
+    lens = [100, 37, 300]
+    s = D ** -0.5
+    q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, NB, lens, torch.bfloat16, seed=2,
+                                             lo=-s, hi=s, permute=True)
+    qd, kcd, vcd, btd, sld = (t.to(DEV) for t in (q, kc, vc, bt, sl))
+    one = torch.tensor(1.0, device=DEV)
+    lib.b200pa_paged_attention_workspace_bytes.restype = ctypes.c_int64
+    need = lib.b200pa_paged_attention_workspace_bytes(D)
+    assert 0 < need < (64 << 20)
+    ws = torch.empty(need, dtype=torch.uint8, device=DEV)
+
+    def call(out, wsp, wsn):
+        p = lambda t: ctypes.c_void_p(t.data_ptr())
+        return lib.b200pa_paged_attention_v1(
+            p(out), p(qd), p(kcd), p(vcd), B, H, Hkv, D, BS, ctypes.c_float(s), p(btd),
+            ctypes.c_int(bt.shape[1]), p(sld), max(lens), None, ctypes.c_int64(qd.stride(0)),
+            ctypes.c_int64(kcd.stride(0)), ctypes.c_int64(kcd.stride(1)), 2, 0, p(one), p(one),
+            0, 0, 0, 64, 0, wsp, ctypes.c_int64(wsn), None)
+
+    torch.cuda.synchronize()
+    out_ws = torch.empty_like(qd)
+    n0 = native.launch_count()
+    assert call(out_ws, ctypes.c_void_p(ws.data_ptr()), need) == 0
+    assert native.launch_count() - n0 == 2          # stream kernel + merge
+    out_nows = torch.empty_like(qd)
+    n0 = native.launch_count()
+    assert call(out_nows, None, 0) == 0
+    assert native.launch_count() - n0 == 1          # generic kernel
+    torch.cuda.synchronize()
+    _close(out_ws.cpu(), out_nows.cpu())
+    native.set_impl(STREAM)
+    try:
+        assert call(out_nows, None, 0) != 0
+        assert b"workspace" in lib.b200pa_last_error()
+        assert call(out_nows, ctypes.c_void_p(ws.data_ptr()), 1024) != 0
+        assert b"workspace too small" in lib.b200pa_last_error()
+    finally:
+        native.set_impl(native.IMPL_AUTO)
+    torch.cuda.synchronize()
+
+
 # ------------------------------------------------------------- layout details
 
 @pytest.mark.parametrize("version", ["v1", "v2"])
@@ -372,11 +538,12 @@ def test_strided_query_and_padded_cache(ops, ora, version, kv):
     _close(out.cpu(), want)
 
 
-@pytest.mark.parametrize("impl", [FAST, GENERIC])
+@pytest.mark.parametrize("impl", [GENERIC])
 def test_v2_scratch_contract(ops, native, impl):
-    """After paged_attention_v2 the scratch buffers hold valid partials: merging
-    them with the reference's reduce formula (attention_kernels.cuh:560-664)
-    reproduces `out`."""
+    """After paged_attention_v2 through the generic kernel the scratch buffers hold the
+    reference's partials: merging them with the reference's reduce formula
+    (attention_kernels.cuh:560-664) reproduces `out`.  (The stream kernel keeps its partials
+    in its own workspace and leaves the caller's scratch untouched.)"""
     B, H, Hkv, D, BS, NB = 4, 16, 4, 128, 16, 600
     lens = [4096, 513, 100, 2049]
     s = D ** -0.5
@@ -407,7 +574,7 @@ def test_zero_length_sequence_v1_gives_zeros(ops, native):
     s = D ** -0.5
     q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, NB, lens, torch.bfloat16, seed=8,
                                              lo=-s, hi=s)
-    for impl in (FAST, GENERIC):
+    for impl in (STREAM, GENERIC):
         native.set_impl(impl)
         try:
             out, *_ = _run_gpu(ops, "v1", q, kc, vc, Hkv, s, bt, sl, BS, 40, None, "auto", 1.0, 1.0)
@@ -436,7 +603,7 @@ def test_tail_page_garbage_is_ignored(ops, native, ora):
             else:
                 kc2[blk, :, :, off:, :] = 0x7F
                 vc2[blk, :, :, off:] = 0x7F
-        for impl in (FAST, GENERIC):
+        for impl in (STREAM, GENERIC):
             native.set_impl(impl)
             try:
                 for version in ("v1", "v2"):
@@ -574,7 +741,7 @@ def test_launch_counter_counts_native_launches(ops, native):
     n0 = native.launch_count()
     ops.paged_attention_v1(torch.empty_like(q), q, kc, vc, Hkv, s, bt, sl, BS, max_len, None,
                            "fp8", one, one)
-    assert native.launch_count() == n0 + 1
+    assert native.launch_count() == n0 + 2   # stream kernel + merge
 
 
 # ------------------------------------------------------ backend (AttentionImpl)

@@ -13,13 +13,14 @@ SHIM_PATH = os.path.join(_HERE, "_b200pa_torch.so")
 C_ABI_SYMBOLS = (
     "b200pa_abi_version", "b200pa_last_error", "b200pa_kv_dtype_from_string",
     "b200pa_set_impl", "b200pa_get_impl", "b200pa_launch_count",
+    "b200pa_paged_attention_workspace_bytes",
     "b200pa_paged_attention_v1", "b200pa_paged_attention_v2",
     "b200pa_reshape_and_cache", "b200pa_reshape_and_cache_flash",
     "b200pa_convert_fp8",
     "b200pa_get_max_shared_memory_per_block_device_attribute",
 )
 
-IMPL_AUTO, IMPL_GENERIC, IMPL_FAST, IMPL_STREAM = 0, 1, 2, 3
+IMPL_AUTO, IMPL_GENERIC, IMPL_STREAM = 0, 1, 2
 
 _lock = threading.Lock()
 _clib = None

@@ -28,18 +28,12 @@ int launch_generic(void*, float*, float*, void*, const void*, const void*, const
                    int, int, int, float, const int32_t*, int, const int32_t*, int, int,
                    const float*, int64_t, int64_t, int64_t, int, int, const float*, const float*,
                    BlockSparse, bool, cudaStream_t);
-bool fast_supported(const void*, const void*, const void*, int, int, int, int, int64_t, int64_t,
-                    int64_t, int, int, int);
-int launch_fast(void*, float*, float*, void*, const void*, const void*, const void*, int, int, int,
-                int, float, const int32_t*, int, const int32_t*, int, int, const float*, int64_t,
-                int64_t, int64_t, int, int, const float*, const float*, bool, int, cudaStream_t);
 bool stream_supported(const void*, const void*, const void*, int, int, int, int, int64_t, int64_t,
                       int64_t, int, int, int);
-int launch_stream(float*, float*, void*, const void*, const void*, const void*, int, int, int, int,
-                  float, const int32_t*, int, const int32_t*, int, const float*, int64_t, int64_t,
+int launch_stream(void*, void*, int64_t, const void*, const void*, const void*, int, int, int, int,
+                  float, const int32_t*, int, const int32_t*, const float*, int64_t, int64_t,
                   int64_t, int, int, const float*, const float*, int, int, cudaStream_t);
-int launch_reduce_warp(void*, const float*, const float*, const void*, const int32_t*, int, int,
-                       int, int, int, cudaStream_t);
+int64_t stream_workspace_bytes(int, int);
 
 static thread_local char g_err[512] = "";
 static std::atomic<int> g_impl{B200PA_IMPL_AUTO};
@@ -102,7 +96,8 @@ static int paged_attention_common(
     int max_seq_len, int max_num_partitions, const float* alibi_slopes, int64_t q_stride,
     int64_t kv_block_stride, int64_t kv_head_stride, int scalar_type, int kv_dtype,
     const float* k_scale, const float* v_scale, int tp_rank, int bs_local_blocks,
-    int bs_vert_stride, int bs_block_size, int bs_head_sliding_step, void* stream_v) {
+    int bs_vert_stride, int bs_block_size, int bs_head_sliding_step, void* workspace,
+    int64_t workspace_bytes, void* stream_v) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
   if (!head_size_ok(head_size))
     return set_error(B200PA_ERR_UNSUPPORTED, "Unsupported head size: %d", head_size);
@@ -148,43 +143,27 @@ static int paged_attention_common(
     return set_error(B200PA_ERR_INVALID, "blocksparse_block_size must be positive");
 
   const int impl = g_impl.load();
-  const bool fast_ok = fast_supported(query, key_cache, value_cache, num_heads, num_kv_heads,
-                                      head_size, block_size, q_stride, kv_block_stride,
-                                      kv_head_stride, scalar_type, kv_dtype, bs_vert_stride);
-  if (impl == B200PA_IMPL_FAST && !fast_ok)
-    return set_error(B200PA_ERR_UNSUPPORTED, "configuration not covered by the fast kernel");
   const bool stream_ok =
-      partitioned && stream_supported(query, key_cache, value_cache, num_heads, num_kv_heads,
-                                      head_size, block_size, q_stride, kv_block_stride,
-                                      kv_head_stride, scalar_type, kv_dtype, bs_vert_stride);
+      stream_supported(query, key_cache, value_cache, num_heads, num_kv_heads, head_size,
+                       block_size, q_stride, kv_block_stride, kv_head_stride, scalar_type,
+                       kv_dtype, bs_vert_stride);
   if (impl == B200PA_IMPL_STREAM && !stream_ok)
     return set_error(B200PA_ERR_UNSUPPORTED, "configuration not covered by the stream kernel");
-  int rc;
-  if (stream_ok && (impl == B200PA_IMPL_AUTO || impl == B200PA_IMPL_STREAM)) {
-    // persistent stream-K kernel + warp-per-row merge
-    rc = launch_stream(exp_sums, max_logits, tmp_out, query, key_cache, value_cache, num_seqs,
-                       num_heads, num_kv_heads, head_size, scale, block_tables,
-                       max_num_blocks_per_seq, seq_lens, max_num_partitions, alibi_slopes,
-                       q_stride, kv_block_stride, kv_head_stride, scalar_type, kv_dtype, k_scale,
-                       v_scale, num_sms(), stream_tune(), stream);
-    if (rc) return rc;
-    return launch_reduce_warp(out, exp_sums, max_logits, tmp_out, seq_lens, num_seqs, num_heads,
-                              head_size, max_num_partitions, scalar_type, stream);
+  if (stream_ok && ((impl == B200PA_IMPL_AUTO && workspace) || impl == B200PA_IMPL_STREAM)) {
+    // persistent stream-K kernel + boundary merge; serves v1 and v2 alike (the caller's v2
+    // scratch is left untouched)
+    return launch_stream(out, workspace, workspace_bytes, query, key_cache, value_cache, num_seqs,
+                         num_heads, num_kv_heads, head_size, scale, block_tables,
+                         max_num_blocks_per_seq, seq_lens, alibi_slopes, q_stride,
+                         kv_block_stride, kv_head_stride, scalar_type, kv_dtype, k_scale, v_scale,
+                         num_sms(), stream_tune(), stream);
   }
-  if (fast_ok && impl != B200PA_IMPL_GENERIC) {
-    rc = launch_fast(out, exp_sums, max_logits, tmp_out, query, key_cache, value_cache, num_seqs,
-                     num_heads, num_kv_heads, head_size, scale, block_tables,
-                     max_num_blocks_per_seq, seq_lens, max_seq_len, max_num_partitions,
-                     alibi_slopes, q_stride, kv_block_stride, kv_head_stride, scalar_type,
-                     kv_dtype, k_scale, v_scale, partitioned, num_sms(), stream);
-  } else {
-    rc = launch_generic(out, exp_sums, max_logits, tmp_out, query, key_cache, value_cache,
-                        num_seqs, num_heads, num_kv_heads, head_size, block_size, scale,
-                        block_tables, max_num_blocks_per_seq, seq_lens, max_seq_len,
-                        max_num_partitions, alibi_slopes, q_stride, kv_block_stride,
-                        kv_head_stride, scalar_type, kv_dtype, k_scale, v_scale, bsp, partitioned,
-                        stream);
-  }
+  int rc = launch_generic(out, exp_sums, max_logits, tmp_out, query, key_cache, value_cache,
+                          num_seqs, num_heads, num_kv_heads, head_size, block_size, scale,
+                          block_tables, max_num_blocks_per_seq, seq_lens, max_seq_len,
+                          max_num_partitions, alibi_slopes, q_stride, kv_block_stride,
+                          kv_head_stride, scalar_type, kv_dtype, k_scale, v_scale, bsp, partitioned,
+                          stream);
   if (rc) return rc;
   if (partitioned)
     rc = launch_reduce(out, exp_sums, max_logits, tmp_out, seq_lens, num_seqs, num_heads,
@@ -213,6 +192,10 @@ void b200pa_set_impl(int impl) { g_impl.store(impl); }
 int b200pa_get_impl(void) { return g_impl.load(); }
 uint64_t b200pa_launch_count(void) { return g_launches.load(); }
 
+int64_t b200pa_paged_attention_workspace_bytes(int head_size) {
+  return stream_workspace_bytes(num_sms(), head_size > 0 ? head_size : 128);
+}
+
 int b200pa_paged_attention_v1(
     void* out, const void* query, const void* key_cache, const void* value_cache, int num_seqs,
     int num_heads, int num_kv_heads, int head_size, int block_size, float scale,
@@ -220,14 +203,16 @@ int b200pa_paged_attention_v1(
     int max_seq_len, const float* alibi_slopes, int64_t q_stride, int64_t kv_block_stride,
     int64_t kv_head_stride, int scalar_type, int kv_dtype, const float* k_scale,
     const float* v_scale, int tp_rank, int blocksparse_local_blocks, int blocksparse_vert_stride,
-    int blocksparse_block_size, int blocksparse_head_sliding_step, void* stream) {
+    int blocksparse_block_size, int blocksparse_head_sliding_step, void* workspace,
+    int64_t workspace_bytes, void* stream) {
   return paged_attention_common(false, out, nullptr, nullptr, nullptr, query, key_cache,
                                 value_cache, num_seqs, num_heads, num_kv_heads, head_size,
                                 block_size, scale, block_tables, max_num_blocks_per_seq, seq_lens,
                                 max_seq_len, 1, alibi_slopes, q_stride, kv_block_stride,
                                 kv_head_stride, scalar_type, kv_dtype, k_scale, v_scale, tp_rank,
                                 blocksparse_local_blocks, blocksparse_vert_stride,
-                                blocksparse_block_size, blocksparse_head_sliding_step, stream);
+                                blocksparse_block_size, blocksparse_head_sliding_step, workspace,
+                                workspace_bytes, stream);
 }
 
 int b200pa_paged_attention_v2(
@@ -238,7 +223,7 @@ int b200pa_paged_attention_v2(
     const float* alibi_slopes, int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
     int scalar_type, int kv_dtype, const float* k_scale, const float* v_scale, int tp_rank,
     int blocksparse_local_blocks, int blocksparse_vert_stride, int blocksparse_block_size,
-    int blocksparse_head_sliding_step, void* stream) {
+    int blocksparse_head_sliding_step, void* workspace, int64_t workspace_bytes, void* stream) {
   return paged_attention_common(true, out, exp_sums, max_logits, tmp_out, query, key_cache,
                                 value_cache, num_seqs, num_heads, num_kv_heads, head_size,
                                 block_size, scale, block_tables, max_num_blocks_per_seq, seq_lens,
@@ -246,7 +231,7 @@ int b200pa_paged_attention_v2(
                                 kv_block_stride, kv_head_stride, scalar_type, kv_dtype, k_scale,
                                 v_scale, tp_rank, blocksparse_local_blocks,
                                 blocksparse_vert_stride, blocksparse_block_size,
-                                blocksparse_head_sliding_step, stream);
+                                blocksparse_head_sliding_step, workspace, workspace_bytes, stream);
 }
 
 static int check_cache_args(const char* op, const void* key, const void* value, void* kc, void* vc,

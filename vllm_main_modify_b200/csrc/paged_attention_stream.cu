@@ -1,39 +1,37 @@
-// Persistent, warp-specialised-free "stream-K" paged-decode attention for sm_100a.
+// Persistent "stream-K" paged-decode attention for sm_100a (serves v1 AND v2).
 //
-// Replaces the split-K decode kernel of the reference
-// (csrc/attention/attention_kernels.cuh:85-491 through paged_attention_v2_kernel
-// :525-557, launched from paged_attention_v2.cu:47-126) for head_size 64/128,
+// Replaces the per-sequence decode kernels of the reference
+// (csrc/attention/attention_kernels.cuh:85-491 through paged_attention_v1_kernel :494-522 and
+// paged_attention_v2_kernel :525-557 + paged_attention_v2_reduce_kernel :560-664, launched from
+// paged_attention_v1.cu:46-125 / paged_attention_v2.cu:47-126) for head_size 64/128,
 // block_size 16, bf16/fp16 query and a 16-bit or fp8-e4m3 KV cache.
 //
-//  * WORK DECOMPOSITION.  The unit of work is one 512-token partition
-//    (_PARTITION_SIZE, paged_attn.py:21) of one (sequence, kv head).  Units are
-//    flattened in (sequence, kv head, partition) order and cut into
-//    gridDim.x * NW equal contiguous spans, one per WARP.  The grid is sized to
-//    exactly fill the machine (SMs x resident CTAs), every warp streams its span
-//    from start to end, so all warps finish together whatever the mix of
-//    sequence lengths (ragged batches need no host-side knowledge of seq_lens:
-//    each warp derives its span from seq_lens on the device).
-//  * Each warp is an independent worker: its own TMA ring, mbarriers, query
-//    fragments and accumulators.  There is no CTA-wide barrier in the kernel.
-//    When a span crosses into another (sequence, kv head) the warp writes the
-//    partial (normalised output, exp-sum, max-logit) of the segment it just
-//    finished to the scratch slot of the segment's first partition (the other
-//    slots of the segment get exp_sum = 0) and carries on; the TMA producer side
-//    runs STAGES ahead across such boundaries, so the pipe never drains.
-//    paged_attention_reduce_kernel merges the partials.
-//  * LOADS.  For one (page, kv head) the x-packed K sub-block [D/x][16][x] and
-//    the V sub-block [D][16] are each one contiguous run (2 KiB fp8 / 4 KiB
-//    16-bit at D=128): one 1-D TMA bulk copy each, PPS pages per pipeline stage,
-//    completing on the stage's mbarrier.  Block-table entries are fetched 32 at
-//    a time (one partition) per warp.
-//  * MATH.  Tokens sit on the M axis of mma.sync.m16n8k16 and the (<= 8) query
-//    heads of the GQA group on the N axis: S^T = K Q^T and O^T = V^T P^T.  One
-//    page is exactly one M tile, so there is no padding of the query group to 16
-//    rows; P^T reaches the B-operand layout with one movmatrix per 8x8 block.
-//    fp8 pages are converted in registers (cvt.rn.f16x2.e4m3x2, exact) and
-//    multiplied in f16, k_scale folded into the softmax scale, v_scale into the
-//    output scale.  Online softmax in the log2 domain with a lazily moved
-//    reference: the steady state has no shuffles, only a warp vote.
+//  * WORK DECOMPOSITION.  The unit of work is one pipeline STAGE: PPS consecutive pages of one
+//    (sequence, kv head) -- 8 KiB of KV.  All stages of the call are flattened in (sequence,
+//    kv head, page) order and cut into gridDim.x * NW equal contiguous spans, one per WARP.
+//    The grid exactly fills the machine (SMs x resident CTAs) and every warp streams its span
+//    from start to end, so all warps finish together whatever the mix of sequence lengths.
+//    Ragged batches need no host-side knowledge of seq_lens: each warp derives its span from
+//    seq_lens on the device (CUDA-graph replays with new lengths just work).
+//  * Each warp is an independent worker: its own TMA ring, mbarriers, query fragments and
+//    accumulators.  There is no CTA-wide barrier in the kernel.  When a span crosses into
+//    another (sequence, kv head) the warp finishes the piece it was on and carries on; the TMA
+//    producer side runs STAGES ahead across such boundaries, so the pipe never drains.
+//    A piece that covers its whole (sequence, kv head) is normalised and written straight to
+//    `out`.  A warp has at most two pieces that do not (its first and its last): their
+//    unnormalised fp32 accumulators + (max, sum) go to workspace slots 2w / 2w+1, and
+//    paged_attention_stream_merge_kernel -- one warp per span boundary -- merges them.
+//  * LOADS.  For one (page, kv head) the x-packed K sub-block [D/x][16][x] and the V sub-block
+//    [D][16] are each one contiguous run (2 KiB fp8 / 4 KiB 16-bit at D=128): one 1-D TMA bulk
+//    copy each, completing on the stage's mbarrier.  Block-table entries are fetched 32 at a
+//    time per warp.
+//  * MATH.  Tokens sit on the M axis of mma.sync.m16n8k16 and the (<= 8) query heads of the GQA
+//    group on the N axis: S^T = K Q^T and O^T = V^T P^T.  One page is exactly one M tile, so
+//    the query group is not padded to 16 rows; P^T reaches the B-operand layout with one
+//    movmatrix per 8x8 block.  fp8 pages are converted in registers (cvt.rn.f16x2.e4m3x2,
+//    exact) and multiplied in f16, k_scale folded into the softmax scale and v_scale into the
+//    output scale.  Online softmax in the log2 domain with a lazily moved reference: the
+//    steady state has no shuffles, only a warp vote.
 #include "common.cuh"
 
 namespace b200pa {
@@ -41,9 +39,7 @@ namespace b200pa {
 namespace {
 
 constexpr int kBS = 16;                      // tokens per page (block_size)
-constexpr int kPagesPerPart = kPartitionSize / kBS;
 constexpr float kLog2e = 1.4426950408889634f;
-constexpr float kLn2 = 0.6931471805599453f;
 constexpr uint32_t kFull = 0xffffffffu;
 
 // ------------------------------------------------------------------ PTX bits
@@ -137,10 +133,10 @@ __device__ __forceinline__ void e4m3x4_to_f16x2x2(uint32_t w, uint32_t& lo, uint
       : "r"(w));
 }
 
+
 struct StreamParams {
-  void* tmp_out;       // [S,H,P,D] scalar_t
-  float* exp_sums;     // [S,H,P]
-  float* max_logits;   // [S,H,P]
+  void* out;           // [S,H,D] scalar_t
+  float* ws;           // workspace: 2 slots per worker, kSlotFloats(D) floats each
   const void* q;
   const void* k_cache;
   const void* v_cache;
@@ -152,44 +148,115 @@ struct StreamParams {
   int64_t q_stride, kv_block_stride, kv_head_stride;  // elements
   int num_seqs, num_heads, num_kv_heads, group;       // group = num_heads / num_kv_heads
   int h_tiles;                                         // ceil(group / 8)
-  int max_num_blocks_per_seq, max_num_partitions;
+  int max_num_blocks_per_seq;
+  int num_workers;                                     // gridDim.x * NW of the main kernel
   float scale;
 };
 
-// Where a worker is in its span of units.  A "segment" is the run of consecutive
-// partitions of one (sequence, virtual kv head) inside the span.
+// workspace slot: O^T fragments [D/16][4][32 lanes] fp32 (unnormalised, v_scale applied),
+// then m[8] (log2 domain), l[8]
+__host__ __device__ constexpr int slot_floats(int d) { return 8 * d + 16; }
+
+template <int PPS> __device__ __forceinline__ int stages_of(int len) {
+  return len <= 0 ? 0 : (len + kBS * PPS - 1) / (kBS * PPS);
+}
+
+// Sum of stages over all sequences (one warp; every lane gets the result).
+template <int PPS>
+__device__ __forceinline__ long long total_stages(const int32_t* seq_lens, int num_seqs, int lane) {
+  int tot = 0;
+  for (int b = lane; b < num_seqs; b += 32) tot += stages_of<PPS>(seq_lens[b]);
+#pragma unroll
+  for (int m = 16; m >= 1; m >>= 1) tot += __shfl_xor_sync(kFull, tot, m);
+  return tot;
+}
+
+// Position of flattened stage index s (order: sequence, virtual head, stage).
+struct Loc { int b, vh, len, ns, st; };
+template <int PPS>
+__device__ __forceinline__ Loc locate_stage(const int32_t* seq_lens, int num_seqs, int vheads,
+                                            long long s, int lane) {
+  Loc loc{0, 0, 0, 1, 0};
+  int base = 0;
+  for (int c = 0; c < num_seqs; c += 32) {
+    const int len = (c + lane < num_seqs) ? seq_lens[c + lane] : 0;
+    const int n = stages_of<PPS>(len);
+    int incl = n;
+#pragma unroll
+    for (int m = 1; m < 32; m <<= 1) {
+      const int v = __shfl_up_sync(kFull, incl, m);
+      if (lane >= m) incl += v;
+    }
+    const int chunk_total = __shfl_sync(kFull, incl, 31);
+    if ((long long)(base + chunk_total) * vheads > s) {
+      const unsigned mask = __ballot_sync(kFull, (long long)(base + incl) * vheads > s);
+      const int l = __ffs(mask) - 1;
+      const int excl = __shfl_sync(kFull, incl - n, l);
+      loc.b = c + l;
+      loc.len = __shfl_sync(kFull, len, l);
+      loc.ns = __shfl_sync(kFull, n, l);
+      const long long rem = s - (long long)(base + excl) * vheads;
+      loc.vh = (int)(rem / loc.ns);
+      loc.st = (int)(rem - (long long)loc.vh * loc.ns);
+      break;
+    }
+    base += chunk_total;
+  }
+  return loc;
+}
+
+// Where a worker is in its span.  A "piece" is the run of consecutive stages of one
+// (sequence, virtual kv head) inside the span.
 struct Cursor {
   int b, vh;        // sequence, virtual kv head (kv head x query-head tile)
-  int len, np;      // seq_lens[b], its partitions
-  int page;         // next page (absolute within the sequence)
-  int page_end;     // end of the current segment (exclusive)
-  int part0;        // first partition of the current segment
-  int nparts;       // partitions in the current segment
-  int units_left;   // units of the span beyond the current segment
+  int len, ns;      // seq_lens[b], its stages
+  int st;           // next stage within the (sequence, head)
+  int st_end;       // end of the current piece (exclusive)
+  int left;         // stages of the span beyond the current piece
 };
-
-__device__ __forceinline__ int parts_of(int len) {
-  return (len + kPartitionSize - 1) / kPartitionSize;
+__device__ __forceinline__ void cursor_open(Cursor& c, int st0) {
+  const int n = min(c.left, c.ns - st0);
+  c.st = st0;
+  c.st_end = st0 + n;
+  c.left -= n;
 }
-__device__ __forceinline__ void cursor_open(Cursor& c, int j) {
-  const int n = min(c.units_left, c.np - j);
-  c.part0 = j;
-  c.nparts = n;
-  c.units_left -= n;
-  c.page = j * kPagesPerPart;
-  c.page_end = min((j + n) * kPagesPerPart, (c.len + kBS - 1) / kBS);
-}
-// precondition: c.units_left > 0 (so another non-empty sequence / head exists)
-__device__ __forceinline__ void cursor_next_segment(Cursor& c, const int32_t* seq_lens, int vheads) {
+// precondition: c.left > 0 (so another non-empty sequence / head exists)
+template <int PPS>
+__device__ __forceinline__ void cursor_next_piece(Cursor& c, const int32_t* seq_lens, int vheads) {
   if (++c.vh == vheads) {
     c.vh = 0;
     do {
       ++c.b;
       c.len = seq_lens[c.b];
-      c.np = parts_of(c.len);
-    } while (c.np == 0);
+      c.ns = stages_of<PPS>(c.len);
+    } while (c.ns == 0);
   }
   cursor_open(c, 0);
+}
+
+// Final output of one (sequence, 8-head tile) from O^T fragments: scale, round to scalar_t,
+// transpose each 8x8 (d, head) block with movmatrix so that every lane stores 32-bit pairs.
+// o[mt][j]: j = 0,1 -> d = 16mt + r, heads 2q, 2q+1 ; j = 2,3 -> d = 16mt + r + 8.
+template <int ST, int D>
+__device__ __forceinline__ void store_out_tile(typename Scalar<ST>::type* out_tile,  // [8 heads][D]
+                                               int mt, const float (&o)[4], float inv0, float inv1,
+                                               int heads_valid, int r, int q4) {
+  constexpr bool BF = (ST == B200PA_BF16);
+  uint32_t* dst = reinterpret_cast<uint32_t*>(out_tile + (int64_t)r * D + 2 * q4);
+  const uint32_t lo = movmatrix_trans(pack2<BF>(o[0] * inv0, o[1] * inv1));
+  const uint32_t hi = movmatrix_trans(pack2<BF>(o[2] * inv0, o[3] * inv1));
+  if (r < heads_valid) {          // after the transpose lane (r, q) holds head r
+    dst[8 * mt] = lo;             // d = 16mt + 2q, 2q+1
+    dst[8 * mt + 4] = hi;         // d = 16mt + 8 + 2q, 2q+1
+  }
+}
+template <int ST, int D>
+__device__ __forceinline__ void store_out(typename Scalar<ST>::type* out_tile,
+                                          const float (&o)[D / 16][4], float inv0, float inv1,
+                                          int heads_valid, int r, int q4) {
+#pragma unroll
+  for (int mt = 0; mt < D / 16; ++mt)
+    store_out_tile<ST, D>(out_tile, mt, o[mt], inv0, inv1, heads_valid, r, q4);
 }
 
 // ST: B200PA_F16 | B200PA_BF16 (query/out type).  FP8: kv cache is e4m3 bytes.
@@ -217,50 +284,24 @@ paged_attention_stream_kernel(const StreamParams p) {
   const int vheads = p.num_kv_heads * p.h_tiles;
 
   // ---------------------------------------------------------------- my span
-  // units = partitions x virtual heads, flattened (seq, vhead, partition)
-  int tot = 0;
-  for (int b = lane; b < p.num_seqs; b += 32) tot += parts_of(p.seq_lens[b]);
-#pragma unroll
-  for (int m = 16; m >= 1; m >>= 1) tot += __shfl_xor_sync(kFull, tot, m);
-  const long long U = (long long)tot * vheads;
-  const long long W = (long long)gridDim.x * NW;
+  const long long Ttot = total_stages<PPS>(p.seq_lens, p.num_seqs, lane) * vheads;
+  const long long W = min((long long)p.num_workers, Ttot);
   const long long w = (long long)blockIdx.x * NW + warp;
-  const long long u0 = (w * U) / W, u1 = ((w + 1) * U) / W;
-  if (u1 == u0) return;  // nothing for this warp (no CTA-wide sync anywhere below)
+  // let the merge kernel's CTAs be scheduled as soon as SM resources free up; they block in
+  // griddepcontrol.wait until this grid has completed and flushed
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  if (w >= W) return;  // nothing for this warp (there is no CTA-wide sync anywhere below)
+  const long long u0 = (w * Ttot) / W, u1 = ((w + 1) * Ttot) / W;
 
   Cursor pc;  // producer cursor; the consumer gets a copy
   {
-    int base = 0;
-    pc.b = 0; pc.vh = 0; pc.len = 0; pc.np = 1;
-    int j0 = 0;
-    for (int c = 0; c < p.num_seqs; c += 32) {
-      const int len = (c + lane < p.num_seqs) ? p.seq_lens[c + lane] : 0;
-      const int n = parts_of(len);
-      int incl = n;
-#pragma unroll
-      for (int m = 1; m < 32; m <<= 1) {
-        const int v = __shfl_up_sync(kFull, incl, m);
-        if (lane >= m) incl += v;
-      }
-      const int chunk_total = __shfl_sync(kFull, incl, 31);
-      if ((long long)(base + chunk_total) * vheads > u0) {
-        const unsigned mask = __ballot_sync(kFull, (long long)(base + incl) * vheads > u0);
-        const int l = __ffs(mask) - 1;
-        const int excl = __shfl_sync(kFull, incl - n, l);
-        pc.b = c + l;
-        pc.len = __shfl_sync(kFull, len, l);
-        pc.np = __shfl_sync(kFull, n, l);
-        const long long rem = u0 - (long long)(base + excl) * vheads;
-        pc.vh = (int)(rem / pc.np);
-        j0 = (int)(rem - (long long)pc.vh * pc.np);
-        break;
-      }
-      base += chunk_total;
-    }
-    pc.units_left = (int)(u1 - u0);
-    cursor_open(pc, j0);
+    const Loc loc = locate_stage<PPS>(p.seq_lens, p.num_seqs, vheads, u0, lane);
+    pc.b = loc.b; pc.vh = loc.vh; pc.len = loc.len; pc.ns = loc.ns;
+    pc.left = (int)(u1 - u0);
+    cursor_open(pc, loc.st);
   }
   Cursor cc = pc;
+  int piece_begin = cc.st;
 
   // ---------------------------------------------------------------- ring + barriers
   uint8_t* ring = smem + (size_t)warp * RING_BYTES;
@@ -282,13 +323,13 @@ paged_attention_stream_kernel(const StreamParams p) {
   bool producing = true;
   int ip = 0;                               // stages issued
   auto produce = [&]() {
-    if (pc.page == pc.page_end) {
-      if (pc.units_left == 0) { producing = false; return; }
-      cursor_next_segment(pc, p.seq_lens, vheads);
+    if (pc.st == pc.st_end) {
+      if (pc.left == 0) { producing = false; return; }
+      cursor_next_piece<PPS>(pc, p.seq_lens, vheads);
     }
-    const int page0 = pc.page;
-    const int npg = min(PPS, pc.page_end - page0);
-    pc.page += npg;
+    const int page0 = pc.st * PPS;
+    const int npg = min(PPS, (pc.len + kBS - 1) / kBS - page0);
+    ++pc.st;
     const int win = page0 >> 5;
     if (pc.b != bt_b || win != bt_win) {
       const int idx = (win << 5) + lane;
@@ -363,7 +404,8 @@ paged_attention_stream_kernel(const StreamParams p) {
     tokB = r + 8;
   }
 
-  auto begin_segment = [&]() {
+  auto begin_piece = [&]() {
+    piece_begin = cc.st;
     const int kvh = cc.vh / p.h_tiles;
     const int tile = cc.vh - kvh * p.h_tiles;
     head0 = kvh * p.group + tile * 8;
@@ -407,50 +449,52 @@ paged_attention_stream_kernel(const StreamParams p) {
     for (int mt = 0; mt < MT; ++mt) o[mt][0] = o[mt][1] = o[mt][2] = o[mt][3] = 0.f;
   };
 
-  auto end_segment = [&]() {
+  auto end_piece = [&]() {
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
       lsum[h] += __shfl_xor_sync(kFull, lsum[h], 4);
       lsum[h] += __shfl_xor_sync(kFull, lsum[h], 8);
       lsum[h] += __shfl_xor_sync(kFull, lsum[h], 16);
     }
-    T* tmp = reinterpret_cast<T*>(p.tmp_out);
+    const bool from_start = piece_begin == 0, to_end = cc.st_end == cc.ns;
+    if (from_start && to_end) {
+      // the piece is the whole (sequence, head tile): final result
+      const float inv0 = out_scale * __fdividef(1.f, lsum[0] + 1e-6f);
+      const float inv1 = out_scale * __fdividef(1.f, lsum[1] + 1e-6f);
+      store_out<ST, D>(reinterpret_cast<T*>(p.out) + ((int64_t)cc.b * p.num_heads + head0) * D, o,
+                       inv0, inv1, heads_valid, r, q4);
+    } else {
+      // slot 2w: my first piece, continuing an earlier worker's; slot 2w+1: my last piece,
+      // continued by a later worker
+      float* slot = p.ws + (size_t)(2 * w + (from_start ? 1 : 0)) * slot_floats(D);
 #pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      const int hd = 2 * q4 + h;
-      if (hd < heads_valid) {
-        const int64_t idx =
-            ((int64_t)cc.b * p.num_heads + head0 + hd) * p.max_num_partitions + cc.part0;
-        const float inv = out_scale * __fdividef(1.f, lsum[h] + 1e-6f);
-        T* dst = tmp + idx * D + r;
+      for (int mt = 0; mt < MT; ++mt)
 #pragma unroll
-        for (int mt = 0; mt < MT; ++mt) {
-          dst[16 * mt] = Scalar<ST>::from_float(o[mt][h] * inv);
-          dst[16 * mt + 8] = Scalar<ST>::from_float(o[mt][2 + h] * inv);
-        }
-        // lane r of the quad column: slot part0 + r, + 8, ... of this segment
-        for (int j = r; j < cc.nparts; j += 8) {
-          p.exp_sums[idx + j] = (j == 0) ? lsum[h] : 0.f;
-          p.max_logits[idx + j] = (j == 0) ? msub[h] * kLn2 : -FLT_MAX;
+        for (int j = 0; j < 4; ++j) slot[(mt * 4 + j) * 32 + lane] = o[mt][j] * out_scale;
+      if (r == 0) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          slot[8 * D + 2 * q4 + h] = msub[h];
+          slot[8 * D + 8 + 2 * q4 + h] = lsum[h];
         }
       }
     }
   };
 
-  begin_segment();
+  begin_piece();
 
   // ---------------------------------------------------------------- main loop
 #pragma unroll 1
   for (int i = 0;; ++i) {
-    if (cc.page == cc.page_end) {
-      end_segment();
-      if (cc.units_left == 0) break;
-      cursor_next_segment(cc, p.seq_lens, vheads);
-      begin_segment();
+    if (cc.st == cc.st_end) {
+      end_piece();
+      if (cc.left == 0) break;
+      cursor_next_piece<PPS>(cc, p.seq_lens, vheads);
+      begin_piece();
     }
-    const int page0 = cc.page;
-    const int npg = min(PPS, cc.page_end - page0);
-    cc.page += npg;
+    const int page0 = cc.st * PPS;
+    const int npg = min(PPS, (cc.len + kBS - 1) / kBS - page0);
+    ++cc.st;
     const int s = i % STAGES;
     const uint32_t sbase = ring_u32 + s * STAGE_BYTES;
     mbar_wait(bar0 + 8 * s, (i / STAGES) & 1);
@@ -495,7 +539,7 @@ paged_attention_stream_kernel(const StreamParams p) {
     auto logits = [&](float neg0, float neg1) {
 #pragma unroll
       for (int g = 0; g < PPS; ++g) {
-        const int nv = min(kBS, cc.len - (tok0 + g * kBS));  // <= 0 for an absent page
+        const int nv = cc.len - (tok0 + g * kBS);  // valid tokens of the page (<= 0: absent)
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const int tk = (j & 2) ? tokB : tokA;
@@ -613,79 +657,98 @@ paged_attention_stream_kernel(const StreamParams p) {
 }
 
 // ---------------------------------------------------------------------------------------
-// Merge of the split-K partials (reference: paged_attention_v2_reduce_kernel,
-// attention_kernels.cuh:560-664): w_j = exp_sum_j * exp(max_j - max), out = sum_j tmp_j w_j /
-// (sum_j w_j + 1e-6).  One WARP per (sequence, head); slots with exp_sum == 0 were merged into
-// an earlier slot by the producer kernel and are skipped without touching tmp_out.
-template <int ST, int D>
-__global__ void __launch_bounds__(256)
-paged_attention_reduce_warp_kernel(typename Scalar<ST>::type* __restrict__ out,
-                                   const float* __restrict__ exp_sums,
-                                   const float* __restrict__ max_logits,
-                                   const typename Scalar<ST>::type* __restrict__ tmp_out,
-                                   const int32_t* __restrict__ seq_lens, int num_rows,
-                                   int num_heads, int max_num_partitions) {
+// Merge of the pieces of every (sequence, head tile) that a span boundary cut (the job of the
+// reference's paged_attention_v2_reduce_kernel, attention_kernels.cuh:560-664: weights
+// l_j * exp(m_j - m), 1e-6 in the denominator).  One CTA per boundary between workers w-1 | w,
+// one warp per 16-element slice of the head (m-tile).  The CTA that owns the FIRST boundary
+// inside a (sequence, head tile) merges all its pieces: slot 2(w-1)+1 (the tail piece of the
+// worker that holds the start) and slots 2w' of every later worker whose span starts inside it.
+// Launched with programmatic stream serialisation: everything up to griddepcontrol.wait
+// overlaps the tail of the main kernel.
+template <int ST, int D, int PPS>
+__global__ void __launch_bounds__(32 * (D / 16))
+paged_attention_stream_merge_kernel(const StreamParams p) {
   using T = typename Scalar<ST>::type;
-  constexpr int VEC = D / 32;  // head elements per lane
-  const int lane = threadIdx.x & 31;
-  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);  // seq * num_heads + head
-  if (row >= num_rows) return;
-  const int seq = row / num_heads;
-  const int np = parts_of(seq_lens[seq]);
-  const int64_t base = (int64_t)row * max_num_partitions;
-  const T* tmp = tmp_out + base * D + lane * VEC;
-  T* dst = out + (int64_t)row * D + lane * VEC;
-  if (np <= 0) return;
-  if (np == 1) {  // reference shortcut :577-589
-#pragma unroll
-    for (int v = 0; v < VEC; ++v) dst[v] = tmp[v];
-    return;
-  }
-  float mx = -FLT_MAX;
-  for (int j = lane; j < np; j += 32)
-    if (exp_sums[base + j] != 0.f) mx = fmaxf(mx, max_logits[base + j]);
-  mx = warp_max(mx);
-  float acc[VEC];
-#pragma unroll
-  for (int v = 0; v < VEC; ++v) acc[v] = 0.f;
-  float wsum = 0.f;
-  for (int c = 0; c < np; c += 32) {
-    const int j = c + lane;
-    float wj = 0.f;
-    if (j < np) {
-      const float l = exp_sums[base + j];
-      if (l != 0.f) wj = l * __expf(max_logits[base + j] - mx);
-    }
-    wsum += wj;
-    unsigned live = __ballot_sync(kFull, wj != 0.f);
-    while (live) {
-      const int l = __ffs(live) - 1;
-      live &= live - 1;
-      const float wl = __shfl_sync(kFull, wj, l);
-      const T* src = tmp + (int64_t)(c + l) * D;
-      if constexpr (ST != B200PA_F32 && VEC == 4) {
-        const uint2 raw = *reinterpret_cast<const uint2*>(src);
-        const T* e = reinterpret_cast<const T*>(&raw);
-#pragma unroll
-        for (int v = 0; v < 4; ++v) acc[v] += Scalar<ST>::to_float(e[v]) * wl;
-      } else {
-#pragma unroll
-        for (int v = 0; v < VEC; ++v) acc[v] += Scalar<ST>::to_float(src[v]) * wl;
-      }
+  const int lane = threadIdx.x & 31, mt = threadIdx.x >> 5;
+  const int r = lane >> 2, q4 = lane & 3;
+  const int vheads = p.num_kv_heads * p.h_tiles;
+  const long long w = (long long)blockIdx.x + 1;
+  // empty sequences: the reference's v1 kernel yields zeros (no keys, zero accumulators)
+  for (long long b = blockIdx.x; b < p.num_seqs; b += gridDim.x) {
+    if (p.seq_lens[b] <= 0) {
+      T* row = reinterpret_cast<T*>(p.out) + b * p.num_heads * D;
+      for (int i = threadIdx.x; i < p.num_heads * D; i += blockDim.x)
+        row[i] = Scalar<ST>::from_float(0.f);
     }
   }
-  wsum = warp_sum(wsum);
-  const float inv = __fdividef(1.f, wsum + 1e-6f);
+  const long long Ttot = total_stages<PPS>(p.seq_lens, p.num_seqs, lane) * vheads;
+  const long long W = min((long long)p.num_workers, Ttot);
+  if (w >= W) return;
+  const long long s = (w * Ttot) / W;              // first stage of worker w
+  const Loc loc = locate_stage<PPS>(p.seq_lens, p.num_seqs, vheads, s, lane);
+  if (loc.st == 0) return;                         // the boundary is not inside a (seq, head)
+  const long long item_begin = s - loc.st, item_end = item_begin + loc.ns;
+  if (((w - 1) * Ttot) / W > item_begin) return;   // an earlier boundary owns this one
+  // pieces: workers w-1 .. w_last (the worker that holds the last stage of the item)
+  const long long w_last = min(W - 1, (item_end * W - 1) / Ttot);
+  const int n = (int)(w_last - (w - 1)) + 1;
+  const size_t SF = slot_floats(D);
+  // piece k: slot 2(w-1)+1 for k = 0, else 2(w-1+k)
+  auto slot_of = [&](int k) { return p.ws + (size_t)(2 * (w - 1 + k) + (k == 0 ? 1 : 0)) * SF; };
+
+  asm volatile("griddepcontrol.wait;" ::: "memory");  // the main kernel's stores are visible
+
+  // pass 1: per-head maximum of the pieces' references (lanes stride over pieces)
+  float mx8[8];
 #pragma unroll
-  for (int v = 0; v < VEC; ++v) dst[v] = Scalar<ST>::from_float(acc[v] * inv);
+  for (int h = 0; h < 8; ++h) mx8[h] = -INFINITY;
+  for (int k = lane; k < n; k += 32) {
+    const float4* m = reinterpret_cast<const float4*>(slot_of(k) + 8 * D);
+    const float4 a = m[0], b = m[1];
+    mx8[0] = fmaxf(mx8[0], a.x); mx8[1] = fmaxf(mx8[1], a.y);
+    mx8[2] = fmaxf(mx8[2], a.z); mx8[3] = fmaxf(mx8[3], a.w);
+    mx8[4] = fmaxf(mx8[4], b.x); mx8[5] = fmaxf(mx8[5], b.y);
+    mx8[6] = fmaxf(mx8[6], b.z); mx8[7] = fmaxf(mx8[7], b.w);
+  }
+#pragma unroll
+  for (int h = 0; h < 8; ++h) mx8[h] = warp_max(mx8[h]);
+  float mx[2];
+#pragma unroll
+  for (int h = 0; h < 8; ++h) {   // select heads 2q4, 2q4+1 without dynamic register indexing
+    if (h == 2 * q4) mx[0] = mx8[h];
+    if (h == 2 * q4 + 1) mx[1] = mx8[h];
+  }
+  // pass 2: weighted sum of this warp's m-tile
+  float o[4] = {0.f, 0.f, 0.f, 0.f};
+  float lsum[2] = {0.f, 0.f};
+#pragma unroll 4
+  for (int k = 0; k < n; ++k) {
+    const float* slot = slot_of(k);
+    const float2 m = *reinterpret_cast<const float2*>(slot + 8 * D + 2 * q4);
+    const float2 l = *reinterpret_cast<const float2*>(slot + 8 * D + 8 + 2 * q4);
+    const float f0 = ex2(m.x - mx[0]), f1 = ex2(m.y - mx[1]);
+    lsum[0] += l.x * f0;
+    lsum[1] += l.y * f1;
+    o[0] += slot[(mt * 4 + 0) * 32 + lane] * f0;
+    o[1] += slot[(mt * 4 + 1) * 32 + lane] * f1;
+    o[2] += slot[(mt * 4 + 2) * 32 + lane] * f0;
+    o[3] += slot[(mt * 4 + 3) * 32 + lane] * f1;
+  }
+  const int kvh = loc.vh / p.h_tiles;
+  const int tile = loc.vh - kvh * p.h_tiles;
+  const int head0 = kvh * p.group + tile * 8;
+  const int heads_valid = min(8, p.group - tile * 8);
+  const float inv0 = __fdividef(1.f, lsum[0] + 1e-6f);
+  const float inv1 = __fdividef(1.f, lsum[1] + 1e-6f);
+  store_out_tile<ST, D>(reinterpret_cast<T*>(p.out) + ((int64_t)loc.b * p.num_heads + head0) * D,
+                        mt, o, inv0, inv1, heads_valid, r, q4);
 }
 
 // ---------------------------------------------------------------------------------------
-struct StreamCfgChoice { int stages, pps, minb; };
+constexpr int kMaxWarpsPerSm = 16;
 
-template <int ST, bool FP8, int D, int STAGES, int PPS, int MINB>
-int launch_stream_t(const StreamParams& p, int num_sms, cudaStream_t stream) {
-  constexpr int NW = 4;
+template <int ST, bool FP8, int D, int NW, int STAGES, int PPS, int MINB>
+int launch_stream_t(StreamParams& p, int num_sms, int64_t workspace_bytes, cudaStream_t stream) {
   constexpr int SMEM = NW * STAGES * PPS * 2 * D * kBS * (FP8 ? 1 : 2);
   auto kern = paged_attention_stream_kernel<ST, FP8, D, NW, STAGES, PPS, MINB>;
   static int ctas_per_sm = 0;  // per instantiation
@@ -697,15 +760,45 @@ int launch_stream_t(const StreamParams& p, int num_sms, cudaStream_t stream) {
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, NW * 32, SMEM);
     if (e != cudaSuccess || n <= 0)
       return set_error(B200PA_ERR_CUDA, "occupancy query failed: %s", cudaGetErrorString(e));
-    ctas_per_sm = n;
+    ctas_per_sm = n * NW <= kMaxWarpsPerSm ? n : kMaxWarpsPerSm / NW;
   }
-  dim3 grid(num_sms * ctas_per_sm), block(NW * 32);
-  kern<<<grid, block, SMEM, stream>>>(p);
+  const int ctas = num_sms * ctas_per_sm;
+  p.num_workers = ctas * NW;
+  const int64_t need = (int64_t)2 * p.num_workers * slot_floats(D) * (int64_t)sizeof(float);
+  if (workspace_bytes < need)
+    return set_error(B200PA_ERR_INVALID, "workspace too small: %lld bytes, need %lld "
+                     "(b200pa_paged_attention_workspace_bytes)", (long long)workspace_bytes,
+                     (long long)need);
+  kern<<<dim3(ctas), dim3(NW * 32), SMEM, stream>>>(p);
   count_launch();
-  return check_launch("paged_attention_v2 (stream)");
+  int rc = check_launch("paged_attention (stream)");
+  if (rc) return rc;
+  if (p.num_workers > 1) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(p.num_workers - 1);   // boundaries 1 .. num_workers-1
+    cfg.blockDim = dim3(32 * (D / 16));
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, paged_attention_stream_merge_kernel<ST, D, PPS>, p);
+    if (e != cudaSuccess)
+      return set_error(B200PA_ERR_CUDA, "stream merge launch: %s", cudaGetErrorString(e));
+    count_launch();
+  }
+  return check_launch("paged_attention (stream merge)");
 }
 
 }  // namespace
+
+// Upper bound of the workspace any stream launch on a device with `num_sms` SMs needs.
+int64_t stream_workspace_bytes(int num_sms, int head_size) {
+  return (int64_t)2 * num_sms * kMaxWarpsPerSm * slot_floats(head_size) *
+         (int64_t)sizeof(float);
+}
 
 bool stream_supported(const void* query, const void* key_cache, const void* value_cache,
                       int num_heads, int num_kv_heads, int head_size, int block_size,
@@ -727,17 +820,19 @@ bool stream_supported(const void* query, const void* key_cache, const void* valu
   return true;
 }
 
-int launch_stream(float* exp_sums, float* max_logits, void* tmp_out, const void* query,
+int launch_stream(void* out, void* workspace, int64_t workspace_bytes, const void* query,
                   const void* key_cache, const void* value_cache, int num_seqs, int num_heads,
                   int num_kv_heads, int head_size, float scale, const int32_t* block_tables,
-                  int max_num_blocks_per_seq, const int32_t* seq_lens, int max_num_partitions,
-                  const float* alibi_slopes, int64_t q_stride, int64_t kv_block_stride,
-                  int64_t kv_head_stride, int scalar_type, int kv_dtype, const float* k_scale,
-                  const float* v_scale, int num_sms, int tune, cudaStream_t stream) {
+                  int max_num_blocks_per_seq, const int32_t* seq_lens, const float* alibi_slopes,
+                  int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
+                  int scalar_type, int kv_dtype, const float* k_scale, const float* v_scale,
+                  int num_sms, int tune, cudaStream_t stream) {
+  if (!workspace || (reinterpret_cast<uintptr_t>(workspace) & 15u))
+    return set_error(B200PA_ERR_INVALID, "the stream kernel needs a 16-byte aligned workspace "
+                     "(b200pa_paged_attention_workspace_bytes)");
   StreamParams p;
-  p.tmp_out = tmp_out;
-  p.exp_sums = exp_sums;
-  p.max_logits = max_logits;
+  p.out = out;
+  p.ws = reinterpret_cast<float*>(workspace);
   p.q = query;
   p.k_cache = key_cache;
   p.v_cache = value_cache;
@@ -755,47 +850,44 @@ int launch_stream(float* exp_sums, float* max_logits, void* tmp_out, const void*
   p.group = num_heads / num_kv_heads;
   p.h_tiles = (p.group + 7) / 8;
   p.max_num_blocks_per_seq = max_num_blocks_per_seq;
-  p.max_num_partitions = max_num_partitions;
+  p.num_workers = 0;
   p.scale = scale;
   const bool fp8 = kv_dtype == B200PA_KV_FP8_E4M3;
-  // (STAGES, PPS, MINB): fp8 stage = PPS x 4 KiB, 16-bit stage = PPS x 8 KiB at D = 128
-#define STREAM_CALL(ST, FP8V, DV, SG, PP, MB) \
-  return launch_stream_t<ST, FP8V, DV, SG, PP, MB>(p, num_sms, stream)
-#define STREAM_TUNE(ST, FP8V, DV)                                   \
-  switch (tune) {                                                   \
-    case 1: STREAM_CALL(ST, FP8V, DV, 2, 2, 3);                     \
-    case 2: STREAM_CALL(ST, FP8V, DV, 4, 1, 3);                     \
-    case 3: STREAM_CALL(ST, FP8V, DV, 3, 1, 4);                     \
-    default: STREAM_CALL(ST, FP8V, DV, 3, 2, 2);                    \
+  // <ST, FP8, D, NW, STAGES, PPS, MINB>: fp8 stage = PPS x 4 KiB, 16-bit stage = PPS x 8 KiB (D=128)
+#define STREAM_CALL(ST, FP8V, DV, NWV, SG, PP, MB) \
+  return launch_stream_t<ST, FP8V, DV, NWV, SG, PP, MB>(p, num_sms, workspace_bytes, stream)
+#define STREAM_TUNE_FP8(ST, DV)                                        \
+  switch (tune) {                                                      \
+    case 1: STREAM_CALL(ST, true, DV, 4, 4, 2, 1);                     \
+    case 2: STREAM_CALL(ST, true, DV, 4, 6, 1, 2);                     \
+    case 3: STREAM_CALL(ST, true, DV, 6, 4, 2, 1);                     \
+    case 4: STREAM_CALL(ST, true, DV, 4, 3, 2, 2);                     \
+    case 5: STREAM_CALL(ST, true, DV, 4, 2, 2, 3);                     \
+    case 6: STREAM_CALL(ST, true, DV, 5, 4, 2, 1);                     \
+    case 7: STREAM_CALL(ST, true, DV, 6, 3, 2, 1);                     \
+    default: STREAM_CALL(ST, true, DV, 8, 3, 2, 1);                    \
+  }
+#define STREAM_TUNE_16(ST, DV)                                         \
+  switch (tune) {                                                      \
+    case 1: STREAM_CALL(ST, false, DV, 4, 2, 1, 3);                    \
+    case 2: STREAM_CALL(ST, false, DV, 6, 2, 2, 1);                    \
+    case 3: STREAM_CALL(ST, false, DV, 6, 4, 1, 1);                    \
+    case 4: STREAM_CALL(ST, false, DV, 8, 3, 1, 1);                    \
+    case 5: STREAM_CALL(ST, false, DV, 4, 3, 1, 2);                    \
+    case 6: STREAM_CALL(ST, false, DV, 4, 6, 1, 1);                    \
+    case 7: STREAM_CALL(ST, false, DV, 5, 4, 1, 1);                    \
+    default: STREAM_CALL(ST, false, DV, 4, 4, 1, 1);                   \
   }
   if (scalar_type == B200PA_BF16) {
-    if (fp8) { if (head_size == 128) { STREAM_TUNE(B200PA_BF16, true, 128) } else { STREAM_TUNE(B200PA_BF16, true, 64) } }
-    else     { if (head_size == 128) { STREAM_CALL(B200PA_BF16, false, 128, 3, 1, 2); } else { STREAM_CALL(B200PA_BF16, false, 64, 3, 2, 2); } }
+    if (fp8) { if (head_size == 128) { STREAM_TUNE_FP8(B200PA_BF16, 128) } else { STREAM_CALL(B200PA_BF16, true, 64, 4, 3, 2, 2); } }
+    else     { if (head_size == 128) { STREAM_TUNE_16(B200PA_BF16, 128) } else { STREAM_CALL(B200PA_BF16, false, 64, 4, 3, 2, 2); } }
   } else {
-    if (fp8) { if (head_size == 128) { STREAM_CALL(B200PA_F16, true, 128, 3, 2, 2); } else { STREAM_CALL(B200PA_F16, true, 64, 3, 2, 2); } }
-    else     { if (head_size == 128) { STREAM_CALL(B200PA_F16, false, 128, 3, 1, 2); } else { STREAM_CALL(B200PA_F16, false, 64, 3, 2, 2); } }
+    if (fp8) { if (head_size == 128) { STREAM_CALL(B200PA_F16, true, 128, 4, 3, 2, 2); } else { STREAM_CALL(B200PA_F16, true, 64, 4, 3, 2, 2); } }
+    else     { if (head_size == 128) { STREAM_CALL(B200PA_F16, false, 128, 4, 4, 1, 1); } else { STREAM_CALL(B200PA_F16, false, 64, 4, 3, 2, 2); } }
   }
-#undef STREAM_TUNE
+#undef STREAM_TUNE_FP8
+#undef STREAM_TUNE_16
 #undef STREAM_CALL
-}
-
-int launch_reduce_warp(void* out, const float* exp_sums, const float* max_logits,
-                       const void* tmp_out, const int32_t* seq_lens, int num_seqs, int num_heads,
-                       int head_size, int max_num_partitions, int scalar_type,
-                       cudaStream_t stream) {
-  const int rows = num_seqs * num_heads;
-  constexpr int WPB = 8;
-  dim3 grid((rows + WPB - 1) / WPB), block(WPB * 32);
-#define RED_CALL(ST, DV)                                                                        \
-  paged_attention_reduce_warp_kernel<ST, DV><<<grid, block, 0, stream>>>(                       \
-      (typename Scalar<ST>::type*)out, exp_sums, max_logits,                                    \
-      (const typename Scalar<ST>::type*)tmp_out, seq_lens, rows, num_heads, max_num_partitions)
-  if (scalar_type == B200PA_BF16) { if (head_size == 128) RED_CALL(B200PA_BF16, 128); else RED_CALL(B200PA_BF16, 64); }
-  else if (scalar_type == B200PA_F16) { if (head_size == 128) RED_CALL(B200PA_F16, 128); else RED_CALL(B200PA_F16, 64); }
-  else return set_error(B200PA_ERR_UNSUPPORTED, "reduce (warp): unsupported scalar type %d", scalar_type);
-#undef RED_CALL
-  count_launch();
-  return check_launch("paged_attention_v2 reduce (warp)");
 }
 
 }  // namespace b200pa

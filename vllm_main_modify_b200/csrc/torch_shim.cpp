@@ -59,6 +59,14 @@ void check_cache_dtype(const torch::Tensor& cache, const torch::Tensor& ref, int
   }
 }
 
+// Scratch of the stream kernel, from torch's caching allocator: stream-ordered reuse and
+// CUDA-graph capture (private pool) are handled by the allocator.
+torch::Tensor attention_workspace(const torch::Tensor& query) {
+  if (b200pa_get_impl() == B200PA_IMPL_GENERIC) return torch::Tensor();
+  const int64_t bytes = b200pa_paged_attention_workspace_bytes((int)query.size(2));
+  return at::empty({bytes}, query.options().dtype(at::kByte));
+}
+
 void paged_attention_v1(torch::Tensor& out, torch::Tensor& query, torch::Tensor& key_cache,
                         torch::Tensor& value_cache, int64_t num_kv_heads, double scale,
                         torch::Tensor& block_tables, torch::Tensor& seq_lens, int64_t block_size,
@@ -81,6 +89,7 @@ void paged_attention_v1(torch::Tensor& out, torch::Tensor& query, torch::Tensor&
   const at::cuda::OptionalCUDAGuard device_guard(device_of(query));
   const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
   const float* alibi = alibi_slopes ? reinterpret_cast<const float*>(alibi_slopes->data_ptr()) : nullptr;
+  const torch::Tensor ws = attention_workspace(query);
   check_status(b200pa_paged_attention_v1(
       out.data_ptr(), query.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(),
       (int)query.size(0), (int)query.size(1), (int)num_kv_heads, (int)query.size(2),
@@ -89,7 +98,8 @@ void paged_attention_v1(torch::Tensor& out, torch::Tensor& query, torch::Tensor&
       key_cache.stride(1), st, kv, reinterpret_cast<const float*>(k_scale.data_ptr()),
       reinterpret_cast<const float*>(v_scale.data_ptr()), (int)tp_rank,
       (int)blocksparse_local_blocks, (int)blocksparse_vert_stride, (int)blocksparse_block_size,
-      (int)blocksparse_head_sliding_step, stream));
+      (int)blocksparse_head_sliding_step, ws.defined() ? ws.data_ptr() : nullptr,
+      ws.defined() ? ws.numel() : 0, stream));
 }
 
 void paged_attention_v2(torch::Tensor& out, torch::Tensor& exp_sums, torch::Tensor& max_logits,
@@ -120,6 +130,7 @@ void paged_attention_v2(torch::Tensor& out, torch::Tensor& exp_sums, torch::Tens
   const at::cuda::OptionalCUDAGuard device_guard(device_of(query));
   const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
   const float* alibi = alibi_slopes ? reinterpret_cast<const float*>(alibi_slopes->data_ptr()) : nullptr;
+  const torch::Tensor ws = attention_workspace(query);
   check_status(b200pa_paged_attention_v2(
       out.data_ptr(), exp_sums.data_ptr<float>(), max_logits.data_ptr<float>(), tmp_out.data_ptr(),
       query.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(), (int)query.size(0),
@@ -129,7 +140,8 @@ void paged_attention_v2(torch::Tensor& out, torch::Tensor& exp_sums, torch::Tens
       key_cache.stride(1), st, kv, reinterpret_cast<const float*>(k_scale.data_ptr()),
       reinterpret_cast<const float*>(v_scale.data_ptr()), (int)tp_rank,
       (int)blocksparse_local_blocks, (int)blocksparse_vert_stride, (int)blocksparse_block_size,
-      (int)blocksparse_head_sliding_step, stream));
+      (int)blocksparse_head_sliding_step, ws.defined() ? ws.data_ptr() : nullptr,
+      ws.defined() ? ws.numel() : 0, stream));
 }
 
 void reshape_and_cache(torch::Tensor& key, torch::Tensor& value, torch::Tensor& key_cache,

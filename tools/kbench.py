@@ -47,11 +47,19 @@ def main():
     ap.add_argument("--tp", type=int, default=1, help="emulate rank 0 of a tp-way KV-head shard")
     ap.add_argument("--impl", type=int, default=0, help="b200pa_set_impl value (0 auto)")
     ap.add_argument("--ops", default="v1,v2,reshape_and_cache")
+    ap.add_argument("--ref-cuda", action="store_true",
+                    help="time the reference's own CUDA kernels (oracle/_ref/libvllm_ref_cuda.so) "
+                         "on the same tensors instead of this repo's")
     args = ap.parse_args()
     from vllm_main_modify_b200 import _custom_ops as ops
     from vllm_main_modify_b200 import _native
     _native.set_impl(args.impl)
     from vllm_main_modify_b200.paged_attn import PagedAttention
+    if args.ref_cuda:
+        from oracle import ref_cuda
+        ref_cuda.load()
+        ops = ref_cuda   # same positional signatures (torch.ops.vllm_ref_cuda.*)
+    tail = (0, 0, 0, 64, 0) if args.ref_cuda else ()
 
     dev = torch.device("cuda", 0)
     peak = 6524.6
@@ -75,11 +83,11 @@ def main():
 
         def v1():
             ops.paged_attention_v1(out, w["q"], kc, vc, w["Hkv"], w["scale"], w["bt"], w["sl"],
-                                   bench.BS, w["max_len"], None, kv, w["ks"], w["vs"])
+                                   bench.BS, w["max_len"], None, kv, w["ks"], w["vs"], *tail)
 
         def v2():
             ops.paged_attention_v2(out, es, ml, tmp, w["q"], kc, vc, w["Hkv"], w["scale"], w["bt"],
-                                   w["sl"], bench.BS, w["max_len"], None, kv, w["ks"], w["vs"])
+                                   w["sl"], bench.BS, w["max_len"], None, kv, w["ks"], w["vs"], *tail)
 
         def wr():
             ops.reshape_and_cache(w["k_new"], w["v_new"], kc, vc, w["slots"], kv, w["ks"], w["vs"])
@@ -87,8 +95,11 @@ def main():
         for name, fn in (("v1", v1), ("v2", v2), ("reshape_and_cache", wr)):
             if name not in args.ops.split(","):
                 continue
+            if args.ref_cuda and name == "v1" and w["max_len"] * 4 > 200 * 1024:
+                continue   # the reference's v1 keeps max_seq_len fp32 logits in shared memory
             med, best = time_op(fn, args.iters, fl)
-            line = {"config": cfg, "tp": args.tp, "impl": args.impl,
+            line = {"config": cfg, "tp": args.tp,
+                    "impl": "reference_cuda" if args.ref_cuda else args.impl,
                     "tune": os.environ.get("B200PA_STREAM_TUNE", "0"), "op": name,
                     "ms_median": round(med, 4),
                     "ms_best": round(best, 4)}

@@ -24,16 +24,20 @@ int launch_reshape_and_cache_flash(const void*, const void*, void*, void*, const
 int launch_convert_fp8(void*, const void*, int64_t, float, int, int, int, cudaStream_t);
 int launch_reduce(void*, const float*, const float*, const void*, const int32_t*, int, int, int,
                   int, int, cudaStream_t);
-int launch_generic(void*, float*, float*, void*, const void*, const void*, const void*, int, int,
+int launch_generic(void*, float*, int64_t, int64_t, float*, float*, void*, const void*, const void*, const void*, int, int,
                    int, int, int, float, const int32_t*, int, const int32_t*, int, int,
                    const float*, int64_t, int64_t, int64_t, int, int, const float*, const float*,
                    BlockSparse, bool, cudaStream_t);
 bool stream_supported(const void*, const void*, const void*, int, int, int, int, int64_t, int64_t,
                       int64_t, int, int, int);
-int launch_stream(void*, void*, int64_t, const void*, const void*, const void*, int, int, int, int,
+int launch_stream(void*, float*, int64_t, int64_t, void*, int64_t, const void*, const void*, const void*, int, int, int, int,
                   float, const int32_t*, int, const int32_t*, const float*, int64_t, int64_t,
                   int64_t, int, int, const float*, const float*, int, int, cudaStream_t);
 int64_t stream_workspace_bytes(int, int);
+int launch_merge_attn_states(void*, float*, const void*, const float*, const void*, const float*,
+                             int64_t, int, int, int, cudaStream_t);
+int launch_correct_attn_out(void*, float*, const float*, int, int, int, int, int, int64_t, int64_t,
+                            int64_t, int64_t, int64_t, int, cudaStream_t);
 
 static thread_local char g_err[512] = "";
 static std::atomic<int> g_impl{B200PA_IMPL_AUTO};
@@ -89,7 +93,8 @@ static bool head_size_ok(int h) {
 }
 
 static int paged_attention_common(
-    bool partitioned, void* out, float* exp_sums, float* max_logits, void* tmp_out,
+    bool partitioned, void* out, float* lse, int64_t lse_seq_stride, int64_t lse_head_stride,
+    float* exp_sums, float* max_logits, void* tmp_out,
     const void* query, const void* key_cache, const void* value_cache, int num_seqs,
     int num_heads, int num_kv_heads, int head_size, int block_size, float scale,
     const int32_t* block_tables, int max_num_blocks_per_seq, const int32_t* seq_lens,
@@ -152,13 +157,13 @@ static int paged_attention_common(
   if (stream_ok && ((impl == B200PA_IMPL_AUTO && workspace) || impl == B200PA_IMPL_STREAM)) {
     // persistent stream-K kernel + boundary merge; serves v1 and v2 alike (the caller's v2
     // scratch is left untouched)
-    return launch_stream(out, workspace, workspace_bytes, query, key_cache, value_cache, num_seqs,
+    return launch_stream(out, lse, lse_seq_stride, lse_head_stride, workspace, workspace_bytes, query, key_cache, value_cache, num_seqs,
                          num_heads, num_kv_heads, head_size, scale, block_tables,
                          max_num_blocks_per_seq, seq_lens, alibi_slopes, q_stride,
                          kv_block_stride, kv_head_stride, scalar_type, kv_dtype, k_scale, v_scale,
                          num_sms(), stream_tune(), stream);
   }
-  int rc = launch_generic(out, exp_sums, max_logits, tmp_out, query, key_cache, value_cache,
+  int rc = launch_generic(out, lse, lse_seq_stride, lse_head_stride, exp_sums, max_logits, tmp_out, query, key_cache, value_cache,
                           num_seqs, num_heads, num_kv_heads, head_size, block_size, scale,
                           block_tables, max_num_blocks_per_seq, seq_lens, max_seq_len,
                           max_num_partitions, alibi_slopes, q_stride, kv_block_stride,
@@ -205,7 +210,7 @@ int b200pa_paged_attention_v1(
     const float* v_scale, int tp_rank, int blocksparse_local_blocks, int blocksparse_vert_stride,
     int blocksparse_block_size, int blocksparse_head_sliding_step, void* workspace,
     int64_t workspace_bytes, void* stream) {
-  return paged_attention_common(false, out, nullptr, nullptr, nullptr, query, key_cache,
+  return paged_attention_common(false, out, nullptr, 0, 0, nullptr, nullptr, nullptr, query, key_cache,
                                 value_cache, num_seqs, num_heads, num_kv_heads, head_size,
                                 block_size, scale, block_tables, max_num_blocks_per_seq, seq_lens,
                                 max_seq_len, 1, alibi_slopes, q_stride, kv_block_stride,
@@ -224,7 +229,7 @@ int b200pa_paged_attention_v2(
     int scalar_type, int kv_dtype, const float* k_scale, const float* v_scale, int tp_rank,
     int blocksparse_local_blocks, int blocksparse_vert_stride, int blocksparse_block_size,
     int blocksparse_head_sliding_step, void* workspace, int64_t workspace_bytes, void* stream) {
-  return paged_attention_common(true, out, exp_sums, max_logits, tmp_out, query, key_cache,
+  return paged_attention_common(true, out, nullptr, 0, 0, exp_sums, max_logits, tmp_out, query, key_cache,
                                 value_cache, num_seqs, num_heads, num_kv_heads, head_size,
                                 block_size, scale, block_tables, max_num_blocks_per_seq, seq_lens,
                                 max_seq_len, max_num_partitions, alibi_slopes, q_stride,
@@ -232,6 +237,65 @@ int b200pa_paged_attention_v2(
                                 v_scale, tp_rank, blocksparse_local_blocks,
                                 blocksparse_vert_stride, blocksparse_block_size,
                                 blocksparse_head_sliding_step, workspace, workspace_bytes, stream);
+}
+
+int b200pa_paged_attention_lse(
+    void* out, float* lse, int64_t lse_seq_stride, int64_t lse_head_stride, const void* query,
+    const void* key_cache, const void* value_cache, int num_seqs, int num_heads, int num_kv_heads,
+    int head_size, int block_size, float scale, const int32_t* block_tables,
+    int max_num_blocks_per_seq, const int32_t* seq_lens, int max_seq_len,
+    const float* alibi_slopes, int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
+    int scalar_type, int kv_dtype, const float* k_scale, const float* v_scale, void* workspace,
+    int64_t workspace_bytes, void* stream) {
+  if (!lse) return set_error(B200PA_ERR_INVALID, "paged_attention_lse: null lse pointer");
+  return paged_attention_common(false, out, lse, lse_seq_stride, lse_head_stride, nullptr, nullptr,
+                                nullptr, query, key_cache, value_cache, num_seqs, num_heads,
+                                num_kv_heads, head_size, block_size, scale, block_tables,
+                                max_num_blocks_per_seq, seq_lens, max_seq_len, 1, alibi_slopes,
+                                q_stride, kv_block_stride, kv_head_stride, scalar_type, kv_dtype,
+                                k_scale, v_scale, 0, 0, 0, 64, 0, workspace, workspace_bytes,
+                                stream);
+}
+
+int b200pa_merge_attn_states(void* output, float* output_lse, const void* prefix_output,
+                             const float* prefix_lse, const void* suffix_output,
+                             const float* suffix_lse, int64_t num_tokens, int num_heads,
+                             int head_size, int scalar_type, void* stream) {
+  if (num_tokens < 0 || num_heads <= 0 || head_size <= 0)
+    return set_error(B200PA_ERR_INVALID, "merge_attn_states: bad shape");
+  if (scalar_type != B200PA_F32 && scalar_type != B200PA_F16 && scalar_type != B200PA_BF16)
+    return set_error(B200PA_ERR_UNSUPPORTED, "Unsupported data type of O: %d", scalar_type);
+  const int pack = scalar_type == B200PA_F32 ? 4 : 8;
+  if (head_size % pack != 0)
+    return set_error(B200PA_ERR_UNSUPPORTED, "headsize must be multiple of pack_size:%d", pack);
+  if (num_tokens == 0) return B200PA_OK;
+  if (!output || !prefix_output || !prefix_lse || !suffix_output || !suffix_lse)
+    return set_error(B200PA_ERR_INVALID, "merge_attn_states: null tensor pointer");
+  if ((reinterpret_cast<uintptr_t>(output) | reinterpret_cast<uintptr_t>(prefix_output) |
+       reinterpret_cast<uintptr_t>(suffix_output)) & 15u)
+    return set_error(B200PA_ERR_INVALID, "merge_attn_states: outputs must be 16-byte aligned");
+  return launch_merge_attn_states(output, output_lse, prefix_output, prefix_lse, suffix_output,
+                                  suffix_lse, num_tokens, num_heads, head_size, scalar_type,
+                                  reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200pa_correct_attn_out(void* out, float* lse_out, const float* lses, int num_ranks,
+                            int rank, int num_seqs, int num_heads, int head_size,
+                            int64_t out_seq_stride, int64_t out_head_stride,
+                            int64_t lses_rank_stride, int64_t lses_seq_stride,
+                            int64_t lses_head_stride, int scalar_type, void* stream) {
+  if (num_ranks <= 0 || rank < 0 || rank >= num_ranks || num_seqs < 0 || num_heads <= 0 ||
+      head_size <= 0)
+    return set_error(B200PA_ERR_INVALID, "correct_attn_out: bad shape");
+  if (scalar_type != B200PA_F32 && scalar_type != B200PA_F16 && scalar_type != B200PA_BF16)
+    return set_error(B200PA_ERR_UNSUPPORTED, "Unsupported data type of O: %d", scalar_type);
+  if (num_seqs == 0) return B200PA_OK;
+  if (!out || !lse_out || !lses)
+    return set_error(B200PA_ERR_INVALID, "correct_attn_out: null tensor pointer");
+  return launch_correct_attn_out(out, lse_out, lses, num_ranks, rank, num_seqs, num_heads,
+                                 head_size, out_seq_stride, out_head_stride, lses_rank_stride,
+                                 lses_seq_stride, lses_head_stride, scalar_type,
+                                 reinterpret_cast<cudaStream_t>(stream));
 }
 
 static int check_cache_args(const char* op, const void* key, const void* value, void* kc, void* vc,

@@ -4,7 +4,7 @@
 // the reference): head sizes {32,64,80,96,112,120,128,192,256}, block sizes
 // {8,16,32}, query dtype {fp32,fp16,bf16}, kv {auto, fp8_e4m3, fp8_e5m2}, ALiBi
 // and block-sparse.  The shapes of the BASELINE configs are served by the
-// TMA-staged tensor-core kernel in paged_attention_fast.cu; this kernel is the
+// persistent stream-K tensor-core kernel in paged_attention_stream.cu; this kernel is the
 // always-available companion (and the in-GPU cross-check in the tests).
 //
 // Differences from the reference kernel (attention_kernels.cuh:85-491) are
@@ -41,6 +41,7 @@ template <int ST, int KV, int BS, bool PARTITIONED>
 __global__ void __launch_bounds__(kGenericThreads)
 paged_attention_generic_kernel(
     typename Scalar<ST>::type* __restrict__ out,  // v1: [S,H,D]; v2: tmp_out [S,H,P,D]
+    float* __restrict__ lse, int64_t lse_seq_stride, int64_t lse_head_stride,  // v1 only, optional
     float* __restrict__ exp_sums, float* __restrict__ max_logits,
     const typename Scalar<ST>::type* __restrict__ q,
     const typename CacheElem<ST, KV>::type* __restrict__ k_cache,
@@ -200,6 +201,9 @@ paged_attention_generic_kernel(
     }
   } else {
     out_ptr = out + ((int64_t)seq * num_heads + head) * head_size;
+    if (lse != nullptr && threadIdx.x == 0)
+      lse[seq * lse_seq_stride + head * lse_head_stride] =
+          (m_all == -INFINITY) ? -INFINITY : m_all + logf(l_all);
   }
   for (int d = threadIdx.x; d < head_size; d += kGenericThreads) {
     float o = 0.f;
@@ -275,7 +279,8 @@ paged_attention_reduce_kernel(typename Scalar<ST>::type* __restrict__ out,
 }
 
 template <int ST, int KV, int BS>
-int launch_generic_t(void* out, float* exp_sums, float* max_logits, void* tmp_out,
+int launch_generic_t(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_head_stride,
+                     float* exp_sums, float* max_logits, void* tmp_out,
                      const void* query, const void* key_cache, const void* value_cache,
                      int num_seqs, int num_heads, int num_kv_heads, int head_size, float scale,
                      const int32_t* block_tables, int max_num_blocks_per_seq,
@@ -289,7 +294,7 @@ int launch_generic_t(void* out, float* exp_sums, float* max_logits, void* tmp_ou
   if (!partitioned) {
     dim3 grid(num_heads, num_seqs, 1);
     paged_attention_generic_kernel<ST, KV, BS, false><<<grid, block, 0, stream>>>(
-        (T*)out, nullptr, nullptr, (const T*)query, (const C*)key_cache, (const C*)value_cache,
+        (T*)out, lse, lse_seq_stride, lse_head_stride, nullptr, nullptr, (const T*)query, (const C*)key_cache, (const C*)value_cache,
         num_kv_heads, head_size, scale, block_tables, seq_lens, max_num_blocks_per_seq,
         alibi_slopes, q_stride, kv_block_stride, kv_head_stride, k_scale, v_scale, 1, bsp);
     count_launch();
@@ -298,7 +303,7 @@ int launch_generic_t(void* out, float* exp_sums, float* max_logits, void* tmp_ou
   const int parts = (max_seq_len + kPartitionSize - 1) / kPartitionSize;
   dim3 grid(num_heads, num_seqs, parts > 0 ? parts : 1);
   paged_attention_generic_kernel<ST, KV, BS, true><<<grid, block, 0, stream>>>(
-      (T*)tmp_out, exp_sums, max_logits, (const T*)query, (const C*)key_cache,
+      (T*)tmp_out, nullptr, 0, 0, exp_sums, max_logits, (const T*)query, (const C*)key_cache,
       (const C*)value_cache, num_kv_heads, head_size, scale, block_tables, seq_lens,
       max_num_blocks_per_seq, alibi_slopes, q_stride, kv_block_stride, kv_head_stride, k_scale,
       v_scale, max_num_partitions, bsp);

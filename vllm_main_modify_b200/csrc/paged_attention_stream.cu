@@ -40,6 +40,7 @@ namespace {
 
 constexpr int kBS = 16;                      // tokens per page (block_size)
 constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
 constexpr uint32_t kFull = 0xffffffffu;
 
 // ------------------------------------------------------------------ PTX bits
@@ -136,6 +137,8 @@ __device__ __forceinline__ void e4m3x4_to_f16x2x2(uint32_t w, uint32_t& lo, uint
 
 struct StreamParams {
   void* out;           // [S,H,D] scalar_t
+  float* lse;          // optional: natural-log sum-exp of the scaled logits per (seq, head)
+  int64_t lse_seq_stride, lse_head_stride;
   float* ws;           // workspace: 2 slots per worker, kSlotFloats(D) floats each
   const void* q;
   const void* k_cache;
@@ -153,7 +156,7 @@ struct StreamParams {
   float scale;
 };
 
-// workspace slot: O^T fragments [D/16][4][32 lanes] fp32 (unnormalised, v_scale applied),
+// workspace slot: O^T fragments [D/16][32 lanes][4] fp32 (unnormalised, v_scale applied),
 // then m[8] (log2 domain), l[8]
 __host__ __device__ constexpr int slot_floats(int d) { return 8 * d + 16; }
 
@@ -463,14 +466,21 @@ paged_attention_stream_kernel(const StreamParams p) {
       const float inv1 = out_scale * __fdividef(1.f, lsum[1] + 1e-6f);
       store_out<ST, D>(reinterpret_cast<T*>(p.out) + ((int64_t)cc.b * p.num_heads + head0) * D, o,
                        inv0, inv1, heads_valid, r, q4);
+      if (p.lse != nullptr && r == 0) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+          if (2 * q4 + h < heads_valid)
+            p.lse[cc.b * p.lse_seq_stride + (head0 + 2 * q4 + h) * p.lse_head_stride] =
+                (msub[h] + __log2f(lsum[h])) * kLn2;
+      }
     } else {
       // slot 2w: my first piece, continuing an earlier worker's; slot 2w+1: my last piece,
       // continued by a later worker
       float* slot = p.ws + (size_t)(2 * w + (from_start ? 1 : 0)) * slot_floats(D);
 #pragma unroll
       for (int mt = 0; mt < MT; ++mt)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) slot[(mt * 4 + j) * 32 + lane] = o[mt][j] * out_scale;
+        reinterpret_cast<float4*>(slot)[mt * 32 + lane] = make_float4(
+            o[mt][0] * out_scale, o[mt][1] * out_scale, o[mt][2] * out_scale, o[mt][3] * out_scale);
       if (r == 0) {
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
@@ -659,17 +669,25 @@ paged_attention_stream_kernel(const StreamParams p) {
 // ---------------------------------------------------------------------------------------
 // Merge of the pieces of every (sequence, head tile) that a span boundary cut (the job of the
 // reference's paged_attention_v2_reduce_kernel, attention_kernels.cuh:560-664: weights
-// l_j * exp(m_j - m), 1e-6 in the denominator).  One CTA per boundary between workers w-1 | w,
-// one warp per 16-element slice of the head (m-tile).  The CTA that owns the FIRST boundary
-// inside a (sequence, head tile) merges all its pieces: slot 2(w-1)+1 (the tail piece of the
-// worker that holds the start) and slots 2w' of every later worker whose span starts inside it.
-// Launched with programmatic stream serialisation: everything up to griddepcontrol.wait
-// overlaps the tail of the main kernel.
+// l_j * exp(m_j - m), 1e-6 in the denominator).  One CTA per boundary between workers w-1 | w.
+// The CTA that owns the FIRST boundary inside a (sequence, head tile) merges all its pieces:
+// slot 2(w-1)+1 (the tail piece of the worker that holds the start) and slots 2w' of every
+// later worker whose span starts inside it.  Pieces are dealt round-robin to the CTA's warps
+// (a 131072-token sequence of one kv head is ~90 pieces on a B200; a lone one ~1200), each warp
+// accumulates whole slots with 16-byte loads, and the warps' sums meet in shared memory in a
+// fixed order (deterministic).  Launched with programmatic stream serialisation: everything up
+// to griddepcontrol.wait overlaps the tail of the main kernel.
+constexpr int kMergeWarps = 8;
+
 template <int ST, int D, int PPS>
-__global__ void __launch_bounds__(32 * (D / 16))
+__global__ void __launch_bounds__(32 * kMergeWarps)
 paged_attention_stream_merge_kernel(const StreamParams p) {
   using T = typename Scalar<ST>::type;
-  const int lane = threadIdx.x & 31, mt = threadIdx.x >> 5;
+  constexpr int MT = D / 16;
+  static_assert(MT <= kMergeWarps, "one warp per m-tile in the final step");
+  __shared__ float4 acc_s[kMergeWarps][MT][32];
+  __shared__ float lsum_s[kMergeWarps][8];
+  const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
   const int r = lane >> 2, q4 = lane & 3;
   const int vheads = p.num_kv_heads * p.h_tiles;
   const long long w = (long long)blockIdx.x + 1;
@@ -679,6 +697,9 @@ paged_attention_stream_merge_kernel(const StreamParams p) {
       T* row = reinterpret_cast<T*>(p.out) + b * p.num_heads * D;
       for (int i = threadIdx.x; i < p.num_heads * D; i += blockDim.x)
         row[i] = Scalar<ST>::from_float(0.f);
+      if (p.lse != nullptr)
+        for (int i = threadIdx.x; i < p.num_heads; i += blockDim.x)
+          p.lse[b * p.lse_seq_stride + i * p.lse_head_stride] = -INFINITY;
     }
   }
   const long long Ttot = total_stages<PPS>(p.seq_lens, p.num_seqs, lane) * vheads;
@@ -718,30 +739,62 @@ paged_attention_stream_merge_kernel(const StreamParams p) {
     if (h == 2 * q4) mx[0] = mx8[h];
     if (h == 2 * q4 + 1) mx[1] = mx8[h];
   }
-  // pass 2: weighted sum of this warp's m-tile
-  float o[4] = {0.f, 0.f, 0.f, 0.f};
+  // pass 2: warp wv sums pieces wv, wv + 8, ... (whole slots)
+  float4 acc[MT];
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt) acc[mt] = make_float4(0.f, 0.f, 0.f, 0.f);
   float lsum[2] = {0.f, 0.f};
-#pragma unroll 4
-  for (int k = 0; k < n; ++k) {
+#pragma unroll 2
+  for (int k = wv; k < n; k += kMergeWarps) {
     const float* slot = slot_of(k);
     const float2 m = *reinterpret_cast<const float2*>(slot + 8 * D + 2 * q4);
     const float2 l = *reinterpret_cast<const float2*>(slot + 8 * D + 8 + 2 * q4);
+    float4 v[MT];
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt) v[mt] = reinterpret_cast<const float4*>(slot)[mt * 32 + lane];
     const float f0 = ex2(m.x - mx[0]), f1 = ex2(m.y - mx[1]);
     lsum[0] += l.x * f0;
     lsum[1] += l.y * f1;
-    o[0] += slot[(mt * 4 + 0) * 32 + lane] * f0;
-    o[1] += slot[(mt * 4 + 1) * 32 + lane] * f1;
-    o[2] += slot[(mt * 4 + 2) * 32 + lane] * f0;
-    o[3] += slot[(mt * 4 + 3) * 32 + lane] * f1;
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt) {
+      acc[mt].x += v[mt].x * f0; acc[mt].y += v[mt].y * f1;
+      acc[mt].z += v[mt].z * f0; acc[mt].w += v[mt].w * f1;
+    }
+  }
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt) acc_s[wv][mt][lane] = acc[mt];
+  if (r == 0) {
+    lsum_s[wv][2 * q4] = lsum[0];
+    lsum_s[wv][2 * q4 + 1] = lsum[1];
+  }
+  __syncthreads();
+  if (wv >= MT) return;
+  // final: warp mt adds the warps' sums of its m-tile in warp order
+  const int mt = wv;
+  float o[4] = {0.f, 0.f, 0.f, 0.f};
+  float lt[2] = {0.f, 0.f};
+#pragma unroll
+  for (int g = 0; g < kMergeWarps; ++g) {
+    const float4 v = acc_s[g][mt][lane];
+    o[0] += v.x; o[1] += v.y; o[2] += v.z; o[3] += v.w;
+    lt[0] += lsum_s[g][2 * q4];
+    lt[1] += lsum_s[g][2 * q4 + 1];
   }
   const int kvh = loc.vh / p.h_tiles;
   const int tile = loc.vh - kvh * p.h_tiles;
   const int head0 = kvh * p.group + tile * 8;
   const int heads_valid = min(8, p.group - tile * 8);
-  const float inv0 = __fdividef(1.f, lsum[0] + 1e-6f);
-  const float inv1 = __fdividef(1.f, lsum[1] + 1e-6f);
+  const float inv0 = __fdividef(1.f, lt[0] + 1e-6f);
+  const float inv1 = __fdividef(1.f, lt[1] + 1e-6f);
   store_out_tile<ST, D>(reinterpret_cast<T*>(p.out) + ((int64_t)loc.b * p.num_heads + head0) * D,
                         mt, o, inv0, inv1, heads_valid, r, q4);
+  if (p.lse != nullptr && mt == 0 && r == 0) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h)
+      if (2 * q4 + h < heads_valid)
+        p.lse[loc.b * p.lse_seq_stride + (head0 + 2 * q4 + h) * p.lse_head_stride] =
+            (mx[h] + __log2f(lt[h])) * kLn2;
+  }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -776,7 +829,7 @@ int launch_stream_t(StreamParams& p, int num_sms, int64_t workspace_bytes, cudaS
   if (p.num_workers > 1) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(p.num_workers - 1);   // boundaries 1 .. num_workers-1
-    cfg.blockDim = dim3(32 * (D / 16));
+    cfg.blockDim = dim3(32 * kMergeWarps);
     cfg.dynamicSmemBytes = 0;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
@@ -820,7 +873,8 @@ bool stream_supported(const void* query, const void* key_cache, const void* valu
   return true;
 }
 
-int launch_stream(void* out, void* workspace, int64_t workspace_bytes, const void* query,
+int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_head_stride,
+                  void* workspace, int64_t workspace_bytes, const void* query,
                   const void* key_cache, const void* value_cache, int num_seqs, int num_heads,
                   int num_kv_heads, int head_size, float scale, const int32_t* block_tables,
                   int max_num_blocks_per_seq, const int32_t* seq_lens, const float* alibi_slopes,
@@ -832,6 +886,9 @@ int launch_stream(void* out, void* workspace, int64_t workspace_bytes, const voi
                      "(b200pa_paged_attention_workspace_bytes)");
   StreamParams p;
   p.out = out;
+  p.lse = lse;
+  p.lse_seq_stride = lse_seq_stride;
+  p.lse_head_stride = lse_head_stride;
   p.ws = reinterpret_cast<float*>(workspace);
   p.q = query;
   p.k_cache = key_cache;

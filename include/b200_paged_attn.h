@@ -18,6 +18,13 @@
  *   b200pa_get_max_shared_memory_per_block_device_attribute
  *                                   csrc/cuda_utils_kernels.cu (schema
  *                                   csrc/torch_bindings.cpp:718-730)
+ *   b200pa_merge_attn_states        csrc/attention/merge_attn_states.cu:172-180
+ *                                   (launcher :131-170; schema csrc/torch_bindings.cpp:80-87)
+ *   b200pa_correct_attn_out         vllm/attention/ops/common.py:86-116 (Triton kernel :9-68)
+ *   b200pa_paged_attention_lse      no reference kernel: decode + log-sum-exp, what
+ *                                   AttentionImpl.can_return_lse_for_decode
+ *                                   (vllm/attention/backends/abstract.py:115-138) asks of a
+ *                                   backend for decode context parallelism
  *
  * Conventions
  *   - All data pointers are DEVICE pointers on the current CUDA device; strides
@@ -46,7 +53,7 @@
 extern "C" {
 #endif
 
-#define B200PA_ABI_VERSION 2
+#define B200PA_ABI_VERSION 3
 
 /* scalar_t of query / out / key / value (reference: VLLM_DISPATCH_FLOATING_TYPES) */
 enum { B200PA_F32 = 0, B200PA_F16 = 1, B200PA_BF16 = 2 };
@@ -135,6 +142,46 @@ int b200pa_paged_attention_v2(
     int blocksparse_vert_stride, int blocksparse_block_size,
     int blocksparse_head_sliding_step, void* workspace, int64_t workspace_bytes,
     void* stream);
+
+/*
+ * paged_attention_v1 (dense, no block-sparse) that also returns, per (sequence, head), the
+ * natural-log sum-exp of the scaled logits:
+ *   lse[seq * lse_seq_stride + head * lse_head_stride] = log(sum_t exp(scale * q.k_t [+ alibi]))
+ * (-inf for an empty sequence; strides in floats, so both [num_seqs, num_heads] and the
+ * [num_heads, num_seqs] layout of merge_attn_states are expressible).
+ */
+int b200pa_paged_attention_lse(
+    void* out, float* lse, int64_t lse_seq_stride, int64_t lse_head_stride,
+    const void* query, const void* key_cache, const void* value_cache,
+    int num_seqs, int num_heads, int num_kv_heads, int head_size, int block_size,
+    float scale, const int32_t* block_tables, int max_num_blocks_per_seq,
+    const int32_t* seq_lens, int max_seq_len, const float* alibi_slopes,
+    int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
+    int scalar_type, int kv_dtype, const float* k_scale, const float* v_scale,
+    void* workspace, int64_t workspace_bytes, void* stream);
+
+/*
+ * output, prefix_output, suffix_output [num_tokens, num_heads, head_size] scalar_t, dense,
+ * 16-byte aligned; prefix_lse, suffix_lse, output_lse (may be NULL) [num_heads, num_tokens] fp32.
+ * head_size must be a multiple of 16 / sizeof(scalar_t).
+ */
+int b200pa_merge_attn_states(
+    void* output, float* output_lse, const void* prefix_output, const float* prefix_lse,
+    const void* suffix_output, const float* suffix_lse, int64_t num_tokens, int num_heads,
+    int head_size, int scalar_type, void* stream);
+
+/*
+ * Decode-context-parallel correction, in place:
+ *   lse_total = log sum_n exp(lses[n, b, h]);  out[b, h, :] *= exp(lses[rank, b, h] - lse_total)
+ * out [num_seqs, num_heads, head_size] scalar_t with element strides out_seq_stride /
+ * out_head_stride (innermost dense); lses [num_ranks, num_seqs, num_heads] fp32 by strides;
+ * lse_out (written) is indexed with lses' seq / head strides.
+ */
+int b200pa_correct_attn_out(
+    void* out, float* lse_out, const float* lses, int num_ranks, int rank, int num_seqs,
+    int num_heads, int head_size, int64_t out_seq_stride, int64_t out_head_stride,
+    int64_t lses_rank_stride, int64_t lses_seq_stride, int64_t lses_head_stride,
+    int scalar_type, void* stream);
 
 /*
  * key, value [num_tokens, num_heads, head_size] scalar_t, row strides key_stride /

@@ -7,7 +7,8 @@
 #   csrc/attention/paged_attention_v1.cu   (all template instances, ~7 min)
 #   csrc/attention/paged_attention_v2.cu
 #   csrc/cache_kernels.cu
-# plus oracle/ref_cuda_binding.cpp (5 op registrations, private namespace).
+#   csrc/attention/merge_attn_states.cu
+# plus oracle/ref_cuda_binding.cpp (op registrations, private namespace).
 # Flags follow the reference's CMakeLists.txt (-DENABLE_FP8,
 # --expt-relaxed-constexpr, c++17).  The reference's cmake is NOT run.
 set -euo pipefail
@@ -45,10 +46,11 @@ TMP="$(mktemp -d)"
 "$NVCC" "${NVFLAGS[@]}" "${INC[@]}" -c "$REF/csrc/attention/paged_attention_v1.cu" -o "$TMP/pa_v1.o" &
 "$NVCC" "${NVFLAGS[@]}" "${INC[@]}" -c "$REF/csrc/attention/paged_attention_v2.cu" -o "$TMP/pa_v2.o" &
 "$NVCC" "${NVFLAGS[@]}" "${INC[@]}" -c "$REF/csrc/cache_kernels.cu" -o "$TMP/cache.o" &
+"$NVCC" "${NVFLAGS[@]}" "${INC[@]}" -c "$REF/csrc/attention/merge_attn_states.cu" -o "$TMP/merge.o" &
 g++ -std=c++17 -O2 -fPIC -w -D_GLIBCXX_USE_CXX11_ABI="$ABI" "${INC[@]}" \
     -c "$HERE/ref_cuda_binding.cpp" -o "$TMP/binding.o" &
 wait
-g++ -shared "$TMP/pa_v1.o" "$TMP/pa_v2.o" "$TMP/cache.o" "$TMP/binding.o" \
+g++ -shared "$TMP/pa_v1.o" "$TMP/pa_v2.o" "$TMP/cache.o" "$TMP/merge.o" "$TMP/binding.o" \
     -L"$TORCH_DIR/lib" -Wl,-rpath,"$TORCH_DIR/lib" -L/usr/local/cuda/lib64 \
     -ltorch -ltorch_cpu -ltorch_cuda -lc10 -lc10_cuda -lcudart -o "$SO"
 rm -rf "$TMP"

@@ -1,7 +1,8 @@
 """TEST INFRASTRUCTURE ONLY -- loader for the reference's own CUDA kernels (oracle tier O1).
 
 ``oracle/build_ref_cuda.sh`` compiles ``csrc/attention/paged_attention_v1.cu``,
-``csrc/attention/paged_attention_v2.cu`` and ``csrc/cache_kernels.cu`` of the reference,
+``csrc/attention/paged_attention_v2.cu``, ``csrc/attention/merge_attn_states.cu`` and
+``csrc/cache_kernels.cu`` of the reference,
 unmodified, for sm_100a into ``oracle/_ref/libvllm_ref_cuda.so``; the ops register under the
 private namespace ``vllm_ref_cuda`` (``oracle/ref_cuda_binding.cpp``).  Used by ``tests/`` as the
 parity target north_star names ("the reference's own paged_attention implementation") and by
@@ -57,3 +58,23 @@ def reshape_and_cache_flash(*args) -> None:
 
 def convert_fp8(*args) -> None:
     _ops().convert_fp8(*args)
+
+
+def merge_attn_states(*args) -> None:
+    _ops().merge_attn_states(*args)
+
+
+def swap_blocks(*args) -> None:
+    _ops().swap_blocks(*args)
+
+
+def copy_blocks(*args) -> None:
+    _ops().copy_blocks(*args)
+
+
+def gather_and_maybe_dequant_cache(*args) -> None:
+    _ops().gather_and_maybe_dequant_cache(*args)
+
+
+def cp_gather_cache(*args) -> None:
+    _ops().cp_gather_cache(*args)

@@ -15,6 +15,7 @@
 
 #include <optional>
 #include <string>
+#include <vector>
 
 // csrc/attention/paged_attention_v1.cu:160, paged_attention_v2.cu:167
 void paged_attention_v1(
@@ -55,6 +56,30 @@ void reshape_and_cache_flash(torch::Tensor& key, torch::Tensor& value,
 void convert_fp8(torch::Tensor& dst_cache, torch::Tensor& src_cache,
                  const double scale, const std::string& kv_cache_dtype);
 
+// csrc/attention/merge_attn_states.cu:172 (declared csrc/ops.h:56-61)
+void merge_attn_states(torch::Tensor& output,
+                       std::optional<torch::Tensor> output_lse,
+                       const torch::Tensor& prefix_output,
+                       const torch::Tensor& prefix_lse,
+                       const torch::Tensor& suffix_output,
+                       const torch::Tensor& suffix_lse);
+
+// csrc/cache_kernels.cu:27, :125, :734, :865 (declared csrc/cache.h:8-60)
+void swap_blocks(torch::Tensor& src, torch::Tensor& dst,
+                 const torch::Tensor& block_mapping);
+void copy_blocks(std::vector<torch::Tensor> const& key_caches,
+                 std::vector<torch::Tensor> const& value_caches,
+                 const torch::Tensor& block_mapping);
+void gather_and_maybe_dequant_cache(
+    torch::Tensor const& src_cache, torch::Tensor const& dst,
+    torch::Tensor const& block_table, torch::Tensor const& cu_seq_lens,
+    int64_t batch_size, const std::string& kv_cache_dtype,
+    torch::Tensor const& scale, std::optional<torch::Tensor> seq_starts);
+void cp_gather_cache(torch::Tensor const& src_cache, torch::Tensor const& dst,
+                     torch::Tensor const& block_table,
+                     torch::Tensor const& cu_seq_lens, int64_t batch_size,
+                     std::optional<torch::Tensor> seq_starts);
+
 #define ATTN_TAIL                                                        \
   "Tensor query, Tensor key_cache, Tensor value_cache, int num_kv_heads," \
   " float scale, Tensor block_tables, Tensor seq_lens, int block_size,"  \
@@ -84,4 +109,25 @@ TORCH_LIBRARY(vllm_ref_cuda, ops) {
       "convert_fp8(Tensor! dst_cache, Tensor src_cache, float scale,"
       " str kv_cache_dtype) -> ()");
   ops.impl("convert_fp8", torch::kCUDA, &convert_fp8);
+  ops.def(
+      "merge_attn_states(Tensor! output, Tensor!? output_lse,"
+      " Tensor prefix_output, Tensor prefix_lse, Tensor suffix_output,"
+      " Tensor suffix_lse) -> ()");
+  ops.impl("merge_attn_states", torch::kCUDA, &merge_attn_states);
+  ops.def("swap_blocks(Tensor src, Tensor! dst, Tensor block_mapping) -> ()");
+  ops.impl("swap_blocks", torch::kCUDA, &swap_blocks);
+  ops.def(
+      "copy_blocks(Tensor(a!)[] key_caches, Tensor[](b!) value_caches,"
+      " Tensor block_mapping) -> ()");
+  ops.impl("copy_blocks", torch::kCUDA, &copy_blocks);
+  ops.def(
+      "gather_and_maybe_dequant_cache(Tensor src_cache, Tensor! dst,"
+      " Tensor block_table, Tensor cu_seq_lens, int batch_size,"
+      " str kv_cache_dtype, Tensor scale, Tensor? seq_starts) -> ()");
+  ops.impl("gather_and_maybe_dequant_cache", torch::kCUDA,
+           &gather_and_maybe_dequant_cache);
+  ops.def(
+      "cp_gather_cache(Tensor src_cache, Tensor! dst, Tensor block_table,"
+      " Tensor cu_seq_lens, int batch_size, Tensor? seq_starts) -> ()");
+  ops.impl("cp_gather_cache", torch::kCUDA, &cp_gather_cache);
 }

@@ -18,6 +18,10 @@ Sources of truth used (all the reference's own code, none of ours):
                     csrc/cpu/attention.cpp (v1 and v2) from oracle/_ref.
   cache_*.npz       the reference's CPU reshape_and_cache (csrc/cpu/cache.cpp)
                     from oracle/_ref.
+  merge_*.npz       `merge_attn_states_torch`, extracted verbatim at run time (ast)
+                    from the reference's
+                    tests/kernels/attention/test_merge_attn_states.py:16-46 and
+                    executed here (inputs include +inf / -inf LSEs like that test).
 """
 from __future__ import annotations
 
@@ -165,7 +169,47 @@ def make_cache_case(name, T, Hkv, D, BS, NB, dtype, seed, strided):
     print(os.path.basename(path), os.path.getsize(path))
 
 
+def load_reference_merge_oracle():
+    path = os.path.join(REF, "tests/kernels/attention/test_merge_attn_states.py")
+    src = open(path).read()
+    tree = ast.parse(src)
+    chunks = [ast.get_source_segment(src, n) for n in tree.body
+              if isinstance(n, ast.FunctionDef) and n.name == "merge_attn_states_torch"]
+    assert len(chunks) == 1
+    ns = {"torch": torch, "Optional": Optional}
+    exec(chunks[0], ns)
+    return ns["merge_attn_states_torch"]
+
+
+def make_merge_case(name, n, h, d, dtype, seed):
+    torch.manual_seed(seed)
+    p_lse = torch.randn(h, n, dtype=torch.float32)
+    s_lse = torch.randn(h, n, dtype=torch.float32)
+    # like the reference test (:113-131): some +inf / -inf entries, never both sides at once
+    mask_p = torch.rand(h, n) < 0.1
+    mask_s = (torch.rand(h, n) < 0.1) & ~mask_p
+    p_lse[mask_p] = float("inf")
+    s_lse[mask_s] = float("inf")
+    s_lse[0, 0] = -float("inf")
+    p_out = torch.randn(n, h, d, dtype=dtype)
+    s_out = torch.randn(n, h, d, dtype=dtype)
+    fn = load_reference_merge_oracle()
+    out, out_lse = fn(torch.empty_like(p_out), p_out.float(), p_lse.clone(), s_out.float(),
+                      s_lse.clone(), torch.empty(h, n))
+    path = os.path.join(HERE, f"merge_{name}.npz")
+    np.savez_compressed(path, prefix_output=bits(p_out), suffix_output=bits(s_out),
+                        prefix_lse=p_lse.numpy(), suffix_lse=s_lse.numpy(),
+                        output_f32=out.float().numpy(), output_lse=out_lse.numpy(),
+                        dtype=str(dtype).split(".")[-1])
+    print(os.path.basename(path), os.path.getsize(path))
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "merge":
+        make_merge_case("bf16_d128", 37, 8, 128, torch.bfloat16, 0)
+        make_merge_case("f16_d96", 19, 4, 96, torch.float16, 1)
+        make_merge_case("f32_d32", 23, 3, 32, torch.float32, 2)
+        sys.exit(0)
     make_fp8()
     bf16 = torch.bfloat16
     make_attn_case("gqa_bf16_d128", 4, 8, 2, 128, 16, 24, [1, 16, 333, 700], bf16, False, 0)
@@ -176,3 +220,6 @@ if __name__ == "__main__":
     make_cache_case("bf16", 13, 4, 128, 16, 8, bf16, 0, False)
     make_cache_case("bf16_strided", 9, 2, 64, 16, 8, bf16, 1, True)
     make_cache_case("f16", 7, 3, 80, 16, 4, torch.float16, 2, False)
+    make_merge_case("bf16_d128", 37, 8, 128, torch.bfloat16, 0)
+    make_merge_case("f16_d96", 19, 4, 96, torch.float16, 1)
+    make_merge_case("f32_d32", 23, 3, 32, torch.float32, 2)

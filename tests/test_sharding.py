@@ -92,3 +92,56 @@ def test_two_rank_gloo_shards_reproduce_the_unsharded_result(kv):
         mp.spawn(_worker, args=(world, port, kv, ret), nprocs=world, join=True)
         assert ret["shape"] == (5, 16, 128)
         assert ret["equal"], "gathered per-rank outputs differ from the unsharded computation"
+
+
+# ------------------------------------------------------------------ decode context parallelism
+def _dcp_worker(rank, world, port, ret):
+    """Rank r holds pages r, r+N, ... of every sequence; oracle kernels stand in for the CUDA ops,
+    the host logic under test is vllm_main_modify_b200.dcp.cp_lse_ag_out_rs."""
+    from oracle import lse_oracle
+    from vllm_main_modify_b200.dcp import cp_lse_ag_out_rs
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        B, H, Hkv, D, BS = 3, 8, 2, 64, 16
+        lens = [16, 640, 1000]           # sequence 0: rank 1 holds no page at all
+        NB = sum((l + BS - 1) // BS for l in lens) + 1
+        s = D ** -0.5
+        q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, NB, lens, torch.float32, seed=12,
+                                                 permute=True)
+        rows, lens_r = [], []
+        for b, L in enumerate(lens):
+            nb = (L + BS - 1) // BS
+            mine = list(range(rank, nb, world))
+            rows.append([int(bt[b, j]) for j in mine])
+            lens_r.append(sum(min(BS, L - j * BS) for j in mine))
+        mb = max(1, max(len(x) for x in rows))
+        bt_r = torch.tensor([x + [0] * (mb - len(x)) for x in rows], dtype=torch.int32)
+        sl_r = torch.tensor(lens_r, dtype=torch.int32)
+        one = torch.tensor(1.0)
+        part = torch.zeros(B, H, D)
+        lse = torch.empty(B, H)
+        lse_oracle.paged_attention_lse(part, lse, q, kc, vc, Hkv, s, bt_r, sl_r, BS,
+                                       max(max(lens_r), 1), None, "auto", one, one)
+        mine = cp_lse_ag_out_rs(part, lse, None, correct_fn=lse_oracle.correct_attn_out)
+        want = hp.torch_reference_attention(q, kc, vc, bt, sl, s, Hkv).float()
+        h = H // world
+        ret[rank] = float((mine - want[:, rank * h:(rank + 1) * h]).abs().max())
+        ret[f"shape{rank}"] = tuple(mine.shape)
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_gloo_decode_context_parallel_reproduces_full_attention():
+    from oracle import oracle as ora
+    ora.lib()
+    world = 2
+    port = _free_port()
+    with mp.Manager() as mgr:
+        ret = mgr.dict()
+        mp.spawn(_dcp_worker, args=(world, port, ret), nprocs=world, join=True)
+        for r in range(world):
+            assert ret[f"shape{r}"] == (3, 4, 64)
+            assert ret[r] < 1e-5, ret[r]

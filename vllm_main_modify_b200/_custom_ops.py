@@ -77,6 +77,53 @@ def paged_attention_v2(
         blocksparse_block_size, blocksparse_head_sliding_step)
 
 
+def merge_attn_states(output: torch.Tensor,
+                      prefix_output: torch.Tensor,
+                      prefix_lse: torch.Tensor,
+                      suffix_output: torch.Tensor,
+                      suffix_lse: torch.Tensor,
+                      output_lse: Optional[torch.Tensor] = None) -> None:
+    """``vllm/_custom_ops.py:143-150``: output [n,h,d], lse tensors [h,n] fp32."""
+    _ops.merge_attn_states(output, output_lse, prefix_output, prefix_lse,
+                           suffix_output, suffix_lse)
+
+
+def paged_attention_lse(
+    out: torch.Tensor,
+    lse: torch.Tensor,
+    query: torch.Tensor,
+    key_cache: torch.Tensor,
+    value_cache: torch.Tensor,
+    num_kv_heads: int,
+    scale: float,
+    block_tables: torch.Tensor,
+    seq_lens: torch.Tensor,
+    block_size: int,
+    max_seq_len: int,
+    alibi_slopes: Optional[torch.Tensor],
+    kv_cache_dtype: str,
+    k_scale: torch.Tensor,
+    v_scale: torch.Tensor,
+) -> None:
+    """``paged_attention_v1`` that also writes ``lse[num_seqs, num_heads]`` (fp32, any strides):
+    the natural-log sum-exp of the scaled logits (``-inf`` for an empty sequence).  No twin in
+    the reference's ``_custom_ops``; it is what ``can_return_lse_for_decode``
+    (``abstract.py:115-121``) needs from a decode backend."""
+    _ops.paged_attention_lse(
+        out, lse, query, key_cache, value_cache, num_kv_heads, scale,
+        block_tables, seq_lens, block_size, max_seq_len, alibi_slopes,
+        kv_cache_dtype, k_scale, v_scale)
+
+
+def correct_attn_out(out: torch.Tensor, lses: torch.Tensor, cp_rank: int,
+                     ctx=None) -> "tuple[torch.Tensor, torch.Tensor]":
+    """``vllm/attention/ops/common.py:86-116`` (``ctx`` is the reference's Triton cache, unused):
+    rescales ``out [B,H,D]`` in place by ``exp(lses[cp_rank] - logsumexp_n(lses))`` and returns
+    ``(out, lse_total)``."""
+    lse = _ops.correct_attn_out(out, lses, cp_rank)
+    return out, lse
+
+
 def reshape_and_cache(
     key: torch.Tensor,
     value: torch.Tensor,

@@ -14,7 +14,8 @@ C_ABI_SYMBOLS = (
     "b200pa_abi_version", "b200pa_last_error", "b200pa_kv_dtype_from_string",
     "b200pa_set_impl", "b200pa_get_impl", "b200pa_launch_count",
     "b200pa_paged_attention_workspace_bytes",
-    "b200pa_paged_attention_v1", "b200pa_paged_attention_v2",
+    "b200pa_paged_attention_v1", "b200pa_paged_attention_v2", "b200pa_paged_attention_lse",
+    "b200pa_merge_attn_states", "b200pa_correct_attn_out",
     "b200pa_reshape_and_cache", "b200pa_reshape_and_cache_flash",
     "b200pa_convert_fp8",
     "b200pa_get_max_shared_memory_per_block_device_attribute",

@@ -95,10 +95,14 @@ class B200PagedAttentionMetadataBuilder:
 class B200PagedAttentionImpl:
     """``AttentionImpl`` (``abstract.py:113-181``) for paged decode on B200."""
 
-    can_return_lse_for_decode: bool = False
+    # abstract.py:115-138 of the reference: the impl can hand back the softmax LSE of the decode
+    # (ops.paged_attention_lse); the runner sets dcp_world_size / dcp_rank and the flag below
+    # becomes true when decode context parallelism is on.
+    can_return_lse_for_decode: bool = True
     need_to_return_lse_for_decode: bool = False
     dcp_world_size: int = 1
     dcp_rank: int = 0
+    dcp_group: Any = None             # torch.distributed group of the DCP ranks
 
     def __init__(
         self,
@@ -171,6 +175,17 @@ class B200PagedAttentionImpl:
                                                 layer._k_scale, layer._v_scale)
         if self.alibi_slopes is not None and self.alibi_slopes.device != q.device:
             self.alibi_slopes = self.alibi_slopes.to(q.device)
+        if self.need_to_return_lse_for_decode or self.dcp_world_size > 1:
+            # decode context parallelism: this rank's KV slice with ALL query heads, then the
+            # reference's cp_lse_ag_out_rs (common.py:119-140): gather LSEs, rescale, reduce-scatter
+            from .dcp import cp_lse_ag_out_rs
+            part = torch.empty_like(q[:n])
+            part, lse = PagedAttention.forward_decode_with_lse(
+                q[:n], key_cache, value_cache, attn_metadata.block_table,
+                attn_metadata.seq_lens, attn_metadata.max_seq_len, self.kv_cache_dtype,
+                self.num_kv_heads, self.scale, self.alibi_slopes, layer._k_scale, layer._v_scale,
+                output=part)
+            return cp_lse_ag_out_rs(part, lse, self.dcp_group)
         PagedAttention.forward_decode(
             q[:n], key_cache, value_cache, attn_metadata.block_table, attn_metadata.seq_lens,
             attn_metadata.max_seq_len, self.kv_cache_dtype, self.num_kv_heads, self.scale,

@@ -1,0 +1,150 @@
+// Log-sum-exp merges of partial attention results (sm_100a).
+//
+//  * merge_attn_states_kernel -- the job of the reference's merge_attn_states
+//    (csrc/attention/merge_attn_states.cu:14-89, launcher :131-170, schema
+//    csrc/torch_bindings.cpp:80-87): combine a "prefix" and a "suffix" partial
+//    attention output with their log-sum-exps (section 2.2 of arXiv 2501.01005),
+//        m = max(lse_p, lse_s);  w_p = e^(lse_p - m), w_s = e^(lse_s - m)
+//        out = (w_p out_p + w_s out_s) / (w_p + w_s);  lse = log(w_p + w_s) + m
+//    with +-inf lse treated as -inf (:45-46).  LSE tensors are [num_heads, num_tokens].
+//  * correct_attn_out_kernel -- the job of the reference's Triton
+//    _correct_attn_cp_out_kernel (vllm/attention/ops/common.py:9-68): decode context
+//    parallelism keeps a slice of every sequence's KV on each rank; after the LSEs
+//    of all ranks are all-gathered, each rank rescales its partial output by
+//    e^(lse_rank - lse_total) (in place) so that a plain sum over ranks (reduce-scatter)
+//    yields the exact attention output.  NaN / +inf LSEs count as -inf (:41, :62-64).
+//
+// Both are pure streaming kernels (HBM-bound, 16-byte accesses, no reuse).
+#include "common.cuh"
+
+namespace b200pa {
+
+namespace {
+
+constexpr int kMergeThreads = 128;
+
+__device__ __forceinline__ float lse_clean_inf(float v) { return isinf(v) ? -INFINITY : v; }
+
+// One thread per 16-byte pack of one (token, head) row.
+template <int ST>
+__global__ void __launch_bounds__(kMergeThreads)
+merge_attn_states_kernel(typename Scalar<ST>::type* __restrict__ output,
+                         float* __restrict__ output_lse,
+                         const typename Scalar<ST>::type* __restrict__ prefix_output,
+                         const float* __restrict__ prefix_lse,
+                         const typename Scalar<ST>::type* __restrict__ suffix_output,
+                         const float* __restrict__ suffix_lse, int64_t num_tokens,
+                         int num_heads, int packs_per_head) {
+  using T = typename Scalar<ST>::type;
+  constexpr int PACK = 16 / (int)sizeof(T);
+  const int64_t total = num_tokens * num_heads * packs_per_head;
+  for (int64_t idx = (int64_t)blockIdx.x * kMergeThreads + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * kMergeThreads) {
+    const int64_t row = idx / packs_per_head;       // token * num_heads + head
+    const int pack = (int)(idx - row * packs_per_head);
+    const int64_t token = row / num_heads;
+    const int head = (int)(row - token * num_heads);
+    float p_lse = lse_clean_inf(prefix_lse[(int64_t)head * num_tokens + token]);
+    float s_lse = lse_clean_inf(suffix_lse[(int64_t)head * num_tokens + token]);
+    const float max_lse = fmaxf(p_lse, s_lse);
+    p_lse -= max_lse;
+    s_lse -= max_lse;
+    const float p_se = expf(p_lse), s_se = expf(s_lse);
+    const float out_se = p_se + s_se;
+    const float p_scale = p_se / out_se, s_scale = s_se / out_se;
+    const int64_t off = row * packs_per_head + pack;  // in 16-byte units
+    const uint4 pp = reinterpret_cast<const uint4*>(prefix_output)[off];
+    const uint4 sp = reinterpret_cast<const uint4*>(suffix_output)[off];
+    uint4 op;
+    const T* pe = reinterpret_cast<const T*>(&pp);
+    const T* se = reinterpret_cast<const T*>(&sp);
+    T* oe = reinterpret_cast<T*>(&op);
+#pragma unroll
+    for (int i = 0; i < PACK; ++i)
+      oe[i] = Scalar<ST>::from_float(Scalar<ST>::to_float(pe[i]) * p_scale +
+                                     (Scalar<ST>::to_float(se[i]) * s_scale));
+    reinterpret_cast<uint4*>(output)[off] = op;
+    if (output_lse != nullptr && pack == 0)
+      output_lse[(int64_t)head * num_tokens + token] = logf(out_se) + max_lse;
+  }
+}
+
+__device__ __forceinline__ float lse_clean(float v) {
+  return (v != v || v == INFINITY) ? -INFINITY : v;
+}
+
+// One warp per (sequence, head): total LSE over ranks, then rescale the row in place.
+template <int ST>
+__global__ void __launch_bounds__(kMergeThreads)
+correct_attn_out_kernel(typename Scalar<ST>::type* __restrict__ out, float* __restrict__ lse_out,
+                        const float* __restrict__ lses, int num_ranks, int rank, int num_seqs,
+                        int num_heads, int head_size, int64_t out_seq_stride,
+                        int64_t out_head_stride, int64_t lses_rank_stride,
+                        int64_t lses_seq_stride, int64_t lses_head_stride) {
+  using T = typename Scalar<ST>::type;
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (int64_t)blockIdx.x * (kMergeThreads / 32) + (threadIdx.x >> 5);
+  if (warp >= (int64_t)num_seqs * num_heads) return;
+  const int64_t b = warp / num_heads;
+  const int h = (int)(warp - b * num_heads);
+  const float* l0 = lses + b * lses_seq_stride + h * lses_head_stride;
+  float mx = -INFINITY;
+  for (int n = lane; n < num_ranks; n += 32) mx = fmaxf(mx, lse_clean(l0[n * lses_rank_stride]));
+  mx = warp_max(mx);
+  float acc = 0.f;
+  for (int n = lane; n < num_ranks; n += 32) acc += expf(lse_clean(l0[n * lses_rank_stride]) - mx);
+  acc = warp_sum(acc);
+  const float lse = logf(acc) + mx;  // all ranks empty: -inf - -inf = NaN, as the reference
+  if (lane == 0) lse_out[b * lses_seq_stride + h * lses_head_stride] = lse;
+  const float factor = expf(lse_clean(l0[rank * lses_rank_stride] - lse));
+  T* row = out + b * out_seq_stride + h * out_head_stride;
+  for (int d = lane; d < head_size; d += 32)
+    row[d] = Scalar<ST>::from_float(Scalar<ST>::to_float(row[d]) * factor);
+}
+
+}  // namespace
+
+int launch_merge_attn_states(void* output, float* output_lse, const void* prefix_output,
+                             const float* prefix_lse, const void* suffix_output,
+                             const float* suffix_lse, int64_t num_tokens, int num_heads,
+                             int head_size, int scalar_type, cudaStream_t stream) {
+  const int pack = scalar_type == B200PA_F32 ? 4 : 8;
+  const int pph = head_size / pack;
+  const int64_t total = num_tokens * num_heads * pph;
+  const int64_t blocks = (total + kMergeThreads - 1) / kMergeThreads;
+  const dim3 grid((unsigned)(blocks < (1 << 20) ? blocks : (1 << 20))), block(kMergeThreads);
+#define MERGE_CALL(ST)                                                                      \
+  merge_attn_states_kernel<ST><<<grid, block, 0, stream>>>(                                 \
+      (typename Scalar<ST>::type*)output, output_lse,                                       \
+      (const typename Scalar<ST>::type*)prefix_output, prefix_lse,                          \
+      (const typename Scalar<ST>::type*)suffix_output, suffix_lse, num_tokens, num_heads, pph)
+  if (scalar_type == B200PA_BF16) MERGE_CALL(B200PA_BF16);
+  else if (scalar_type == B200PA_F16) MERGE_CALL(B200PA_F16);
+  else MERGE_CALL(B200PA_F32);
+#undef MERGE_CALL
+  count_launch();
+  return check_launch("merge_attn_states");
+}
+
+int launch_correct_attn_out(void* out, float* lse_out, const float* lses, int num_ranks, int rank,
+                            int num_seqs, int num_heads, int head_size, int64_t out_seq_stride,
+                            int64_t out_head_stride, int64_t lses_rank_stride,
+                            int64_t lses_seq_stride, int64_t lses_head_stride, int scalar_type,
+                            cudaStream_t stream) {
+  const int64_t warps = (int64_t)num_seqs * num_heads;
+  const int wpb = kMergeThreads / 32;
+  const dim3 grid((unsigned)((warps + wpb - 1) / wpb)), block(kMergeThreads);
+#define CORRECT_CALL(ST)                                                                    \
+  correct_attn_out_kernel<ST><<<grid, block, 0, stream>>>(                                  \
+      (typename Scalar<ST>::type*)out, lse_out, lses, num_ranks, rank, num_seqs, num_heads, \
+      head_size, out_seq_stride, out_head_stride, lses_rank_stride, lses_seq_stride,        \
+      lses_head_stride)
+  if (scalar_type == B200PA_BF16) CORRECT_CALL(B200PA_BF16);
+  else if (scalar_type == B200PA_F16) CORRECT_CALL(B200PA_F16);
+  else CORRECT_CALL(B200PA_F32);
+#undef CORRECT_CALL
+  count_launch();
+  return check_launch("correct_attn_out");
+}
+
+}  // namespace b200pa

@@ -336,8 +336,8 @@ int launch_reduce(void* out, const float* exp_sums, const float* max_logits, con
   return check_launch("paged_attention_v2 reduce");
 }
 
-int launch_generic(void* out, float* exp_sums, float* max_logits, void* tmp_out,
-                   const void* query, const void* key_cache, const void* value_cache,
+int launch_generic(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_head_stride,
+                   float* exp_sums, float* max_logits, void* tmp_out, const void* query, const void* key_cache, const void* value_cache,
                    int num_seqs, int num_heads, int num_kv_heads, int head_size, int block_size,
                    float scale, const int32_t* block_tables, int max_num_blocks_per_seq,
                    const int32_t* seq_lens, int max_seq_len, int max_num_partitions,
@@ -346,8 +346,9 @@ int launch_generic(void* out, float* exp_sums, float* max_logits, void* tmp_out,
                    const float* v_scale, BlockSparse bsp, bool partitioned,
                    cudaStream_t stream) {
 #define GEN_ARGS                                                                               \
-  out, exp_sums, max_logits, tmp_out, query, key_cache, value_cache, num_seqs, num_heads,      \
-      num_kv_heads, head_size, scale, block_tables, max_num_blocks_per_seq, seq_lens,          \
+  out, lse, lse_seq_stride, lse_head_stride, exp_sums, max_logits, tmp_out, query, key_cache, \
+      value_cache, num_seqs, num_heads, num_kv_heads,                                          \
+      head_size, scale, block_tables, max_num_blocks_per_seq, seq_lens,          \
       max_seq_len, max_num_partitions, alibi_slopes, q_stride, kv_block_stride,                \
       kv_head_stride, k_scale, v_scale, bsp, partitioned, stream
 #define GEN_BS(ST, KV)                                                                         \

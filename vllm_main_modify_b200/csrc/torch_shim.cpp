@@ -144,6 +144,108 @@ void paged_attention_v2(torch::Tensor& out, torch::Tensor& exp_sums, torch::Tens
       ws.defined() ? ws.numel() : 0, stream));
 }
 
+// Decode + log-sum-exp (b200pa namespace only; the reference has no such op -- it is what
+// AttentionImpl.can_return_lse_for_decode, abstract.py:115-138, asks of a backend).
+// lse: [num_seqs, num_heads] fp32, any strides.
+void paged_attention_lse(torch::Tensor& out, torch::Tensor& lse, torch::Tensor& query,
+                         torch::Tensor& key_cache, torch::Tensor& value_cache,
+                         int64_t num_kv_heads, double scale, torch::Tensor& block_tables,
+                         torch::Tensor& seq_lens, int64_t block_size, int64_t max_seq_len,
+                         const std::optional<torch::Tensor>& alibi_slopes,
+                         const std::string& kv_cache_dtype, torch::Tensor& k_scale,
+                         torch::Tensor& v_scale) {
+  check_cuda(query, "query");
+  const int kv = kv_code(kv_cache_dtype);
+  const int st = scalar_code(query.scalar_type());
+  check_cache_dtype(key_cache, query, kv, "key_cache");
+  TORCH_CHECK(block_tables.scalar_type() == at::ScalarType::Int, "block_tables must be int32");
+  TORCH_CHECK(seq_lens.scalar_type() == at::ScalarType::Int, "seq_lens must be int32");
+  TORCH_CHECK(lse.scalar_type() == at::ScalarType::Float && lse.dim() == 2 &&
+                  lse.size(0) == query.size(0) && lse.size(1) == query.size(1),
+              "lse must be float32 [num_seqs, num_heads]");
+  TORCH_CHECK(out.is_contiguous(), "out must be contiguous");
+  TORCH_CHECK(query.stride(2) == 1 && query.stride(1) == query.size(2),
+              "query heads must be densely packed");
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(query));
+  const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  const float* alibi = alibi_slopes ? reinterpret_cast<const float*>(alibi_slopes->data_ptr()) : nullptr;
+  const torch::Tensor ws = attention_workspace(query);
+  check_status(b200pa_paged_attention_lse(
+      out.data_ptr(), lse.data_ptr<float>(), lse.stride(0), lse.stride(1), query.data_ptr(),
+      key_cache.data_ptr(), value_cache.data_ptr(), (int)query.size(0), (int)query.size(1),
+      (int)num_kv_heads, (int)query.size(2), (int)block_size, (float)scale,
+      block_tables.data_ptr<int>(), (int)block_tables.size(1), seq_lens.data_ptr<int>(),
+      (int)max_seq_len, alibi, query.stride(0), key_cache.stride(0), key_cache.stride(1), st, kv,
+      reinterpret_cast<const float*>(k_scale.data_ptr()),
+      reinterpret_cast<const float*>(v_scale.data_ptr()), ws.defined() ? ws.data_ptr() : nullptr,
+      ws.defined() ? ws.numel() : 0, stream));
+}
+
+// csrc/attention/merge_attn_states.cu:131-180 of the reference (same checks, same messages)
+void merge_attn_states(torch::Tensor& output, std::optional<torch::Tensor> output_lse,
+                       const torch::Tensor& prefix_output, const torch::Tensor& prefix_lse,
+                       const torch::Tensor& suffix_output, const torch::Tensor& suffix_lse) {
+  check_cuda(output, "output");
+  const at::ScalarType t = output.scalar_type();
+  TORCH_CHECK(t == at::ScalarType::Float || t == at::ScalarType::Half ||
+                  t == at::ScalarType::BFloat16,
+              "Unsupported data type of O: ", t);
+  const int st = scalar_code(t);
+  const int64_t head_size = output.size(2);
+  const int64_t pack_size = 16 / output.element_size();
+  TORCH_CHECK(head_size % pack_size == 0, "headsize must be multiple of pack_size:", pack_size);
+  TORCH_CHECK(output.stride(-2) == head_size && output.stride(-1) == 1,
+              "output heads must be contiguous in memory");
+  TORCH_CHECK(prefix_output.stride(-2) == head_size && prefix_output.stride(-1) == 1,
+              "prefix_output heads must be contiguous in memory");
+  TORCH_CHECK(suffix_output.stride(-2) == head_size && suffix_output.stride(-1) == 1,
+              "suffix_output heads must be contiguous in memory");
+  // the kernel indexes [token, head] rows densely, as the reference kernel does (:37-38)
+  TORCH_CHECK(output.is_contiguous() && prefix_output.is_contiguous() &&
+                  suffix_output.is_contiguous() && prefix_lse.is_contiguous() &&
+                  suffix_lse.is_contiguous(),
+              "merge_attn_states works on contiguous tensors");
+  TORCH_CHECK(prefix_output.scalar_type() == t && suffix_output.scalar_type() == t,
+              "prefix_output / suffix_output dtype must match output");
+  TORCH_CHECK(prefix_lse.scalar_type() == at::ScalarType::Float &&
+                  suffix_lse.scalar_type() == at::ScalarType::Float,
+              "prefix_lse / suffix_lse must be float32");
+  float* out_lse = nullptr;
+  if (output_lse.has_value()) {
+    TORCH_CHECK(output_lse->scalar_type() == at::ScalarType::Float && output_lse->is_contiguous(),
+                "output_lse must be contiguous float32");
+    out_lse = output_lse->data_ptr<float>();
+  }
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(prefix_output));
+  const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  check_status(b200pa_merge_attn_states(
+      output.data_ptr(), out_lse, prefix_output.data_ptr(), prefix_lse.data_ptr<float>(),
+      suffix_output.data_ptr(), suffix_lse.data_ptr<float>(), output.size(0), (int)output.size(1),
+      (int)head_size, st, stream));
+}
+
+// vllm/attention/ops/common.py:86-116 of the reference: out [B,H,D] corrected IN PLACE with the
+// all-gathered lses [N,B,H]; returns the total lse (empty_like(lses[0])).
+torch::Tensor correct_attn_out(torch::Tensor& out, const torch::Tensor& lses, int64_t cp_rank) {
+  check_cuda(out, "out");
+  TORCH_CHECK(out.dim() == 3 && lses.dim() == 3 && lses.size(1) == out.size(0) &&
+                  lses.size(2) == out.size(1),
+              "correct_attn_out: out [B,H,D], lses [N,B,H]");
+  TORCH_CHECK(lses.scalar_type() == at::ScalarType::Float, "lses must be float32");
+  TORCH_CHECK(out.stride(2) == 1, "out head elements must be contiguous");
+  TORCH_CHECK(cp_rank >= 0 && cp_rank < lses.size(0), "cp_rank out of range");
+  const int st = scalar_code(out.scalar_type());
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(out));
+  const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  torch::Tensor lse = at::empty_strided({lses.size(1), lses.size(2)},
+                                        {lses.stride(1), lses.stride(2)}, lses.options());
+  check_status(b200pa_correct_attn_out(
+      out.data_ptr(), lse.data_ptr<float>(), lses.data_ptr<float>(), (int)lses.size(0),
+      (int)cp_rank, (int)out.size(0), (int)out.size(1), (int)out.size(2), out.stride(0),
+      out.stride(1), lses.stride(0), lses.stride(1), lses.stride(2), st, stream));
+  return lse;
+}
+
 void reshape_and_cache(torch::Tensor& key, torch::Tensor& value, torch::Tensor& key_cache,
                        torch::Tensor& value_cache, torch::Tensor& slot_mapping,
                        const std::string& kv_cache_dtype, torch::Tensor& k_scale,
@@ -237,6 +339,23 @@ constexpr const char* kSchemaV2 =
     "    int tp_rank, int blocksparse_local_blocks,"
     "    int blocksparse_vert_stride, int blocksparse_block_size,"
     "    int blocksparse_head_sliding_step) -> ()";
+constexpr const char* kSchemaMerge =
+    "merge_attn_states("
+    "    Tensor! output,"
+    "    Tensor!? output_lse,"
+    "    Tensor prefix_output,"
+    "    Tensor prefix_lse,"
+    "    Tensor suffix_output,"
+    "    Tensor suffix_lse) -> ()";
+constexpr const char* kSchemaLse =
+    "paged_attention_lse("
+    "    Tensor! out, Tensor! lse, Tensor query, Tensor key_cache,"
+    "    Tensor value_cache, int num_kv_heads, float scale,"
+    "    Tensor block_tables, Tensor seq_lens, int block_size,"
+    "    int max_seq_len, Tensor? alibi_slopes,"
+    "    str kv_cache_dtype, Tensor k_scale, Tensor v_scale) -> ()";
+constexpr const char* kSchemaCorrect =
+    "correct_attn_out(Tensor! out, Tensor lses, int cp_rank) -> Tensor";
 constexpr const char* kSchemaReshape =
     "reshape_and_cache(Tensor key, Tensor value,"
     "                  Tensor! key_cache, Tensor! value_cache,"
@@ -260,6 +379,14 @@ void define_attention(torch::Library& ops) {
   ops.impl("paged_attention_v1", torch::kCUDA, &paged_attention_v1);
   ops.def(kSchemaV2);
   ops.impl("paged_attention_v2", torch::kCUDA, &paged_attention_v2);
+  ops.def(kSchemaMerge);
+  ops.impl("merge_attn_states", torch::kCUDA, &merge_attn_states);
+}
+void define_extras(torch::Library& ops) {
+  ops.def(kSchemaLse);
+  ops.impl("paged_attention_lse", torch::kCUDA, &paged_attention_lse);
+  ops.def(kSchemaCorrect);
+  ops.impl("correct_attn_out", torch::kCUDA, &correct_attn_out);
 }
 void define_cache(torch::Library& ops) {
   ops.def(kSchemaReshape);
@@ -282,6 +409,7 @@ std::vector<std::unique_ptr<torch::Library>> g_vllm_libs;
 
 TORCH_LIBRARY(b200pa, ops) {
   define_attention(ops);
+  define_extras(ops);
   define_cache(ops);
   define_utils(ops);
 }

@@ -115,3 +115,31 @@ class PagedAttention:
                 blocksparse_vert_stride, blocksparse_block_size,
                 blocksparse_head_sliding_step)
         return output
+
+    @staticmethod
+    def forward_decode_with_lse(
+        query: torch.Tensor,
+        key_cache: torch.Tensor,
+        value_cache: torch.Tensor,
+        block_tables: torch.Tensor,
+        seq_lens: torch.Tensor,
+        max_seq_len: int,
+        kv_cache_dtype: str,
+        num_kv_heads: int,
+        scale: float,
+        alibi_slopes: Optional[torch.Tensor],
+        k_scale: torch.Tensor,
+        v_scale: torch.Tensor,
+        output: Optional[torch.Tensor] = None,
+        lse: Optional[torch.Tensor] = None,
+    ) -> Tuple[torch.Tensor, torch.Tensor]:
+        """Decode + softmax log-sum-exp ``[num_seqs, num_heads]`` fp32 (no reference twin: it is
+        what ``AttentionImpl.can_return_lse_for_decode``, ``abstract.py:115-138``, asks for)."""
+        if output is None:
+            output = torch.empty_like(query)
+        if lse is None:
+            lse = torch.empty(query.shape[:2], dtype=torch.float32, device=query.device)
+        ops.paged_attention_lse(output, lse, query, key_cache, value_cache, num_kv_heads, scale,
+                                block_tables, seq_lens, value_cache.shape[3], max_seq_len,
+                                alibi_slopes, kv_cache_dtype, k_scale, v_scale)
+        return output, lse

@@ -18,6 +18,9 @@ import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
+# A/B runs on one box: B200PA_PKG_ROOT=<dir holding another built copy of the package>
+if os.environ.get("B200PA_PKG_ROOT"):
+    sys.path.insert(0, os.environ["B200PA_PKG_ROOT"])
 
 import bench  # noqa: E402
 
@@ -101,6 +104,7 @@ def main():
             line = {"config": cfg, "tp": args.tp,
                     "impl": "reference_cuda" if args.ref_cuda else args.impl,
                     "tune": os.environ.get("B200PA_STREAM_TUNE", "0"), "op": name,
+                    "build": os.environ.get("B200PA_AB_LABEL", "tree"),
                     "ms_median": round(med, 4),
                     "ms_best": round(best, 4)}
             if name != "reshape_and_cache":

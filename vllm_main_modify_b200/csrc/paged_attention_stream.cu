@@ -14,13 +14,18 @@
 //    Ragged batches need no host-side knowledge of seq_lens: each warp derives its span from
 //    seq_lens on the device (CUDA-graph replays with new lengths just work).
 //  * Each warp is an independent worker: its own TMA ring, mbarriers, query fragments and
-//    accumulators.  There is no CTA-wide barrier in the kernel.  When a span crosses into
+//    accumulators.  There is no CTA-wide barrier in the main loop.  When a span crosses into
 //    another (sequence, kv head) the warp finishes the piece it was on and carries on; the TMA
 //    producer side runs STAGES ahead across such boundaries, so the pipe never drains.
 //    A piece that covers its whole (sequence, kv head) is normalised and written straight to
 //    `out`.  A warp has at most two pieces that do not (its first and its last): their
-//    unnormalised fp32 accumulators + (max, sum) go to workspace slots 2w / 2w+1, and
-//    paged_attention_stream_merge_kernel -- one warp per span boundary -- merges them.
+//    unnormalised fp32 accumulators + (max, sum) go to workspace slots 2w / 2w+1.  At the end of
+//    the kernel -- the only CTA-wide barrier -- each CTA merges the pieces of its own warps:
+//    items that begin and end inside the CTA are finished there, and what is cut by a CTA
+//    boundary (at most two runs per CTA) goes to the CTA's slots.  Only those reach
+//    paged_attention_stream_merge_kernel (one small CTA per boundary between main-kernel CTAs;
+//    ncu showed the per-warp-boundary version instruction-bound at 13-23 us,
+//    profiles/r01_small_shard_launches.csv).
 //  * LOADS.  For one (page, kv head) the x-packed K sub-block [D/x][16][x] and the V sub-block
 //    [D][16] are each one contiguous run (2 KiB fp8 / 4 KiB 16-bit at D=128): one 1-D TMA bulk
 //    copy each, completing on the stage's mbarrier.  Block-table entries are fetched 32 at a
@@ -153,6 +158,7 @@ struct StreamParams {
   int h_tiles;                                         // ceil(group / 8)
   int max_num_blocks_per_seq;
   int num_workers;                                     // gridDim.x * NW of the main kernel
+  int nw;                                              // NW: warps per CTA of the main kernel
   float scale;
 };
 
@@ -293,7 +299,13 @@ paged_attention_stream_kernel(const StreamParams p) {
   // let the merge kernel's CTAs be scheduled as soon as SM resources free up; they block in
   // griddepcontrol.wait until this grid has completed and flushed
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-  if (w >= W) return;  // nothing for this warp (there is no CTA-wide sync anywhere below)
+  // what this warp leaves for the in-CTA merge: bit 0 head piece (slot 2w, continues an earlier
+  // worker's item), bit 1 the head piece reaches the item's end, bit 2 tail piece (slot 2w+1,
+  // from the item's start, continued by a later worker)
+  __shared__ int meta_s[NW][5];   // flags, head (b, vh), tail (b, vh)
+  __shared__ float hdr_s[2 * NW][16];  // per piece (2i head, 2i+1 tail): m[8] (log2), l[8]
+  int mflags = 0, mh_b = 0, mh_vh = 0, mt_b = 0, mt_vh = 0;
+  if (w < W) {  // idle warps (fewer stages than warps) go straight to the barrier
   const long long u0 = (w * Ttot) / W, u1 = ((w + 1) * Ttot) / W;
 
   Cursor pc;  // producer cursor; the consumer gets a copy
@@ -476,16 +488,19 @@ paged_attention_stream_kernel(const StreamParams p) {
     } else {
       // slot 2w: my first piece, continuing an earlier worker's; slot 2w+1: my last piece,
       // continued by a later worker
+      if (from_start) { mflags |= 4; mt_b = cc.b; mt_vh = cc.vh; }
+      else { mflags |= to_end ? 3 : 1; mh_b = cc.b; mh_vh = cc.vh; }
       float* slot = p.ws + (size_t)(2 * w + (from_start ? 1 : 0)) * slot_floats(D);
 #pragma unroll
       for (int mt = 0; mt < MT; ++mt)
         reinterpret_cast<float4*>(slot)[mt * 32 + lane] = make_float4(
             o[mt][0] * out_scale, o[mt][1] * out_scale, o[mt][2] * out_scale, o[mt][3] * out_scale);
       if (r == 0) {
+        float* hdr = hdr_s[2 * warp + (from_start ? 1 : 0)];
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-          slot[8 * D + 2 * q4 + h] = msub[h];
-          slot[8 * D + 8 + 2 * q4 + h] = lsum[h];
+          hdr[2 * q4 + h] = msub[h];
+          hdr[8 + 2 * q4 + h] = lsum[h];
         }
       }
     }
@@ -664,33 +679,154 @@ paged_attention_stream_kernel(const StreamParams p) {
     __syncwarp();
     if (producing) produce();
   }
+  }  // w < W
+
+  // ---------------------------------------------------------------- in-CTA merge
+  // Pieces in worker order: index 2i (head of warp i), 2i+1 (tail of warp i).  A run = the
+  // consecutive pieces of one (sequence, head tile).  Every warp walks the same runs (metadata in
+  // shared memory, so all branches are warp-uniform); run j is summed by warp j % NW, pieces in
+  // index order (deterministic), two pieces' loads in flight at a time.  The (m, l) headers come
+  // from shared memory, so the only global round trip is the one for the O fragments.  A run that
+  // starts at the item's start and reaches its end is final; one that continues an earlier CTA's
+  // item goes to CTA slot 2c, one that is continued by a later CTA to 2c+1 (same convention as
+  // the warp slots).
+  if (lane == 0) {
+    meta_s[warp][0] = mflags;
+    meta_s[warp][1] = mh_b; meta_s[warp][2] = mh_vh;
+    meta_s[warp][3] = mt_b; meta_s[warp][4] = mt_vh;
+  }
+  __syncthreads();   // also orders the warps' global slot stores before the loads below
+  {
+    constexpr int SF = slot_floats(D);
+    const float* const my_slots = p.ws + (size_t)2 * ((size_t)blockIdx.x * NW) * SF;
+    float* const cta_slots = p.ws + ((size_t)2 * p.num_workers + (size_t)2 * blockIdx.x) * SF;
+    uint32_t pmask = 0;
+#pragma unroll
+    for (int i = 0; i < NW; ++i) {
+      const int f = meta_s[i][0];
+      pmask |= (uint32_t)(f & 1) << (2 * i);
+      pmask |= (uint32_t)((f >> 2) & 1) << (2 * i + 1);
+    }
+    int run = 0;
+    auto emit = [&](int ps, int pe, bool closed) {
+      if ((run++ % NW) != warp) return;
+      const bool from_start = ps & 1;
+      const uint32_t mk = pmask & (0xffffffffu >> (31 - pe)) & (0xffffffffu << ps);
+      float mx0 = -INFINITY, mx1 = -INFINITY;
+      for (uint32_t t = mk; t; t &= t - 1) {
+        const float* h = hdr_s[__ffs(t) - 1];
+        mx0 = fmaxf(mx0, h[2 * q4]);
+        mx1 = fmaxf(mx1, h[2 * q4 + 1]);
+      }
+      float4 acc[MT];
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt) acc[mt] = make_float4(0.f, 0.f, 0.f, 0.f);
+      float l0 = 0.f, l1 = 0.f;
+      for (uint32_t t = mk; t;) {
+        const int pa = __ffs(t) - 1;
+        t &= t - 1;
+        const bool two = t != 0;
+        const int pb = two ? __ffs(t) - 1 : pa;
+        t &= t - 1;   // (0 & anything stays 0)
+        const float4* sa = reinterpret_cast<const float4*>(my_slots + (size_t)pa * SF);
+        const float4* sb = reinterpret_cast<const float4*>(my_slots + (size_t)pb * SF);
+        float4 va[MT], vb[MT];
+#pragma unroll
+        for (int mt = 0; mt < MT; ++mt) va[mt] = sa[mt * 32 + lane];
+        if (two) {
+#pragma unroll
+          for (int mt = 0; mt < MT; ++mt) vb[mt] = sb[mt * 32 + lane];
+        }
+        const float* ha = hdr_s[pa];
+        const float fa0 = ex2(ha[2 * q4] - mx0), fa1 = ex2(ha[2 * q4 + 1] - mx1);
+        l0 += ha[8 + 2 * q4] * fa0;
+        l1 += ha[8 + 2 * q4 + 1] * fa1;
+#pragma unroll
+        for (int mt = 0; mt < MT; ++mt) {
+          acc[mt].x += va[mt].x * fa0; acc[mt].y += va[mt].y * fa1;
+          acc[mt].z += va[mt].z * fa0; acc[mt].w += va[mt].w * fa1;
+        }
+        if (two) {
+          const float* hb = hdr_s[pb];
+          const float fb0 = ex2(hb[2 * q4] - mx0), fb1 = ex2(hb[2 * q4 + 1] - mx1);
+          l0 += hb[8 + 2 * q4] * fb0;
+          l1 += hb[8 + 2 * q4 + 1] * fb1;
+#pragma unroll
+          for (int mt = 0; mt < MT; ++mt) {
+            acc[mt].x += vb[mt].x * fb0; acc[mt].y += vb[mt].y * fb1;
+            acc[mt].z += vb[mt].z * fb0; acc[mt].w += vb[mt].w * fb1;
+          }
+        }
+      }
+      if (closed && from_start) {
+        const int b = meta_s[ps >> 1][3], vh = meta_s[ps >> 1][4];
+        const int kvh = vh / p.h_tiles, tile = vh - kvh * p.h_tiles;
+        const int hd0 = kvh * p.group + tile * 8, hv = min(8, p.group - tile * 8);
+        const float inv0 = __fdividef(1.f, l0 + 1e-6f), inv1 = __fdividef(1.f, l1 + 1e-6f);
+        T* dst = reinterpret_cast<T*>(p.out) + ((int64_t)b * p.num_heads + hd0) * D;
+#pragma unroll
+        for (int mt = 0; mt < MT; ++mt) {
+          const float o4[4] = {acc[mt].x, acc[mt].y, acc[mt].z, acc[mt].w};
+          store_out_tile<ST, D>(dst, mt, o4, inv0, inv1, hv, r, q4);
+        }
+        if (p.lse != nullptr && r == 0) {
+          if (2 * q4 < hv)
+            p.lse[b * p.lse_seq_stride + (hd0 + 2 * q4) * p.lse_head_stride] =
+                (mx0 + __log2f(l0)) * kLn2;
+          if (2 * q4 + 1 < hv)
+            p.lse[b * p.lse_seq_stride + (hd0 + 2 * q4 + 1) * p.lse_head_stride] =
+                (mx1 + __log2f(l1)) * kLn2;
+        }
+      } else {
+        float* dst = cta_slots + (from_start ? SF : 0);
+#pragma unroll
+        for (int mt = 0; mt < MT; ++mt) reinterpret_cast<float4*>(dst)[mt * 32 + lane] = acc[mt];
+        if (r == 0) {
+          *reinterpret_cast<float2*>(dst + 8 * D + 2 * q4) = make_float2(mx0, mx1);
+          *reinterpret_cast<float2*>(dst + 8 * D + 8 + 2 * q4) = make_float2(l0, l1);
+        }
+      }
+    };
+    int ps = -1;
+#pragma unroll 1
+    for (int i = 0; i < NW; ++i) {
+      const int f = meta_s[i][0];
+      if (f & 1) {
+        if (ps < 0) ps = 2 * i;
+        if (f & 2) { emit(ps, 2 * i, true); ps = -1; }
+      }
+      if (f & 4) ps = 2 * i + 1;
+    }
+    if (ps >= 0) emit(ps, 2 * NW - 1, false);
+  }
 }
 
 // ---------------------------------------------------------------------------------------
-// Merge of the pieces of every (sequence, head tile) that a span boundary cut (the job of the
-// reference's paged_attention_v2_reduce_kernel, attention_kernels.cuh:560-664: weights
-// l_j * exp(m_j - m), 1e-6 in the denominator).  One CTA per boundary between workers w-1 | w.
-// The CTA that owns the FIRST boundary inside a (sequence, head tile) merges all its pieces:
-// slot 2(w-1)+1 (the tail piece of the worker that holds the start) and slots 2w' of every
-// later worker whose span starts inside it.  Pieces are dealt round-robin to the CTA's warps
-// (a 131072-token sequence of one kv head is ~90 pieces on a B200; a lone one ~1200), each warp
-// accumulates whole slots with 16-byte loads, and the warps' sums meet in shared memory in a
-// fixed order (deterministic).  Launched with programmatic stream serialisation: everything up
-// to griddepcontrol.wait overlaps the tail of the main kernel.
-constexpr int kMergeWarps = 8;
+// Merge of the pieces of every (sequence, head tile) that a boundary between two CTAs of the
+// main kernel cut (the job of the reference's paged_attention_v2_reduce_kernel,
+// attention_kernels.cuh:560-664: weights l_j * exp(m_j - m), 1e-6 in the denominator).  The main
+// kernel has already merged inside each CTA, so a "worker" here is a main-kernel CTA c with span
+// [cta_begin(c), cta_begin(c+1)) and CTA slots 2c (continues an earlier CTA's item) / 2c+1
+// (continued by a later CTA).  One CTA per boundary c-1 | c; the CTA that owns the FIRST boundary
+// inside an item merges all its pieces: slot 2(c-1)+1 and slots 2c' of every later CTA whose span
+// starts inside the item (2-3 pieces typically, ~150 for a lone 131072-token sequence on one kv
+// head).  Pieces are dealt round-robin to the warps, which accumulate whole slots with 16-byte
+// loads and meet in shared memory in a fixed order (deterministic).  The CTA is small enough
+// (4 warps, 16.6 KiB) to become resident beside a main-kernel CTA: launched with programmatic
+// stream serialisation, everything up to griddepcontrol.wait overlaps the main kernel.
+constexpr int kMergeWarps = 4;
 
 template <int ST, int D, int PPS>
 __global__ void __launch_bounds__(32 * kMergeWarps)
 paged_attention_stream_merge_kernel(const StreamParams p) {
   using T = typename Scalar<ST>::type;
   constexpr int MT = D / 16;
-  static_assert(MT <= kMergeWarps, "one warp per m-tile in the final step");
   __shared__ float4 acc_s[kMergeWarps][MT][32];
   __shared__ float lsum_s[kMergeWarps][8];
   const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
   const int r = lane >> 2, q4 = lane & 3;
   const int vheads = p.num_kv_heads * p.h_tiles;
-  const long long w = (long long)blockIdx.x + 1;
+  const long long c = (long long)blockIdx.x + 1;
   // empty sequences: the reference's v1 kernel yields zeros (no keys, zero accumulators)
   for (long long b = blockIdx.x; b < p.num_seqs; b += gridDim.x) {
     if (p.seq_lens[b] <= 0) {
@@ -704,18 +840,22 @@ paged_attention_stream_merge_kernel(const StreamParams p) {
   }
   const long long Ttot = total_stages<PPS>(p.seq_lens, p.num_seqs, lane) * vheads;
   const long long W = min((long long)p.num_workers, Ttot);
-  if (w >= W) return;
-  const long long s = (w * Ttot) / W;              // first stage of worker w
+  const long long NW = p.nw;
+  if (c * NW >= W) return;                         // main-kernel CTA c had no work
+  // first stage of main-kernel CTA x (its first warp is worker x * NW)
+  auto cta_begin = [&](long long x) { return (min(x * NW, W) * Ttot) / W; };
+  const long long s = cta_begin(c);
   const Loc loc = locate_stage<PPS>(p.seq_lens, p.num_seqs, vheads, s, lane);
   if (loc.st == 0) return;                         // the boundary is not inside a (seq, head)
   const long long item_begin = s - loc.st, item_end = item_begin + loc.ns;
-  if (((w - 1) * Ttot) / W > item_begin) return;   // an earlier boundary owns this one
-  // pieces: workers w-1 .. w_last (the worker that holds the last stage of the item)
-  const long long w_last = min(W - 1, (item_end * W - 1) / Ttot);
-  const int n = (int)(w_last - (w - 1)) + 1;
+  if (cta_begin(c - 1) > item_begin) return;       // an earlier boundary owns this one
+  // pieces: CTAs c-1 .. c_last (the CTA of the worker that holds the last stage of the item)
+  const long long c_last = min(W - 1, (item_end * W - 1) / Ttot) / NW;
+  const int n = (int)(c_last - (c - 1)) + 1;
   const size_t SF = slot_floats(D);
-  // piece k: slot 2(w-1)+1 for k = 0, else 2(w-1+k)
-  auto slot_of = [&](int k) { return p.ws + (size_t)(2 * (w - 1 + k) + (k == 0 ? 1 : 0)) * SF; };
+  const float* const cta_slots = p.ws + (size_t)2 * p.num_workers * SF;
+  // piece k: slot 2(c-1)+1 for k = 0, else 2(c-1+k)
+  auto slot_of = [&](int k) { return cta_slots + (size_t)(2 * (c - 1 + k) + (k == 0 ? 1 : 0)) * SF; };
 
   asm volatile("griddepcontrol.wait;" ::: "memory");  // the main kernel's stores are visible
 
@@ -739,7 +879,7 @@ paged_attention_stream_merge_kernel(const StreamParams p) {
     if (h == 2 * q4) mx[0] = mx8[h];
     if (h == 2 * q4 + 1) mx[1] = mx8[h];
   }
-  // pass 2: warp wv sums pieces wv, wv + 8, ... (whole slots)
+  // pass 2: warp wv sums pieces wv, wv + kMergeWarps, ... (whole slots)
   float4 acc[MT];
 #pragma unroll
   for (int mt = 0; mt < MT; ++mt) acc[mt] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -768,15 +908,10 @@ paged_attention_stream_merge_kernel(const StreamParams p) {
     lsum_s[wv][2 * q4 + 1] = lsum[1];
   }
   __syncthreads();
-  if (wv >= MT) return;
-  // final: warp mt adds the warps' sums of its m-tile in warp order
-  const int mt = wv;
-  float o[4] = {0.f, 0.f, 0.f, 0.f};
+  // final: warp wv adds the warps' sums of m-tiles wv, wv + kMergeWarps, ... in warp order
   float lt[2] = {0.f, 0.f};
 #pragma unroll
   for (int g = 0; g < kMergeWarps; ++g) {
-    const float4 v = acc_s[g][mt][lane];
-    o[0] += v.x; o[1] += v.y; o[2] += v.z; o[3] += v.w;
     lt[0] += lsum_s[g][2 * q4];
     lt[1] += lsum_s[g][2 * q4 + 1];
   }
@@ -786,9 +921,17 @@ paged_attention_stream_merge_kernel(const StreamParams p) {
   const int heads_valid = min(8, p.group - tile * 8);
   const float inv0 = __fdividef(1.f, lt[0] + 1e-6f);
   const float inv1 = __fdividef(1.f, lt[1] + 1e-6f);
-  store_out_tile<ST, D>(reinterpret_cast<T*>(p.out) + ((int64_t)loc.b * p.num_heads + head0) * D,
-                        mt, o, inv0, inv1, heads_valid, r, q4);
-  if (p.lse != nullptr && mt == 0 && r == 0) {
+  for (int mt = wv; mt < MT; mt += kMergeWarps) {
+    float o[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int g = 0; g < kMergeWarps; ++g) {
+      const float4 v = acc_s[g][mt][lane];
+      o[0] += v.x; o[1] += v.y; o[2] += v.z; o[3] += v.w;
+    }
+    store_out_tile<ST, D>(reinterpret_cast<T*>(p.out) + ((int64_t)loc.b * p.num_heads + head0) * D,
+                          mt, o, inv0, inv1, heads_valid, r, q4);
+  }
+  if (p.lse != nullptr && wv == 0 && r == 0) {
 #pragma unroll
     for (int h = 0; h < 2; ++h)
       if (2 * q4 + h < heads_valid)
@@ -817,7 +960,9 @@ int launch_stream_t(StreamParams& p, int num_sms, int64_t workspace_bytes, cudaS
   }
   const int ctas = num_sms * ctas_per_sm;
   p.num_workers = ctas * NW;
-  const int64_t need = (int64_t)2 * p.num_workers * slot_floats(D) * (int64_t)sizeof(float);
+  p.nw = NW;
+  // 2 slots per warp (pieces) + 2 per CTA (what the in-CTA merge leaves for the merge kernel)
+  const int64_t need = (int64_t)2 * (p.num_workers + ctas) * slot_floats(D) * (int64_t)sizeof(float);
   if (workspace_bytes < need)
     return set_error(B200PA_ERR_INVALID, "workspace too small: %lld bytes, need %lld "
                      "(b200pa_paged_attention_workspace_bytes)", (long long)workspace_bytes,
@@ -826,9 +971,9 @@ int launch_stream_t(StreamParams& p, int num_sms, int64_t workspace_bytes, cudaS
   count_launch();
   int rc = check_launch("paged_attention (stream)");
   if (rc) return rc;
-  if (p.num_workers > 1) {
+  if (ctas > 1) {
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(p.num_workers - 1);   // boundaries 1 .. num_workers-1
+    cfg.gridDim = dim3(ctas - 1);            // boundaries between main-kernel CTAs c-1 | c
     cfg.blockDim = dim3(32 * kMergeWarps);
     cfg.dynamicSmemBytes = 0;
     cfg.stream = stream;
@@ -849,7 +994,8 @@ int launch_stream_t(StreamParams& p, int num_sms, int64_t workspace_bytes, cudaS
 
 // Upper bound of the workspace any stream launch on a device with `num_sms` SMs needs.
 int64_t stream_workspace_bytes(int num_sms, int head_size) {
-  return (int64_t)2 * num_sms * kMaxWarpsPerSm * slot_floats(head_size) *
+  // warps per SM + (at most 4) CTAs per SM, two slots each
+  return (int64_t)2 * num_sms * (kMaxWarpsPerSm + 4) * slot_floats(head_size) *
          (int64_t)sizeof(float);
 }
 
@@ -908,6 +1054,7 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
   p.h_tiles = (p.group + 7) / 8;
   p.max_num_blocks_per_seq = max_num_blocks_per_seq;
   p.num_workers = 0;
+  p.nw = 0;
   p.scale = scale;
   const bool fp8 = kv_dtype == B200PA_KV_FP8_E4M3;
   // <ST, FP8, D, NW, STAGES, PPS, MINB>: fp8 stage = PPS x 4 KiB, 16-bit stage = PPS x 8 KiB (D=128)

@@ -18,6 +18,11 @@
  *   b200pa_get_max_shared_memory_per_block_device_attribute
  *                                   csrc/cuda_utils_kernels.cu (schema
  *                                   csrc/torch_bindings.cpp:718-730)
+ *   b200pa_swap_blocks              csrc/cache_kernels.cu:27-70   (schema torch_bindings.cpp:652-654)
+ *   b200pa_copy_blocks              csrc/cache_kernels.cu:125-172 (kernel :74-101; schema :657-660)
+ *   b200pa_gather_and_maybe_dequant_cache
+ *                                   csrc/cache_kernels.cu:734-782 (kernel :628-712; schema :703-710)
+ *   b200pa_cp_gather_cache          csrc/cache_kernels.cu:865-926 (kernel :785-849; schema :712-715)
  *   b200pa_merge_attn_states        csrc/attention/merge_attn_states.cu:172-180
  *                                   (launcher :131-170; schema csrc/torch_bindings.cpp:80-87)
  *   b200pa_correct_attn_out         vllm/attention/ops/common.py:86-116 (Triton kernel :9-68)
@@ -53,7 +58,7 @@
 extern "C" {
 #endif
 
-#define B200PA_ABI_VERSION 3
+#define B200PA_ABI_VERSION 4
 
 /* scalar_t of query / out / key / value (reference: VLLM_DISPATCH_FLOATING_TYPES) */
 enum { B200PA_F32 = 0, B200PA_F16 = 1, B200PA_BF16 = 2 };
@@ -182,6 +187,59 @@ int b200pa_correct_attn_out(
     int num_heads, int head_size, int64_t out_seq_stride, int64_t out_head_stride,
     int64_t lses_rank_stride, int64_t lses_seq_stride, int64_t lses_head_stride,
     int scalar_type, void* stream);
+
+/*
+ * Block management on the same caches (the reference's _C_cache_ops.swap_blocks / copy_blocks /
+ * gather_and_maybe_dequant_cache / cp_gather_cache).
+ */
+enum { B200PA_COPY_D2D = 0, B200PA_COPY_D2H = 1, B200PA_COPY_H2D = 2 };
+
+/*
+ * For every pair (s, d) of block_mapping (HOST memory, [num_pairs][2] int64, as the reference
+ * requires a CPU tensor): copy block_bytes bytes from src + s*block_bytes to dst + d*block_bytes,
+ * asynchronously on `stream` (cudaMemcpyAsync; block_bytes = element_size * src.stride(0), padding
+ * included).  Runs of consecutive (s+1, d+1) pairs are issued as one copy.
+ */
+int b200pa_swap_blocks(const void* src, void* dst, int64_t block_bytes,
+                       const int64_t* block_mapping_host, int64_t num_pairs, int direction,
+                       void* stream);
+
+/*
+ * key_cache_ptrs / value_cache_ptrs: HOST arrays of num_layers DEVICE pointers; block_mapping:
+ * DEVICE [num_pairs][2] int64.  In every layer, block s of the key cache is copied onto block d of
+ * the key cache, same for the value cache; block_bytes = numel of one block * element size (the
+ * reference's numel_per_block, no padding).  No allocation and no host synchronisation (the
+ * reference uploads the pointer arrays with a blocking copy).
+ */
+int b200pa_copy_blocks(void* const* key_cache_ptrs, void* const* value_cache_ptrs, int num_layers,
+                       const int64_t* block_mapping, int num_pairs, int64_t block_bytes,
+                       void* stream);
+
+/*
+ * src_cache [num_blocks, block_size, entry...] cache_t by strides (elements), dst [tot_tokens,
+ * entry_size] scalar_t (row stride dst_entry_stride), block_table [batch, *] int32 (row stride
+ * block_table_stride), cu_seq_lens [batch + 1] int32, seq_starts [batch] int32 or NULL
+ * (seq_starts[b] / block_size whole blocks are skipped at the front of row b), scale: device fp32
+ * (read for fp8 caches only).  kv_dtype auto: cache_t == scalar_t, plain gather; fp8: bytes ->
+ * scalar_t(float(half(fp8)) * scale).  tot_tokens (dst rows; only used to size the grid -- the
+ * kernel reads the true total from cu_seq_lens[batch]).
+ */
+int b200pa_gather_and_maybe_dequant_cache(
+    const void* src_cache, void* dst, const int32_t* block_table, const int32_t* cu_seq_lens,
+    int batch_size, int block_size, int entry_size, int64_t block_table_stride,
+    int64_t cache_block_stride, int64_t cache_entry_stride, int64_t dst_entry_stride,
+    int scalar_type, int kv_dtype, const float* scale, const int32_t* seq_starts,
+    int64_t tot_tokens, void* stream);
+
+/*
+ * Same gather without conversion for elements of element_bytes in {1, 2, 4}; seq_starts counts
+ * TOKENS and need not be a multiple of block_size.
+ */
+int b200pa_cp_gather_cache(
+    const void* src_cache, void* dst, const int32_t* block_table, const int32_t* cu_seq_lens,
+    int batch_size, int block_size, int entry_size, int64_t block_table_stride,
+    int64_t cache_block_stride, int64_t cache_entry_stride, int64_t dst_entry_stride,
+    int element_bytes, const int32_t* seq_starts, int64_t tot_tokens, void* stream);
 
 /*
  * key, value [num_tokens, num_heads, head_size] scalar_t, row strides key_stride /

@@ -162,3 +162,38 @@ def convert_fp8(output: torch.Tensor,
 def get_max_shared_memory_per_block_device_attribute(device: int) -> int:
     """vllm/_custom_ops.py ``get_max_shared_memory_per_block_device_attribute``."""
     return _ops.get_max_shared_memory_per_block_device_attribute(device)
+
+
+def copy_blocks(key_caches: "list[torch.Tensor]", value_caches: "list[torch.Tensor]",
+                block_mapping: torch.Tensor) -> None:
+    """``vllm/_custom_ops.py:1634-1637``; ``block_mapping`` [num_pairs, 2] int64 on the GPU."""
+    _ops.copy_blocks(key_caches, value_caches, block_mapping)
+
+
+def swap_blocks(src: torch.Tensor, dst: torch.Tensor, block_mapping: torch.Tensor) -> None:
+    """``vllm/_custom_ops.py:1645-1647``; ``block_mapping`` [num_pairs, 2] int64 on the CPU;
+    src / dst: GPU<->GPU (same device), GPU->CPU or CPU->GPU."""
+    _ops.swap_blocks(src, dst, block_mapping)
+
+
+def gather_and_maybe_dequant_cache(src_cache: torch.Tensor,
+                                   dst: torch.Tensor,
+                                   block_table: torch.Tensor,
+                                   cu_seq_lens: torch.Tensor,
+                                   batch_size: int,
+                                   kv_cache_dtype: str,
+                                   scale: torch.Tensor,
+                                   seq_starts: Optional[torch.Tensor] = None) -> None:
+    """``vllm/_custom_ops.py:1657-1668``."""
+    _ops.gather_and_maybe_dequant_cache(src_cache, dst, block_table, cu_seq_lens, batch_size,
+                                        kv_cache_dtype, scale, seq_starts)
+
+
+def cp_gather_cache(src_cache: torch.Tensor,
+                    dst: torch.Tensor,
+                    block_table: torch.Tensor,
+                    cu_seq_lens: torch.Tensor,
+                    batch_size: int,
+                    seq_starts: Optional[torch.Tensor] = None) -> None:
+    """``vllm/_custom_ops.py:1671-1678``."""
+    _ops.cp_gather_cache(src_cache, dst, block_table, cu_seq_lens, batch_size, seq_starts)

@@ -29,7 +29,7 @@ NVCC = os.path.join(CUDA_HOME, "bin", "nvcc")
 HOST_CXX = "/usr/bin/g++"
 
 CU_SOURCES = ["c_abi.cu", "cache_kernels.cu", "paged_attention_generic.cu",
-              "paged_attention_stream.cu", "merge_attn_states.cu"]
+              "paged_attention_stream.cu", "merge_attn_states.cu", "block_ops.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
               "-Xcompiler", "-fPIC", "-ccbin", HOST_CXX, "--expt-relaxed-constexpr",
               "-Xptxas", "-v", "-Wno-deprecated-gpu-targets"]

@@ -39,6 +39,14 @@ int launch_merge_attn_states(void*, float*, const void*, const float*, const voi
 int launch_correct_attn_out(void*, float*, const float*, int, int, int, int, int, int64_t, int64_t,
                             int64_t, int64_t, int64_t, int, cudaStream_t);
 
+int launch_copy_blocks(void* const*, void* const*, int, const int64_t*, int, int64_t, cudaStream_t);
+int launch_gather_cache(const void*, void*, const int32_t*, const int32_t*, int, int, int, int64_t,
+                        int64_t, int64_t, int64_t, int, int, const float*, const int32_t*, int64_t,
+                        int, cudaStream_t);
+int launch_cp_gather_cache(const void*, void*, const int32_t*, const int32_t*, int, int, int,
+                           int64_t, int64_t, int64_t, int64_t, int, const int32_t*, int64_t, int,
+                           cudaStream_t);
+
 static thread_local char g_err[512] = "";
 static std::atomic<int> g_impl{B200PA_IMPL_AUTO};
 static std::atomic<uint64_t> g_launches{0};
@@ -355,6 +363,107 @@ int b200pa_convert_fp8(void* dst, const void* src, int64_t num_elements, float s
     return set_error(B200PA_ERR_UNSUPPORTED, "Unsupported input type of kv cache: %d", scalar_type);
   return launch_convert_fp8(dst, src, num_elements, scale, scalar_type, kv_dtype, to_fp8,
                             reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200pa_swap_blocks(const void* src, void* dst, int64_t block_bytes,
+                       const int64_t* block_mapping_host, int64_t num_pairs, int direction,
+                       void* stream) {
+  if (num_pairs < 0 || block_bytes < 0) return set_error(B200PA_ERR_INVALID, "swap_blocks: negative size");
+  if (num_pairs == 0 || block_bytes == 0) return B200PA_OK;
+  if (!src || !dst || !block_mapping_host)
+    return set_error(B200PA_ERR_INVALID, "swap_blocks: null pointer");
+  cudaMemcpyKind kind;
+  switch (direction) {
+    case B200PA_COPY_D2D: kind = cudaMemcpyDeviceToDevice; break;
+    case B200PA_COPY_D2H: kind = cudaMemcpyDeviceToHost; break;
+    case B200PA_COPY_H2D: kind = cudaMemcpyHostToDevice; break;
+    default: return set_error(B200PA_ERR_INVALID, "Invalid device combination");
+  }
+  const char* s = static_cast<const char*>(src);
+  char* d = static_cast<char*>(dst);
+  int64_t i = 0;
+  while (i < num_pairs) {
+    // one copy per run of consecutive (src + 1, dst + 1) pairs
+    const int64_t s0 = block_mapping_host[2 * i], d0 = block_mapping_host[2 * i + 1];
+    int64_t n = 1;
+    while (i + n < num_pairs && block_mapping_host[2 * (i + n)] == s0 + n &&
+           block_mapping_host[2 * (i + n) + 1] == d0 + n)
+      ++n;
+    const cudaError_t e = cudaMemcpyAsync(d + d0 * block_bytes, s + s0 * block_bytes,
+                                          (size_t)(n * block_bytes), kind,
+                                          reinterpret_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) {
+      (void)cudaGetLastError();
+      return set_error(B200PA_ERR_CUDA, "swap_blocks: cudaMemcpyAsync: %s", cudaGetErrorString(e));
+    }
+    i += n;
+  }
+  return B200PA_OK;
+}
+
+int b200pa_copy_blocks(void* const* key_cache_ptrs, void* const* value_cache_ptrs, int num_layers,
+                       const int64_t* block_mapping, int num_pairs, int64_t block_bytes,
+                       void* stream) {
+  if (num_layers < 0 || num_pairs < 0 || block_bytes < 0)
+    return set_error(B200PA_ERR_INVALID, "copy_blocks: negative size");
+  if (num_layers == 0 || num_pairs == 0 || block_bytes == 0) return B200PA_OK;
+  if (!key_cache_ptrs || !value_cache_ptrs || !block_mapping)
+    return set_error(B200PA_ERR_INVALID, "copy_blocks: null pointer");
+  for (int l = 0; l < num_layers; ++l)
+    if (!key_cache_ptrs[l] || !value_cache_ptrs[l])
+      return set_error(B200PA_ERR_INVALID, "copy_blocks: null cache pointer in layer %d", l);
+  return launch_copy_blocks(key_cache_ptrs, value_cache_ptrs, num_layers, block_mapping, num_pairs,
+                            block_bytes, reinterpret_cast<cudaStream_t>(stream));
+}
+
+static int check_gather_args(const char* op, const void* src_cache, void* dst,
+                             const int32_t* block_table, const int32_t* cu_seq_lens,
+                             int batch_size, int block_size, int entry_size) {
+  if (batch_size < 0) return set_error(B200PA_ERR_INVALID, "%s: negative batch_size", op);
+  if (block_size <= 0 || entry_size <= 0) return set_error(B200PA_ERR_INVALID, "%s: bad shape", op);
+  if (!cu_seq_lens) return set_error(B200PA_ERR_INVALID, "%s: null cu_seq_lens", op);
+  if (batch_size > 0 && (!src_cache || !dst || !block_table))
+    return set_error(B200PA_ERR_INVALID, "%s: null tensor pointer", op);
+  return B200PA_OK;
+}
+
+int b200pa_gather_and_maybe_dequant_cache(
+    const void* src_cache, void* dst, const int32_t* block_table, const int32_t* cu_seq_lens,
+    int batch_size, int block_size, int entry_size, int64_t block_table_stride,
+    int64_t cache_block_stride, int64_t cache_entry_stride, int64_t dst_entry_stride,
+    int scalar_type, int kv_dtype, const float* scale, const int32_t* seq_starts,
+    int64_t tot_tokens, void* stream) {
+  int rc = check_gather_args("gather_and_maybe_dequant_cache", src_cache, dst, block_table,
+                             cu_seq_lens, batch_size, block_size, entry_size);
+  if (rc) return rc;
+  if (scalar_type != B200PA_F32 && scalar_type != B200PA_F16 && scalar_type != B200PA_BF16)
+    return set_error(B200PA_ERR_UNSUPPORTED, "Unsupported input type of kv cache: %d", scalar_type);
+  if (kv_dtype != B200PA_KV_AUTO && kv_dtype != B200PA_KV_FP8_E4M3 && kv_dtype != B200PA_KV_FP8_E5M2)
+    return set_error(B200PA_ERR_UNSUPPORTED, "Unsupported data type of kv cache: %d", kv_dtype);
+  if (kv_dtype != B200PA_KV_AUTO && !scale)
+    return set_error(B200PA_ERR_INVALID, "gather_and_maybe_dequant_cache: fp8 cache needs scale");
+  if (batch_size == 0 || tot_tokens == 0) return B200PA_OK;
+  return launch_gather_cache(src_cache, dst, block_table, cu_seq_lens, batch_size, block_size,
+                             entry_size, block_table_stride, cache_block_stride, cache_entry_stride,
+                             dst_entry_stride, scalar_type, kv_dtype, scale, seq_starts, tot_tokens,
+                             num_sms(), reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200pa_cp_gather_cache(
+    const void* src_cache, void* dst, const int32_t* block_table, const int32_t* cu_seq_lens,
+    int batch_size, int block_size, int entry_size, int64_t block_table_stride,
+    int64_t cache_block_stride, int64_t cache_entry_stride, int64_t dst_entry_stride,
+    int element_bytes, const int32_t* seq_starts, int64_t tot_tokens, void* stream) {
+  int rc = check_gather_args("cp_gather_cache", src_cache, dst, block_table, cu_seq_lens,
+                             batch_size, block_size, entry_size);
+  if (rc) return rc;
+  if (element_bytes != 1 && element_bytes != 2 && element_bytes != 4)
+    return set_error(B200PA_ERR_UNSUPPORTED, "Unsupported data type width: %d", element_bytes * 8);
+  if (batch_size == 0 || tot_tokens == 0) return B200PA_OK;
+  return launch_cp_gather_cache(src_cache, dst, block_table, cu_seq_lens, batch_size, block_size,
+                                entry_size, block_table_stride, cache_block_stride,
+                                cache_entry_stride, dst_entry_stride, element_bytes, seq_starts,
+                                tot_tokens, num_sms(), reinterpret_cast<cudaStream_t>(stream));
 }
 
 int b200pa_get_max_shared_memory_per_block_device_attribute(int device_id, int64_t* value) {

@@ -312,6 +312,128 @@ void convert_fp8(torch::Tensor& dst_cache, torch::Tensor& src_cache, const doubl
                                   (float)scale, st, kv, to_fp8 ? 1 : 0, stream));
 }
 
+// csrc/cache_kernels.cu:27-70 of the reference: same device rules, same messages; block_mapping
+// must be a CPU tensor [num_pairs, 2] int64.
+void swap_blocks(torch::Tensor& src, torch::Tensor& dst, const torch::Tensor& block_mapping) {
+  const torch::Device sd = src.device(), dd = dst.device();
+  int direction;
+  if (sd.is_cuda() && dd.is_cuda()) {
+    TORCH_CHECK(sd.index() == dd.index(), "src and dst must be on the same GPU");
+    direction = B200PA_COPY_D2D;
+  } else if (sd.is_cuda() && dd.is_cpu()) {
+    direction = B200PA_COPY_D2H;
+  } else if (sd.is_cpu() && dd.is_cuda()) {
+    direction = B200PA_COPY_H2D;
+  } else {
+    TORCH_CHECK(false, "Invalid device combination");
+  }
+  TORCH_CHECK(block_mapping.device().is_cpu(), "block_mapping must be on CPU");
+  TORCH_CHECK(block_mapping.scalar_type() == at::ScalarType::Long && block_mapping.dim() == 2 &&
+                  block_mapping.size(1) == 2,
+              "block_mapping must be int64 [num_pairs, 2]");
+  const torch::Tensor map = block_mapping.contiguous();
+  const int64_t block_bytes = src.element_size() * src.stride(0);
+  const at::cuda::OptionalCUDAGuard device_guard(sd.is_cuda() ? sd : dd);
+  const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  check_status(b200pa_swap_blocks(src.data_ptr(), dst.data_ptr(), block_bytes,
+                                  map.data_ptr<int64_t>(), map.size(0), direction, stream));
+}
+
+// csrc/cache_kernels.cu:125-172 of the reference (block_mapping on the device, [num_pairs, 2])
+void copy_blocks(std::vector<torch::Tensor> const& key_caches,
+                 std::vector<torch::Tensor> const& value_caches,
+                 const torch::Tensor& block_mapping) {
+  const int num_layers = (int)key_caches.size();
+  TORCH_CHECK(num_layers == (int)value_caches.size());
+  if (num_layers == 0) return;
+  const torch::Device dev = key_caches[0].device();
+  TORCH_CHECK(dev.is_cuda());
+  TORCH_CHECK(block_mapping.is_cuda() && block_mapping.scalar_type() == at::ScalarType::Long &&
+                  block_mapping.is_contiguous(),
+              "block_mapping must be a contiguous int64 tensor on the GPU");
+  std::vector<void*> kp(num_layers), vp(num_layers);
+  for (int l = 0; l < num_layers; ++l) {
+    kp[l] = key_caches[l].data_ptr();
+    vp[l] = value_caches[l].data_ptr();
+  }
+  const int64_t block_bytes = key_caches[0][0].numel() * key_caches[0].element_size();
+  const at::cuda::OptionalCUDAGuard device_guard(dev);
+  const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  check_status(b200pa_copy_blocks(kp.data(), vp.data(), num_layers,
+                                  block_mapping.data_ptr<int64_t>(), (int)block_mapping.size(0),
+                                  block_bytes, stream));
+}
+
+static void check_gather_tensors(torch::Tensor const& src_cache, torch::Tensor const& dst,
+                                 torch::Tensor const& block_table,
+                                 torch::Tensor const& cu_seq_lens,
+                                 const std::optional<torch::Tensor>& seq_starts) {
+  // csrc/cache_kernels.cu:748-768 / :879-899 of the reference
+  TORCH_CHECK(block_table.dtype() == torch::kInt32, "block_table must be int32");
+  TORCH_CHECK(cu_seq_lens.dtype() == torch::kInt32, "cu_seq_lens must be int32");
+  if (seq_starts.has_value()) {
+    TORCH_CHECK(seq_starts.value().dtype() == torch::kInt32, "seq_starts must be int32");
+  }
+  TORCH_CHECK(src_cache.device() == dst.device(), "src_cache and dst must be on the same device");
+  TORCH_CHECK(src_cache.device() == block_table.device(),
+              "src_cache and block_table must be on the same device");
+  TORCH_CHECK(src_cache.device() == cu_seq_lens.device(),
+              "src_cache and cu_seq_lens must be on the same device");
+  if (seq_starts.has_value()) {
+    TORCH_CHECK(src_cache.device() == seq_starts.value().device(),
+                "src_cache and seq_starts must be on the same device");
+  }
+  TORCH_CHECK(src_cache.is_cuda(), "src_cache must be on a GPU (this package has no CPU path)");
+  TORCH_CHECK(block_table.stride(-1) == 1 && cu_seq_lens.is_contiguous(),
+              "block_table rows and cu_seq_lens must be dense");
+}
+
+void gather_and_maybe_dequant_cache(torch::Tensor const& src_cache, torch::Tensor const& dst,
+                                    torch::Tensor const& block_table,
+                                    torch::Tensor const& cu_seq_lens, int64_t batch_size,
+                                    const std::string& kv_cache_dtype, torch::Tensor const& scale,
+                                    std::optional<torch::Tensor> seq_starts) {
+  check_gather_tensors(src_cache, dst, block_table, cu_seq_lens, seq_starts);
+  const int kv = kv_code(kv_cache_dtype);
+  const int st = scalar_code(dst.scalar_type());
+  if (kv == B200PA_KV_AUTO) {
+    TORCH_CHECK(src_cache.scalar_type() == dst.scalar_type(),
+                "kv_cache_dtype \"auto\": src_cache and dst must have the same dtype");
+  } else {
+    TORCH_CHECK(src_cache.element_size() == 1, "fp8 kv cache must be a 1-byte tensor");
+  }
+  const int64_t entry_size = src_cache.flatten(2, -1).size(2);
+  TORCH_CHECK(src_cache.dim() == 3 || src_cache.flatten(2, -1).stride(2) == 1,
+              "cache entries must be dense");
+  at::cuda::OptionalCUDAGuard device_guard(src_cache.device());
+  const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  check_status(b200pa_gather_and_maybe_dequant_cache(
+      src_cache.data_ptr(), dst.data_ptr(), block_table.data_ptr<int32_t>(),
+      cu_seq_lens.data_ptr<int32_t>(), (int)batch_size, (int)src_cache.size(1), (int)entry_size,
+      block_table.stride(0), src_cache.stride(0), src_cache.stride(1), dst.stride(0), st, kv,
+      reinterpret_cast<const float*>(scale.data_ptr()),
+      seq_starts.has_value() ? seq_starts.value().data_ptr<int32_t>() : nullptr, dst.size(0),
+      stream));
+}
+
+void cp_gather_cache(torch::Tensor const& src_cache, torch::Tensor const& dst,
+                     torch::Tensor const& block_table, torch::Tensor const& cu_seq_lens,
+                     int64_t batch_size, std::optional<torch::Tensor> seq_starts) {
+  check_gather_tensors(src_cache, dst, block_table, cu_seq_lens, seq_starts);
+  TORCH_CHECK(src_cache.dtype() == dst.dtype(), "src_cache and dst must have the same dtype");
+  const int eb = (int)src_cache.element_size();
+  TORCH_CHECK(eb == 1 || eb == 2 || eb == 4, "Unsupported data type width: ", eb * 8);
+  const int64_t entry_size = src_cache.flatten(2, -1).size(2);
+  at::cuda::OptionalCUDAGuard device_guard(src_cache.device());
+  const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  check_status(b200pa_cp_gather_cache(
+      src_cache.data_ptr(), dst.data_ptr(), block_table.data_ptr<int32_t>(),
+      cu_seq_lens.data_ptr<int32_t>(), (int)batch_size, (int)src_cache.size(1), (int)entry_size,
+      block_table.stride(0), src_cache.stride(0), src_cache.stride(1), dst.stride(0), eb,
+      seq_starts.has_value() ? seq_starts.value().data_ptr<int32_t>() : nullptr, dst.size(0),
+      stream));
+}
+
 int64_t get_max_shared_memory_per_block_device_attribute(int64_t device_id) {
   int64_t v = 0;
   check_status(b200pa_get_max_shared_memory_per_block_device_attribute((int)device_id, &v));
@@ -389,6 +511,21 @@ void define_extras(torch::Library& ops) {
   ops.impl("correct_attn_out", torch::kCUDA, &correct_attn_out);
 }
 void define_cache(torch::Library& ops) {
+  // csrc/torch_bindings.cpp:652-660, 703-715 of the reference
+  ops.def("swap_blocks(Tensor src, Tensor! dst, Tensor block_mapping) -> ()");
+  ops.impl("swap_blocks", torch::kCUDA, &swap_blocks);
+  ops.def("copy_blocks(Tensor(a!)[] key_caches, Tensor[](b!) value_caches, "
+          "Tensor block_mapping) -> ()");
+  ops.impl("copy_blocks", torch::kCUDA, &copy_blocks);
+  ops.def("gather_and_maybe_dequant_cache(Tensor src_cache, Tensor! dst, "
+          "                               Tensor block_table, Tensor cu_seq_lens, "
+          "                               int batch_size, "
+          "                               str kv_cache_dtype, "
+          "                               Tensor scale, Tensor? seq_starts) -> ()");
+  ops.impl("gather_and_maybe_dequant_cache", torch::kCUDA, &gather_and_maybe_dequant_cache);
+  ops.def("cp_gather_cache(Tensor src_cache, Tensor! dst, Tensor block_table, "
+          "Tensor cu_seq_lens, int batch_size, Tensor? seq_starts) -> ()");
+  ops.impl("cp_gather_cache", torch::kCUDA, &cp_gather_cache);
   ops.def(kSchemaReshape);
   ops.impl("reshape_and_cache", torch::kCUDA, &reshape_and_cache);
   ops.def(kSchemaReshapeFlash);

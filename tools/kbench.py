@@ -39,7 +39,9 @@ def time_op(fn, iters, flush=None):
         b.record()
         evs.append((a, b))
     torch.cuda.synchronize()
-    ts = sorted(a.elapsed_time(b) for a, b in evs)
+    series = [a.elapsed_time(b) for a, b in evs]
+    ts = sorted(series)
+    time_op.last_series = series
     return ts[len(ts) // 2], ts[0]
 
 
@@ -50,6 +52,7 @@ def main():
     ap.add_argument("--tp", type=int, default=1, help="emulate rank 0 of a tp-way KV-head shard")
     ap.add_argument("--impl", type=int, default=0, help="b200pa_set_impl value (0 auto)")
     ap.add_argument("--ops", default="v1,v2,reshape_and_cache")
+    ap.add_argument("--series", action="store_true", help="also print the per-launch times in order")
     ap.add_argument("--ref-cuda", action="store_true",
                     help="time the reference's own CUDA kernels (oracle/_ref/libvllm_ref_cuda.so) "
                          "on the same tensors instead of this repo's")
@@ -95,9 +98,14 @@ def main():
         def wr():
             ops.reshape_and_cache(w["k_new"], w["v_new"], kc, vc, w["slots"], kv, w["ks"], w["vs"])
 
-        for name, fn in (("v1", v1), ("v2", v2), ("reshape_and_cache", wr)):
-            if name not in args.ops.split(","):
-                continue
+        def step():      # one decode step of one layer: write the new token, then attend
+            wr()
+            v2()
+
+        fns = {"v1": v1, "v2": v2, "reshape_and_cache": wr, "step": step}
+        # ops run in the order given (repeats allowed: "v2,step,v2" separates op from order effects)
+        for name in args.ops.split(","):
+            fn = fns[name]
             if args.ref_cuda and name == "v1" and w["max_len"] * 4 > 200 * 1024:
                 continue   # the reference's v1 keeps max_seq_len fp32 logits in shared memory
             med, best = time_op(fn, args.iters, fl)
@@ -112,6 +120,8 @@ def main():
                 line.update(kv_gib=round(nbytes / 2**30, 3), gbs=round(gbs, 1),
                             frac_measured=round(gbs / peak, 4), pct_8tb=round(gbs / 80.0, 2),
                             heuristic_v1=PagedAttention.use_v1(w["max_len"], B, w["H"]))
+            if args.series:
+                line["series_us"] = [round(t * 1e3, 1) for t in time_op.last_series]
             print(json.dumps(line), flush=True)
         del w, kc, vc, tmp, es, ml, out
         torch.cuda.empty_cache()

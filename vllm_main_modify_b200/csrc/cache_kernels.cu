@@ -40,6 +40,10 @@ __global__ void reshape_and_cache_kernel(
     int block_size, int x, const float* __restrict__ k_scale,
     const float* __restrict__ v_scale) {
   using T = typename Scalar<ST>::type;
+  // programmatic dependent launch: a decode kernel queued behind this one (launched with
+  // programmatic stream serialisation) may be scheduled now; it blocks in griddepcontrol.wait
+  // until this grid has completed and its stores are visible.  A no-op for any other successor.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int64_t token = blockIdx.x;
   const int64_t slot = slot_mapping[token];
   if (slot < 0) return;  // padding token
@@ -119,6 +123,10 @@ __global__ void reshape_and_cache_flash_kernel(
     const float* __restrict__ v_scale) {
   using T = typename Scalar<ST>::type;
   using C = typename std::conditional<KV == B200PA_KV_AUTO, T, uint8_t>::type;
+  // programmatic dependent launch: a decode kernel queued behind this one (launched with
+  // programmatic stream serialisation) may be scheduled now; it blocks in griddepcontrol.wait
+  // until this grid has completed and its stores are visible.  A no-op for any other successor.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int64_t token = blockIdx.x;
   const int64_t slot = slot_mapping[token];
   if (slot < 0) return;

@@ -292,6 +292,12 @@ paged_attention_stream_kernel(const StreamParams p) {
   const int r = lane >> 2, q4 = lane & 3;
   const int vheads = p.num_kv_heads * p.h_tiles;
 
+  // Launched with programmatic stream serialisation: this CTA may have been scheduled while the
+  // previous kernel of the stream (typically reshape_and_cache writing this step's token) was
+  // still running.  Nothing produced by earlier kernels -- seq_lens, q, the cache -- is read
+  // before this wait; what overlaps is the launch itself.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+
   // ---------------------------------------------------------------- my span
   const long long Ttot = total_stages<PPS>(p.seq_lens, p.num_seqs, lane) * vheads;
   const long long W = min((long long)p.num_workers, Ttot);
@@ -967,7 +973,21 @@ int launch_stream_t(StreamParams& p, int num_sms, int64_t workspace_bytes, cudaS
     return set_error(B200PA_ERR_INVALID, "workspace too small: %lld bytes, need %lld "
                      "(b200pa_paged_attention_workspace_bytes)", (long long)workspace_bytes,
                      (long long)need);
-  kern<<<dim3(ctas), dim3(NW * 32), SMEM, stream>>>(p);
+  {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(ctas);
+    cfg.blockDim = dim3(NW * 32);
+    cfg.dynamicSmemBytes = SMEM;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, p);
+    if (e != cudaSuccess)
+      return set_error(B200PA_ERR_CUDA, "stream kernel launch: %s", cudaGetErrorString(e));
+  }
   count_launch();
   int rc = check_launch("paged_attention (stream)");
   if (rc) return rc;

@@ -229,8 +229,19 @@ def run_ours(args):
     launches0 = _native.launch_count()
     barrier()
     ev0.record()
+    fused = not args.unfused
+    impl.fused_decode_step = fused
     for i in range(K):
         # the step, with events around the attention op (the dominant kernel)
+        if fused:
+            # one launch: the decode kernel also quantises + stores the new token (decode_step)
+            a_ev[i][0].record()
+            PagedAttention.write_and_decode(w["q"], w["k_new"], w["v_new"], key_cache, value_cache,
+                                            w["slots"], w["bt"], w["sl"], w["max_len"], kv,
+                                            w["Hkv"], w["scale"], None, w["ks"], w["vs"],
+                                            output=out.view(B, w["H"], D))
+            a_ev[i][1].record()
+            continue
         PagedAttention.write_to_paged_cache(w["k_new"], w["v_new"], key_cache, value_cache,
                                             w["slots"], kv, w["ks"], w["vs"])
         a_ev[i][0].record()
@@ -337,7 +348,10 @@ def run_ours(args):
             else "bf16 KV/q/out, f32 accumulate", "data": "synthetic",
             "config": {"workload": f"{cfg}: {desc}", "tp": world, "batch": B,
                        "kv_bytes_total": int(total_bytes),
-                       "step": "reshape_and_cache (new token K/V) + paged_attention_v2",
+                       "step": ("decode_step: new token K/V quantised + stored and the whole "
+                                "context attended in one launch (= reshape_and_cache + "
+                                "paged_attention)") if fused else
+                               "reshape_and_cache (new token K/V) + paged_attention_v2",
                        "l2": "inputs larger than L2: KV read per GPU per step = "
                              f"{int(total_bytes / world) >> 20} MiB vs 126 MB L2; no flush"},
             "tokens_per_s": round(B / (ms_step * 1e-3), 1),
@@ -353,7 +367,8 @@ def run_ours(args):
             "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak,
                          "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic,
                          "kernel": "paged_attention_stream_kernel (+ its merge launch; CUDA "
-                                   "events around the paged_attention_v2 op, in-loop)",
+                                   "events around the attention op, in-loop"
+                                   + ("; includes the fused cache write)" if fused else ")"),
                          "kernel_ms": round(attn_ms, 4), "peak_source": peak_src,
                          "bytes": "sum(seq_len) * Hkv_local * D * 2 (K,V) * sizeof(cache_t)"},
             "clocks": clocks,
@@ -504,6 +519,8 @@ def main():
     ap.add_argument("--config", default="cfg4", choices=sorted(CONFIGS))
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--unfused", action="store_true",
+                    help="step = reshape_and_cache + paged_attention_v2 as two ops (A/B)")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     args = ap.parse_args()
     if args.impl == "reference":

@@ -58,7 +58,7 @@
 extern "C" {
 #endif
 
-#define B200PA_ABI_VERSION 4
+#define B200PA_ABI_VERSION 5
 
 /* scalar_t of query / out / key / value (reference: VLLM_DISPATCH_FLOATING_TYPES) */
 enum { B200PA_F32 = 0, B200PA_F16 = 1, B200PA_BF16 = 2 };
@@ -158,6 +158,34 @@ int b200pa_paged_attention_v2(
 int b200pa_paged_attention_lse(
     void* out, float* lse, int64_t lse_seq_stride, int64_t lse_head_stride,
     const void* query, const void* key_cache, const void* value_cache,
+    int num_seqs, int num_heads, int num_kv_heads, int head_size, int block_size,
+    float scale, const int32_t* block_tables, int max_num_blocks_per_seq,
+    const int32_t* seq_lens, int max_seq_len, const float* alibi_slopes,
+    int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
+    int scalar_type, int kv_dtype, const float* k_scale, const float* v_scale,
+    void* workspace, int64_t workspace_bytes, void* stream);
+
+/*
+ * One decode step of one attention layer in ONE launch: the effect of
+ *   b200pa_reshape_and_cache(key, value, key_cache, value_cache, slot_mapping, num_tokens = num_seqs)
+ * followed by b200pa_paged_attention_v1 (and the lse store of b200pa_paged_attention_lse when
+ * lse != NULL), i.e. PagedAttention.write_to_paged_cache + forward_decode of the reference
+ * (vllm/attention/ops/paged_attn.py:73-92, 94-198) for a pure decode batch.
+ *   key, value [num_seqs, num_kv_heads, head_size] scalar_t, row strides key_stride /
+ *   value_stride; slot_mapping[num_seqs] int64 (< 0: token neither stored nor patched in).
+ * PRECONDITION (what a decode batch is): token b is position seq_lens[b] - 1 of sequence b, so
+ * slot_mapping[b] == block_tables[b][(seq_lens[b]-1) / block_size] * block_size +
+ * (seq_lens[b]-1) % block_size, and seq_lens[b] >= 1.  The kv cache must be dense.
+ * Where the stream kernel serves the shape (and key/value rows are 16-byte aligned) the warp
+ * that reaches the end of a (sequence, kv head) takes the new token from key/value, quantised
+ * exactly as reshape_and_cache does, and stores it to the cache; otherwise the two kernels are
+ * launched back to back.  The resulting cache bytes and attention output are the same as those
+ * of the two separate calls.
+ */
+int b200pa_decode_step(
+    void* out, float* lse, int64_t lse_seq_stride, int64_t lse_head_stride, const void* query,
+    const void* key, const void* value, int64_t key_stride, int64_t value_stride,
+    const int64_t* slot_mapping, void* key_cache, void* value_cache,
     int num_seqs, int num_heads, int num_kv_heads, int head_size, int block_size,
     float scale, const int32_t* block_tables, int max_num_blocks_per_seq,
     const int32_t* seq_lens, int max_seq_len, const float* alibi_slopes,

@@ -102,7 +102,12 @@ def main():
             wr()
             v2()
 
-        fns = {"v1": v1, "v2": v2, "reshape_and_cache": wr, "step": step}
+        def fstep():     # the same step in one launch (not available from the reference)
+            ops.decode_step(out, None, w["q"], w["k_new"], w["v_new"], kc, vc, w["slots"], w["Hkv"],
+                            w["scale"], w["bt"], w["sl"], bench.BS, w["max_len"], None, kv,
+                            w["ks"], w["vs"])
+
+        fns = {"v1": v1, "v2": v2, "reshape_and_cache": wr, "step": step, "fstep": fstep}
         # ops run in the order given (repeats allowed: "v2,step,v2" separates op from order effects)
         for name in args.ops.split(","):
             fn = fns[name]

@@ -115,6 +115,37 @@ def paged_attention_lse(
         kv_cache_dtype, k_scale, v_scale)
 
 
+def decode_step(
+    out: torch.Tensor,
+    lse: Optional[torch.Tensor],
+    query: torch.Tensor,
+    key: torch.Tensor,
+    value: torch.Tensor,
+    key_cache: torch.Tensor,
+    value_cache: torch.Tensor,
+    slot_mapping: torch.Tensor,
+    num_kv_heads: int,
+    scale: float,
+    block_tables: torch.Tensor,
+    seq_lens: torch.Tensor,
+    block_size: int,
+    max_seq_len: int,
+    alibi_slopes: Optional[torch.Tensor],
+    kv_cache_dtype: str,
+    k_scale: torch.Tensor,
+    v_scale: torch.Tensor,
+) -> None:
+    """``reshape_and_cache`` of one new token per sequence + ``paged_attention_v1`` (+ ``lse``
+    when given) in ONE launch: what ``PagedAttention.write_to_paged_cache`` followed by
+    ``forward_decode`` (``paged_attn.py:73-198``) do for a pure decode batch.  Token ``b`` must be
+    position ``seq_lens[b] - 1`` of sequence ``b`` (``slot_mapping[b]`` its slot).  Same cache
+    bytes and same output as the two ops; no twin in the reference's ``_custom_ops``."""
+    _ops.decode_step(
+        out, lse, query, key, value, key_cache, value_cache, slot_mapping, num_kv_heads, scale,
+        block_tables, seq_lens, block_size, max_seq_len, alibi_slopes, kv_cache_dtype,
+        k_scale, v_scale)
+
+
 def correct_attn_out(out: torch.Tensor, lses: torch.Tensor, cp_rank: int,
                      ctx=None) -> "tuple[torch.Tensor, torch.Tensor]":
     """``vllm/attention/ops/common.py:86-116`` (``ctx`` is the reference's Triton cache, unused):

@@ -17,6 +17,8 @@ backends do (``cpu_attn.py:584-612``) -- see SURVEY.md section 8(f) row 1.
 """
 from __future__ import annotations
 
+import os
+
 from dataclasses import dataclass
 from typing import Any, List, Optional, Tuple, Type
 
@@ -103,6 +105,9 @@ class B200PagedAttentionImpl:
     dcp_world_size: int = 1
     dcp_rank: int = 0
     dcp_group: Any = None             # torch.distributed group of the DCP ranks
+    # pure decode batches: cache write + attention in one launch (ops.decode_step);
+    # B200PA_FUSED_STEP=0 keeps the reference's two calls (A/B runs)
+    fused_decode_step: bool = os.environ.get("B200PA_FUSED_STEP", "1") != "0"
 
     def __init__(
         self,
@@ -167,15 +172,29 @@ class B200PagedAttentionImpl:
         out = output.view(-1, self.num_heads, self.head_size)
         key_cache, value_cache = PagedAttention.split_kv_cache(kv_cache, self.num_kv_heads,
                                                                self.head_size)
+        if self.alibi_slopes is not None and self.alibi_slopes.device != q.device:
+            self.alibi_slopes = self.alibi_slopes.to(q.device)
+        want_lse = self.need_to_return_lse_for_decode or self.dcp_world_size > 1
+        k = v = None
         if key is not None and value is not None:
             k = key.view(-1, self.num_kv_heads, self.head_size)
             v = value.view(-1, self.num_kv_heads, self.head_size)
+        # pure decode batch, one new token per sequence: cache write + attention in one launch
+        fused = (k is not None and self.fused_decode_step and not want_lse
+                 and k.shape[0] == n and attn_metadata.slot_mapping.numel() == n
+                 and attn_metadata.seq_lens.shape[0] == n)
+        if fused:
+            PagedAttention.write_and_decode(
+                q[:n], k, v, key_cache, value_cache, attn_metadata.slot_mapping,
+                attn_metadata.block_table, attn_metadata.seq_lens, attn_metadata.max_seq_len,
+                self.kv_cache_dtype, self.num_kv_heads, self.scale, self.alibi_slopes,
+                layer._k_scale, layer._v_scale, output=out[:n])
+            return output
+        if k is not None:
             PagedAttention.write_to_paged_cache(k, v, key_cache, value_cache,
                                                 attn_metadata.slot_mapping, self.kv_cache_dtype,
                                                 layer._k_scale, layer._v_scale)
-        if self.alibi_slopes is not None and self.alibi_slopes.device != q.device:
-            self.alibi_slopes = self.alibi_slopes.to(q.device)
-        if self.need_to_return_lse_for_decode or self.dcp_world_size > 1:
+        if want_lse:
             # decode context parallelism: this rank's KV slice with ALL query heads, then the
             # reference's cp_lse_ag_out_rs (common.py:119-140): gather LSEs, rescale, reduce-scatter
             from .dcp import cp_lse_ag_out_rs

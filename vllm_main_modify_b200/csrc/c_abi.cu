@@ -32,7 +32,9 @@ bool stream_supported(const void*, const void*, const void*, int, int, int, int,
                       int64_t, int, int, int);
 int launch_stream(void*, float*, int64_t, int64_t, void*, int64_t, const void*, const void*, const void*, int, int, int, int,
                   float, const int32_t*, int, const int32_t*, const float*, int64_t, int64_t,
-                  int64_t, int, int, const float*, const float*, int, int, cudaStream_t);
+                  int64_t, int, int, const float*, const float*, const FusedWrite*, int, int,
+                  cudaStream_t);
+bool stream_fused_supported(const FusedWrite&, int);
 int64_t stream_workspace_bytes(int, int);
 int launch_merge_attn_states(void*, float*, const void*, const float*, const void*, const float*,
                              int64_t, int, int, int, cudaStream_t);
@@ -110,7 +112,7 @@ static int paged_attention_common(
     int64_t kv_block_stride, int64_t kv_head_stride, int scalar_type, int kv_dtype,
     const float* k_scale, const float* v_scale, int tp_rank, int bs_local_blocks,
     int bs_vert_stride, int bs_block_size, int bs_head_sliding_step, void* workspace,
-    int64_t workspace_bytes, void* stream_v) {
+    int64_t workspace_bytes, void* stream_v, const FusedWrite* fused = nullptr) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
   if (!head_size_ok(head_size))
     return set_error(B200PA_ERR_UNSUPPORTED, "Unsupported head size: %d", head_size);
@@ -162,14 +164,26 @@ static int paged_attention_common(
                        kv_dtype, bs_vert_stride);
   if (impl == B200PA_IMPL_STREAM && !stream_ok)
     return set_error(B200PA_ERR_UNSUPPORTED, "configuration not covered by the stream kernel");
-  if (stream_ok && ((impl == B200PA_IMPL_AUTO && workspace) || impl == B200PA_IMPL_STREAM)) {
+  const bool use_stream =
+      stream_ok && ((impl == B200PA_IMPL_AUTO && workspace) || impl == B200PA_IMPL_STREAM);
+  if (fused && !(use_stream && stream_fused_supported(*fused, scalar_type))) {
+    // decode_step outside the fused kernel's domain: the two launches it stands for
+    int rc = launch_reshape_and_cache(fused->key, fused->value, const_cast<void*>(key_cache),
+                                      const_cast<void*>(value_cache), fused->slot_mapping, num_seqs,
+                                      fused->key_stride, fused->value_stride, num_kv_heads,
+                                      head_size, block_size, x, scalar_type, kv_dtype, k_scale,
+                                      v_scale, stream);
+    if (rc) return rc;
+    fused = nullptr;
+  }
+  if (use_stream) {
     // persistent stream-K kernel + boundary merge; serves v1 and v2 alike (the caller's v2
     // scratch is left untouched)
     return launch_stream(out, lse, lse_seq_stride, lse_head_stride, workspace, workspace_bytes, query, key_cache, value_cache, num_seqs,
                          num_heads, num_kv_heads, head_size, scale, block_tables,
                          max_num_blocks_per_seq, seq_lens, alibi_slopes, q_stride,
                          kv_block_stride, kv_head_stride, scalar_type, kv_dtype, k_scale, v_scale,
-                         num_sms(), stream_tune(), stream);
+                         fused, num_sms(), stream_tune(), stream);
   }
   int rc = launch_generic(out, lse, lse_seq_stride, lse_head_stride, exp_sums, max_logits, tmp_out, query, key_cache, value_cache,
                           num_seqs, num_heads, num_kv_heads, head_size, block_size, scale,
@@ -263,6 +277,31 @@ int b200pa_paged_attention_lse(
                                 q_stride, kv_block_stride, kv_head_stride, scalar_type, kv_dtype,
                                 k_scale, v_scale, 0, 0, 0, 64, 0, workspace, workspace_bytes,
                                 stream);
+}
+
+int b200pa_decode_step(
+    void* out, float* lse, int64_t lse_seq_stride, int64_t lse_head_stride, const void* query,
+    const void* key, const void* value, int64_t key_stride, int64_t value_stride,
+    const int64_t* slot_mapping, void* key_cache, void* value_cache, int num_seqs, int num_heads,
+    int num_kv_heads, int head_size, int block_size, float scale, const int32_t* block_tables,
+    int max_num_blocks_per_seq, const int32_t* seq_lens, int max_seq_len,
+    const float* alibi_slopes, int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
+    int scalar_type, int kv_dtype, const float* k_scale, const float* v_scale, void* workspace,
+    int64_t workspace_bytes, void* stream) {
+  if (!key || !value || !slot_mapping)
+    return set_error(B200PA_ERR_INVALID, "decode_step: null key / value / slot_mapping pointer");
+  // reshape_and_cache indexes a dense cache (cache_kernels.cu:231-247 of the reference)
+  if (kv_head_stride != (int64_t)head_size * block_size ||
+      kv_block_stride != (int64_t)num_kv_heads * head_size * block_size)
+    return set_error(B200PA_ERR_INVALID, "decode_step: the kv cache must be dense");
+  const FusedWrite fw{key, value, key_stride, value_stride, slot_mapping};
+  return paged_attention_common(false, out, lse, lse_seq_stride, lse_head_stride, nullptr, nullptr,
+                                nullptr, query, key_cache, value_cache, num_seqs, num_heads,
+                                num_kv_heads, head_size, block_size, scale, block_tables,
+                                max_num_blocks_per_seq, seq_lens, max_seq_len, 1, alibi_slopes,
+                                q_stride, kv_block_stride, kv_head_stride, scalar_type, kv_dtype,
+                                k_scale, v_scale, 0, 0, 0, 64, 0, workspace, workspace_bytes,
+                                stream, &fw);
 }
 
 int b200pa_merge_attn_states(void* output, float* output_lse, const void* prefix_output,

@@ -112,6 +112,16 @@ struct BlockSparse {
   int tp_rank;
 };
 
+// The new token of every sequence for the fused "write the cache + attend" launch
+// (b200pa_decode_step): key/value [num_seqs, num_kv_heads, head_size] scalar_t, token b being
+// position seq_lens[b] - 1 of sequence b, stored at slot_mapping[b] (< 0: not stored).
+struct FusedWrite {
+  const void* key;
+  const void* value;
+  int64_t key_stride, value_stride;  // elements per token
+  const int64_t* slot_mapping;
+};
+
 }  // namespace b200pa
 
 // ---- host-side error plumbing (defined in c_abi.cu) -------------------------

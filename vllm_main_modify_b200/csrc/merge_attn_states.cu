@@ -25,47 +25,62 @@ constexpr int kMergeThreads = 128;
 
 __device__ __forceinline__ float lse_clean_inf(float v) { return isinf(v) ? -INFINITY : v; }
 
-// One thread per 16-byte pack of one (token, head) row.
-template <int ST>
+// One thread per 16-byte pack of one (token, head) row, U rows' packs per thread with all loads
+// issued before the first use (bytes in flight), 32-bit index arithmetic whenever the problem
+// allows (IdxT), streaming (evict-first) accesses: nothing here is read twice.
+template <int ST, typename IdxT, int U>
 __global__ void __launch_bounds__(kMergeThreads)
 merge_attn_states_kernel(typename Scalar<ST>::type* __restrict__ output,
                          float* __restrict__ output_lse,
                          const typename Scalar<ST>::type* __restrict__ prefix_output,
                          const float* __restrict__ prefix_lse,
                          const typename Scalar<ST>::type* __restrict__ suffix_output,
-                         const float* __restrict__ suffix_lse, int64_t num_tokens,
-                         int num_heads, int packs_per_head) {
+                         const float* __restrict__ suffix_lse, IdxT num_tokens,
+                         IdxT num_heads, IdxT packs_per_head, IdxT total) {
   using T = typename Scalar<ST>::type;
   constexpr int PACK = 16 / (int)sizeof(T);
-  const int64_t total = num_tokens * num_heads * packs_per_head;
-  for (int64_t idx = (int64_t)blockIdx.x * kMergeThreads + threadIdx.x; idx < total;
-       idx += (int64_t)gridDim.x * kMergeThreads) {
-    const int64_t row = idx / packs_per_head;       // token * num_heads + head
-    const int pack = (int)(idx - row * packs_per_head);
-    const int64_t token = row / num_heads;
-    const int head = (int)(row - token * num_heads);
-    float p_lse = lse_clean_inf(prefix_lse[(int64_t)head * num_tokens + token]);
-    float s_lse = lse_clean_inf(suffix_lse[(int64_t)head * num_tokens + token]);
-    const float max_lse = fmaxf(p_lse, s_lse);
-    p_lse -= max_lse;
-    s_lse -= max_lse;
-    const float p_se = expf(p_lse), s_se = expf(s_lse);
+  const IdxT base = (IdxT)blockIdx.x * (IdxT)(kMergeThreads * U) + threadIdx.x;
+  IdxT lse_off[U];
+  bool live[U], first[U];
+  float p_lse[U], s_lse[U];
+  uint4 pp[U], sp[U];
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const IdxT idx = base + (IdxT)(u * kMergeThreads);
+    live[u] = idx < total;
+    const IdxT row = idx / packs_per_head;  // token * num_heads + head
+    first[u] = idx == row * packs_per_head;
+    const IdxT token = row / num_heads;
+    const IdxT head = row - token * num_heads;
+    lse_off[u] = head * num_tokens + token;
+    if (live[u]) {
+      p_lse[u] = __ldg(prefix_lse + lse_off[u]);
+      s_lse[u] = __ldg(suffix_lse + lse_off[u]);
+      pp[u] = __ldcs(reinterpret_cast<const uint4*>(prefix_output) + idx);
+      sp[u] = __ldcs(reinterpret_cast<const uint4*>(suffix_output) + idx);
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    if (!live[u]) continue;
+    const IdxT idx = base + (IdxT)(u * kMergeThreads);
+    float pl = lse_clean_inf(p_lse[u]), sl = lse_clean_inf(s_lse[u]);
+    const float max_lse = fmaxf(pl, sl);
+    pl -= max_lse;
+    sl -= max_lse;
+    const float p_se = expf(pl), s_se = expf(sl);
     const float out_se = p_se + s_se;
     const float p_scale = p_se / out_se, s_scale = s_se / out_se;
-    const int64_t off = row * packs_per_head + pack;  // in 16-byte units
-    const uint4 pp = reinterpret_cast<const uint4*>(prefix_output)[off];
-    const uint4 sp = reinterpret_cast<const uint4*>(suffix_output)[off];
     uint4 op;
-    const T* pe = reinterpret_cast<const T*>(&pp);
-    const T* se = reinterpret_cast<const T*>(&sp);
+    const T* pe = reinterpret_cast<const T*>(&pp[u]);
+    const T* se = reinterpret_cast<const T*>(&sp[u]);
     T* oe = reinterpret_cast<T*>(&op);
 #pragma unroll
     for (int i = 0; i < PACK; ++i)
       oe[i] = Scalar<ST>::from_float(Scalar<ST>::to_float(pe[i]) * p_scale +
                                      (Scalar<ST>::to_float(se[i]) * s_scale));
-    reinterpret_cast<uint4*>(output)[off] = op;
-    if (output_lse != nullptr && pack == 0)
-      output_lse[(int64_t)head * num_tokens + token] = logf(out_se) + max_lse;
+    __stcs(reinterpret_cast<uint4*>(output) + idx, op);
+    if (output_lse != nullptr && first[u]) output_lse[lse_off[u]] = logf(out_se) + max_lse;
   }
 }
 
@@ -102,6 +117,45 @@ correct_attn_out_kernel(typename Scalar<ST>::type* __restrict__ out, float* __re
     row[d] = Scalar<ST>::from_float(Scalar<ST>::to_float(row[d]) * factor);
 }
 
+// 16-byte variant (rows 16-byte aligned, head_size a multiple of the pack): one thread per
+// pack, the row's LSEs re-read by its packs_per_head neighbours (L1 broadcast), row data
+// streamed with one 16-byte load and one 16-byte store per thread.
+template <int ST>
+__global__ void __launch_bounds__(kMergeThreads)
+correct_attn_out_vec_kernel(typename Scalar<ST>::type* __restrict__ out,
+                            float* __restrict__ lse_out, const float* __restrict__ lses,
+                            int num_ranks, int rank, unsigned total, unsigned num_heads,
+                            unsigned packs_per_head, int64_t out_seq_stride,
+                            int64_t out_head_stride, int64_t lses_rank_stride,
+                            int64_t lses_seq_stride, int64_t lses_head_stride) {
+  using T = typename Scalar<ST>::type;
+  constexpr int PACK = 16 / (int)sizeof(T);
+  const unsigned idx = blockIdx.x * kMergeThreads + threadIdx.x;
+  if (idx >= total) return;
+  const unsigned row = idx / packs_per_head;
+  const unsigned pack = idx - row * packs_per_head;
+  const unsigned b = row / num_heads;
+  const unsigned h = row - b * num_heads;
+  uint4* ptr = reinterpret_cast<uint4*>(out + b * out_seq_stride + h * out_head_stride) + pack;
+  const uint4 v = __ldcs(ptr);
+  const float* l0 = lses + b * lses_seq_stride + h * lses_head_stride;
+  float mx = -INFINITY;
+  for (int n = 0; n < num_ranks; ++n) mx = fmaxf(mx, lse_clean(__ldg(l0 + n * lses_rank_stride)));
+  float acc = 0.f;
+  for (int n = 0; n < num_ranks; ++n)
+    acc += expf(lse_clean(__ldg(l0 + n * lses_rank_stride)) - mx);
+  const float lse = logf(acc) + mx;
+  if (pack == 0) lse_out[b * lses_seq_stride + h * lses_head_stride] = lse;
+  const float factor = expf(lse_clean(__ldg(l0 + rank * lses_rank_stride) - lse));
+  uint4 o;
+  const T* ve = reinterpret_cast<const T*>(&v);
+  T* oe = reinterpret_cast<T*>(&o);
+#pragma unroll
+  for (int i = 0; i < PACK; ++i)
+    oe[i] = Scalar<ST>::from_float(Scalar<ST>::to_float(ve[i]) * factor);
+  __stcs(ptr, o);
+}
+
 }  // namespace
 
 int launch_merge_attn_states(void* output, float* output_lse, const void* prefix_output,
@@ -111,16 +165,29 @@ int launch_merge_attn_states(void* output, float* output_lse, const void* prefix
   const int pack = scalar_type == B200PA_F32 ? 4 : 8;
   const int pph = head_size / pack;
   const int64_t total = num_tokens * num_heads * pph;
-  const int64_t blocks = (total + kMergeThreads - 1) / kMergeThreads;
-  const dim3 grid((unsigned)(blocks < (1 << 20) ? blocks : (1 << 20))), block(kMergeThreads);
+  if (total == 0) return 0;
+  constexpr int U = 2;
+  const int64_t blocks = (total + kMergeThreads * U - 1) / (kMergeThreads * U);
+  if (blocks > 0x7fffffffLL) return set_error(B200PA_ERR_UNSUPPORTED, "merge_attn_states: too large");
+  const dim3 grid((unsigned)blocks), block(kMergeThreads);
+  // 32-bit indices when every offset (incl. the rounded-up tail) fits
+  const bool small = total + kMergeThreads * U < (1LL << 32);
 #define MERGE_CALL(ST)                                                                      \
-  merge_attn_states_kernel<ST><<<grid, block, 0, stream>>>(                                 \
-      (typename Scalar<ST>::type*)output, output_lse,                                       \
-      (const typename Scalar<ST>::type*)prefix_output, prefix_lse,                          \
-      (const typename Scalar<ST>::type*)suffix_output, suffix_lse, num_tokens, num_heads, pph)
-  if (scalar_type == B200PA_BF16) MERGE_CALL(B200PA_BF16);
-  else if (scalar_type == B200PA_F16) MERGE_CALL(B200PA_F16);
-  else MERGE_CALL(B200PA_F32);
+  if (small)                                                                                \
+    merge_attn_states_kernel<ST, uint32_t, U><<<grid, block, 0, stream>>>(                  \
+        (typename Scalar<ST>::type*)output, output_lse,                                     \
+        (const typename Scalar<ST>::type*)prefix_output, prefix_lse,                        \
+        (const typename Scalar<ST>::type*)suffix_output, suffix_lse, (uint32_t)num_tokens,  \
+        (uint32_t)num_heads, (uint32_t)pph, (uint32_t)total);                               \
+  else                                                                                      \
+    merge_attn_states_kernel<ST, int64_t, U><<<grid, block, 0, stream>>>(                   \
+        (typename Scalar<ST>::type*)output, output_lse,                                     \
+        (const typename Scalar<ST>::type*)prefix_output, prefix_lse,                        \
+        (const typename Scalar<ST>::type*)suffix_output, suffix_lse, (int64_t)num_tokens,   \
+        (int64_t)num_heads, (int64_t)pph, (int64_t)total)
+  if (scalar_type == B200PA_BF16) { MERGE_CALL(B200PA_BF16); }
+  else if (scalar_type == B200PA_F16) { MERGE_CALL(B200PA_F16); }
+  else { MERGE_CALL(B200PA_F32); }
 #undef MERGE_CALL
   count_launch();
   return check_launch("merge_attn_states");
@@ -132,6 +199,24 @@ int launch_correct_attn_out(void* out, float* lse_out, const float* lses, int nu
                             int64_t lses_seq_stride, int64_t lses_head_stride, int scalar_type,
                             cudaStream_t stream) {
   const int64_t warps = (int64_t)num_seqs * num_heads;
+  if (warps == 0) return 0;
+  const int pack = scalar_type == B200PA_F32 ? 4 : 8;
+  const int64_t vec_total = warps * (head_size / pack);
+  if (head_size % pack == 0 && out_seq_stride % pack == 0 && out_head_stride % pack == 0 &&
+      ((uintptr_t)out & 15) == 0 && vec_total < (1LL << 32) - kMergeThreads) {
+    const dim3 vgrid((unsigned)((vec_total + kMergeThreads - 1) / kMergeThreads));
+#define CORRECT_VEC_CALL(ST)                                                                 \
+  correct_attn_out_vec_kernel<ST><<<vgrid, kMergeThreads, 0, stream>>>(                      \
+      (typename Scalar<ST>::type*)out, lse_out, lses, num_ranks, rank, (unsigned)vec_total,  \
+      (unsigned)num_heads, (unsigned)(head_size / pack), out_seq_stride, out_head_stride,    \
+      lses_rank_stride, lses_seq_stride, lses_head_stride)
+    if (scalar_type == B200PA_BF16) CORRECT_VEC_CALL(B200PA_BF16);
+    else if (scalar_type == B200PA_F16) CORRECT_VEC_CALL(B200PA_F16);
+    else CORRECT_VEC_CALL(B200PA_F32);
+#undef CORRECT_VEC_CALL
+    count_launch();
+    return check_launch("correct_attn_out");
+  }
   const int wpb = kMergeThreads / 32;
   const dim3 grid((unsigned)((warps + wpb - 1) / wpb)), block(kMergeThreads);
 #define CORRECT_CALL(ST)                                                                    \

@@ -153,6 +153,13 @@ struct StreamParams {
   const float* alibi_slopes;
   const float* k_scale;
   const float* v_scale;
+  // fused cache write (decode_step), new_key == nullptr: plain attention.  The warp that
+  // consumes the last stage of a (sequence, kv head) patches the new token into its shared-memory
+  // copy of the page (every head tile) and stores it to the global cache (head tile 0 only).
+  const void* new_key;
+  const void* new_value;
+  const int64_t* slot_mapping;
+  int64_t new_key_stride, new_value_stride;           // elements per token
   int64_t q_stride, kv_block_stride, kv_head_stride;  // elements
   int num_seqs, num_heads, num_kv_heads, group;       // group = num_heads / num_kv_heads
   int h_tiles;                                         // ceil(group / 8)
@@ -529,6 +536,74 @@ paged_attention_stream_kernel(const StreamParams p) {
     const int s = i % STAGES;
     const uint32_t sbase = ring_u32 + s * STAGE_BYTES;
     mbar_wait(bar0 + 8 * s, (i / STAGES) & 1);
+
+    // ---- fused cache write: the stage that ends the sequence holds position len - 1, whose
+    // K/V come from this step's key/value rows (quantised exactly as reshape_and_cache does),
+    // not from the bytes the TMA copy found in the cache.
+    if (p.new_key != nullptr && cc.st == cc.ns) {
+      const int64_t slot = p.slot_mapping[cc.b];
+      if (slot >= 0) {
+        constexpr int X = 16 / CES;       // elements per 16-byte chunk of the x-packed K layout
+        const int t = cc.len - 1 - page0 * kBS;
+        uint8_t* pg = ring + s * STAGE_BYTES + (t >> 4) * (2 * PAGE_BYTES);
+        const int tt = t & 15;
+        const int kvh = cc.vh / p.h_tiles;
+        const bool to_global = cc.vh == kvh * p.h_tiles;
+        const T* kn = reinterpret_cast<const T*>(p.new_key) + (int64_t)cc.b * p.new_key_stride +
+                      (int64_t)kvh * D;
+        const T* vn = reinterpret_cast<const T*>(p.new_value) + (int64_t)cc.b * p.new_value_stride +
+                      (int64_t)kvh * D;
+        const int64_t goff = (slot / kBS) * blk_stride_bytes + kvh * head_stride_bytes;
+        const int off = (int)(slot % kBS);
+        uint8_t* kg = reinterpret_cast<uint8_t*>(const_cast<void*>(p.k_cache)) + goff;
+        uint8_t* vg = reinterpret_cast<uint8_t*>(const_cast<void*>(p.v_cache)) + goff;
+        if (lane < D / X) {
+          uint4 val;
+          if constexpr (FP8) {
+            const float ks = *p.k_scale;
+            uint4 raw[2];
+            raw[0] = reinterpret_cast<const uint4*>(kn + lane * X)[0];
+            raw[1] = reinterpret_cast<const uint4*>(kn + lane * X)[1];
+            const T* e = reinterpret_cast<const T*>(raw);
+            uint32_t w4[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint32_t lo = fp8_quant2<B200PA_KV_FP8_E4M3>(
+                  Scalar<ST>::to_float(e[4 * j + 0]), Scalar<ST>::to_float(e[4 * j + 1]), ks);
+              const uint32_t hi = fp8_quant2<B200PA_KV_FP8_E4M3>(
+                  Scalar<ST>::to_float(e[4 * j + 2]), Scalar<ST>::to_float(e[4 * j + 3]), ks);
+              w4[j] = lo | (hi << 16);
+            }
+            val = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+          } else {
+            val = *reinterpret_cast<const uint4*>(kn + lane * X);
+          }
+          *reinterpret_cast<uint4*>(pg + (lane * kBS + tt) * 16) = val;
+          if (to_global) *reinterpret_cast<uint4*>(kg + (lane * kBS + off) * 16) = val;
+        }
+        if constexpr (FP8) {
+          const float vs = *p.v_scale;
+#pragma unroll
+          for (int dd = 0; dd < D / 32; ++dd) {
+            const int e = dd * 32 + lane;
+            const uint8_t b8 = fp8_quant<B200PA_KV_FP8_E4M3>(Scalar<ST>::to_float(vn[e]), vs);
+            pg[PAGE_BYTES + e * kBS + tt] = b8;
+            if (to_global) vg[e * kBS + off] = b8;
+          }
+        } else {
+#pragma unroll
+          for (int dd = 0; dd < D / 32; ++dd) {
+            const int e = dd * 32 + lane;
+            const T v16 = vn[e];
+            reinterpret_cast<T*>(pg + PAGE_BYTES)[e * kBS + tt] = v16;
+            if (to_global) reinterpret_cast<T*>(vg)[e * kBS + off] = v16;
+          }
+        }
+        // generic-proxy stores to a buffer the TMA engine refills later
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      }
+      __syncwarp();
+    }
 
     // ---- S^T = K Q^T : per page one 16(token) x 8(head) tile, two k chains
     float sc[PPS][4];
@@ -1039,6 +1114,14 @@ bool stream_supported(const void* query, const void* key_cache, const void* valu
   return true;
 }
 
+// The fused write reads the new key/value rows with 16-byte loads.
+bool stream_fused_supported(const FusedWrite& f, int scalar_type) {
+  const int es = scalar_type == B200PA_F32 ? 4 : 2;
+  auto a16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };
+  return f.key && f.value && f.slot_mapping && a16(f.key) && a16(f.value) &&
+         (f.key_stride * es) % 16 == 0 && (f.value_stride * es) % 16 == 0;
+}
+
 int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_head_stride,
                   void* workspace, int64_t workspace_bytes, const void* query,
                   const void* key_cache, const void* value_cache, int num_seqs, int num_heads,
@@ -1046,7 +1129,7 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
                   int max_num_blocks_per_seq, const int32_t* seq_lens, const float* alibi_slopes,
                   int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
                   int scalar_type, int kv_dtype, const float* k_scale, const float* v_scale,
-                  int num_sms, int tune, cudaStream_t stream) {
+                  const FusedWrite* fused, int num_sms, int tune, cudaStream_t stream) {
   if (!workspace || (reinterpret_cast<uintptr_t>(workspace) & 15u))
     return set_error(B200PA_ERR_INVALID, "the stream kernel needs a 16-byte aligned workspace "
                      "(b200pa_paged_attention_workspace_bytes)");
@@ -1064,6 +1147,11 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
   p.alibi_slopes = alibi_slopes;
   p.k_scale = k_scale;
   p.v_scale = v_scale;
+  p.new_key = fused ? fused->key : nullptr;
+  p.new_value = fused ? fused->value : nullptr;
+  p.slot_mapping = fused ? fused->slot_mapping : nullptr;
+  p.new_key_stride = fused ? fused->key_stride : 0;
+  p.new_value_stride = fused ? fused->value_stride : 0;
   p.q_stride = q_stride;
   p.kv_block_stride = kv_block_stride;
   p.kv_head_stride = kv_head_stride;

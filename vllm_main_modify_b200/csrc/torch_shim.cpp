@@ -181,6 +181,63 @@ void paged_attention_lse(torch::Tensor& out, torch::Tensor& lse, torch::Tensor& 
       ws.defined() ? ws.numel() : 0, stream));
 }
 
+// reshape_and_cache + paged_attention_v1 (+ lse) of a pure decode batch in one launch
+// (b200pa_decode_step); the checks are those of the two ops it stands for.
+void decode_step(torch::Tensor& out, const std::optional<torch::Tensor>& lse, torch::Tensor& query,
+                 torch::Tensor& key, torch::Tensor& value, torch::Tensor& key_cache,
+                 torch::Tensor& value_cache, torch::Tensor& slot_mapping, int64_t num_kv_heads,
+                 double scale, torch::Tensor& block_tables, torch::Tensor& seq_lens,
+                 int64_t block_size, int64_t max_seq_len,
+                 const std::optional<torch::Tensor>& alibi_slopes,
+                 const std::string& kv_cache_dtype, torch::Tensor& k_scale,
+                 torch::Tensor& v_scale) {
+  check_cuda(query, "query");
+  check_cuda(key, "key");
+  const int kv = kv_code(kv_cache_dtype);
+  const int st = scalar_code(query.scalar_type());
+  check_cache_dtype(key_cache, query, kv, "key_cache");
+  check_cache_dtype(value_cache, query, kv, "value_cache");
+  TORCH_CHECK(key.scalar_type() == query.scalar_type() && value.scalar_type() == query.scalar_type(),
+              "key / value dtype must match query");
+  TORCH_CHECK(block_tables.scalar_type() == at::ScalarType::Int, "block_tables must be int32");
+  TORCH_CHECK(seq_lens.scalar_type() == at::ScalarType::Int, "seq_lens must be int32");
+  TORCH_CHECK(slot_mapping.scalar_type() == at::ScalarType::Long, "slot_mapping must be int64");
+  TORCH_CHECK(key.size(0) == query.size(0) && slot_mapping.size(0) == query.size(0) &&
+                  value.size(0) == query.size(0),
+              "decode_step takes one new token per sequence");
+  TORCH_CHECK(key.size(1) == num_kv_heads && key.size(2) == query.size(2) &&
+                  key.stride(2) == 1 && key.stride(1) == key.size(2) && value.stride(2) == 1 &&
+                  value.stride(1) == value.size(2),
+              "key / value must be [num_seqs, num_kv_heads, head_size] with dense heads");
+  TORCH_CHECK(out.is_contiguous(), "out must be contiguous");
+  TORCH_CHECK(query.stride(2) == 1 && query.stride(1) == query.size(2),
+              "query heads must be densely packed");
+  float* lse_ptr = nullptr;
+  int64_t ls0 = 0, ls1 = 0;
+  if (lse.has_value()) {
+    TORCH_CHECK(lse->scalar_type() == at::ScalarType::Float && lse->dim() == 2 &&
+                    lse->size(0) == query.size(0) && lse->size(1) == query.size(1),
+                "lse must be float32 [num_seqs, num_heads]");
+    lse_ptr = lse->data_ptr<float>();
+    ls0 = lse->stride(0);
+    ls1 = lse->stride(1);
+  }
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(query));
+  const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  const float* alibi = alibi_slopes ? reinterpret_cast<const float*>(alibi_slopes->data_ptr()) : nullptr;
+  const torch::Tensor ws = attention_workspace(query);
+  check_status(b200pa_decode_step(
+      out.data_ptr(), lse_ptr, ls0, ls1, query.data_ptr(), key.data_ptr(), value.data_ptr(),
+      key.stride(0), value.stride(0), slot_mapping.data_ptr<int64_t>(), key_cache.data_ptr(),
+      value_cache.data_ptr(), (int)query.size(0), (int)query.size(1), (int)num_kv_heads,
+      (int)query.size(2), (int)block_size, (float)scale, block_tables.data_ptr<int>(),
+      (int)block_tables.size(1), seq_lens.data_ptr<int>(), (int)max_seq_len, alibi,
+      query.stride(0), key_cache.stride(0), key_cache.stride(1), st, kv,
+      reinterpret_cast<const float*>(k_scale.data_ptr()),
+      reinterpret_cast<const float*>(v_scale.data_ptr()), ws.defined() ? ws.data_ptr() : nullptr,
+      ws.defined() ? ws.numel() : 0, stream));
+}
+
 // csrc/attention/merge_attn_states.cu:131-180 of the reference (same checks, same messages)
 void merge_attn_states(torch::Tensor& output, std::optional<torch::Tensor> output_lse,
                        const torch::Tensor& prefix_output, const torch::Tensor& prefix_lse,
@@ -476,6 +533,14 @@ constexpr const char* kSchemaLse =
     "    Tensor block_tables, Tensor seq_lens, int block_size,"
     "    int max_seq_len, Tensor? alibi_slopes,"
     "    str kv_cache_dtype, Tensor k_scale, Tensor v_scale) -> ()";
+constexpr const char* kSchemaStep =
+    "decode_step("
+    "    Tensor! out, Tensor!? lse, Tensor query, Tensor key, Tensor value,"
+    "    Tensor! key_cache, Tensor! value_cache, Tensor slot_mapping,"
+    "    int num_kv_heads, float scale,"
+    "    Tensor block_tables, Tensor seq_lens, int block_size,"
+    "    int max_seq_len, Tensor? alibi_slopes,"
+    "    str kv_cache_dtype, Tensor k_scale, Tensor v_scale) -> ()";
 constexpr const char* kSchemaCorrect =
     "correct_attn_out(Tensor! out, Tensor lses, int cp_rank) -> Tensor";
 constexpr const char* kSchemaReshape =
@@ -507,6 +572,8 @@ void define_attention(torch::Library& ops) {
 void define_extras(torch::Library& ops) {
   ops.def(kSchemaLse);
   ops.impl("paged_attention_lse", torch::kCUDA, &paged_attention_lse);
+  ops.def(kSchemaStep);
+  ops.impl("decode_step", torch::kCUDA, &decode_step);
   ops.def(kSchemaCorrect);
   ops.impl("correct_attn_out", torch::kCUDA, &correct_attn_out);
 }

@@ -117,6 +117,37 @@ class PagedAttention:
         return output
 
     @staticmethod
+    def write_and_decode(
+        query: torch.Tensor,
+        key: torch.Tensor,
+        value: torch.Tensor,
+        key_cache: torch.Tensor,
+        value_cache: torch.Tensor,
+        slot_mapping: torch.Tensor,
+        block_tables: torch.Tensor,
+        seq_lens: torch.Tensor,
+        max_seq_len: int,
+        kv_cache_dtype: str,
+        num_kv_heads: int,
+        scale: float,
+        alibi_slopes: Optional[torch.Tensor],
+        k_scale: torch.Tensor,
+        v_scale: torch.Tensor,
+        output: Optional[torch.Tensor] = None,
+        lse: Optional[torch.Tensor] = None,
+    ) -> torch.Tensor:
+        """``write_to_paged_cache`` + ``forward_decode`` (:73-92, :94-198 of the reference's
+        ``paged_attn.py``) of a pure decode batch (one new token per sequence, the sequence's
+        last) in one launch (``ops.decode_step``)."""
+        if output is None:
+            output = torch.empty_like(query)
+        ops.decode_step(output, lse, query, key, value, key_cache, value_cache,
+                        slot_mapping.flatten(), num_kv_heads, scale, block_tables, seq_lens,
+                        value_cache.shape[3], max_seq_len, alibi_slopes, kv_cache_dtype,
+                        k_scale, v_scale)
+        return output
+
+    @staticmethod
     def forward_decode_with_lse(
         query: torch.Tensor,
         key_cache: torch.Tensor,

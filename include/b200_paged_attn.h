@@ -58,7 +58,7 @@
 extern "C" {
 #endif
 
-#define B200PA_ABI_VERSION 5
+#define B200PA_ABI_VERSION 6
 
 /* scalar_t of query / out / key / value (reference: VLLM_DISPATCH_FLOATING_TYPES) */
 enum { B200PA_F32 = 0, B200PA_F16 = 1, B200PA_BF16 = 2 };
@@ -190,6 +190,35 @@ int b200pa_decode_step(
     float scale, const int32_t* block_tables, int max_num_blocks_per_seq,
     const int32_t* seq_lens, int max_seq_len, const float* alibi_slopes,
     int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
+    int scalar_type, int kv_dtype, const float* k_scale, const float* v_scale,
+    void* workspace, int64_t workspace_bytes, void* stream);
+
+/*
+ * Decode attention over a TOKEN-MAJOR ("flash") cache -- the layout reshape_and_cache_flash
+ * writes (csrc/cache_kernels.cu:280-353 of the reference) and every flash-attention style
+ * backend and KV connector of the reference uses -- so that the decode kernel serves it without
+ * a layout conversion:
+ *   key_cache, value_cache: [num_blocks][block_size][num_kv_heads][head_size] by strides
+ *   (elements): block_stride, page_stride (between two tokens of a block), head_stride;
+ *   NHD: page_stride = num_kv_heads*head_size, head_stride = head_size;
+ *   HND: head_stride = block_size*head_size, page_stride = head_size.
+ * Same math, same output contract as b200pa_paged_attention_v1 / _lse (lse may be NULL).
+ * key / value / slot_mapping all non-NULL: additionally the effect of
+ * b200pa_reshape_and_cache_flash(key, value, ..., slot_mapping, num_tokens = num_seqs) BEFORE the
+ * attention, in the same launch, under b200pa_decode_step's precondition (token b is position
+ * seq_lens[b] - 1 of sequence b).  All three NULL: attention only.
+ * Domain: head_size 64 / 128, block_size 16, f16 / bf16 query, auto / fp8_e4m3 cache, 16-byte
+ * aligned rows; anything else is B200PA_ERR_UNSUPPORTED (there is no second kernel for this
+ * layout).  A workspace (b200pa_paged_attention_workspace_bytes) is required.
+ */
+int b200pa_paged_attention_flash(
+    void* out, float* lse, int64_t lse_seq_stride, int64_t lse_head_stride, const void* query,
+    const void* key, const void* value, int64_t key_stride, int64_t value_stride,
+    const int64_t* slot_mapping, void* key_cache, void* value_cache,
+    int num_seqs, int num_heads, int num_kv_heads, int head_size, int block_size,
+    float scale, const int32_t* block_tables, int max_num_blocks_per_seq,
+    const int32_t* seq_lens, int max_seq_len, const float* alibi_slopes,
+    int64_t q_stride, int64_t block_stride, int64_t page_stride, int64_t head_stride,
     int scalar_type, int kv_dtype, const float* k_scale, const float* v_scale,
     void* workspace, int64_t workspace_bytes, void* stream);
 

@@ -72,3 +72,24 @@ def cp_gather_cache(src_cache: torch.Tensor, dst: torch.Tensor, block_table: tor
         for p in range(hi - lo):
             t = start + p
             dst[lo + p].copy_(flat[int(block_table[b, t // BS]), t % BS])
+
+
+def xpacked_to_flash(key_cache: torch.Tensor, value_cache: torch.Tensor):
+    """x-packed caches ``key_cache[NB,Hkv,D/x,BS,x]``, ``value_cache[NB,Hkv,D,BS]``
+    (what ``reshape_and_cache`` writes, ``csrc/cache_kernels.cu:212-264`` of the reference) ->
+    the token-major NHD caches ``[NB,BS,Hkv,D]`` that ``reshape_and_cache_flash`` writes
+    (``:280-353``).  Pure re-indexing, no arithmetic: element (block, head, d, token) of one
+    layout is element (block, token, head, d) of the other."""
+    NB, Hkv, Dx, BS, x = key_cache.shape
+    kf = key_cache.permute(0, 3, 1, 2, 4).reshape(NB, BS, Hkv, Dx * x).contiguous()
+    vf = value_cache.permute(0, 3, 1, 2).contiguous()
+    return kf, vf
+
+
+def flash_to_xpacked(key_cache: torch.Tensor, value_cache: torch.Tensor):
+    """Inverse of :func:`xpacked_to_flash` for ``[NB,BS,Hkv,D]`` caches (any strides)."""
+    NB, BS, Hkv, D = key_cache.shape
+    x = 16 // key_cache.element_size()
+    kx = key_cache.reshape(NB, BS, Hkv, D // x, x).permute(0, 2, 3, 1, 4).contiguous()
+    vx = value_cache.permute(0, 2, 3, 1).contiguous()
+    return kx, vx

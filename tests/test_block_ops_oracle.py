@@ -89,3 +89,38 @@ def test_copy_and_swap_blocks():
     src, dst = torch.randn(6, 20, generator=g), torch.zeros(8, 20)
     co.swap_blocks(src, dst, torch.tensor([[1, 7], [4, 0]], dtype=torch.int64))
     assert torch.equal(dst[7], src[1]) and torch.equal(dst[0], src[4]) and (dst[1:7] == 0).all()
+
+
+def test_layout_converters_pinned_on_the_two_cache_write_oracles():
+    """reshape_and_cache (x-packed) and reshape_and_cache_flash (token-major) are both pinned
+    against the reference (tests/test_oracle.py): writing the same tokens through either and
+    converting must give the same bytes -- which pins xpacked_to_flash / flash_to_xpacked, the
+    re-indexing the flash-layout attention tests rely on."""
+    import pytest
+    for dtype, kv in ((torch.bfloat16, "auto"), (torch.float16, "auto"), (torch.bfloat16, "fp8")):
+        g = torch.Generator().manual_seed(3)
+        NB, BS, Hkv, D, T = 7, 16, 3, 64, 60
+        cache_dt = dtype if kv == "auto" else torch.uint8
+        x = 16 // torch.tensor([], dtype=cache_dt).element_size()
+        key = torch.randn(T, Hkv, D, generator=g).to(dtype)
+        value = torch.randn(T, Hkv, D, generator=g).to(dtype)
+        slots = torch.randperm(NB * BS, generator=g)[:T].to(torch.int64)
+        ks, vs = torch.tensor(0.03), torch.tensor(0.04)
+        kx = torch.zeros(NB, Hkv, D // x, BS, x, dtype=cache_dt)
+        vx = torch.zeros(NB, Hkv, D, BS, dtype=cache_dt)
+        oracle.reshape_and_cache(key, value, kx, vx, slots, kv, ks, vs)
+        kf = torch.zeros(NB, BS, Hkv, D, dtype=cache_dt)
+        vf = torch.zeros_like(kf)
+        oracle.reshape_and_cache_flash(key, value, kf, vf, slots, kv, ks, vs)
+        kf2, vf2 = co.xpacked_to_flash(kx, vx)
+        assert torch.equal(kf2.view(torch.uint8), kf.view(torch.uint8))
+        assert torch.equal(vf2.view(torch.uint8), vf.view(torch.uint8))
+        kx2, vx2 = co.flash_to_xpacked(kf, vf)
+        assert torch.equal(kx2.view(torch.uint8), kx.view(torch.uint8))
+        assert torch.equal(vx2.view(torch.uint8), vx.view(torch.uint8))
+        # HND-strided views convert the same
+        kh = kf.permute(0, 2, 1, 3).contiguous().permute(0, 2, 1, 3)
+        vh = vf.permute(0, 2, 1, 3).contiguous().permute(0, 2, 1, 3)
+        kx3, vx3 = co.flash_to_xpacked(kh, vh)
+        assert torch.equal(kx3.view(torch.uint8), kx.view(torch.uint8))
+        assert torch.equal(vx3.view(torch.uint8), vx.view(torch.uint8))

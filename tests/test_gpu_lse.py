@@ -203,6 +203,29 @@ def test_correct_attn_out_matches_oracle(ops, lora, dtype):
         assert (buf[:, 0] == 0).all() and (buf[:, H + 1:] == 0).all()
 
 
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_correct_attn_out_many_ranks_and_empty_rows(ops, lora, dtype):
+    """More ranks than the kernel loads at once (8): leading ranks empty, one row empty on every
+    rank (NaN LSE and zero factor, as the reference's kernel: common.py:44-64), dense 16-byte path
+    and an odd head size that takes the scalar kernel."""
+    N, B, H = 19, 5, 6
+    g = torch.Generator().manual_seed(1)
+    lses = torch.randn(N, B, H, generator=g) * 4
+    lses[:9, 1, :] = -float("inf")          # first chunk of ranks holds nothing of sequence 1
+    lses[:, 2, 3] = -float("inf")           # nobody holds anything of (2, 3)
+    lses[12, 4, 0] = float("nan")
+    for D in (128, 72, 20):
+        out = torch.randn(B, H, D, generator=g).to(dtype)
+        for rank in (0, 10, 18):
+            want, want_lse = lora.correct_attn_out(out.clone(), lses, rank)
+            got, got_lse = ops.correct_attn_out(out.clone().to(DEV), lses.to(DEV), rank)
+            torch.testing.assert_close(got.cpu().float(), want.float(), atol=1e-6, rtol=2 ** -7,
+                                       equal_nan=True)
+            torch.testing.assert_close(got_lse.cpu(), want_lse, atol=1e-5, rtol=1e-5,
+                                       equal_nan=True)
+            assert torch.isnan(got_lse[2, 3]) and float(got[2, 3].float().abs().sum()) == 0.0
+
+
 @pytest.mark.parametrize("kv", ["auto", "fp8"])
 def test_decode_context_parallel_property_on_gpu(ops, kv):
     """Two emulated DCP ranks (tokens interleaved by page): partial decode + LSE on each,

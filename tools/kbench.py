@@ -107,7 +107,30 @@ def main():
                             w["scale"], w["bt"], w["sl"], bench.BS, w["max_len"], None, kv,
                             w["ks"], w["vs"])
 
-        fns = {"v1": v1, "v2": v2, "reshape_and_cache": wr, "step": step, "fstep": fstep}
+        # token-major views of the same memory (timing only: the bytes mean other tokens there)
+        NBk = kc.shape[0]
+        kf_nhd = kc.reshape(NBk, -1).view(NBk, bench.BS, w["Hkv"], bench.D)
+        vf_nhd = vc.reshape(NBk, -1).view(NBk, bench.BS, w["Hkv"], bench.D)
+        kf_hnd = kc.reshape(NBk, -1).view(NBk, w["Hkv"], bench.BS, bench.D).permute(0, 2, 1, 3)
+        vf_hnd = vc.reshape(NBk, -1).view(NBk, w["Hkv"], bench.BS, bench.D).permute(0, 2, 1, 3)
+
+        def flash_nhd():
+            ops.paged_attention_flash(out, None, w["q"], None, None, kf_nhd, vf_nhd, None,
+                                      w["scale"], w["bt"], w["sl"], w["max_len"], None, kv,
+                                      w["ks"], w["vs"])
+
+        def flash_hnd():
+            ops.paged_attention_flash(out, None, w["q"], None, None, kf_hnd, vf_hnd, None,
+                                      w["scale"], w["bt"], w["sl"], w["max_len"], None, kv,
+                                      w["ks"], w["vs"])
+
+        def fflash_nhd():    # cache write fused
+            ops.paged_attention_flash(out, None, w["q"], w["k_new"], w["v_new"], kf_nhd, vf_nhd,
+                                      w["slots"], w["scale"], w["bt"], w["sl"], w["max_len"], None,
+                                      kv, w["ks"], w["vs"])
+
+        fns = {"v1": v1, "v2": v2, "reshape_and_cache": wr, "step": step, "fstep": fstep,
+               "flash_nhd": flash_nhd, "flash_hnd": flash_hnd, "fflash_nhd": fflash_nhd}
         # ops run in the order given (repeats allowed: "v2,step,v2" separates op from order effects)
         for name in args.ops.split(","):
             fn = fns[name]

@@ -146,6 +146,36 @@ def decode_step(
         k_scale, v_scale)
 
 
+def paged_attention_flash(
+    out: torch.Tensor,
+    lse: Optional[torch.Tensor],
+    query: torch.Tensor,
+    key: Optional[torch.Tensor],
+    value: Optional[torch.Tensor],
+    key_cache: torch.Tensor,
+    value_cache: torch.Tensor,
+    slot_mapping: Optional[torch.Tensor],
+    scale: float,
+    block_tables: torch.Tensor,
+    seq_lens: torch.Tensor,
+    max_seq_len: int,
+    alibi_slopes: Optional[torch.Tensor],
+    kv_cache_dtype: str,
+    k_scale: torch.Tensor,
+    v_scale: torch.Tensor,
+) -> None:
+    """Paged decode attention over the token-major cache ``reshape_and_cache_flash`` writes:
+    ``key_cache`` / ``value_cache`` ``[num_blocks, block_size, num_kv_heads, head_size]``, NHD or
+    HND by strides (``cache_kernels.cu:280-353`` of the reference).  Same math as
+    ``paged_attention_v1`` (+ ``lse`` when given).  With ``key`` / ``value`` / ``slot_mapping`` the
+    new token of every sequence is quantised and stored in the same launch (the effect of
+    ``reshape_and_cache_flash`` before the attention).  No twin in the reference's
+    ``_custom_ops``: its paged_attention ops only read the x-packed layout (SURVEY note 1)."""
+    _ops.paged_attention_flash(
+        out, lse, query, key, value, key_cache, value_cache, slot_mapping, scale,
+        block_tables, seq_lens, max_seq_len, alibi_slopes, kv_cache_dtype, k_scale, v_scale)
+
+
 def correct_attn_out(out: torch.Tensor, lses: torch.Tensor, cp_rank: int,
                      ctx=None) -> "tuple[torch.Tensor, torch.Tensor]":
     """``vllm/attention/ops/common.py:86-116`` (``ctx`` is the reference's Triton cache, unused):

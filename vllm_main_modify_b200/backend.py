@@ -272,3 +272,98 @@ class B200PagedAttentionBackend:
     @staticmethod
     def use_cascade_attention(*args, **kwargs) -> bool:
         return False
+
+
+# --------------------------------------------------------------------------------------------
+# The same decode path over the TOKEN-MAJOR cache: the layout every flash-
+# attention style backend of the reference allocates (``FlashAttentionBackend.get_kv_cache_shape``
+# = ``(2, num_blocks, block_size, num_kv_heads, head_size)``), ``reshape_and_cache_flash`` writes
+# (``csrc/cache_kernels.cu:280-353``) and the KV connectors move
+# (``distributed/kv_transfer/kv_connector/utils.py:91``).  One launch per decode step:
+# ``ops.paged_attention_flash`` with the new token's key / value / slot.
+# --------------------------------------------------------------------------------------------
+class B200FlashLayoutAttentionImpl(B200PagedAttentionImpl):
+    """``AttentionImpl`` for decode on a ``(2, num_blocks, block_size, num_kv_heads, head_size)``
+    cache (NHD, or HND when the runner permutes it: strides are honoured)."""
+
+    def forward(self, layer: Any, query: torch.Tensor, key: Optional[torch.Tensor],
+                value: Optional[torch.Tensor], kv_cache: torch.Tensor,
+                attn_metadata: Optional[B200PagedAttentionMetadata],
+                output: Optional[torch.Tensor] = None,
+                output_scale: Optional[torch.Tensor] = None,
+                output_block_scale: Optional[torch.Tensor] = None) -> torch.Tensor:
+        from . import _custom_ops as ops
+        if output_scale is not None or output_block_scale is not None:
+            raise NotImplementedError("fused output quantization is not yet supported "
+                                      "for B200FlashLayoutAttentionImpl")
+        if output is None:
+            output = torch.empty_like(query)
+        if attn_metadata is None:        # profiling run
+            return output
+        if attn_metadata.max_query_len > 1:
+            raise NotImplementedError(
+                "B200FlashLayoutAttentionImpl implements the decode path; prefill / chunked "
+                "prefill batches must be routed to a prefill backend by the caller")
+        n = attn_metadata.num_actual_tokens
+        q = query.view(-1, self.num_heads, self.head_size)
+        out = output.view(-1, self.num_heads, self.head_size)
+        key_cache, value_cache = kv_cache.unbind(0)
+        if self.alibi_slopes is not None and self.alibi_slopes.device != q.device:
+            self.alibi_slopes = self.alibi_slopes.to(q.device)
+        want_lse = self.need_to_return_lse_for_decode or self.dcp_world_size > 1
+        k = v = slots = None
+        if key is not None and value is not None:
+            k = key.view(-1, self.num_kv_heads, self.head_size)
+            v = value.view(-1, self.num_kv_heads, self.head_size)
+            slots = attn_metadata.slot_mapping.flatten()
+            fused = (self.fused_decode_step and not want_lse and k.shape[0] == n
+                     and slots.numel() == n and attn_metadata.seq_lens.shape[0] == n)
+            if not fused:
+                ops.reshape_and_cache_flash(k, v, key_cache, value_cache, slots,
+                                            self.kv_cache_dtype, layer._k_scale, layer._v_scale)
+                k = v = slots = None
+        lse = None
+        part = out[:n]
+        if want_lse:
+            part = torch.empty_like(q[:n])
+            lse = torch.empty(n, self.num_heads, dtype=torch.float32, device=q.device)
+        ops.paged_attention_flash(part, lse, q[:n], k, v, key_cache, value_cache, slots, self.scale,
+                                  attn_metadata.block_table, attn_metadata.seq_lens,
+                                  attn_metadata.max_seq_len, self.alibi_slopes,
+                                  self.kv_cache_dtype, layer._k_scale, layer._v_scale)
+        if want_lse:
+            from .dcp import cp_lse_ag_out_rs
+            return cp_lse_ag_out_rs(part, lse, self.dcp_group)
+        return output
+
+
+class B200FlashLayoutAttentionBackend(B200PagedAttentionBackend):
+    """``AttentionBackend`` twin whose cache is the flash layout."""
+
+    @staticmethod
+    def get_name() -> str:
+        return "B200_PAGED_ATTN_FLASH_LAYOUT"
+
+    @staticmethod
+    def get_impl_cls() -> Type[B200FlashLayoutAttentionImpl]:
+        return B200FlashLayoutAttentionImpl
+
+    @staticmethod
+    def get_kv_cache_shape(num_blocks: int, block_size: int, num_kv_heads: int,
+                           head_size: int, cache_dtype_str: str = "auto") -> Tuple[int, ...]:
+        if block_size != 16:
+            raise ValueError("B200_PAGED_ATTN_FLASH_LAYOUT serves block_size 16")
+        return (2, num_blocks, block_size, num_kv_heads, head_size)
+
+    @staticmethod
+    def get_kv_cache_stride_order() -> Tuple[int, ...]:
+        # NHD physical order; a runner that wants HND permutes dims 2 and 3 (the kernel reads strides)
+        return (0, 1, 2, 3, 4)
+
+    @staticmethod
+    def get_supported_head_sizes() -> List[int]:
+        return [64, 128]
+
+    @classmethod
+    def get_supported_dtypes(cls) -> List[torch.dtype]:
+        return [torch.float16, torch.bfloat16]

@@ -32,8 +32,10 @@ bool stream_supported(const void*, const void*, const void*, int, int, int, int,
                       int64_t, int, int, int);
 int launch_stream(void*, float*, int64_t, int64_t, void*, int64_t, const void*, const void*, const void*, int, int, int, int,
                   float, const int32_t*, int, const int32_t*, const float*, int64_t, int64_t,
-                  int64_t, int, int, const float*, const float*, const FusedWrite*, int, int,
-                  cudaStream_t);
+                  int64_t, int, int, const float*, const float*, const FusedWrite*, int64_t, int,
+                  int, cudaStream_t);
+bool stream_flash_supported(const void*, const void*, const void*, int, int, int, int, int64_t,
+                            int64_t, int64_t, int64_t, int, int);
 bool stream_fused_supported(const FusedWrite&, int);
 int64_t stream_workspace_bytes(int, int);
 int launch_merge_attn_states(void*, float*, const void*, const float*, const void*, const float*,
@@ -183,7 +185,7 @@ static int paged_attention_common(
                          num_heads, num_kv_heads, head_size, scale, block_tables,
                          max_num_blocks_per_seq, seq_lens, alibi_slopes, q_stride,
                          kv_block_stride, kv_head_stride, scalar_type, kv_dtype, k_scale, v_scale,
-                         fused, num_sms(), stream_tune(), stream);
+                         fused, 0, num_sms(), stream_tune(), stream);
   }
   int rc = launch_generic(out, lse, lse_seq_stride, lse_head_stride, exp_sums, max_logits, tmp_out, query, key_cache, value_cache,
                           num_seqs, num_heads, num_kv_heads, head_size, block_size, scale,
@@ -302,6 +304,59 @@ int b200pa_decode_step(
                                 q_stride, kv_block_stride, kv_head_stride, scalar_type, kv_dtype,
                                 k_scale, v_scale, 0, 0, 0, 64, 0, workspace, workspace_bytes,
                                 stream, &fw);
+}
+
+int b200pa_paged_attention_flash(
+    void* out, float* lse, int64_t lse_seq_stride, int64_t lse_head_stride, const void* query,
+    const void* key, const void* value, int64_t key_stride, int64_t value_stride,
+    const int64_t* slot_mapping, void* key_cache, void* value_cache, int num_seqs, int num_heads,
+    int num_kv_heads, int head_size, int block_size, float scale, const int32_t* block_tables,
+    int max_num_blocks_per_seq, const int32_t* seq_lens, int max_seq_len,
+    const float* alibi_slopes, int64_t q_stride, int64_t block_stride, int64_t page_stride,
+    int64_t head_stride, int scalar_type, int kv_dtype, const float* k_scale,
+    const float* v_scale, void* workspace, int64_t workspace_bytes, void* stream_v) {
+  (void)max_seq_len;
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
+  if (!out || !query || !key_cache || !value_cache || !block_tables || !seq_lens)
+    return set_error(B200PA_ERR_INVALID, "null tensor pointer");
+  if (num_seqs < 0 || num_heads <= 0 || num_kv_heads <= 0 || num_heads % num_kv_heads != 0)
+    return set_error(B200PA_ERR_INVALID, "num_heads %d must be a positive multiple of num_kv_heads %d",
+                     num_heads, num_kv_heads);
+  if (kv_dtype != B200PA_KV_AUTO && (!k_scale || !v_scale))
+    return set_error(B200PA_ERR_INVALID, "fp8 kv cache needs k_scale and v_scale");
+  if (head_size != 64 && head_size != 128)
+    return set_error(B200PA_ERR_UNSUPPORTED, "Unsupported head size: %d (flash layout: 64, 128)",
+                     head_size);
+  if (block_size != 16)
+    return set_error(B200PA_ERR_UNSUPPORTED, "Unsupported block size: %d (flash layout: 16)",
+                     block_size);
+  if (!stream_flash_supported(query, key_cache, value_cache, num_heads, num_kv_heads, head_size,
+                              block_size, q_stride, block_stride, page_stride, head_stride,
+                              scalar_type, kv_dtype))
+    return set_error(B200PA_ERR_UNSUPPORTED,
+                     "paged_attention_flash: needs a 16-bit query, an auto or fp8_e4m3 cache and "
+                     "16-byte aligned cache rows");
+  const bool want_write = key || value || slot_mapping;
+  if (want_write && (!key || !value || !slot_mapping))
+    return set_error(B200PA_ERR_INVALID, "paged_attention_flash: key, value and slot_mapping go together");
+  if (num_seqs == 0) return B200PA_OK;
+  FusedWrite fw{key, value, key_stride, value_stride, slot_mapping};
+  const FusedWrite* fused = want_write ? &fw : nullptr;
+  if (fused && !stream_fused_supported(fw, scalar_type)) {
+    // rows the fused path cannot load: the write it stands for, as its own launch
+    int rc = launch_reshape_and_cache_flash(key, value, key_cache, value_cache, slot_mapping,
+                                            num_seqs, key_stride, value_stride, block_stride,
+                                            page_stride, head_stride, num_kv_heads, head_size,
+                                            block_size, scalar_type, kv_dtype, k_scale, v_scale,
+                                            stream);
+    if (rc) return rc;
+    fused = nullptr;
+  }
+  return launch_stream(out, lse, lse_seq_stride, lse_head_stride, workspace, workspace_bytes, query,
+                       key_cache, value_cache, num_seqs, num_heads, num_kv_heads, head_size, scale,
+                       block_tables, max_num_blocks_per_seq, seq_lens, alibi_slopes, q_stride,
+                       block_stride, head_stride, scalar_type, kv_dtype, k_scale, v_scale, fused,
+                       page_stride, num_sms(), 0, stream);
 }
 
 int b200pa_merge_attn_states(void* output, float* output_lse, const void* prefix_output,

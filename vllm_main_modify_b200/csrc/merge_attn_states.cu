@@ -117,11 +117,16 @@ correct_attn_out_kernel(typename Scalar<ST>::type* __restrict__ out, float* __re
     row[d] = Scalar<ST>::from_float(Scalar<ST>::to_float(row[d]) * factor);
 }
 
-// 16-byte variant (rows 16-byte aligned, head_size a multiple of the pack): one thread per
-// pack, the row's LSEs re-read by its packs_per_head neighbours (L1 broadcast), row data
-// streamed with one 16-byte load and one 16-byte store per thread.
+// 16-byte variant (rows 16-byte aligned, head_size a multiple of the pack).  A CTA owns
+// kCorrPacks consecutive 16-byte packs (64 rows at head size 128, 16-bit): every thread first
+// issues the loads of its kCorrU packs, then one thread per ROW computes that row's total LSE
+// and factor (the ranks' LSEs 8 loads at a time) into shared memory, then the packs are scaled
+// and stored.  (One thread per pack each recomputing the row's log-sum-exp was issue-bound:
+// ~350 instructions per 32 bytes moved, 0.39 of the HBM peak in tools/opbench.py.)
+constexpr int kCorrThreads = 256, kCorrU = 4, kCorrPacks = kCorrThreads * kCorrU;
+
 template <int ST>
-__global__ void __launch_bounds__(kMergeThreads)
+__global__ void __launch_bounds__(kCorrThreads)
 correct_attn_out_vec_kernel(typename Scalar<ST>::type* __restrict__ out,
                             float* __restrict__ lse_out, const float* __restrict__ lses,
                             int num_ranks, int rank, unsigned total, unsigned num_heads,
@@ -130,30 +135,67 @@ correct_attn_out_vec_kernel(typename Scalar<ST>::type* __restrict__ out,
                             int64_t lses_seq_stride, int64_t lses_head_stride) {
   using T = typename Scalar<ST>::type;
   constexpr int PACK = 16 / (int)sizeof(T);
-  const unsigned idx = blockIdx.x * kMergeThreads + threadIdx.x;
-  if (idx >= total) return;
-  const unsigned row = idx / packs_per_head;
-  const unsigned pack = idx - row * packs_per_head;
-  const unsigned b = row / num_heads;
-  const unsigned h = row - b * num_heads;
-  uint4* ptr = reinterpret_cast<uint4*>(out + b * out_seq_stride + h * out_head_stride) + pack;
-  const uint4 v = __ldcs(ptr);
-  const float* l0 = lses + b * lses_seq_stride + h * lses_head_stride;
-  float mx = -INFINITY;
-  for (int n = 0; n < num_ranks; ++n) mx = fmaxf(mx, lse_clean(__ldg(l0 + n * lses_rank_stride)));
-  float acc = 0.f;
-  for (int n = 0; n < num_ranks; ++n)
-    acc += expf(lse_clean(__ldg(l0 + n * lses_rank_stride)) - mx);
-  const float lse = logf(acc) + mx;
-  if (pack == 0) lse_out[b * lses_seq_stride + h * lses_head_stride] = lse;
-  const float factor = expf(lse_clean(__ldg(l0 + rank * lses_rank_stride) - lse));
-  uint4 o;
-  const T* ve = reinterpret_cast<const T*>(&v);
-  T* oe = reinterpret_cast<T*>(&o);
+  __shared__ float fac_s[kCorrPacks + 1];
+  const unsigned p0 = blockIdx.x * kCorrPacks;
+  const unsigned p1 = min(p0 + (unsigned)kCorrPacks, total);
+  const unsigned row0 = p0 / packs_per_head, row1 = (p1 - 1) / packs_per_head;
+  uint4* ptr[kCorrU];
+  uint4 v[kCorrU];
+  unsigned lrow[kCorrU];
 #pragma unroll
-  for (int i = 0; i < PACK; ++i)
-    oe[i] = Scalar<ST>::from_float(Scalar<ST>::to_float(ve[i]) * factor);
-  __stcs(ptr, o);
+  for (int u = 0; u < kCorrU; ++u) {
+    const unsigned idx = p0 + u * kCorrThreads + threadIdx.x;
+    const unsigned row = idx / packs_per_head;
+    const unsigned pack = idx - row * packs_per_head;
+    const unsigned b = row / num_heads;
+    const unsigned h = row - b * num_heads;
+    lrow[u] = row - row0;
+    ptr[u] = reinterpret_cast<uint4*>(out + b * out_seq_stride + h * out_head_stride) + pack;
+    if (idx < p1) v[u] = __ldcs(ptr[u]);
+  }
+  for (unsigned i = threadIdx.x; i <= row1 - row0; i += kCorrThreads) {
+    const unsigned row = row0 + i;
+    const unsigned b = row / num_heads;
+    const unsigned h = row - b * num_heads;
+    const float* l0 = lses + b * lses_seq_stride + h * lses_head_stride;
+    const float mine = lse_clean(__ldg(l0 + rank * lses_rank_stride));
+    constexpr int CH = 8;
+    float mx = -INFINITY, acc = 0.f;
+    for (int n0 = 0; n0 < num_ranks; n0 += CH) {
+      float l[CH];
+#pragma unroll
+      for (int j = 0; j < CH; ++j)
+        l[j] = (n0 + j < num_ranks) ? lse_clean(__ldg(l0 + (n0 + j) * lses_rank_stride)) : -INFINITY;
+      float nm = mx;
+#pragma unroll
+      for (int j = 0; j < CH; ++j) nm = fmaxf(nm, l[j]);
+      if (nm == -INFINITY) continue;   // nothing but empty ranks so far
+      float sum = expf(l[0] - nm);
+#pragma unroll
+      for (int j = 1; j < CH; ++j)
+        if (n0 + j < num_ranks) sum += expf(l[j] - nm);
+      acc = acc * expf(mx - nm) + sum;
+      mx = nm;
+    }
+    // every rank empty: -inf - -inf = NaN in the reference (common.py:44-50)
+    const float lse = mx == -INFINITY ? __int_as_float(0x7fc00000) : logf(acc) + mx;
+    if (row * packs_per_head >= p0)   // the CTA that holds the row's first pack
+      lse_out[b * lses_seq_stride + h * lses_head_stride] = lse;
+    fac_s[i] = expf(lse_clean(mine - lse));
+  }
+  __syncthreads();
+#pragma unroll
+  for (int u = 0; u < kCorrU; ++u) {
+    if (p0 + u * kCorrThreads + threadIdx.x >= p1) continue;
+    const float factor = fac_s[lrow[u]];
+    uint4 o;
+    const T* ve = reinterpret_cast<const T*>(&v[u]);
+    T* oe = reinterpret_cast<T*>(&o);
+#pragma unroll
+    for (int i = 0; i < PACK; ++i)
+      oe[i] = Scalar<ST>::from_float(Scalar<ST>::to_float(ve[i]) * factor);
+    __stcs(ptr[u], o);
+  }
 }
 
 }  // namespace
@@ -203,10 +245,10 @@ int launch_correct_attn_out(void* out, float* lse_out, const float* lses, int nu
   const int pack = scalar_type == B200PA_F32 ? 4 : 8;
   const int64_t vec_total = warps * (head_size / pack);
   if (head_size % pack == 0 && out_seq_stride % pack == 0 && out_head_stride % pack == 0 &&
-      ((uintptr_t)out & 15) == 0 && vec_total < (1LL << 32) - kMergeThreads) {
-    const dim3 vgrid((unsigned)((vec_total + kMergeThreads - 1) / kMergeThreads));
+      ((uintptr_t)out & 15) == 0 && vec_total < (1LL << 32) - kCorrPacks) {
+    const dim3 vgrid((unsigned)((vec_total + kCorrPacks - 1) / kCorrPacks));
 #define CORRECT_VEC_CALL(ST)                                                                 \
-  correct_attn_out_vec_kernel<ST><<<vgrid, kMergeThreads, 0, stream>>>(                      \
+  correct_attn_out_vec_kernel<ST><<<vgrid, kCorrThreads, 0, stream>>>(                      \
       (typename Scalar<ST>::type*)out, lse_out, lses, num_ranks, rank, (unsigned)vec_total,  \
       (unsigned)num_heads, (unsigned)(head_size / pack), out_seq_stride, out_head_stride,    \
       lses_rank_stride, lses_seq_stride, lses_head_stride)

@@ -90,6 +90,17 @@ __device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], uint32_t addr) {
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
                : "r"(addr));
 }
+__device__ __forceinline__ void ldmatrix_x4_trans(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
+template <uint32_t SEL>
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b) {
+  uint32_t d;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "n"(SEL));
+  return d;
+}
 __device__ __forceinline__ uint32_t movmatrix_trans(uint32_t a) {
   uint32_t d;
   asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(d) : "r"(a));
@@ -161,6 +172,7 @@ struct StreamParams {
   const int64_t* slot_mapping;
   int64_t new_key_stride, new_value_stride;           // elements per token
   int64_t q_stride, kv_block_stride, kv_head_stride;  // elements
+  int64_t kv_token_stride;   // flash layout only: elements between two tokens of a block
   int num_seqs, num_heads, num_kv_heads, group;       // group = num_heads / num_kv_heads
   int h_tiles;                                         // ceil(group / 8)
   int max_num_blocks_per_seq;
@@ -253,38 +265,55 @@ __device__ __forceinline__ void cursor_next_piece(Cursor& c, const int32_t* seq_
 // Final output of one (sequence, 8-head tile) from O^T fragments: scale, round to scalar_t,
 // transpose each 8x8 (d, head) block with movmatrix so that every lane stores 32-bit pairs.
 // o[mt][j]: j = 0,1 -> d = 16mt + r, heads 2q, 2q+1 ; j = 2,3 -> d = 16mt + r + 8.
-template <int ST, int D>
+// DPERM (fp8 pages of the flash layout): the m-tile's rows are permuted, o[mt][0,1] holding
+// d = 16mt + 2r and o[mt][2,3] d = 16mt + 2r + 1 -- after the transposes lane (r, q) holds head r,
+// d = 16mt + 4q .. 4q+3: one 8-byte store.
+template <int ST, int D, bool DPERM>
 __device__ __forceinline__ void store_out_tile(typename Scalar<ST>::type* out_tile,  // [8 heads][D]
                                                int mt, const float (&o)[4], float inv0, float inv1,
                                                int heads_valid, int r, int q4) {
   constexpr bool BF = (ST == B200PA_BF16);
-  uint32_t* dst = reinterpret_cast<uint32_t*>(out_tile + (int64_t)r * D + 2 * q4);
   const uint32_t lo = movmatrix_trans(pack2<BF>(o[0] * inv0, o[1] * inv1));
   const uint32_t hi = movmatrix_trans(pack2<BF>(o[2] * inv0, o[3] * inv1));
-  if (r < heads_valid) {          // after the transpose lane (r, q) holds head r
-    dst[8 * mt] = lo;             // d = 16mt + 2q, 2q+1
-    dst[8 * mt + 4] = hi;         // d = 16mt + 8 + 2q, 2q+1
+  if constexpr (DPERM) {
+    if (r < heads_valid)
+      *reinterpret_cast<uint2*>(out_tile + (int64_t)r * D + 16 * mt + 4 * q4) =
+          make_uint2(prmt<0x5410>(lo, hi), prmt<0x7632>(lo, hi));
+  } else {
+    uint32_t* dst = reinterpret_cast<uint32_t*>(out_tile + (int64_t)r * D + 2 * q4);
+    if (r < heads_valid) {          // after the transpose lane (r, q) holds head r
+      dst[8 * mt] = lo;             // d = 16mt + 2q, 2q+1
+      dst[8 * mt + 4] = hi;         // d = 16mt + 8 + 2q, 2q+1
+    }
   }
 }
-template <int ST, int D>
+template <int ST, int D, bool DPERM>
 __device__ __forceinline__ void store_out(typename Scalar<ST>::type* out_tile,
                                           const float (&o)[D / 16][4], float inv0, float inv1,
                                           int heads_valid, int r, int q4) {
 #pragma unroll
   for (int mt = 0; mt < D / 16; ++mt)
-    store_out_tile<ST, D>(out_tile, mt, o[mt], inv0, inv1, heads_valid, r, q4);
+    store_out_tile<ST, D, DPERM>(out_tile, mt, o[mt], inv0, inv1, heads_valid, r, q4);
 }
 
 // ST: B200PA_F16 | B200PA_BF16 (query/out type).  FP8: kv cache is e4m3 bytes.
 // PPS: pages per pipeline stage.
-template <int ST, bool FP8, int D, int NW, int STAGES, int PPS, int MINB>
+// FLASH: the cache is token-major, [block][token][head][D] by strides (NHD or HND, what
+// reshape_and_cache_flash writes): every token row of D elements is one bulk copy into a shared
+// row padded by 16 bytes (conflict-free ldmatrix), K fragments come from plain and V fragments
+// from transposing ldmatrix.
+template <int ST, bool FP8, int D, int NW, int STAGES, int PPS, int MINB, bool FLASH>
 __global__ void __launch_bounds__(NW * 32, MINB)
 paged_attention_stream_kernel(const StreamParams p) {
   using T = typename Scalar<ST>::type;
   constexpr bool MMA_BF16 = (!FP8) && (ST == B200PA_BF16);  // fp8 pages compute in f16
   constexpr int CES = FP8 ? 1 : 2;                           // cache element bytes
   constexpr int PAGE_BYTES = D * kBS * CES;                  // one K (or V) page of one kv head
-  constexpr int STAGE_BYTES = PPS * 2 * PAGE_BYTES;
+  constexpr int ROW_DATA = D * CES;                          // flash: one token row of one head
+  constexpr int ROWB = ROW_DATA + 16;                        // ... and its padded shared-memory row
+  constexpr int PAGE_SMEM = FLASH ? kBS * ROWB : PAGE_BYTES; // shared-memory footprint of a page
+  constexpr int STAGE_BYTES = PPS * 2 * PAGE_SMEM;
+  constexpr bool DPERM = FLASH && FP8;                       // see store_out_tile
   constexpr int KSTEPS = D / 16;                             // QK k-steps
   constexpr int MT = D / 16;                                 // PV m-tiles (16 head elements each)
   constexpr int RING_BYTES = STAGES * STAGE_BYTES;
@@ -369,7 +398,24 @@ paged_attention_stream_kernel(const StreamParams p) {
     int phys[PPS];
 #pragma unroll
     for (int g = 0; g < PPS; ++g) phys[g] = __shfl_sync(kFull, bt_reg, (page0 + g) & 31);
-    if (lane == 0) {
+    if constexpr (FLASH) {
+      const int s = ip % STAGES;
+      const uint32_t bar = bar0 + 8 * s;
+      if (lane == 0) mbar_expect_tx(bar, npg * 2 * PAGE_BYTES);
+      __syncwarp();
+      // lanes 0-15: K row of token lane; lanes 16-31: V row of token lane - 16
+      const int tok = lane & 15;
+      const bool isv = lane >= 16;
+      const int kvh = pc.vh / p.h_tiles;
+      const uint8_t* src = reinterpret_cast<const uint8_t*>(isv ? p.v_cache : p.k_cache) +
+                           kvh * head_stride_bytes + tok * p.kv_token_stride * CES;
+      const uint32_t dst = ring_u32 + s * STAGE_BYTES + (isv ? PAGE_SMEM : 0) + tok * ROWB;
+#pragma unroll
+      for (int g = 0; g < PPS; ++g)
+        if (g < npg)
+          tma_load_1d(dst + g * 2 * PAGE_SMEM, src + (int64_t)phys[g] * blk_stride_bytes, ROW_DATA,
+                      bar, policy);
+    } else if (lane == 0) {
       const int s = ip % STAGES;
       const uint32_t bar = bar0 + 8 * s;
       const uint32_t dst = ring_u32 + s * STAGE_BYTES;
@@ -401,16 +447,31 @@ paged_attention_stream_kernel(const StreamParams p) {
   const bool has_alibi = p.alibi_slopes != nullptr;
   float sl2 = p.scale * kLog2e;
   float out_scale = 1.f;
+  float ks_raw = 1.f;           // k_scale itself (the fused cache write quantises with it)
   if constexpr (FP8) {
-    sl2 *= *p.k_scale;
+    ks_raw = *p.k_scale;
+    sl2 *= ks_raw;
     out_scale = *p.v_scale;
   }
+  // fused cache write: this lane's EPL head elements of the new token's K and V (raw scalar_t
+  // pairs) and its slot, fetched when a piece that reaches the end of its sequence begins
+  constexpr int EPL = D / 32;
+  uint32_t nt_k[EPL / 2], nt_v[EPL / 2];
+  int64_t nt_slot = -1;
 
   // ldmatrix lane addressing
   const int mat = lane >> 3, mi = lane & 7;
   uint32_t k_lane_off, v_lane_off;
   int tokA, tokB;  // tokens (within the page) of accumulator rows r and r + 8
-  if constexpr (FP8) {
+  if constexpr (FLASH) {
+    // K x4 (plain) = {tok 0-7, 16 B | tok 8-15, same 16 B | tok 0-7, next 16 B | tok 8-15, next}
+    // V x4 (transposing): 16-bit {tok 0-7, d 0-7 | tok 0-7, d 8-15 | tok 8-15, d 0-7 | tok 8-15,
+    // d 8-15}; fp8 {tok 0-7, d 0-15 | tok 8-15, d 0-15 | tok 0-7, d 16-31 | tok 8-15, d 16-31}
+    k_lane_off = ((mat & 1) * 8 + mi) * ROWB + (mat >> 1) * 16;
+    v_lane_off = FP8 ? k_lane_off : ((mat >> 1) * 8 + mi) * ROWB + (mat & 1) * 16;
+    tokA = r;
+    tokB = r + 8;
+  } else if constexpr (FP8) {
     // K x4 = {chunk c, slots 0-7 | chunk c, slots 8-15 | chunk c+1, slots 0-7 | chunk c+1, 8-15}
     // (chunk = 16 head elements).  Slot i < 8 is token sig0(i) = 4(i/2) + (i%2) + (i >= 4 ? 2 : 0)
     // and slot 8 + i is token sig0(i) ^ 2: both halves touch 8 distinct 16-byte bank groups, and
@@ -435,6 +496,21 @@ paged_attention_stream_kernel(const StreamParams p) {
   auto begin_piece = [&]() {
     piece_begin = cc.st;
     const int kvh = cc.vh / p.h_tiles;
+    if (p.new_key != nullptr) {
+      nt_slot = -1;
+      if (cc.st_end == cc.ns) {
+        nt_slot = p.slot_mapping[cc.b];
+        const T* kn = reinterpret_cast<const T*>(p.new_key) + (int64_t)cc.b * p.new_key_stride +
+                      (int64_t)kvh * D + lane * EPL;
+        const T* vn = reinterpret_cast<const T*>(p.new_value) + (int64_t)cc.b * p.new_value_stride +
+                      (int64_t)kvh * D + lane * EPL;
+#pragma unroll
+        for (int j = 0; j < EPL / 2; ++j) {
+          nt_k[j] = reinterpret_cast<const uint32_t*>(kn)[j];
+          nt_v[j] = reinterpret_cast<const uint32_t*>(vn)[j];
+        }
+      }
+    }
     const int tile = cc.vh - kvh * p.h_tiles;
     head0 = kvh * p.group + tile * 8;
     heads_valid = min(8, p.group - tile * 8);
@@ -489,7 +565,7 @@ paged_attention_stream_kernel(const StreamParams p) {
       // the piece is the whole (sequence, head tile): final result
       const float inv0 = out_scale * __fdividef(1.f, lsum[0] + 1e-6f);
       const float inv1 = out_scale * __fdividef(1.f, lsum[1] + 1e-6f);
-      store_out<ST, D>(reinterpret_cast<T*>(p.out) + ((int64_t)cc.b * p.num_heads + head0) * D, o,
+      store_out<ST, D, DPERM>(reinterpret_cast<T*>(p.out) + ((int64_t)cc.b * p.num_heads + head0) * D, o,
                        inv0, inv1, heads_valid, r, q4);
       if (p.lse != nullptr && r == 0) {
 #pragma unroll
@@ -538,70 +614,69 @@ paged_attention_stream_kernel(const StreamParams p) {
     mbar_wait(bar0 + 8 * s, (i / STAGES) & 1);
 
     // ---- fused cache write: the stage that ends the sequence holds position len - 1, whose
-    // K/V come from this step's key/value rows (quantised exactly as reshape_and_cache does),
-    // not from the bytes the TMA copy found in the cache.
-    if (p.new_key != nullptr && cc.st == cc.ns) {
-      const int64_t slot = p.slot_mapping[cc.b];
-      if (slot >= 0) {
-        constexpr int X = 16 / CES;       // elements per 16-byte chunk of the x-packed K layout
-        const int t = cc.len - 1 - page0 * kBS;
-        uint8_t* pg = ring + s * STAGE_BYTES + (t >> 4) * (2 * PAGE_BYTES);
-        const int tt = t & 15;
-        const int kvh = cc.vh / p.h_tiles;
-        const bool to_global = cc.vh == kvh * p.h_tiles;
-        const T* kn = reinterpret_cast<const T*>(p.new_key) + (int64_t)cc.b * p.new_key_stride +
-                      (int64_t)kvh * D;
-        const T* vn = reinterpret_cast<const T*>(p.new_value) + (int64_t)cc.b * p.new_value_stride +
-                      (int64_t)kvh * D;
-        const int64_t goff = (slot / kBS) * blk_stride_bytes + kvh * head_stride_bytes;
-        const int off = (int)(slot % kBS);
-        uint8_t* kg = reinterpret_cast<uint8_t*>(const_cast<void*>(p.k_cache)) + goff;
-        uint8_t* vg = reinterpret_cast<uint8_t*>(const_cast<void*>(p.v_cache)) + goff;
-        if (lane < D / X) {
-          uint4 val;
-          if constexpr (FP8) {
-            const float ks = *p.k_scale;
-            uint4 raw[2];
-            raw[0] = reinterpret_cast<const uint4*>(kn + lane * X)[0];
-            raw[1] = reinterpret_cast<const uint4*>(kn + lane * X)[1];
-            const T* e = reinterpret_cast<const T*>(raw);
-            uint32_t w4[4];
+    // K/V come from this step's key/value rows (in registers since begin_piece, quantised here
+    // exactly as reshape_and_cache does), not from the bytes the TMA copy found in the cache.
+    if (p.new_key != nullptr && cc.st == cc.ns && nt_slot >= 0) {
+      constexpr int X = 16 / CES;       // elements per 16-byte chunk of the x-packed K layout
+      constexpr int NBYTES = EPL * CES; // bytes this lane contributes to the K (and V) row
+      const int t = cc.len - 1 - page0 * kBS;
+      uint8_t* pg = ring + s * STAGE_BYTES + (t >> 4) * (2 * PAGE_SMEM);
+      const int tt = t & 15;
+      const int kvh = cc.vh / p.h_tiles;
+      const bool to_global = cc.vh == kvh * p.h_tiles;
+      const int64_t goff = (nt_slot / kBS) * blk_stride_bytes + kvh * head_stride_bytes;
+      const int off = (int)(nt_slot % kBS);
+      uint8_t* kg = reinterpret_cast<uint8_t*>(const_cast<void*>(p.k_cache)) + goff;
+      uint8_t* vg = reinterpret_cast<uint8_t*>(const_cast<void*>(p.v_cache)) + goff;
+      const int e0 = lane * EPL;        // my head elements e0 .. e0+EPL-1
+      uint32_t kw[2] = {0u, 0u}, vw[2] = {0u, 0u};   // NBYTES packed cache bytes of K and of V
+      if constexpr (FP8) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const uint32_t lo = fp8_quant2<B200PA_KV_FP8_E4M3>(
-                  Scalar<ST>::to_float(e[4 * j + 0]), Scalar<ST>::to_float(e[4 * j + 1]), ks);
-              const uint32_t hi = fp8_quant2<B200PA_KV_FP8_E4M3>(
-                  Scalar<ST>::to_float(e[4 * j + 2]), Scalar<ST>::to_float(e[4 * j + 3]), ks);
-              w4[j] = lo | (hi << 16);
-            }
-            val = make_uint4(w4[0], w4[1], w4[2], w4[3]);
-          } else {
-            val = *reinterpret_cast<const uint4*>(kn + lane * X);
-          }
-          *reinterpret_cast<uint4*>(pg + (lane * kBS + tt) * 16) = val;
-          if (to_global) *reinterpret_cast<uint4*>(kg + (lane * kBS + off) * 16) = val;
+        for (int j = 0; j < EPL / 2; ++j) {
+          const T* ke = reinterpret_cast<const T*>(&nt_k[j]);
+          const T* ve = reinterpret_cast<const T*>(&nt_v[j]);
+          kw[0] |= (uint32_t)fp8_quant2<B200PA_KV_FP8_E4M3>(
+                       Scalar<ST>::to_float(ke[0]), Scalar<ST>::to_float(ke[1]), ks_raw) << (16 * j);
+          vw[0] |= (uint32_t)fp8_quant2<B200PA_KV_FP8_E4M3>(
+                       Scalar<ST>::to_float(ve[0]), Scalar<ST>::to_float(ve[1]), out_scale) << (16 * j);
         }
-        if constexpr (FP8) {
-          const float vs = *p.v_scale;
+      } else {
 #pragma unroll
-          for (int dd = 0; dd < D / 32; ++dd) {
-            const int e = dd * 32 + lane;
-            const uint8_t b8 = fp8_quant<B200PA_KV_FP8_E4M3>(Scalar<ST>::to_float(vn[e]), vs);
-            pg[PAGE_BYTES + e * kBS + tt] = b8;
-            if (to_global) vg[e * kBS + off] = b8;
-          }
-        } else {
-#pragma unroll
-          for (int dd = 0; dd < D / 32; ++dd) {
-            const int e = dd * 32 + lane;
-            const T v16 = vn[e];
-            reinterpret_cast<T*>(pg + PAGE_BYTES)[e * kBS + tt] = v16;
-            if (to_global) reinterpret_cast<T*>(vg)[e * kBS + off] = v16;
-          }
-        }
-        // generic-proxy stores to a buffer the TMA engine refills later
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        for (int j = 0; j < EPL / 2; ++j) { kw[j] = nt_k[j]; vw[j] = nt_v[j]; }
       }
+      auto put = [&](uint8_t* dst, const uint32_t (&w)[2]) {
+        if constexpr (NBYTES == 8) *reinterpret_cast<uint2*>(dst) = make_uint2(w[0], w[1]);
+        else if constexpr (NBYTES == 4) *reinterpret_cast<uint32_t*>(dst) = w[0];
+        else *reinterpret_cast<uint16_t*>(dst) = (uint16_t)w[0];
+      };
+      if constexpr (FLASH) {
+        // token-major rows: K and V of the token are contiguous runs
+        const int64_t tsb = p.kv_token_stride * CES;
+        put(pg + tt * ROWB + e0 * CES, kw);
+        put(pg + PAGE_SMEM + tt * ROWB + e0 * CES, vw);
+        if (to_global) {
+          put(kg + off * tsb + e0 * CES, kw);
+          put(vg + off * tsb + e0 * CES, vw);
+        }
+      } else {
+        const int kchunk = (e0 / X) * kBS * 16 + (e0 % X) * CES;    // + token * 16
+        put(pg + kchunk + tt * 16, kw);
+        if (to_global) put(kg + kchunk + off * 16, kw);
+#pragma unroll
+        for (int i = 0; i < EPL; ++i) {   // V [D][16]: one element per head-element row
+          if constexpr (FP8) {
+            const uint8_t b8 = (uint8_t)(vw[0] >> (8 * i));
+            pg[PAGE_SMEM + (e0 + i) * kBS + tt] = b8;
+            if (to_global) vg[(e0 + i) * kBS + off] = b8;
+          } else {
+            const uint16_t v16 = (uint16_t)(vw[i / 2] >> (16 * (i & 1)));
+            reinterpret_cast<uint16_t*>(pg + PAGE_SMEM)[(e0 + i) * kBS + tt] = v16;
+            if (to_global) reinterpret_cast<uint16_t*>(vg)[(e0 + i) * kBS + off] = v16;
+          }
+        }
+      }
+      // generic-proxy stores to a buffer the TMA engine refills later
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       __syncwarp();
     }
 
@@ -611,13 +686,13 @@ paged_attention_stream_kernel(const StreamParams p) {
     for (int g = 0; g < PPS; ++g) {
       sc[g][0] = sc[g][1] = sc[g][2] = sc[g][3] = 0.f;
       if (g < npg) {
-        const uint32_t kbase = sbase + g * 2 * PAGE_BYTES;
+        const uint32_t kbase = sbase + g * 2 * PAGE_SMEM;
         float sb[4] = {0.f, 0.f, 0.f, 0.f};
         if constexpr (FP8) {
 #pragma unroll
           for (int c = 0; c < KSTEPS; c += 2) {
             uint32_t w4[4], a[4];
-            ldmatrix_x4(w4, kbase + c * (kBS * 16) + k_lane_off);
+            ldmatrix_x4(w4, kbase + c * (FLASH ? 16 : kBS * 16) + k_lane_off);
             e4m3x4_to_f16x2x2(w4[0], a[0], a[2]);
             e4m3x4_to_f16x2x2(w4[1], a[1], a[3]);
             mma16816<false>(sc[g], a, qb[c][0], qb[c][1]);
@@ -629,7 +704,7 @@ paged_attention_stream_kernel(const StreamParams p) {
 #pragma unroll
           for (int ks = 0; ks < KSTEPS; ++ks) {
             uint32_t a[4];
-            ldmatrix_x4(a, kbase + ks * (2 * kBS * 16) + k_lane_off);
+            ldmatrix_x4(a, kbase + ks * (FLASH ? 32 : 2 * kBS * 16) + k_lane_off);
             if (ks & 1) mma16816<MMA_BF16>(sb, a, qb[ks][0], qb[ks][1]);
             else mma16816<MMA_BF16>(sc[g], a, qb[ks][0], qb[ks][1]);
           }
@@ -699,7 +774,7 @@ paged_attention_stream_kernel(const StreamParams p) {
       // 8x8 blocks (token slot x head) -> transpose -> B fragments (k = token, n = head)
       const uint32_t ta = movmatrix_trans(pack2<MMA_BF16>(pr[0], pr[1]));
       const uint32_t tb = movmatrix_trans(pack2<MMA_BF16>(pr[2], pr[3]));
-      if constexpr (FP8) {
+      if constexpr (FP8 && !FLASH) {
         pb[g][0] = (q4 >= 2) ? tb : ta;
         pb[g][1] = (q4 >= 2) ? ta : tb;
       } else {
@@ -711,18 +786,35 @@ paged_attention_stream_kernel(const StreamParams p) {
     // ---- O^T += V^T P^T
     auto pv = [&](int g, auto masked) {
       constexpr bool MASKED = decltype(masked)::value;
-      const uint32_t vbase = sbase + g * 2 * PAGE_BYTES + PAGE_BYTES;
+      const uint32_t vbase = sbase + g * 2 * PAGE_SMEM + PAGE_SMEM;
       // tail page: V columns past the context may hold NaN bit patterns; the reference
       // zeroes them (attention_kernels.cuh:415-425).  m01 masks a[0], a[1]; m23 a[2], a[3].
       uint32_t m01 = 0xffffffffu, m23 = 0xffffffffu;
       if constexpr (MASKED) {
         const int nv = cc.len - (tok0 + g * kBS);
-        const int t01 = FP8 ? 4 * q4 : 2 * q4;
-        const int t23 = FP8 ? 4 * q4 + 2 : 2 * q4 + 8;
+        const int t01 = (FP8 && !FLASH) ? 4 * q4 : 2 * q4;
+        const int t23 = (FP8 && !FLASH) ? 4 * q4 + 2 : 2 * q4 + 8;
         m01 = (t01 < nv ? 0x0000ffffu : 0u) | (t01 + 1 < nv ? 0xffff0000u : 0u);
         m23 = (t23 < nv ? 0x0000ffffu : 0u) | (t23 + 1 < nv ? 0xffff0000u : 0u);
       }
-      if constexpr (FP8) {
+      if constexpr (FP8 && FLASH) {
+        // transposed 8x8 blocks of byte PAIRS: w4[0] = tokens (2q, 2q+1) x d (2r, 2r+1) of the
+        // first 16 d, w4[1] the same for tokens + 8, w4[2], w4[3] for the next 16 d.  Rows of
+        // the m-tile are assigned d = 2r (a[0], a[2]) and d = 2r + 1 (a[1], a[3]): DPERM.
+#pragma unroll
+        for (int gg = 0; gg < D / 32; ++gg) {
+          uint32_t w4[4], a[4];
+          ldmatrix_x4_trans(w4, vbase + gg * 32 + v_lane_off);
+          e4m3x4_to_f16x2x2(prmt<0x6420>(w4[0], w4[1]), a[0], a[2]);
+          e4m3x4_to_f16x2x2(prmt<0x7531>(w4[0], w4[1]), a[1], a[3]);
+          if constexpr (MASKED) { a[0] &= m01; a[1] &= m01; a[2] &= m23; a[3] &= m23; }
+          mma16816<false>(o[2 * gg], a, pb[g][0], pb[g][1]);
+          e4m3x4_to_f16x2x2(prmt<0x6420>(w4[2], w4[3]), a[0], a[2]);
+          e4m3x4_to_f16x2x2(prmt<0x7531>(w4[2], w4[3]), a[1], a[3]);
+          if constexpr (MASKED) { a[0] &= m01; a[1] &= m01; a[2] &= m23; a[3] &= m23; }
+          mma16816<false>(o[2 * gg + 1], a, pb[g][0], pb[g][1]);
+        }
+      } else if constexpr (FP8) {
 #pragma unroll
         for (int gg = 0; gg < D / 32; ++gg) {
           uint32_t w4[4], a[4];
@@ -740,7 +832,8 @@ paged_attention_stream_kernel(const StreamParams p) {
 #pragma unroll
         for (int mt = 0; mt < MT; ++mt) {
           uint32_t a[4];
-          ldmatrix_x4(a, vbase + mt * (16 * 32) + v_lane_off);
+          if constexpr (FLASH) ldmatrix_x4_trans(a, vbase + mt * 32 + v_lane_off);
+          else ldmatrix_x4(a, vbase + mt * (16 * 32) + v_lane_off);
           if constexpr (MASKED) { a[0] &= m01; a[1] &= m01; a[2] &= m23; a[3] &= m23; }
           mma16816<MMA_BF16>(o[mt], a, pb[g][0], pb[g][1]);
         }
@@ -848,7 +941,7 @@ paged_attention_stream_kernel(const StreamParams p) {
 #pragma unroll
         for (int mt = 0; mt < MT; ++mt) {
           const float o4[4] = {acc[mt].x, acc[mt].y, acc[mt].z, acc[mt].w};
-          store_out_tile<ST, D>(dst, mt, o4, inv0, inv1, hv, r, q4);
+          store_out_tile<ST, D, DPERM>(dst, mt, o4, inv0, inv1, hv, r, q4);
         }
         if (p.lse != nullptr && r == 0) {
           if (2 * q4 < hv)
@@ -897,7 +990,7 @@ paged_attention_stream_kernel(const StreamParams p) {
 // stream serialisation, everything up to griddepcontrol.wait overlaps the main kernel.
 constexpr int kMergeWarps = 4;
 
-template <int ST, int D, int PPS>
+template <int ST, int D, int PPS, bool DPERM>
 __global__ void __launch_bounds__(32 * kMergeWarps)
 paged_attention_stream_merge_kernel(const StreamParams p) {
   using T = typename Scalar<ST>::type;
@@ -1009,7 +1102,7 @@ paged_attention_stream_merge_kernel(const StreamParams p) {
       const float4 v = acc_s[g][mt][lane];
       o[0] += v.x; o[1] += v.y; o[2] += v.z; o[3] += v.w;
     }
-    store_out_tile<ST, D>(reinterpret_cast<T*>(p.out) + ((int64_t)loc.b * p.num_heads + head0) * D,
+    store_out_tile<ST, D, DPERM>(reinterpret_cast<T*>(p.out) + ((int64_t)loc.b * p.num_heads + head0) * D,
                           mt, o, inv0, inv1, heads_valid, r, q4);
   }
   if (p.lse != nullptr && wv == 0 && r == 0) {
@@ -1024,10 +1117,11 @@ paged_attention_stream_merge_kernel(const StreamParams p) {
 // ---------------------------------------------------------------------------------------
 constexpr int kMaxWarpsPerSm = 16;
 
-template <int ST, bool FP8, int D, int NW, int STAGES, int PPS, int MINB>
+template <int ST, bool FP8, int D, int NW, int STAGES, int PPS, int MINB, bool FLASH = false>
 int launch_stream_t(StreamParams& p, int num_sms, int64_t workspace_bytes, cudaStream_t stream) {
-  constexpr int SMEM = NW * STAGES * PPS * 2 * D * kBS * (FP8 ? 1 : 2);
-  auto kern = paged_attention_stream_kernel<ST, FP8, D, NW, STAGES, PPS, MINB>;
+  constexpr int CES = FP8 ? 1 : 2;
+  constexpr int SMEM = NW * STAGES * PPS * 2 * kBS * (FLASH ? D * CES + 16 : D * CES);
+  auto kern = paged_attention_stream_kernel<ST, FP8, D, NW, STAGES, PPS, MINB, FLASH>;
   static int ctas_per_sm = 0;  // per instantiation
   if (ctas_per_sm == 0) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
@@ -1077,7 +1171,8 @@ int launch_stream_t(StreamParams& p, int num_sms, int64_t workspace_bytes, cudaS
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, paged_attention_stream_merge_kernel<ST, D, PPS>, p);
+    cudaError_t e = cudaLaunchKernelEx(
+        &cfg, paged_attention_stream_merge_kernel<ST, D, PPS, FLASH && FP8>, p);
     if (e != cudaSuccess)
       return set_error(B200PA_ERR_CUDA, "stream merge launch: %s", cudaGetErrorString(e));
     count_launch();
@@ -1114,12 +1209,32 @@ bool stream_supported(const void* query, const void* key_cache, const void* valu
   return true;
 }
 
-// The fused write reads the new key/value rows with 16-byte loads.
+// Token-major ("flash") caches: every token row of one head is one bulk copy.
+bool stream_flash_supported(const void* query, const void* key_cache, const void* value_cache,
+                            int num_heads, int num_kv_heads, int head_size, int block_size,
+                            int64_t q_stride, int64_t block_stride, int64_t token_stride,
+                            int64_t head_stride, int scalar_type, int kv_dtype) {
+  if (block_size != kBS) return false;
+  if (head_size != 64 && head_size != 128) return false;
+  if (scalar_type != B200PA_BF16 && scalar_type != B200PA_F16) return false;
+  if (kv_dtype != B200PA_KV_AUTO && kv_dtype != B200PA_KV_FP8_E4M3) return false;
+  if (num_kv_heads <= 0 || num_heads % num_kv_heads != 0) return false;
+  const int ces = kv_dtype == B200PA_KV_AUTO ? 2 : 1;
+  auto aligned = [](const void* p, uintptr_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; };
+  if (!aligned(key_cache, 16) || !aligned(value_cache, 16) || !aligned(query, 8)) return false;
+  if ((block_stride * ces) % 16 != 0 || (token_stride * ces) % 16 != 0 ||
+      (head_stride * ces) % 16 != 0) return false;
+  if (token_stride <= 0 || head_stride < head_size) return false;
+  if (q_stride % 4 != 0) return false;
+  return true;
+}
+
+// The fused write reads the new key/value rows with 4-byte loads (pairs of 16-bit elements).
 bool stream_fused_supported(const FusedWrite& f, int scalar_type) {
-  const int es = scalar_type == B200PA_F32 ? 4 : 2;
-  auto a16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };
-  return f.key && f.value && f.slot_mapping && a16(f.key) && a16(f.value) &&
-         (f.key_stride * es) % 16 == 0 && (f.value_stride * es) % 16 == 0;
+  if (scalar_type == B200PA_F32) return false;
+  auto a4 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 3u) == 0; };
+  return f.key && f.value && f.slot_mapping && a4(f.key) && a4(f.value) &&
+         f.key_stride % 2 == 0 && f.value_stride % 2 == 0;
 }
 
 int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_head_stride,
@@ -1129,7 +1244,10 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
                   int max_num_blocks_per_seq, const int32_t* seq_lens, const float* alibi_slopes,
                   int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
                   int scalar_type, int kv_dtype, const float* k_scale, const float* v_scale,
-                  const FusedWrite* fused, int num_sms, int tune, cudaStream_t stream) {
+                  const FusedWrite* fused, int64_t flash_token_stride, int num_sms, int tune,
+                  cudaStream_t stream) {
+  // flash_token_stride > 0: token-major cache (kv_block_stride / flash_token_stride /
+  // kv_head_stride are the strides of [block][token][head][D]); 0: the x-packed layout
   if (!workspace || (reinterpret_cast<uintptr_t>(workspace) & 15u))
     return set_error(B200PA_ERR_INVALID, "the stream kernel needs a 16-byte aligned workspace "
                      "(b200pa_paged_attention_workspace_bytes)");
@@ -1155,6 +1273,7 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
   p.q_stride = q_stride;
   p.kv_block_stride = kv_block_stride;
   p.kv_head_stride = kv_head_stride;
+  p.kv_token_stride = flash_token_stride;
   p.num_seqs = num_seqs;
   p.num_heads = num_heads;
   p.num_kv_heads = num_kv_heads;
@@ -1166,8 +1285,8 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
   p.scale = scale;
   const bool fp8 = kv_dtype == B200PA_KV_FP8_E4M3;
   // <ST, FP8, D, NW, STAGES, PPS, MINB>: fp8 stage = PPS x 4 KiB, 16-bit stage = PPS x 8 KiB (D=128)
-#define STREAM_CALL(ST, FP8V, DV, NWV, SG, PP, MB) \
-  return launch_stream_t<ST, FP8V, DV, NWV, SG, PP, MB>(p, num_sms, workspace_bytes, stream)
+#define STREAM_CALL(ST, FP8V, DV, NWV, SG, PP, MB, ...) \
+  return launch_stream_t<ST, FP8V, DV, NWV, SG, PP, MB, ##__VA_ARGS__>(p, num_sms, workspace_bytes, stream)
 #define STREAM_TUNE_FP8(ST, DV)                                        \
   switch (tune) {                                                      \
     case 1: STREAM_CALL(ST, true, DV, 4, 4, 2, 1);                     \
@@ -1189,6 +1308,17 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
     case 6: STREAM_CALL(ST, false, DV, 4, 6, 1, 1);                    \
     case 7: STREAM_CALL(ST, false, DV, 5, 4, 1, 1);                    \
     default: STREAM_CALL(ST, false, DV, 4, 4, 1, 1);                   \
+  }
+  if (flash_token_stride > 0) {
+    // one instantiation per (scalar_t, cache type, head size): the default shapes of the
+    // x-packed kernel (the padded rows make the fp8 D=128 ring 216 KiB)
+    if (scalar_type == B200PA_BF16) {
+      if (fp8) { if (head_size == 128) { STREAM_CALL(B200PA_BF16, true, 128, 8, 3, 2, 1, true); } else { STREAM_CALL(B200PA_BF16, true, 64, 4, 3, 2, 2, true); } }
+      else     { if (head_size == 128) { STREAM_CALL(B200PA_BF16, false, 128, 4, 4, 1, 1, true); } else { STREAM_CALL(B200PA_BF16, false, 64, 4, 3, 2, 2, true); } }
+    } else {
+      if (fp8) { if (head_size == 128) { STREAM_CALL(B200PA_F16, true, 128, 4, 3, 2, 2, true); } else { STREAM_CALL(B200PA_F16, true, 64, 4, 3, 2, 2, true); } }
+      else     { if (head_size == 128) { STREAM_CALL(B200PA_F16, false, 128, 4, 4, 1, 1, true); } else { STREAM_CALL(B200PA_F16, false, 64, 4, 3, 2, 2, true); } }
+    }
   }
   if (scalar_type == B200PA_BF16) {
     if (fp8) { if (head_size == 128) { STREAM_TUNE_FP8(B200PA_BF16, 128) } else { STREAM_CALL(B200PA_BF16, true, 64, 4, 3, 2, 2); } }

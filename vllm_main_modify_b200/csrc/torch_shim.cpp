@@ -238,6 +238,85 @@ void decode_step(torch::Tensor& out, const std::optional<torch::Tensor>& lse, to
       ws.defined() ? ws.numel() : 0, stream));
 }
 
+// Decode attention over the token-major cache of reshape_and_cache_flash:
+// key_cache / value_cache [num_blocks, block_size, num_kv_heads, head_size], NHD or HND by strides
+// (the logical shape the reference's flash backends use).  key / value / slot_mapping given:
+// the cache write happens in the same launch (b200pa_paged_attention_flash).
+void paged_attention_flash(torch::Tensor& out, const std::optional<torch::Tensor>& lse,
+                           torch::Tensor& query, const std::optional<torch::Tensor>& key,
+                           const std::optional<torch::Tensor>& value, torch::Tensor& key_cache,
+                           torch::Tensor& value_cache,
+                           const std::optional<torch::Tensor>& slot_mapping, double scale,
+                           torch::Tensor& block_tables, torch::Tensor& seq_lens,
+                           int64_t max_seq_len, const std::optional<torch::Tensor>& alibi_slopes,
+                           const std::string& kv_cache_dtype, torch::Tensor& k_scale,
+                           torch::Tensor& v_scale) {
+  check_cuda(query, "query");
+  const int kv = kv_code(kv_cache_dtype);
+  const int st = scalar_code(query.scalar_type());
+  check_cache_dtype(key_cache, query, kv, "key_cache");
+  check_cache_dtype(value_cache, query, kv, "value_cache");
+  TORCH_CHECK(key_cache.dim() == 4 && value_cache.dim() == 4,
+              "flash caches are [num_blocks, block_size, num_kv_heads, head_size]");
+  TORCH_CHECK(key_cache.stride(3) == 1 && value_cache.stride(3) == 1,
+              "head elements must be contiguous in the cache");
+  TORCH_CHECK(key_cache.strides() == value_cache.strides(),
+              "key_cache and value_cache must share their strides");
+  TORCH_CHECK(key_cache.size(3) == query.size(2), "head_size of cache and query differ");
+  TORCH_CHECK(block_tables.scalar_type() == at::ScalarType::Int, "block_tables must be int32");
+  TORCH_CHECK(seq_lens.scalar_type() == at::ScalarType::Int, "seq_lens must be int32");
+  TORCH_CHECK(out.is_contiguous(), "out must be contiguous");
+  TORCH_CHECK(query.stride(2) == 1 && query.stride(1) == query.size(2),
+              "query heads must be densely packed");
+  const int64_t num_kv_heads = key_cache.size(2);
+  float* lse_ptr = nullptr;
+  int64_t ls0 = 0, ls1 = 0;
+  if (lse.has_value()) {
+    TORCH_CHECK(lse->scalar_type() == at::ScalarType::Float && lse->dim() == 2 &&
+                    lse->size(0) == query.size(0) && lse->size(1) == query.size(1),
+                "lse must be float32 [num_seqs, num_heads]");
+    lse_ptr = lse->data_ptr<float>();
+    ls0 = lse->stride(0);
+    ls1 = lse->stride(1);
+  }
+  const void *kp = nullptr, *vp = nullptr;
+  const int64_t* sp = nullptr;
+  int64_t kst = 0, vst = 0;
+  TORCH_CHECK(key.has_value() == value.has_value() && key.has_value() == slot_mapping.has_value(),
+              "key, value and slot_mapping go together");
+  if (key.has_value()) {
+    TORCH_CHECK(key->scalar_type() == query.scalar_type() &&
+                    value->scalar_type() == query.scalar_type(),
+                "key / value dtype must match query");
+    TORCH_CHECK(slot_mapping->scalar_type() == at::ScalarType::Long, "slot_mapping must be int64");
+    TORCH_CHECK(key->size(0) == query.size(0) && value->size(0) == query.size(0) &&
+                    slot_mapping->size(0) == query.size(0),
+                "the fused write takes one new token per sequence");
+    TORCH_CHECK(key->size(1) == num_kv_heads && key->size(2) == query.size(2) &&
+                    key->stride(2) == 1 && key->stride(1) == key->size(2) &&
+                    value->stride(2) == 1 && value->stride(1) == value->size(2),
+                "key / value must be [num_seqs, num_kv_heads, head_size] with dense heads");
+    kp = key->data_ptr();
+    vp = value->data_ptr();
+    sp = slot_mapping->data_ptr<int64_t>();
+    kst = key->stride(0);
+    vst = value->stride(0);
+  }
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(query));
+  const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  const float* alibi = alibi_slopes ? reinterpret_cast<const float*>(alibi_slopes->data_ptr()) : nullptr;
+  const int64_t ws_bytes = b200pa_paged_attention_workspace_bytes((int)query.size(2));
+  const torch::Tensor ws = at::empty({ws_bytes}, query.options().dtype(at::kByte));
+  check_status(b200pa_paged_attention_flash(
+      out.data_ptr(), lse_ptr, ls0, ls1, query.data_ptr(), kp, vp, kst, vst, sp,
+      key_cache.data_ptr(), value_cache.data_ptr(), (int)query.size(0), (int)query.size(1),
+      (int)num_kv_heads, (int)query.size(2), (int)key_cache.size(1), (float)scale,
+      block_tables.data_ptr<int>(), (int)block_tables.size(1), seq_lens.data_ptr<int>(),
+      (int)max_seq_len, alibi, query.stride(0), key_cache.stride(0), key_cache.stride(1),
+      key_cache.stride(2), st, kv, reinterpret_cast<const float*>(k_scale.data_ptr()),
+      reinterpret_cast<const float*>(v_scale.data_ptr()), ws.data_ptr(), ws.numel(), stream));
+}
+
 // csrc/attention/merge_attn_states.cu:131-180 of the reference (same checks, same messages)
 void merge_attn_states(torch::Tensor& output, std::optional<torch::Tensor> output_lse,
                        const torch::Tensor& prefix_output, const torch::Tensor& prefix_lse,
@@ -541,6 +620,12 @@ constexpr const char* kSchemaStep =
     "    Tensor block_tables, Tensor seq_lens, int block_size,"
     "    int max_seq_len, Tensor? alibi_slopes,"
     "    str kv_cache_dtype, Tensor k_scale, Tensor v_scale) -> ()";
+constexpr const char* kSchemaFlash =
+    "paged_attention_flash("
+    "    Tensor! out, Tensor!? lse, Tensor query, Tensor? key, Tensor? value,"
+    "    Tensor! key_cache, Tensor! value_cache, Tensor? slot_mapping, float scale,"
+    "    Tensor block_tables, Tensor seq_lens, int max_seq_len, Tensor? alibi_slopes,"
+    "    str kv_cache_dtype, Tensor k_scale, Tensor v_scale) -> ()";
 constexpr const char* kSchemaCorrect =
     "correct_attn_out(Tensor! out, Tensor lses, int cp_rank) -> Tensor";
 constexpr const char* kSchemaReshape =
@@ -574,6 +659,8 @@ void define_extras(torch::Library& ops) {
   ops.impl("paged_attention_lse", torch::kCUDA, &paged_attention_lse);
   ops.def(kSchemaStep);
   ops.impl("decode_step", torch::kCUDA, &decode_step);
+  ops.def(kSchemaFlash);
+  ops.impl("paged_attention_flash", torch::kCUDA, &paged_attention_flash);
   ops.def(kSchemaCorrect);
   ops.impl("correct_attn_out", torch::kCUDA, &correct_attn_out);
 }

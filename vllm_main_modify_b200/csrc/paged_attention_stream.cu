@@ -85,6 +85,17 @@ __device__ __forceinline__ void tma_load_1d(uint32_t dst, const void* src, uint3
       "l"(src), "r"(bytes), "r"(bar), "l"(policy)
       : "memory");
 }
+// 16-byte asynchronous copy global -> shared (LDGSTS), L1 bypassed, L2 evict-first
+__device__ __forceinline__ void cp_async_16(uint32_t dst, const void* src, uint64_t policy) {
+  asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(dst), "l"(src),
+               "l"(policy)
+               : "memory");
+}
+// this thread's earlier cp.async copies arrive on the mbarrier when they have landed (the
+// arrival counts against the barrier's expected count: .noinc)
+__device__ __forceinline__ void cp_async_mbar_arrive(uint32_t bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
 __device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], uint32_t addr) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
@@ -366,7 +377,7 @@ paged_attention_stream_kernel(const StreamParams p) {
   const uint32_t bar0 = smem_u32(&bars[warp * STAGES]);
   if (lane == 0) {
 #pragma unroll
-    for (int s = 0; s < STAGES; ++s) mbar_init(bar0 + 8 * s, 1);
+    for (int s = 0; s < STAGES; ++s) mbar_init(bar0 + 8 * s, FLASH ? 32 : 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncwarp();
@@ -399,22 +410,36 @@ paged_attention_stream_kernel(const StreamParams p) {
 #pragma unroll
     for (int g = 0; g < PPS; ++g) phys[g] = __shfl_sync(kFull, bt_reg, (page0 + g) & 31);
     if constexpr (FLASH) {
+      // Token rows of one head are D elements apart from each other by the token stride: no
+      // single run to bulk-copy.  (One TMA bulk copy per 128/256-byte row reached 3.0 TB/s on
+      // every shape, profiles/r01e_kbench_flash.jsonl.)  16-byte cp.async granules instead,
+      // dealt to the lanes so that a warp instruction covers whole rows; every lane arrives
+      // once per stage on the stage's mbarrier (expected count 32).
+      constexpr int GR = ROW_DATA / 16;            // granules per token row
+      constexpr int PER_LANE = kBS * GR / 32;      // granules per lane per K (or V) page
       const int s = ip % STAGES;
       const uint32_t bar = bar0 + 8 * s;
-      if (lane == 0) mbar_expect_tx(bar, npg * 2 * PAGE_BYTES);
-      __syncwarp();
-      // lanes 0-15: K row of token lane; lanes 16-31: V row of token lane - 16
-      const int tok = lane & 15;
-      const bool isv = lane >= 16;
       const int kvh = pc.vh / p.h_tiles;
-      const uint8_t* src = reinterpret_cast<const uint8_t*>(isv ? p.v_cache : p.k_cache) +
-                           kvh * head_stride_bytes + tok * p.kv_token_stride * CES;
-      const uint32_t dst = ring_u32 + s * STAGE_BYTES + (isv ? PAGE_SMEM : 0) + tok * ROWB;
+      const int64_t tsb = p.kv_token_stride * CES;
+      const uint8_t* kc = reinterpret_cast<const uint8_t*>(p.k_cache) + kvh * head_stride_bytes;
+      const uint8_t* vc = reinterpret_cast<const uint8_t*>(p.v_cache) + kvh * head_stride_bytes;
+      const uint32_t dst = ring_u32 + s * STAGE_BYTES;
 #pragma unroll
-      for (int g = 0; g < PPS; ++g)
-        if (g < npg)
-          tma_load_1d(dst + g * 2 * PAGE_SMEM, src + (int64_t)phys[g] * blk_stride_bytes, ROW_DATA,
-                      bar, policy);
+      for (int g = 0; g < PPS; ++g) {
+        if (g < npg) {
+          const int64_t boff = (int64_t)phys[g] * blk_stride_bytes;
+#pragma unroll
+          for (int i = 0; i < PER_LANE; ++i) {
+            const int idx = i * 32 + lane;
+            const int row = idx / GR, col = idx % GR;
+            const int64_t goff = boff + row * tsb + col * 16;
+            const uint32_t soff = g * 2 * PAGE_SMEM + row * ROWB + col * 16;
+            cp_async_16(dst + soff, kc + goff, policy);
+            cp_async_16(dst + soff + PAGE_SMEM, vc + goff, policy);
+          }
+        }
+      }
+      cp_async_mbar_arrive(bar);
     } else if (lane == 0) {
       const int s = ip % STAGES;
       const uint32_t bar = bar0 + 8 * s;

@@ -11,9 +11,11 @@ meaning and error behaviour, so that registering this class as
 
 It is deliberately free of ``import vllm``: the classes below are structural
 twins of the ABCs, not subclasses, so the package works (and is tested) without
-the reference installed.  Scope: decode (one query token per sequence).  Prefill /
-chunked prefill are delegated by the caller, as the reference's paged-attention
-backends do (``cpu_attn.py:584-612``) -- see SURVEY.md section 8(f) row 1.
+the reference installed.  Scope: decode (one query token per sequence).  Batches
+with longer queries (prefill / chunked prefill / mixed), which the reference's
+paged-attention backends hand to a second kernel (``cpu_attn.py:584-612``), are
+served by the same decode kernel, one single-query attention per token
+(:func:`expand_queries_to_sequences`): correct, O(T x context) -- SURVEY.md 8(f) row 1.
 """
 from __future__ import annotations
 
@@ -53,6 +55,29 @@ class B200PagedAttentionMetadata:
     @property
     def num_decode_tokens(self) -> int:
         return self.num_actual_tokens if self.max_query_len <= 1 else 0
+
+
+def expand_queries_to_sequences(meta: "B200PagedAttentionMetadata"):
+    """Prefill / chunked-prefill / mixed batches on the decode kernel: every query token becomes
+    a single-query "sequence" that shares its sequence's block-table row and whose length is its
+    causal context (``seq_len - query_len + position + 1``), so the kernel's ``seq_lens`` mask IS
+    the causal mask.  The reference's paged backends delegate such batches to a second kernel
+    (``cpu_attn.py:584-612``, ``rocm_attn.py:360-426``); this keeps them on the one sm_100a
+    kernel -- O(T x context) KV reads, i.e. a correct fallback, not a prefill kernel.
+    Device-side indexing only (no host synchronisation): returns
+    ``(block_table[T, max_blocks], seq_lens[T])``."""
+    n = meta.num_actual_tokens
+    qsl = meta.query_start_loc
+    if qsl is None:
+        raise ValueError("batches with max_query_len > 1 need attn_metadata.query_start_loc")
+    num_seqs = qsl.shape[0] - 1
+    qsl = qsl.to(torch.int64)
+    qlens = qsl[1:] - qsl[:-1]
+    seqs = torch.arange(num_seqs, device=qsl.device)
+    seq_of_tok = torch.repeat_interleave(seqs, qlens, output_size=n)
+    pos = torch.arange(n, device=qsl.device) - qsl[seq_of_tok]
+    ctx = meta.seq_lens[:num_seqs].to(torch.int64)[seq_of_tok] - qlens[seq_of_tok] + pos + 1
+    return meta.block_table.index_select(0, seq_of_tok).contiguous(), ctx.to(torch.int32)
 
 
 class B200PagedAttentionMetadataBuilder:
@@ -164,9 +189,10 @@ class B200PagedAttentionImpl:
         if attn_metadata is None:        # profiling run
             return output
         if attn_metadata.max_query_len > 1:
-            raise NotImplementedError(
-                "B200PagedAttentionImpl implements the decode path; prefill / chunked prefill "
-                "batches must be routed to a prefill backend by the caller")
+            if self.need_to_return_lse_for_decode or self.dcp_world_size > 1:
+                raise NotImplementedError("decode context parallelism serves decode batches only")
+            return self._forward_multi_query(layer, query, key, value, kv_cache, attn_metadata,
+                                             output)
         n = attn_metadata.num_actual_tokens
         q = query.view(-1, self.num_heads, self.head_size)
         out = output.view(-1, self.num_heads, self.head_size)
@@ -209,6 +235,29 @@ class B200PagedAttentionImpl:
             q[:n], key_cache, value_cache, attn_metadata.block_table, attn_metadata.seq_lens,
             attn_metadata.max_seq_len, self.kv_cache_dtype, self.num_kv_heads, self.scale,
             self.alibi_slopes, layer._k_scale, layer._v_scale, output=out[:n])
+        return output
+
+    def _forward_multi_query(self, layer, query, key, value, kv_cache, attn_metadata, output):
+        """Batches with more than one query token per sequence (prefill, chunked prefill, mixed):
+        write every new token, then one single-query attention per token (see
+        :func:`expand_queries_to_sequences`)."""
+        n = attn_metadata.num_actual_tokens
+        q = query.view(-1, self.num_heads, self.head_size)
+        out = output.view(-1, self.num_heads, self.head_size)
+        key_cache, value_cache = PagedAttention.split_kv_cache(kv_cache, self.num_kv_heads,
+                                                               self.head_size)
+        if key is not None and value is not None:
+            PagedAttention.write_to_paged_cache(
+                key.view(-1, self.num_kv_heads, self.head_size),
+                value.view(-1, self.num_kv_heads, self.head_size), key_cache, value_cache,
+                attn_metadata.slot_mapping, self.kv_cache_dtype, layer._k_scale, layer._v_scale)
+        if self.alibi_slopes is not None and self.alibi_slopes.device != q.device:
+            self.alibi_slopes = self.alibi_slopes.to(q.device)
+        bt_tok, sl_tok = expand_queries_to_sequences(attn_metadata)
+        PagedAttention.forward_decode(
+            q[:n], key_cache, value_cache, bt_tok, sl_tok, attn_metadata.max_seq_len,
+            self.kv_cache_dtype, self.num_kv_heads, self.scale, self.alibi_slopes,
+            layer._k_scale, layer._v_scale, output=out[:n])
         return output
 
     def fused_output_quant_supported(self, quant_key: Any) -> bool:
@@ -300,10 +349,7 @@ class B200FlashLayoutAttentionImpl(B200PagedAttentionImpl):
             output = torch.empty_like(query)
         if attn_metadata is None:        # profiling run
             return output
-        if attn_metadata.max_query_len > 1:
-            raise NotImplementedError(
-                "B200FlashLayoutAttentionImpl implements the decode path; prefill / chunked "
-                "prefill batches must be routed to a prefill backend by the caller")
+        multi = attn_metadata.max_query_len > 1
         n = attn_metadata.num_actual_tokens
         q = query.view(-1, self.num_heads, self.head_size)
         out = output.view(-1, self.num_heads, self.head_size)
@@ -311,12 +357,17 @@ class B200FlashLayoutAttentionImpl(B200PagedAttentionImpl):
         if self.alibi_slopes is not None and self.alibi_slopes.device != q.device:
             self.alibi_slopes = self.alibi_slopes.to(q.device)
         want_lse = self.need_to_return_lse_for_decode or self.dcp_world_size > 1
+        if multi and want_lse:
+            raise NotImplementedError("decode context parallelism serves decode batches only")
+        block_table, seq_lens = attn_metadata.block_table, attn_metadata.seq_lens
+        if multi:   # prefill / chunked prefill / mixed: one single-query attention per token
+            block_table, seq_lens = expand_queries_to_sequences(attn_metadata)
         k = v = slots = None
         if key is not None and value is not None:
             k = key.view(-1, self.num_kv_heads, self.head_size)
             v = value.view(-1, self.num_kv_heads, self.head_size)
             slots = attn_metadata.slot_mapping.flatten()
-            fused = (self.fused_decode_step and not want_lse and k.shape[0] == n
+            fused = (self.fused_decode_step and not want_lse and not multi and k.shape[0] == n
                      and slots.numel() == n and attn_metadata.seq_lens.shape[0] == n)
             if not fused:
                 ops.reshape_and_cache_flash(k, v, key_cache, value_cache, slots,
@@ -328,8 +379,7 @@ class B200FlashLayoutAttentionImpl(B200PagedAttentionImpl):
             part = torch.empty_like(q[:n])
             lse = torch.empty(n, self.num_heads, dtype=torch.float32, device=q.device)
         ops.paged_attention_flash(part, lse, q[:n], k, v, key_cache, value_cache, slots, self.scale,
-                                  attn_metadata.block_table, attn_metadata.seq_lens,
-                                  attn_metadata.max_seq_len, self.alibi_slopes,
+                                  block_table, seq_lens, attn_metadata.max_seq_len, self.alibi_slopes,
                                   self.kv_cache_dtype, layer._k_scale, layer._v_scale)
         if want_lse:
             from .dcp import cp_lse_ag_out_rs

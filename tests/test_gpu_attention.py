@@ -112,14 +112,14 @@ def _alibi(H):
 @pytest.mark.parametrize("impl", [GENERIC, STREAM])
 @pytest.mark.parametrize("use_alibi", [False, True])
 @pytest.mark.parametrize("heads", [(40, 40), (64, 8)])
-@pytest.mark.parametrize("head_size", [32, 64, 80, 128, 256])
+@pytest.mark.parametrize("head_size", [32, 64, 80, 96, 128, 192, 256])
 @pytest.mark.parametrize("block_size", [16, 32])
 @pytest.mark.parametrize("kv", ["auto", "fp8"])
 def test_paged_attention_sweep(ops, native, ora, version, impl, heads, head_size, block_size,
                                use_alibi, kv):
     H, Hkv = heads
     dtype = torch.bfloat16
-    stream_ok = block_size == 16 and head_size in (64, 128)
+    stream_ok = block_size == 16 and head_size in (32, 64, 96, 128, 192, 256)
     if impl == STREAM and not stream_ok:
         pytest.skip("shape served by the generic kernel")
     if kv == "fp8" and head_size % 16:
@@ -373,6 +373,13 @@ SCHED_CASES = [
     ("one_long_bf16", 1, 8, 1, 128, [70001], torch.bfloat16, "auto", False, 20.0),
     ("one_long_fp8", 1, 64, 8, 128, [131072], torch.bfloat16, "fp8", False, 20.0),
     ("tiny", 2, 8, 8, 128, [1, 2], torch.bfloat16, "auto", False, 1.0),
+    ("gemma_d256_fp8", 5, 16, 8, 256, [1000, 17, 512, 4100, 3333], torch.bfloat16, "fp8", False, 10.0),
+    ("gemma_d256_bf16", 5, 16, 8, 256, [1000, 17, 512, 4100, 3333], torch.bfloat16, "auto", False, 10.0),
+    ("d192_f16_fp8_alibi", 4, 24, 3, 192, [700, 33, 2049, 16], torch.float16, "fp8", True, 5.0),
+    ("phi_d96_bf16", 6, 32, 32, 96, [1, 16, 17, 999, 2048, 31], torch.bfloat16, "auto", False, 5.0),
+    ("d96_fp8_gqa12", 4, 24, 2, 96, [300, 5000, 12, 640], torch.bfloat16, "fp8", False, 5.0),
+    ("d32_bf16", 4, 8, 2, 32, [300, 5000, 12, 640], torch.bfloat16, "auto", False, 5.0),
+    ("d32_fp8", 4, 8, 8, 32, [300, 1500, 12, 640], torch.float16, "fp8", False, 5.0),
 ]
 
 

@@ -53,6 +53,12 @@ CASES = [
     ("many_short_fp8", 300, 16, 2, 128, [_RND.randint(1, 700) for _ in range(300)], torch.bfloat16, "fp8", False),
     ("one_long_fp8", 1, 64, 8, 128, [131072], torch.bfloat16, "fp8", False),
     ("llama70b_shard_fp8", 16, 8, 1, 128, [32768] * 16, torch.bfloat16, "fp8", False),
+    ("gemma_d256_fp8", 5, 16, 8, 256, [1000, 17, 512, 4100, 3333], torch.bfloat16, "fp8", False),
+    ("gemma_d256_bf16", 5, 16, 8, 256, [1000, 17, 512, 4100, 3333], torch.bfloat16, "auto", False),
+    ("d192_f16_fp8", 4, 24, 3, 192, [700, 33, 2049, 16], torch.float16, "fp8", False),
+    ("phi_d96_bf16", 6, 32, 32, 96, [1, 16, 17, 999, 2048, 31], torch.bfloat16, "auto", False),
+    ("d96_fp8_gqa12", 4, 24, 2, 96, [300, 5000, 12, 640], torch.bfloat16, "fp8", False),
+    ("d32_fp8", 4, 8, 8, 32, [300, 1500, 12, 640], torch.float16, "fp8", False),
 ]
 
 

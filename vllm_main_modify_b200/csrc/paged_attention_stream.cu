@@ -478,10 +478,11 @@ paged_attention_stream_kernel(const StreamParams p) {
     sl2 *= ks_raw;
     out_scale = *p.v_scale;
   }
-  // fused cache write: this lane's EPL head elements of the new token's K and V (raw scalar_t
-  // pairs) and its slot, fetched when a piece that reaches the end of its sequence begins
-  constexpr int EPL = D / 32;
-  uint32_t nt_k[EPL / 2], nt_v[EPL / 2];
+  // fused cache write: this lane's pairs of head elements (2(lane + 32j), +1) of the new token's
+  // K and V (raw scalar_t pairs) and its slot, fetched when a piece that reaches the end of its
+  // sequence begins
+  constexpr int NP = (D / 2 + 31) / 32;
+  uint32_t nt_k[NP], nt_v[NP];
   int64_t nt_slot = -1;
 
   // ldmatrix lane addressing
@@ -525,14 +526,18 @@ paged_attention_stream_kernel(const StreamParams p) {
       nt_slot = -1;
       if (cc.st_end == cc.ns) {
         nt_slot = p.slot_mapping[cc.b];
-        const T* kn = reinterpret_cast<const T*>(p.new_key) + (int64_t)cc.b * p.new_key_stride +
-                      (int64_t)kvh * D + lane * EPL;
-        const T* vn = reinterpret_cast<const T*>(p.new_value) + (int64_t)cc.b * p.new_value_stride +
-                      (int64_t)kvh * D + lane * EPL;
+        const uint32_t* kn = reinterpret_cast<const uint32_t*>(
+            reinterpret_cast<const T*>(p.new_key) + (int64_t)cc.b * p.new_key_stride + (int64_t)kvh * D);
+        const uint32_t* vn = reinterpret_cast<const uint32_t*>(
+            reinterpret_cast<const T*>(p.new_value) + (int64_t)cc.b * p.new_value_stride + (int64_t)kvh * D);
 #pragma unroll
-        for (int j = 0; j < EPL / 2; ++j) {
-          nt_k[j] = reinterpret_cast<const uint32_t*>(kn)[j];
-          nt_v[j] = reinterpret_cast<const uint32_t*>(vn)[j];
+        for (int j = 0; j < NP; ++j) {
+          const int pi = lane + 32 * j;
+          nt_k[j] = nt_v[j] = 0u;
+          if (pi < D / 2) {
+            nt_k[j] = kn[pi];
+            nt_v[j] = vn[pi];
+          }
         }
       }
     }
@@ -643,7 +648,6 @@ paged_attention_stream_kernel(const StreamParams p) {
     // exactly as reshape_and_cache does), not from the bytes the TMA copy found in the cache.
     if (p.new_key != nullptr && cc.st == cc.ns && nt_slot >= 0) {
       constexpr int X = 16 / CES;       // elements per 16-byte chunk of the x-packed K layout
-      constexpr int NBYTES = EPL * CES; // bytes this lane contributes to the K (and V) row
       const int t = cc.len - 1 - page0 * kBS;
       uint8_t* pg = ring + s * STAGE_BYTES + (t >> 4) * (2 * PAGE_SMEM);
       const int tt = t & 15;
@@ -653,50 +657,49 @@ paged_attention_stream_kernel(const StreamParams p) {
       const int off = (int)(nt_slot % kBS);
       uint8_t* kg = reinterpret_cast<uint8_t*>(const_cast<void*>(p.k_cache)) + goff;
       uint8_t* vg = reinterpret_cast<uint8_t*>(const_cast<void*>(p.v_cache)) + goff;
-      const int e0 = lane * EPL;        // my head elements e0 .. e0+EPL-1
-      uint32_t kw[2] = {0u, 0u}, vw[2] = {0u, 0u};   // NBYTES packed cache bytes of K and of V
-      if constexpr (FP8) {
-#pragma unroll
-        for (int j = 0; j < EPL / 2; ++j) {
-          const T* ke = reinterpret_cast<const T*>(&nt_k[j]);
-          const T* ve = reinterpret_cast<const T*>(&nt_v[j]);
-          kw[0] |= (uint32_t)fp8_quant2<B200PA_KV_FP8_E4M3>(
-                       Scalar<ST>::to_float(ke[0]), Scalar<ST>::to_float(ke[1]), ks_raw) << (16 * j);
-          vw[0] |= (uint32_t)fp8_quant2<B200PA_KV_FP8_E4M3>(
-                       Scalar<ST>::to_float(ve[0]), Scalar<ST>::to_float(ve[1]), out_scale) << (16 * j);
-        }
-      } else {
-#pragma unroll
-        for (int j = 0; j < EPL / 2; ++j) { kw[j] = nt_k[j]; vw[j] = nt_v[j]; }
-      }
-      auto put = [&](uint8_t* dst, const uint32_t (&w)[2]) {
-        if constexpr (NBYTES == 8) *reinterpret_cast<uint2*>(dst) = make_uint2(w[0], w[1]);
-        else if constexpr (NBYTES == 4) *reinterpret_cast<uint32_t*>(dst) = w[0];
-        else *reinterpret_cast<uint16_t*>(dst) = (uint16_t)w[0];
+      // a pair of cache elements: 2 bytes (fp8) or 4 bytes (16-bit)
+      auto put = [&](uint8_t* dst, uint32_t w) {
+        if constexpr (FP8) *reinterpret_cast<uint16_t*>(dst) = (uint16_t)w;
+        else *reinterpret_cast<uint32_t*>(dst) = w;
       };
-      if constexpr (FLASH) {
-        // token-major rows: K and V of the token are contiguous runs
-        const int64_t tsb = p.kv_token_stride * CES;
-        put(pg + tt * ROWB + e0 * CES, kw);
-        put(pg + PAGE_SMEM + tt * ROWB + e0 * CES, vw);
-        if (to_global) {
-          put(kg + off * tsb + e0 * CES, kw);
-          put(vg + off * tsb + e0 * CES, vw);
-        }
-      } else {
-        const int kchunk = (e0 / X) * kBS * 16 + (e0 % X) * CES;    // + token * 16
-        put(pg + kchunk + tt * 16, kw);
-        if (to_global) put(kg + kchunk + off * 16, kw);
 #pragma unroll
-        for (int i = 0; i < EPL; ++i) {   // V [D][16]: one element per head-element row
+      for (int j = 0; j < NP; ++j) {
+        const int e0 = 2 * (lane + 32 * j);      // head elements e0, e0 + 1
+        if (e0 < D) {
+          uint32_t kw = nt_k[j], vw = nt_v[j];
           if constexpr (FP8) {
-            const uint8_t b8 = (uint8_t)(vw[0] >> (8 * i));
-            pg[PAGE_SMEM + (e0 + i) * kBS + tt] = b8;
-            if (to_global) vg[(e0 + i) * kBS + off] = b8;
+            const T* ke = reinterpret_cast<const T*>(&nt_k[j]);
+            const T* ve = reinterpret_cast<const T*>(&nt_v[j]);
+            kw = fp8_quant2<B200PA_KV_FP8_E4M3>(Scalar<ST>::to_float(ke[0]),
+                                                Scalar<ST>::to_float(ke[1]), ks_raw);
+            vw = fp8_quant2<B200PA_KV_FP8_E4M3>(Scalar<ST>::to_float(ve[0]),
+                                                Scalar<ST>::to_float(ve[1]), out_scale);
+          }
+          if constexpr (FLASH) {
+            // token-major rows: K and V of the token are contiguous runs
+            const int64_t tsb = p.kv_token_stride * CES;
+            put(pg + tt * ROWB + e0 * CES, kw);
+            put(pg + PAGE_SMEM + tt * ROWB + e0 * CES, vw);
+            if (to_global) {
+              put(kg + off * tsb + e0 * CES, kw);
+              put(vg + off * tsb + e0 * CES, vw);
+            }
           } else {
-            const uint16_t v16 = (uint16_t)(vw[i / 2] >> (16 * (i & 1)));
-            reinterpret_cast<uint16_t*>(pg + PAGE_SMEM)[(e0 + i) * kBS + tt] = v16;
-            if (to_global) reinterpret_cast<uint16_t*>(vg)[(e0 + i) * kBS + off] = v16;
+            const int kchunk = (e0 / X) * kBS * 16 + (e0 % X) * CES;    // + token * 16
+            put(pg + kchunk + tt * 16, kw);
+            if (to_global) put(kg + kchunk + off * 16, kw);
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {   // V [D][16]: one element per head-element row
+              if constexpr (FP8) {
+                const uint8_t b8 = (uint8_t)(vw >> (8 * i));
+                pg[PAGE_SMEM + (e0 + i) * kBS + tt] = b8;
+                if (to_global) vg[(e0 + i) * kBS + off] = b8;
+              } else {
+                const uint16_t v16 = (uint16_t)(vw >> (16 * i));
+                reinterpret_cast<uint16_t*>(pg + PAGE_SMEM)[(e0 + i) * kBS + tt] = v16;
+                if (to_global) reinterpret_cast<uint16_t*>(vg)[(e0 + i) * kBS + off] = v16;
+              }
+            }
           }
         }
       }
@@ -1220,7 +1223,9 @@ bool stream_supported(const void* query, const void* key_cache, const void* valu
                       int scalar_type, int kv_dtype, int blocksparse_vert_stride) {
   if (blocksparse_vert_stride > 1) return false;
   if (block_size != kBS) return false;
-  if (head_size != 64 && head_size != 128) return false;
+  // multiples of 32 of the reference's head sizes (80, 112, 120 stay on the generic kernel)
+  if (head_size != 32 && head_size != 64 && head_size != 96 && head_size != 128 &&
+      head_size != 192 && head_size != 256) return false;
   if (scalar_type != B200PA_BF16 && scalar_type != B200PA_F16) return false;
   if (kv_dtype != B200PA_KV_AUTO && kv_dtype != B200PA_KV_FP8_E4M3) return false;
   if (num_kv_heads <= 0 || num_heads % num_kv_heads != 0) return false;
@@ -1345,13 +1350,23 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
       else     { if (head_size == 128) { STREAM_CALL(B200PA_F16, false, 128, 4, 4, 1, 1, true); } else { STREAM_CALL(B200PA_F16, false, 64, 4, 3, 2, 2, true); } }
     }
   }
-  if (scalar_type == B200PA_BF16) {
-    if (fp8) { if (head_size == 128) { STREAM_TUNE_FP8(B200PA_BF16, 128) } else { STREAM_CALL(B200PA_BF16, true, 64, 4, 3, 2, 2); } }
-    else     { if (head_size == 128) { STREAM_TUNE_16(B200PA_BF16, 128) } else { STREAM_CALL(B200PA_BF16, false, 64, 4, 3, 2, 2); } }
-  } else {
-    if (fp8) { if (head_size == 128) { STREAM_CALL(B200PA_F16, true, 128, 4, 3, 2, 2); } else { STREAM_CALL(B200PA_F16, true, 64, 4, 3, 2, 2); } }
-    else     { if (head_size == 128) { STREAM_CALL(B200PA_F16, false, 128, 4, 4, 1, 1); } else { STREAM_CALL(B200PA_F16, false, 64, 4, 3, 2, 2); } }
+  if (scalar_type == B200PA_BF16 && head_size == 128) {
+    if (fp8) { STREAM_TUNE_FP8(B200PA_BF16, 128) } else { STREAM_TUNE_16(B200PA_BF16, 128) }
   }
+  // the other head sizes (and f16 at 128): one shape each.  192 / 256: 12-16 KiB stages, 4 warps.
+#define STREAM_BY_HEAD_SIZE(ST)                                                              \
+  switch (head_size) {                                                                       \
+    case 32:  if (fp8) { STREAM_CALL(ST, true, 32, 4, 3, 2, 2); }  else { STREAM_CALL(ST, false, 32, 4, 3, 2, 2); }  \
+    case 64:  if (fp8) { STREAM_CALL(ST, true, 64, 4, 3, 2, 2); }  else { STREAM_CALL(ST, false, 64, 4, 3, 2, 2); }  \
+    case 96:  if (fp8) { STREAM_CALL(ST, true, 96, 4, 3, 2, 2); }  else { STREAM_CALL(ST, false, 96, 4, 3, 2, 1); }  \
+    case 128: if (fp8) { STREAM_CALL(ST, true, 128, 4, 3, 2, 2); } else { STREAM_CALL(ST, false, 128, 4, 4, 1, 1); } \
+    case 192: if (fp8) { STREAM_CALL(ST, true, 192, 4, 4, 2, 1); } else { STREAM_CALL(ST, false, 192, 4, 4, 1, 1); } \
+    case 256: if (fp8) { STREAM_CALL(ST, true, 256, 4, 3, 2, 1); } else { STREAM_CALL(ST, false, 256, 4, 3, 1, 1); } \
+    default: return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: head size %d", head_size);  \
+  }
+  if (scalar_type == B200PA_BF16) { STREAM_BY_HEAD_SIZE(B200PA_BF16) }
+  else { STREAM_BY_HEAD_SIZE(B200PA_F16) }
+#undef STREAM_BY_HEAD_SIZE
 #undef STREAM_TUNE_FP8
 #undef STREAM_TUNE_16
 #undef STREAM_CALL

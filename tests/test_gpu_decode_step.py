@@ -62,7 +62,7 @@ CASES = [
 ]
 
 
-def _inputs(B, H, Hkv, D, lens, dtype, kv, seed=7):
+def _inputs(B, H, Hkv, D, lens, dtype, kv, seed=7, BS=BS):
     s = D ** -0.5
     NB = sum((L + BS - 1) // BS for L in lens) + 5
     q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, NB, lens, dtype, seed=seed, kv=kv,
@@ -75,7 +75,7 @@ def _inputs(B, H, Hkv, D, lens, dtype, kv, seed=7):
     return s, q, kc, vc, bt, sl, key, value, slots
 
 
-def _poison(kc, vc, slots, kv):
+def _poison(kc, vc, slots, kv, BS=BS):
     """NaN in the slots the step is about to fill (fp8: code 0x7F; 16-bit: a NaN pattern)."""
     blk, off = slots // BS, slots % BS
     live = slots >= 0
@@ -94,7 +94,7 @@ def _scales(kv):
 
 
 def _two_ops(ops, q, key, value, kc, vc, slots, Hkv, s, bt, sl, max_len, alibi, kv, ks, vs,
-             lse=None):
+             lse=None, BS=BS):
     ops.reshape_and_cache(key, value, kc, vc, slots, kv, ks, vs)
     out = torch.full_like(q, float("nan"))
     if lse is None:
@@ -148,6 +148,56 @@ def test_decode_step_equals_write_then_attend(ops, native, ora, case, impl):
                                torch.tensor(ks), torch.tensor(vs))
         atol = ATOL * max(1.0, float(ref.float().abs().max()))
         torch.testing.assert_close(got.cpu().float(), ref.float(), atol=atol, rtol=RTOL)
+
+
+BS32_CASES = [c for c in CASES if c[0] in ("gqa8_fp8_page_edges", "gqa4_bf16_page_edges",
+                                            "gqa16_two_tiles_fp8", "mha_f16_d64_alibi",
+                                            "gemma_d256_fp8", "gemma_d256_bf16", "d192_f16_fp8",
+                                            "phi_d96_bf16", "many_short_fp8")]
+
+
+@pytest.mark.parametrize("case", BS32_CASES, ids=[c[0] for c in BS32_CASES])
+def test_decode_step_block_size_32(ops, native, ora, case):
+    """The same contract on 32-token cache blocks (two 16-token tiles per block in the kernel)."""
+    name, B, H, Hkv, D, lens, dtype, kv, use_alibi = case
+    bs = 32
+    s, q, kc, vc, bt, sl, key, value, slots = _inputs(B, H, Hkv, D, lens, dtype, kv, BS=bs)
+    _poison(kc, vc, slots, kv, BS=bs)
+    ks, vs = _scales(kv)
+    alibi = None
+    if use_alibi:
+        alibi = torch.tensor([2.0 ** (-(i + 1) * 8.0 / H) for i in range(H)], dtype=torch.float32)
+    max_len = max(lens)
+    d = lambda t: None if t is None else t.to(DEV)
+    qd, btd, sld, keyd, vald, slotsd, ald = d(q), d(bt), d(sl), d(key), d(value), d(slots), d(alibi)
+    ksd, vsd = torch.tensor(ks, device=DEV), torch.tensor(vs, device=DEV)
+    native.set_impl(STREAM)
+    try:
+        kc1, vc1 = d(kc), d(vc)
+        want = _two_ops(ops, qd, keyd, vald, kc1, vc1, slotsd, Hkv, s, btd, sld, max_len, ald, kv,
+                        ksd, vsd, BS=bs)
+        kc2, vc2 = d(kc), d(vc)
+        got = torch.full_like(qd, float("nan"))
+        n0 = native.launch_count()
+        ops.decode_step(got, None, qd, keyd, vald, kc2, vc2, slotsd, Hkv, s, btd, sld, bs, max_len,
+                        ald, kv, ksd, vsd)
+        assert native.launch_count() - n0 <= 2
+        torch.cuda.synchronize()
+    finally:
+        native.set_impl(native.IMPL_AUTO)
+    assert torch.equal(kc2.view(torch.uint8), kc1.view(torch.uint8)), "key cache bytes"
+    assert torch.equal(vc2.view(torch.uint8), vc1.view(torch.uint8)), "value cache bytes"
+    assert not torch.isnan(got.float()).any()
+    assert torch.equal(got, want)
+    kc_o, vc_o = kc.clone(), vc.clone()
+    ora.reshape_and_cache(key, value, kc_o, vc_o, slots, kv, torch.tensor(ks), torch.tensor(vs))
+    assert torch.equal(kc2.cpu().view(torch.uint8), kc_o.view(torch.uint8))
+    assert torch.equal(vc2.cpu().view(torch.uint8), vc_o.view(torch.uint8))
+    ref = torch.empty_like(q)
+    ora.paged_attention_v1(ref, q, kc_o, vc_o, Hkv, s, bt, sl, bs, max_len, alibi, kv,
+                           torch.tensor(ks), torch.tensor(vs))
+    atol = ATOL * max(1.0, float(ref.float().abs().max()))
+    torch.testing.assert_close(got.cpu().float(), ref.float(), atol=atol, rtol=RTOL)
 
 
 @pytest.mark.parametrize("kv", ["auto", "fp8"])

@@ -25,6 +25,10 @@ SHAPES = [
     ("phi_d96_bf16", 64, 32, 32, 96, 2048, "auto"),
     ("d192_fp8", 64, 24, 8, 192, 8192, "fp8"),
     ("d64_fp8_gqa8", 128, 64, 8, 64, 8192, "fp8"),
+    # 32-token cache blocks
+    ("llama8b_bs32_bf16", 64, 32, 8, 128, 4096, "auto", 32),
+    ("llama8b_bs32_fp8", 256, 32, 8, 128, 8192, "fp8", 32),
+    ("gemma_d256_bs32_fp8", 64, 16, 8, 256, 8192, "fp8", 32),
 ]
 
 
@@ -58,9 +62,9 @@ def main():
             ref = ref_cuda
     except Exception as e:  # noqa: BLE001
         print(json.dumps({"ref_cuda": f"unavailable: {e}"}))
-    BS = 16
     g = torch.Generator(device=DEV).manual_seed(0)
-    for name, B, H, Hkv, D, ctx, kv in SHAPES:
+    for name, B, H, Hkv, D, ctx, kv, *rest in SHAPES:
+        BS = rest[0] if rest else 16
         nblk = ctx // BS
         NB = B * nblk
         if kv == "auto":
@@ -99,7 +103,7 @@ def main():
             ms = timeit(ours, args.iters)
             outs[label] = out.clone()
             print(json.dumps({"shape": name, "B": B, "H": H, "Hkv": Hkv, "D": D, "ctx": ctx,
-                              "kv": kv, "impl": label, "ms": round(ms, 4),
+                              "block_size": BS, "kv": kv, "impl": label, "ms": round(ms, 4),
                               "gbs": round(nbytes / ms / 1e6, 1)}), flush=True)
         _native.set_impl(_native.IMPL_AUTO)
         if ref is not None:

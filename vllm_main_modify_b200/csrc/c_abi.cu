@@ -33,7 +33,7 @@ bool stream_supported(const void*, const void*, const void*, int, int, int, int,
 int launch_stream(void*, float*, int64_t, int64_t, void*, int64_t, const void*, const void*, const void*, int, int, int, int,
                   float, const int32_t*, int, const int32_t*, const float*, int64_t, int64_t,
                   int64_t, int, int, const float*, const float*, const FusedWrite*, int64_t, int,
-                  int, cudaStream_t);
+                  int, int, cudaStream_t);
 bool stream_flash_supported(const void*, const void*, const void*, int, int, int, int, int64_t,
                             int64_t, int64_t, int64_t, int, int);
 bool stream_fused_supported(const FusedWrite&, int);
@@ -185,7 +185,7 @@ static int paged_attention_common(
                          num_heads, num_kv_heads, head_size, scale, block_tables,
                          max_num_blocks_per_seq, seq_lens, alibi_slopes, q_stride,
                          kv_block_stride, kv_head_stride, scalar_type, kv_dtype, k_scale, v_scale,
-                         fused, 0, num_sms(), stream_tune(), stream);
+                         fused, 0, block_size, num_sms(), stream_tune(), stream);
   }
   int rc = launch_generic(out, lse, lse_seq_stride, lse_head_stride, exp_sums, max_logits, tmp_out, query, key_cache, value_cache,
                           num_seqs, num_heads, num_kv_heads, head_size, block_size, scale,
@@ -356,7 +356,7 @@ int b200pa_paged_attention_flash(
                        key_cache, value_cache, num_seqs, num_heads, num_kv_heads, head_size, scale,
                        block_tables, max_num_blocks_per_seq, seq_lens, alibi_slopes, q_stride,
                        block_stride, head_stride, scalar_type, kv_dtype, k_scale, v_scale, fused,
-                       page_stride, num_sms(), 0, stream);
+                       page_stride, block_size, num_sms(), 0, stream);
 }
 
 int b200pa_merge_attn_states(void* output, float* output_lse, const void* prefix_output,

@@ -3,8 +3,10 @@
 // Replaces the per-sequence decode kernels of the reference
 // (csrc/attention/attention_kernels.cuh:85-491 through paged_attention_v1_kernel :494-522 and
 // paged_attention_v2_kernel :525-557 + paged_attention_v2_reduce_kernel :560-664, launched from
-// paged_attention_v1.cu:46-125 / paged_attention_v2.cu:47-126) for head_size 64/128,
-// block_size 16, bf16/fp16 query and a 16-bit or fp8-e4m3 KV cache.
+// paged_attention_v1.cu:46-125 / paged_attention_v2.cu:47-126) for head_size 32/64/96/128/192/256,
+// block_size 16/32, bf16/fp16 query and a 16-bit or fp8-e4m3 KV cache -- x-packed layout, or
+// (FLASH, block_size 16, head_size 64/128) the token-major layout of reshape_and_cache_flash --
+// with the new token's cache write optionally fused in (decode_step).
 //
 //  * WORK DECOMPOSITION.  The unit of work is one pipeline STAGE: PPS consecutive pages of one
 //    (sequence, kv head) -- 8 KiB of KV.  All stages of the call are flattened in (sequence,
@@ -313,7 +315,10 @@ __device__ __forceinline__ void store_out(typename Scalar<ST>::type* out_tile,
 // reshape_and_cache_flash writes): every token row of D elements is one bulk copy into a shared
 // row padded by 16 bytes (conflict-free ldmatrix), K fragments come from plain and V fragments
 // from transposing ldmatrix.
-template <int ST, bool FP8, int D, int NW, int STAGES, int PPS, int MINB, bool FLASH>
+// BSZ: tokens per cache block (16 or 32).  The kernel's unit stays the 16-token M tile ("page"
+// below); with BSZ = 32 a cache block is two tiles that arrive in one bulk copy and are addressed
+// inside the block by the layout's strides (K chunk stride BSZ*16 B, V row stride BSZ elements).
+template <int ST, bool FP8, int D, int NW, int STAGES, int PPS, int MINB, bool FLASH, int BSZ>
 __global__ void __launch_bounds__(NW * 32, MINB)
 paged_attention_stream_kernel(const StreamParams p) {
   using T = typename Scalar<ST>::type;
@@ -325,6 +330,20 @@ paged_attention_stream_kernel(const StreamParams p) {
   constexpr int PAGE_SMEM = FLASH ? kBS * ROWB : PAGE_BYTES; // shared-memory footprint of a page
   constexpr int STAGE_BYTES = PPS * 2 * PAGE_SMEM;
   constexpr bool DPERM = FLASH && FP8;                       // see store_out_tile
+  constexpr int TPB = BSZ / kBS;                             // 16-token tiles per cache block
+  constexpr int BPS = PPS / TPB;                             // cache blocks per stage
+  constexpr int BLOCK_BYTES = TPB * PAGE_BYTES;              // one K (or V) block of one kv head
+  constexpr int BLOCK_SMEM = TPB * PAGE_SMEM;
+  constexpr int KCS = BSZ * 16;                              // x-packed K: bytes between 16-byte chunks
+  constexpr int VRS = BSZ * CES;                             // x-packed V: bytes per head-element row
+  static_assert(BSZ == 16 || BSZ == 32, "block size");
+  static_assert(PPS % TPB == 0 && 32 % BPS == 0, "a stage holds whole cache blocks");
+  static_assert(!FLASH || BSZ == 16, "the flash-layout variant serves block size 16");
+  // tile g of a stage: block g / TPB, half g % TPB
+  auto k_tile = [](int g) { return (g / TPB) * 2 * BLOCK_SMEM + (g % TPB) * (FLASH ? 0 : kBS * 16); };
+  auto v_tile = [](int g) {
+    return (g / TPB) * 2 * BLOCK_SMEM + BLOCK_SMEM + (g % TPB) * (FLASH ? 0 : kBS * CES);
+  };
   constexpr int KSTEPS = D / 16;                             // QK k-steps
   constexpr int MT = D / 16;                                 // PV m-tiles (16 head elements each)
   constexpr int RING_BYTES = STAGES * STAGE_BYTES;
@@ -398,7 +417,9 @@ paged_attention_stream_kernel(const StreamParams p) {
     const int page0 = pc.st * PPS;
     const int npg = min(PPS, (pc.len + kBS - 1) / kBS - page0);
     ++pc.st;
-    const int win = page0 >> 5;
+    const int blk0 = page0 / TPB;                 // first cache block of the stage
+    const int nblk = (npg + TPB - 1) / TPB;       // blocks with at least one valid tile
+    const int win = blk0 >> 5;
     if (pc.b != bt_b || win != bt_win) {
       const int idx = (win << 5) + lane;
       bt_reg = (idx < p.max_num_blocks_per_seq)
@@ -406,9 +427,9 @@ paged_attention_stream_kernel(const StreamParams p) {
       bt_b = pc.b;
       bt_win = win;
     }
-    int phys[PPS];
+    int phys[BPS];
 #pragma unroll
-    for (int g = 0; g < PPS; ++g) phys[g] = __shfl_sync(kFull, bt_reg, (page0 + g) & 31);
+    for (int g = 0; g < BPS; ++g) phys[g] = __shfl_sync(kFull, bt_reg, (blk0 + g) & 31);
     if constexpr (FLASH) {
       // Token rows of one head are D elements apart from each other by the token stride: no
       // single run to bulk-copy.  (One TMA bulk copy per 128/256-byte row reached 3.0 TB/s on
@@ -447,14 +468,14 @@ paged_attention_stream_kernel(const StreamParams p) {
       const int kvh = pc.vh / p.h_tiles;
       const uint8_t* kc = reinterpret_cast<const uint8_t*>(p.k_cache) + kvh * head_stride_bytes;
       const uint8_t* vc = reinterpret_cast<const uint8_t*>(p.v_cache) + kvh * head_stride_bytes;
-      mbar_expect_tx(bar, npg * 2 * PAGE_BYTES);
+      mbar_expect_tx(bar, nblk * 2 * BLOCK_BYTES);
 #pragma unroll
-      for (int g = 0; g < PPS; ++g) {
-        if (g < npg) {
-          tma_load_1d(dst + g * 2 * PAGE_BYTES, kc + (int64_t)phys[g] * blk_stride_bytes,
-                      PAGE_BYTES, bar, policy);
-          tma_load_1d(dst + g * 2 * PAGE_BYTES + PAGE_BYTES,
-                      vc + (int64_t)phys[g] * blk_stride_bytes, PAGE_BYTES, bar, policy);
+      for (int g = 0; g < BPS; ++g) {
+        if (g < nblk) {
+          tma_load_1d(dst + g * 2 * BLOCK_BYTES, kc + (int64_t)phys[g] * blk_stride_bytes,
+                      BLOCK_BYTES, bar, policy);
+          tma_load_1d(dst + g * 2 * BLOCK_BYTES + BLOCK_BYTES,
+                      vc + (int64_t)phys[g] * blk_stride_bytes, BLOCK_BYTES, bar, policy);
         }
       }
     }
@@ -505,16 +526,16 @@ paged_attention_stream_kernel(const StreamParams p) {
     // gets from a V row (b0/b1 swapped for q >= 2).
     const int sig0 = 4 * (mi >> 1) + (mi & 1) + ((mi >= 4) ? 2 : 0);
     const int tok = (mat & 1) ? (sig0 ^ 2) : sig0;
-    k_lane_off = ((mat >> 1) * kBS + tok) * 16;
-    v_lane_off = lane * 16;  // 32 consecutive V rows (head elements) per x4
+    k_lane_off = (mat >> 1) * KCS + tok * 16;
+    v_lane_off = lane * VRS;  // 32 consecutive V rows (head elements) per x4
     tokA = 4 * (r >> 1) + (r & 1) + ((r >= 4) ? 2 : 0);
     tokB = tokA ^ 2;
   } else {
     // K x4 = {chunk 2ks, tok 0-7 | chunk 2ks, tok 8-15 | chunk 2ks+1, tok 0-7 | chunk 2ks+1, tok 8-15}
     // (chunk = 8 head elements)
-    k_lane_off = ((mat >> 1) * kBS + (mat & 1) * 8 + mi) * 16;
+    k_lane_off = (mat >> 1) * KCS + ((mat & 1) * 8 + mi) * 16;
     // V x4 = {d 0-7, tok 0-7 | d 8-15, tok 0-7 | d 0-7, tok 8-15 | d 8-15, tok 8-15}
-    v_lane_off = ((mat & 1) * 8 + mi) * 32 + (mat >> 1) * 16;
+    v_lane_off = ((mat & 1) * 8 + mi) * VRS + (mat >> 1) * 16;
     tokA = r;
     tokB = r + 8;
   }
@@ -649,12 +670,12 @@ paged_attention_stream_kernel(const StreamParams p) {
     if (p.new_key != nullptr && cc.st == cc.ns && nt_slot >= 0) {
       constexpr int X = 16 / CES;       // elements per 16-byte chunk of the x-packed K layout
       const int t = cc.len - 1 - page0 * kBS;
-      uint8_t* pg = ring + s * STAGE_BYTES + (t >> 4) * (2 * PAGE_SMEM);
-      const int tt = t & 15;
+      uint8_t* pg = ring + s * STAGE_BYTES + ((t >> 4) / TPB) * (2 * BLOCK_SMEM);   // the block
+      const int tt = t & (BSZ - 1);                                                 // token in it
       const int kvh = cc.vh / p.h_tiles;
       const bool to_global = cc.vh == kvh * p.h_tiles;
-      const int64_t goff = (nt_slot / kBS) * blk_stride_bytes + kvh * head_stride_bytes;
-      const int off = (int)(nt_slot % kBS);
+      const int64_t goff = (nt_slot / BSZ) * blk_stride_bytes + kvh * head_stride_bytes;
+      const int off = (int)(nt_slot % BSZ);
       uint8_t* kg = reinterpret_cast<uint8_t*>(const_cast<void*>(p.k_cache)) + goff;
       uint8_t* vg = reinterpret_cast<uint8_t*>(const_cast<void*>(p.v_cache)) + goff;
       // a pair of cache elements: 2 bytes (fp8) or 4 bytes (16-bit)
@@ -685,19 +706,19 @@ paged_attention_stream_kernel(const StreamParams p) {
               put(vg + off * tsb + e0 * CES, vw);
             }
           } else {
-            const int kchunk = (e0 / X) * kBS * 16 + (e0 % X) * CES;    // + token * 16
+            const int kchunk = (e0 / X) * KCS + (e0 % X) * CES;    // + token * 16
             put(pg + kchunk + tt * 16, kw);
             if (to_global) put(kg + kchunk + off * 16, kw);
 #pragma unroll
             for (int i = 0; i < 2; ++i) {   // V [D][16]: one element per head-element row
               if constexpr (FP8) {
                 const uint8_t b8 = (uint8_t)(vw >> (8 * i));
-                pg[PAGE_SMEM + (e0 + i) * kBS + tt] = b8;
-                if (to_global) vg[(e0 + i) * kBS + off] = b8;
+                pg[BLOCK_SMEM + (e0 + i) * BSZ + tt] = b8;
+                if (to_global) vg[(e0 + i) * BSZ + off] = b8;
               } else {
                 const uint16_t v16 = (uint16_t)(vw >> (16 * i));
-                reinterpret_cast<uint16_t*>(pg + PAGE_SMEM)[(e0 + i) * kBS + tt] = v16;
-                if (to_global) reinterpret_cast<uint16_t*>(vg)[(e0 + i) * kBS + off] = v16;
+                reinterpret_cast<uint16_t*>(pg + BLOCK_SMEM)[(e0 + i) * BSZ + tt] = v16;
+                if (to_global) reinterpret_cast<uint16_t*>(vg)[(e0 + i) * BSZ + off] = v16;
               }
             }
           }
@@ -714,13 +735,13 @@ paged_attention_stream_kernel(const StreamParams p) {
     for (int g = 0; g < PPS; ++g) {
       sc[g][0] = sc[g][1] = sc[g][2] = sc[g][3] = 0.f;
       if (g < npg) {
-        const uint32_t kbase = sbase + g * 2 * PAGE_SMEM;
+        const uint32_t kbase = sbase + k_tile(g);
         float sb[4] = {0.f, 0.f, 0.f, 0.f};
         if constexpr (FP8) {
 #pragma unroll
           for (int c = 0; c < KSTEPS; c += 2) {
             uint32_t w4[4], a[4];
-            ldmatrix_x4(w4, kbase + c * (FLASH ? 16 : kBS * 16) + k_lane_off);
+            ldmatrix_x4(w4, kbase + c * (FLASH ? 16 : KCS) + k_lane_off);
             e4m3x4_to_f16x2x2(w4[0], a[0], a[2]);
             e4m3x4_to_f16x2x2(w4[1], a[1], a[3]);
             mma16816<false>(sc[g], a, qb[c][0], qb[c][1]);
@@ -732,7 +753,7 @@ paged_attention_stream_kernel(const StreamParams p) {
 #pragma unroll
           for (int ks = 0; ks < KSTEPS; ++ks) {
             uint32_t a[4];
-            ldmatrix_x4(a, kbase + ks * (FLASH ? 32 : 2 * kBS * 16) + k_lane_off);
+            ldmatrix_x4(a, kbase + ks * (FLASH ? 32 : 2 * KCS) + k_lane_off);
             if (ks & 1) mma16816<MMA_BF16>(sb, a, qb[ks][0], qb[ks][1]);
             else mma16816<MMA_BF16>(sc[g], a, qb[ks][0], qb[ks][1]);
           }
@@ -814,7 +835,7 @@ paged_attention_stream_kernel(const StreamParams p) {
     // ---- O^T += V^T P^T
     auto pv = [&](int g, auto masked) {
       constexpr bool MASKED = decltype(masked)::value;
-      const uint32_t vbase = sbase + g * 2 * PAGE_SMEM + PAGE_SMEM;
+      const uint32_t vbase = sbase + v_tile(g);
       // tail page: V columns past the context may hold NaN bit patterns; the reference
       // zeroes them (attention_kernels.cuh:415-425).  m01 masks a[0], a[1]; m23 a[2], a[3].
       uint32_t m01 = 0xffffffffu, m23 = 0xffffffffu;
@@ -846,7 +867,7 @@ paged_attention_stream_kernel(const StreamParams p) {
 #pragma unroll
         for (int gg = 0; gg < D / 32; ++gg) {
           uint32_t w4[4], a[4];
-          ldmatrix_x4(w4, vbase + gg * (32 * 16) + v_lane_off);
+          ldmatrix_x4(w4, vbase + gg * (32 * VRS) + v_lane_off);
           e4m3x4_to_f16x2x2(w4[0], a[0], a[2]);
           e4m3x4_to_f16x2x2(w4[1], a[1], a[3]);
           if constexpr (MASKED) { a[0] &= m01; a[1] &= m01; a[2] &= m23; a[3] &= m23; }
@@ -861,7 +882,7 @@ paged_attention_stream_kernel(const StreamParams p) {
         for (int mt = 0; mt < MT; ++mt) {
           uint32_t a[4];
           if constexpr (FLASH) ldmatrix_x4_trans(a, vbase + mt * 32 + v_lane_off);
-          else ldmatrix_x4(a, vbase + mt * (16 * 32) + v_lane_off);
+          else ldmatrix_x4(a, vbase + mt * (16 * VRS) + v_lane_off);
           if constexpr (MASKED) { a[0] &= m01; a[1] &= m01; a[2] &= m23; a[3] &= m23; }
           mma16816<MMA_BF16>(o[mt], a, pb[g][0], pb[g][1]);
         }
@@ -1145,11 +1166,12 @@ paged_attention_stream_merge_kernel(const StreamParams p) {
 // ---------------------------------------------------------------------------------------
 constexpr int kMaxWarpsPerSm = 16;
 
-template <int ST, bool FP8, int D, int NW, int STAGES, int PPS, int MINB, bool FLASH = false>
+template <int ST, bool FP8, int D, int NW, int STAGES, int PPS, int MINB, bool FLASH = false,
+          int BSZ = 16>
 int launch_stream_t(StreamParams& p, int num_sms, int64_t workspace_bytes, cudaStream_t stream) {
   constexpr int CES = FP8 ? 1 : 2;
   constexpr int SMEM = NW * STAGES * PPS * 2 * kBS * (FLASH ? D * CES + 16 : D * CES);
-  auto kern = paged_attention_stream_kernel<ST, FP8, D, NW, STAGES, PPS, MINB, FLASH>;
+  auto kern = paged_attention_stream_kernel<ST, FP8, D, NW, STAGES, PPS, MINB, FLASH, BSZ>;
   static int ctas_per_sm = 0;  // per instantiation
   if (ctas_per_sm == 0) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
@@ -1222,7 +1244,7 @@ bool stream_supported(const void* query, const void* key_cache, const void* valu
                       int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
                       int scalar_type, int kv_dtype, int blocksparse_vert_stride) {
   if (blocksparse_vert_stride > 1) return false;
-  if (block_size != kBS) return false;
+  if (block_size != 16 && block_size != 32) return false;
   // multiples of 32 of the reference's head sizes (80, 112, 120 stay on the generic kernel)
   if (head_size != 32 && head_size != 64 && head_size != 96 && head_size != 128 &&
       head_size != 192 && head_size != 256) return false;
@@ -1274,8 +1296,8 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
                   int max_num_blocks_per_seq, const int32_t* seq_lens, const float* alibi_slopes,
                   int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
                   int scalar_type, int kv_dtype, const float* k_scale, const float* v_scale,
-                  const FusedWrite* fused, int64_t flash_token_stride, int num_sms, int tune,
-                  cudaStream_t stream) {
+                  const FusedWrite* fused, int64_t flash_token_stride, int block_size, int num_sms,
+                  int tune, cudaStream_t stream) {
   // flash_token_stride > 0: token-major cache (kv_block_stride / flash_token_stride /
   // kv_head_stride are the strides of [block][token][head][D]); 0: the x-packed layout
   if (!workspace || (reinterpret_cast<uintptr_t>(workspace) & 15u))
@@ -1349,6 +1371,22 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
       if (fp8) { if (head_size == 128) { STREAM_CALL(B200PA_F16, true, 128, 4, 3, 2, 2, true); } else { STREAM_CALL(B200PA_F16, true, 64, 4, 3, 2, 2, true); } }
       else     { if (head_size == 128) { STREAM_CALL(B200PA_F16, false, 128, 4, 4, 1, 1, true); } else { STREAM_CALL(B200PA_F16, false, 64, 4, 3, 2, 2, true); } }
     }
+  }
+  if (block_size == 32) {
+    // 32-token cache blocks: stages of two 16-token tiles = one block (PPS = 2 everywhere)
+#define STREAM_BY_HEAD_SIZE_32(ST)                                                           \
+  switch (head_size) {                                                                       \
+    case 32:  if (fp8) { STREAM_CALL(ST, true, 32, 4, 3, 2, 2, false, 32); }  else { STREAM_CALL(ST, false, 32, 4, 3, 2, 2, false, 32); }  \
+    case 64:  if (fp8) { STREAM_CALL(ST, true, 64, 4, 3, 2, 2, false, 32); }  else { STREAM_CALL(ST, false, 64, 4, 3, 2, 2, false, 32); }  \
+    case 96:  if (fp8) { STREAM_CALL(ST, true, 96, 4, 3, 2, 2, false, 32); }  else { STREAM_CALL(ST, false, 96, 4, 3, 2, 1, false, 32); }  \
+    case 128: if (fp8) { STREAM_CALL(ST, true, 128, 8, 3, 2, 1, false, 32); } else { STREAM_CALL(ST, false, 128, 4, 3, 2, 1, false, 32); } \
+    case 192: if (fp8) { STREAM_CALL(ST, true, 192, 4, 4, 2, 1, false, 32); } else { STREAM_CALL(ST, false, 192, 4, 2, 2, 1, false, 32); } \
+    case 256: if (fp8) { STREAM_CALL(ST, true, 256, 4, 3, 2, 1, false, 32); } else { STREAM_CALL(ST, false, 256, 3, 2, 2, 1, false, 32); } \
+    default: return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: head size %d", head_size);  \
+  }
+    if (scalar_type == B200PA_BF16) { STREAM_BY_HEAD_SIZE_32(B200PA_BF16) }
+    else { STREAM_BY_HEAD_SIZE_32(B200PA_F16) }
+#undef STREAM_BY_HEAD_SIZE_32
   }
   if (scalar_type == B200PA_BF16 && head_size == 128) {
     if (fp8) { STREAM_TUNE_FP8(B200PA_BF16, 128) } else { STREAM_TUNE_16(B200PA_BF16, 128) }

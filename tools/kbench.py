@@ -45,6 +45,22 @@ def time_op(fn, iters, flush=None):
     return ts[len(ts) // 2], ts[0]
 
 
+def graphed(fn):
+    """Capture fn into a CUDA graph (side stream, after a warm-up) and return the replay callable:
+    what a full-graph decode capture of the runner (gpu_model_runner.py:3468) replays per step."""
+    stream = torch.cuda.Stream()
+    stream.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(stream):
+        fn()
+        stream.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=stream):
+            fn()
+    torch.cuda.current_stream().wait_stream(stream)
+    torch.cuda.synchronize()
+    return graph.replay
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--configs", default="cfg1,cfg2,cfg3,cfg4,cfg5")
@@ -53,6 +69,8 @@ def main():
     ap.add_argument("--impl", type=int, default=0, help="b200pa_set_impl value (0 auto)")
     ap.add_argument("--ops", default="v1,v2,reshape_and_cache")
     ap.add_argument("--series", action="store_true", help="also print the per-launch times in order")
+    ap.add_argument("--graph", action="store_true",
+                    help="time CUDA-graph replays of each op instead of eager launches")
     ap.add_argument("--ref-cuda", action="store_true",
                     help="time the reference's own CUDA kernels (oracle/_ref/libvllm_ref_cuda.so) "
                          "on the same tensors instead of this repo's")
@@ -136,10 +154,13 @@ def main():
             fn = fns[name]
             if args.ref_cuda and name == "v1" and w["max_len"] * 4 > 200 * 1024:
                 continue   # the reference's v1 keeps max_seq_len fp32 logits in shared memory
+            if args.graph:
+                fn = graphed(fn)
             med, best = time_op(fn, args.iters, fl)
             line = {"config": cfg, "tp": args.tp,
                     "impl": "reference_cuda" if args.ref_cuda else args.impl,
                     "tune": os.environ.get("B200PA_STREAM_TUNE", "0"), "op": name,
+                    "launch": "graph" if args.graph else "eager",
                     "build": os.environ.get("B200PA_AB_LABEL", "tree"),
                     "ms_median": round(med, 4),
                     "ms_best": round(best, 4)}

@@ -207,8 +207,8 @@ int b200pa_decode_step(
  * b200pa_reshape_and_cache_flash(key, value, ..., slot_mapping, num_tokens = num_seqs) BEFORE the
  * attention, in the same launch, under b200pa_decode_step's precondition (token b is position
  * seq_lens[b] - 1 of sequence b).  All three NULL: attention only.
- * Domain: head_size 64 / 128, block_size 16, f16 / bf16 query, auto / fp8_e4m3 cache, 16-byte
- * aligned rows; anything else is B200PA_ERR_UNSUPPORTED (there is no second kernel for this
+ * Domain: head_size 32 / 64 / 96 / 128 / 192 / 256, block_size 16, f16 / bf16 query, auto /
+ * fp8_e4m3 cache, 16-byte aligned rows; anything else is B200PA_ERR_UNSUPPORTED (there is no second kernel for this
  * layout).  A workspace (b200pa_paged_attention_workspace_bytes) is required.
  */
 int b200pa_paged_attention_flash(

@@ -65,6 +65,13 @@ CASES = [
     ("with_empties_fp8", 9, 8, 1, 128, [0, 600, 0, 0, 31, 5000, 0, 512, 0], torch.bfloat16, "fp8", False),
     ("one_long_bf16", 1, 8, 1, 128, [70001], torch.bfloat16, "auto", False),
     ("llama70b_shard_fp8", 16, 8, 1, 128, [32768] * 16, torch.bfloat16, "fp8", False),
+    ("gemma_d256_fp8", 5, 16, 8, 256, [1000, 17, 512, 4100, 3333], torch.bfloat16, "fp8", False),
+    ("gemma_d256_bf16", 5, 16, 8, 256, [1000, 17, 512, 4100, 3333], torch.bfloat16, "auto", False),
+    ("d192_f16_fp8", 4, 24, 3, 192, [700, 33, 2049, 16], torch.float16, "fp8", False),
+    ("phi_d96_bf16", 6, 32, 32, 96, [1, 16, 17, 999, 2048, 31], torch.bfloat16, "auto", False),
+    ("d96_fp8_gqa12", 4, 24, 2, 96, [300, 5000, 12, 640], torch.bfloat16, "fp8", False),
+    ("d32_fp8", 4, 8, 8, 32, [300, 1500, 12, 640], torch.float16, "fp8", False),
+    ("d32_bf16", 4, 8, 2, 32, [300, 5000, 12, 640], torch.bfloat16, "auto", False),
 ]
 
 

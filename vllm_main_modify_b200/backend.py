@@ -412,7 +412,7 @@ class B200FlashLayoutAttentionBackend(B200PagedAttentionBackend):
 
     @staticmethod
     def get_supported_head_sizes() -> List[int]:
-        return [64, 128]
+        return [32, 64, 96, 128, 192, 256]
 
     @classmethod
     def get_supported_dtypes(cls) -> List[torch.dtype]:

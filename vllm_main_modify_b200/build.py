@@ -28,8 +28,15 @@ NVCC = os.path.join(CUDA_HOME, "bin", "nvcc")
 # The image exports CC/CXX=/opt/gcc/bin/*, a wrapper without libgomp; pin the system one.
 HOST_CXX = "/usr/bin/g++"
 
-CU_SOURCES = ["c_abi.cu", "cache_kernels.cu", "paged_attention_generic.cu",
-              "paged_attention_stream.cu", "merge_attn_states.cu", "block_ops.cu"]
+# (source, extra defines, object name): the stream kernel's instantiations are spread over four
+# translation units (STREAM_PART, see the end of paged_attention_stream.cu) to build in parallel
+CU_SOURCES = [("c_abi.cu", [], "c_abi.o"), ("cache_kernels.cu", [], "cache_kernels.o"),
+              ("paged_attention_generic.cu", [], "paged_attention_generic.o"),
+              ("paged_attention_stream.cu", ["-DSTREAM_PART=0"], "paged_attention_stream.o"),
+              ("paged_attention_stream.cu", ["-DSTREAM_PART=1"], "paged_attention_stream_flash.o"),
+              ("paged_attention_stream.cu", ["-DSTREAM_PART=2"], "paged_attention_stream_bs32.o"),
+              ("paged_attention_stream.cu", ["-DSTREAM_PART=3"], "paged_attention_stream_other.o"),
+              ("merge_attn_states.cu", [], "merge_attn_states.o"), ("block_ops.cu", [], "block_ops.o")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
               "-Xcompiler", "-fPIC", "-ccbin", HOST_CXX, "--expt-relaxed-constexpr",
               "-Xptxas", "-v", "-Wno-deprecated-gpu-targets"]
@@ -49,23 +56,24 @@ def _headers():
     return hs
 
 
-def _compile_cu(src: str, verbose: bool) -> str:
+def _compile_cu(unit, verbose: bool) -> str:
+    src, defines, objname = unit
     os.makedirs(BUILD, exist_ok=True)
-    obj = os.path.join(BUILD, src.replace(".cu", ".o"))
+    obj = os.path.join(BUILD, objname)
     stamp = obj + ".sha1"
-    key = _digest([os.path.join(CSRC, src)] + _headers(), " ".join(NVCC_FLAGS))
+    key = _digest([os.path.join(CSRC, src)] + _headers(), " ".join(NVCC_FLAGS + defines))
     if os.path.exists(obj) and os.path.exists(stamp) and open(stamp).read() == key:
         return obj
-    cmd = [NVCC] + NVCC_FLAGS + ["-c", os.path.join(CSRC, src), "-o", obj]
+    cmd = [NVCC] + NVCC_FLAGS + defines + ["-c", os.path.join(CSRC, src), "-o", obj]
     res = subprocess.run(cmd, capture_output=True, text=True)
-    log = os.path.join(BUILD, src + ".log")
+    log = os.path.join(BUILD, objname.replace(".o", ".cu") + ".log")
     with open(log, "w") as f:
         f.write(" ".join(cmd) + "\n" + res.stdout + res.stderr)
     if res.returncode != 0:
         sys.stderr.write(res.stdout + res.stderr)
-        raise RuntimeError(f"nvcc failed on {src}")
+        raise RuntimeError(f"nvcc failed on {src} {' '.join(defines)}")
     if verbose:
-        sys.stderr.write(f"[build] {src} ok (ptxas log: {log})\n")
+        sys.stderr.write(f"[build] {objname} ok (ptxas log: {log})\n")
     with open(stamp, "w") as f:
         f.write(key)
     return obj

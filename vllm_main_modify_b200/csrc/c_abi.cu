@@ -324,9 +324,10 @@ int b200pa_paged_attention_flash(
                      num_heads, num_kv_heads);
   if (kv_dtype != B200PA_KV_AUTO && (!k_scale || !v_scale))
     return set_error(B200PA_ERR_INVALID, "fp8 kv cache needs k_scale and v_scale");
-  if (head_size != 64 && head_size != 128)
-    return set_error(B200PA_ERR_UNSUPPORTED, "Unsupported head size: %d (flash layout: 64, 128)",
-                     head_size);
+  if (head_size != 32 && head_size != 64 && head_size != 96 && head_size != 128 &&
+      head_size != 192 && head_size != 256)
+    return set_error(B200PA_ERR_UNSUPPORTED,
+                     "Unsupported head size: %d (flash layout: 32, 64, 96, 128, 192, 256)", head_size);
   if (block_size != 16)
     return set_error(B200PA_ERR_UNSUPPORTED, "Unsupported block size: %d (flash layout: 16)",
                      block_size);

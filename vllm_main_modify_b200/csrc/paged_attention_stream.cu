@@ -164,6 +164,9 @@ __device__ __forceinline__ void e4m3x4_to_f16x2x2(uint32_t w, uint32_t& lo, uint
 }
 
 
+}  // namespace
+
+// (named, not file-local: the launchers of the four translation-unit parts below share it)
 struct StreamParams {
   void* out;           // [S,H,D] scalar_t
   float* lse;          // optional: natural-log sum-exp of the scaled logits per (seq, head)
@@ -193,6 +196,8 @@ struct StreamParams {
   int nw;                                              // NW: warps per CTA of the main kernel
   float scale;
 };
+
+namespace {
 
 // workspace slot: O^T fragments [D/16][32 lanes][4] fp32 (unnormalised, v_scale applied),
 // then m[8] (log2 domain), l[8]
@@ -1232,6 +1237,79 @@ int launch_stream_t(StreamParams& p, int num_sms, int64_t workspace_bytes, cudaS
 
 }  // namespace
 
+// The instantiations are spread over four translation units (this file compiled with
+// -DSTREAM_PART=0..3, see build.py) so that they build in parallel:
+//   0: entry point, support queries, the bf16 head-size-128 shapes (with the tuning variants)
+//   1: token-major ("flash") layout     2: 32-token cache blocks     3: the other head sizes
+#ifndef STREAM_PART
+#define STREAM_PART 0
+#endif
+int launch_stream_flash(StreamParams& p, bool fp8, int scalar_type, int head_size, int num_sms,
+    int64_t workspace_bytes, cudaStream_t stream);
+int launch_stream_bs32(StreamParams& p, bool fp8, int scalar_type, int head_size, int num_sms,
+    int64_t workspace_bytes, cudaStream_t stream);
+int launch_stream_other(StreamParams& p, bool fp8, int scalar_type, int head_size, int num_sms,
+    int64_t workspace_bytes, cudaStream_t stream);
+
+#define STREAM_CALL(ST, FP8V, DV, NWV, SG, PP, MB, ...) \
+  return launch_stream_t<ST, FP8V, DV, NWV, SG, PP, MB, ##__VA_ARGS__>(p, num_sms, workspace_bytes, stream)
+
+#if STREAM_PART == 1
+int launch_stream_flash(StreamParams& p, bool fp8, int scalar_type, int head_size, int num_sms,
+    int64_t workspace_bytes, cudaStream_t stream) {
+    // one instantiation per (scalar_t, cache type, head size): the default shapes of the
+    // x-packed kernel (the padded rows make the fp8 D=128 ring 216 KiB)
+#define STREAM_FLASH_BY_HEAD_SIZE(ST, NW128)                                                  \
+  switch (head_size) {                                                                       \
+    case 32:  if (fp8) { STREAM_CALL(ST, true, 32, 4, 3, 2, 2, true); }  else { STREAM_CALL(ST, false, 32, 4, 3, 2, 2, true); }  \
+    case 64:  if (fp8) { STREAM_CALL(ST, true, 64, 4, 3, 2, 2, true); }  else { STREAM_CALL(ST, false, 64, 4, 3, 2, 2, true); }  \
+    case 96:  if (fp8) { STREAM_CALL(ST, true, 96, 4, 3, 2, 2, true); }  else { STREAM_CALL(ST, false, 96, 4, 3, 2, 1, true); }  \
+    case 128: if (fp8) { STREAM_CALL(ST, true, 128, NW128, 3, 2, 1, true); } else { STREAM_CALL(ST, false, 128, 4, 4, 1, 1, true); } \
+    case 192: if (fp8) { STREAM_CALL(ST, true, 192, 4, 4, 2, 1, true); } else { STREAM_CALL(ST, false, 192, 4, 4, 1, 1, true); } \
+    case 256: if (fp8) { STREAM_CALL(ST, true, 256, 4, 3, 2, 1, true); } else { STREAM_CALL(ST, false, 256, 4, 3, 1, 1, true); } \
+    default: return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: head size %d", head_size);  \
+  }
+    if (scalar_type == B200PA_BF16) { STREAM_FLASH_BY_HEAD_SIZE(B200PA_BF16, 8) }
+    else { STREAM_FLASH_BY_HEAD_SIZE(B200PA_F16, 8) }
+#undef STREAM_FLASH_BY_HEAD_SIZE
+}
+#elif STREAM_PART == 2
+int launch_stream_bs32(StreamParams& p, bool fp8, int scalar_type, int head_size, int num_sms,
+    int64_t workspace_bytes, cudaStream_t stream) {
+    // 32-token cache blocks: stages of two 16-token tiles = one block (PPS = 2 everywhere)
+#define STREAM_BY_HEAD_SIZE_32(ST)                                                           \
+  switch (head_size) {                                                                       \
+    case 32:  if (fp8) { STREAM_CALL(ST, true, 32, 4, 3, 2, 2, false, 32); }  else { STREAM_CALL(ST, false, 32, 4, 3, 2, 2, false, 32); }  \
+    case 64:  if (fp8) { STREAM_CALL(ST, true, 64, 4, 3, 2, 2, false, 32); }  else { STREAM_CALL(ST, false, 64, 4, 3, 2, 2, false, 32); }  \
+    case 96:  if (fp8) { STREAM_CALL(ST, true, 96, 4, 3, 2, 2, false, 32); }  else { STREAM_CALL(ST, false, 96, 4, 3, 2, 1, false, 32); }  \
+    case 128: if (fp8) { STREAM_CALL(ST, true, 128, 8, 3, 2, 1, false, 32); } else { STREAM_CALL(ST, false, 128, 4, 3, 2, 1, false, 32); } \
+    case 192: if (fp8) { STREAM_CALL(ST, true, 192, 4, 4, 2, 1, false, 32); } else { STREAM_CALL(ST, false, 192, 4, 2, 2, 1, false, 32); } \
+    case 256: if (fp8) { STREAM_CALL(ST, true, 256, 4, 3, 2, 1, false, 32); } else { STREAM_CALL(ST, false, 256, 3, 2, 2, 1, false, 32); } \
+    default: return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: head size %d", head_size);  \
+  }
+    if (scalar_type == B200PA_BF16) { STREAM_BY_HEAD_SIZE_32(B200PA_BF16) }
+    else { STREAM_BY_HEAD_SIZE_32(B200PA_F16) }
+#undef STREAM_BY_HEAD_SIZE_32
+}
+#elif STREAM_PART == 3
+int launch_stream_other(StreamParams& p, bool fp8, int scalar_type, int head_size, int num_sms,
+    int64_t workspace_bytes, cudaStream_t stream) {
+  // the other head sizes (and f16 at 128): one shape each.  192 / 256: 12-16 KiB stages, 4 warps.
+#define STREAM_BY_HEAD_SIZE(ST)                                                              \
+  switch (head_size) {                                                                       \
+    case 32:  if (fp8) { STREAM_CALL(ST, true, 32, 4, 3, 2, 2); }  else { STREAM_CALL(ST, false, 32, 4, 3, 2, 2); }  \
+    case 64:  if (fp8) { STREAM_CALL(ST, true, 64, 4, 3, 2, 2); }  else { STREAM_CALL(ST, false, 64, 4, 3, 2, 2); }  \
+    case 96:  if (fp8) { STREAM_CALL(ST, true, 96, 4, 3, 2, 2); }  else { STREAM_CALL(ST, false, 96, 4, 3, 2, 1); }  \
+    case 128: if (fp8) { STREAM_CALL(ST, true, 128, 4, 3, 2, 2); } else { STREAM_CALL(ST, false, 128, 4, 4, 1, 1); } \
+    case 192: if (fp8) { STREAM_CALL(ST, true, 192, 4, 4, 2, 1); } else { STREAM_CALL(ST, false, 192, 4, 4, 1, 1); } \
+    case 256: if (fp8) { STREAM_CALL(ST, true, 256, 4, 3, 2, 1); } else { STREAM_CALL(ST, false, 256, 4, 3, 1, 1); } \
+    default: return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: head size %d", head_size);  \
+  }
+  if (scalar_type == B200PA_BF16) { STREAM_BY_HEAD_SIZE(B200PA_BF16) }
+  else { STREAM_BY_HEAD_SIZE(B200PA_F16) }
+#undef STREAM_BY_HEAD_SIZE
+}
+#else
 // Upper bound of the workspace any stream launch on a device with `num_sms` SMs needs.
 int64_t stream_workspace_bytes(int num_sms, int head_size) {
   // warps per SM + (at most 4) CTAs per SM, two slots each
@@ -1267,7 +1345,8 @@ bool stream_flash_supported(const void* query, const void* key_cache, const void
                             int64_t q_stride, int64_t block_stride, int64_t token_stride,
                             int64_t head_stride, int scalar_type, int kv_dtype) {
   if (block_size != kBS) return false;
-  if (head_size != 64 && head_size != 128) return false;
+  if (head_size != 32 && head_size != 64 && head_size != 96 && head_size != 128 &&
+      head_size != 192 && head_size != 256) return false;
   if (scalar_type != B200PA_BF16 && scalar_type != B200PA_F16) return false;
   if (kv_dtype != B200PA_KV_AUTO && kv_dtype != B200PA_KV_FP8_E4M3) return false;
   if (num_kv_heads <= 0 || num_heads % num_kv_heads != 0) return false;
@@ -1336,9 +1415,11 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
   p.nw = 0;
   p.scale = scale;
   const bool fp8 = kv_dtype == B200PA_KV_FP8_E4M3;
+  if (flash_token_stride > 0)
+    return launch_stream_flash(p, fp8, scalar_type, head_size, num_sms, workspace_bytes, stream);
+  if (block_size == 32)
+    return launch_stream_bs32(p, fp8, scalar_type, head_size, num_sms, workspace_bytes, stream);
   // <ST, FP8, D, NW, STAGES, PPS, MINB>: fp8 stage = PPS x 4 KiB, 16-bit stage = PPS x 8 KiB (D=128)
-#define STREAM_CALL(ST, FP8V, DV, NWV, SG, PP, MB, ...) \
-  return launch_stream_t<ST, FP8V, DV, NWV, SG, PP, MB, ##__VA_ARGS__>(p, num_sms, workspace_bytes, stream)
 #define STREAM_TUNE_FP8(ST, DV)                                        \
   switch (tune) {                                                      \
     case 1: STREAM_CALL(ST, true, DV, 4, 4, 2, 1);                     \
@@ -1361,53 +1442,14 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
     case 7: STREAM_CALL(ST, false, DV, 5, 4, 1, 1);                    \
     default: STREAM_CALL(ST, false, DV, 4, 4, 1, 1);                   \
   }
-  if (flash_token_stride > 0) {
-    // one instantiation per (scalar_t, cache type, head size): the default shapes of the
-    // x-packed kernel (the padded rows make the fp8 D=128 ring 216 KiB)
-    if (scalar_type == B200PA_BF16) {
-      if (fp8) { if (head_size == 128) { STREAM_CALL(B200PA_BF16, true, 128, 8, 3, 2, 1, true); } else { STREAM_CALL(B200PA_BF16, true, 64, 4, 3, 2, 2, true); } }
-      else     { if (head_size == 128) { STREAM_CALL(B200PA_BF16, false, 128, 4, 4, 1, 1, true); } else { STREAM_CALL(B200PA_BF16, false, 64, 4, 3, 2, 2, true); } }
-    } else {
-      if (fp8) { if (head_size == 128) { STREAM_CALL(B200PA_F16, true, 128, 4, 3, 2, 2, true); } else { STREAM_CALL(B200PA_F16, true, 64, 4, 3, 2, 2, true); } }
-      else     { if (head_size == 128) { STREAM_CALL(B200PA_F16, false, 128, 4, 4, 1, 1, true); } else { STREAM_CALL(B200PA_F16, false, 64, 4, 3, 2, 2, true); } }
-    }
-  }
-  if (block_size == 32) {
-    // 32-token cache blocks: stages of two 16-token tiles = one block (PPS = 2 everywhere)
-#define STREAM_BY_HEAD_SIZE_32(ST)                                                           \
-  switch (head_size) {                                                                       \
-    case 32:  if (fp8) { STREAM_CALL(ST, true, 32, 4, 3, 2, 2, false, 32); }  else { STREAM_CALL(ST, false, 32, 4, 3, 2, 2, false, 32); }  \
-    case 64:  if (fp8) { STREAM_CALL(ST, true, 64, 4, 3, 2, 2, false, 32); }  else { STREAM_CALL(ST, false, 64, 4, 3, 2, 2, false, 32); }  \
-    case 96:  if (fp8) { STREAM_CALL(ST, true, 96, 4, 3, 2, 2, false, 32); }  else { STREAM_CALL(ST, false, 96, 4, 3, 2, 1, false, 32); }  \
-    case 128: if (fp8) { STREAM_CALL(ST, true, 128, 8, 3, 2, 1, false, 32); } else { STREAM_CALL(ST, false, 128, 4, 3, 2, 1, false, 32); } \
-    case 192: if (fp8) { STREAM_CALL(ST, true, 192, 4, 4, 2, 1, false, 32); } else { STREAM_CALL(ST, false, 192, 4, 2, 2, 1, false, 32); } \
-    case 256: if (fp8) { STREAM_CALL(ST, true, 256, 4, 3, 2, 1, false, 32); } else { STREAM_CALL(ST, false, 256, 3, 2, 2, 1, false, 32); } \
-    default: return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: head size %d", head_size);  \
-  }
-    if (scalar_type == B200PA_BF16) { STREAM_BY_HEAD_SIZE_32(B200PA_BF16) }
-    else { STREAM_BY_HEAD_SIZE_32(B200PA_F16) }
-#undef STREAM_BY_HEAD_SIZE_32
-  }
   if (scalar_type == B200PA_BF16 && head_size == 128) {
     if (fp8) { STREAM_TUNE_FP8(B200PA_BF16, 128) } else { STREAM_TUNE_16(B200PA_BF16, 128) }
   }
-  // the other head sizes (and f16 at 128): one shape each.  192 / 256: 12-16 KiB stages, 4 warps.
-#define STREAM_BY_HEAD_SIZE(ST)                                                              \
-  switch (head_size) {                                                                       \
-    case 32:  if (fp8) { STREAM_CALL(ST, true, 32, 4, 3, 2, 2); }  else { STREAM_CALL(ST, false, 32, 4, 3, 2, 2); }  \
-    case 64:  if (fp8) { STREAM_CALL(ST, true, 64, 4, 3, 2, 2); }  else { STREAM_CALL(ST, false, 64, 4, 3, 2, 2); }  \
-    case 96:  if (fp8) { STREAM_CALL(ST, true, 96, 4, 3, 2, 2); }  else { STREAM_CALL(ST, false, 96, 4, 3, 2, 1); }  \
-    case 128: if (fp8) { STREAM_CALL(ST, true, 128, 4, 3, 2, 2); } else { STREAM_CALL(ST, false, 128, 4, 4, 1, 1); } \
-    case 192: if (fp8) { STREAM_CALL(ST, true, 192, 4, 4, 2, 1); } else { STREAM_CALL(ST, false, 192, 4, 4, 1, 1); } \
-    case 256: if (fp8) { STREAM_CALL(ST, true, 256, 4, 3, 2, 1); } else { STREAM_CALL(ST, false, 256, 4, 3, 1, 1); } \
-    default: return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: head size %d", head_size);  \
-  }
-  if (scalar_type == B200PA_BF16) { STREAM_BY_HEAD_SIZE(B200PA_BF16) }
-  else { STREAM_BY_HEAD_SIZE(B200PA_F16) }
-#undef STREAM_BY_HEAD_SIZE
 #undef STREAM_TUNE_FP8
 #undef STREAM_TUNE_16
-#undef STREAM_CALL
+  return launch_stream_other(p, fp8, scalar_type, head_size, num_sms, workspace_bytes, stream);
 }
+#endif
+#undef STREAM_CALL
 
 }  // namespace b200pa

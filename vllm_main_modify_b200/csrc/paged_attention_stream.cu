@@ -5,7 +5,7 @@
 // paged_attention_v2_kernel :525-557 + paged_attention_v2_reduce_kernel :560-664, launched from
 // paged_attention_v1.cu:46-125 / paged_attention_v2.cu:47-126) for head_size 32/64/96/128/192/256,
 // block_size 16/32, bf16/fp16 query and a 16-bit or fp8-e4m3 KV cache -- x-packed layout, or
-// (FLASH, block_size 16, head_size 64/128) the token-major layout of reshape_and_cache_flash --
+// (FLASH, block_size 16, the same head sizes) the token-major layout of reshape_and_cache_flash --
 // with the new token's cache write optionally fused in (decode_step).
 //
 //  * WORK DECOMPOSITION.  The unit of work is one pipeline STAGE: PPS consecutive pages of one

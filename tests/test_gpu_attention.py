@@ -603,6 +603,32 @@ def test_zero_length_sequence_v1_gives_zeros(ops, native):
         assert float(out[0].float().abs().sum()) > 0.0
 
 
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+@pytest.mark.parametrize("kv", ["auto", "fp8"])
+def test_second_device_in_one_process(ops, native, ora, kv):
+    """The stream kernel's shared-memory opt-in is a per-device function attribute: a process
+    that has already launched on cuda:0 must still be able to launch on cuda:1 (the reference's
+    ops run under an OptionalCUDAGuard of the query's device, paged_attention_v1.cu:88)."""
+    B, H, Hkv, D, BS, NB = 3, 16, 2, 128, 16, 80
+    lens = [300, 17, 1000]
+    s = D ** -0.5
+    q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, NB, lens, torch.bfloat16, seed=21,
+                                             kv=kv, lo=-s, hi=s, permute=True)
+    want = _run_oracle(ora, "v1", q, kc, vc, Hkv, s, bt, sl, BS, max(lens), None, kv, 1.0, 1.0)
+    native.set_impl(STREAM)
+    try:
+        for dev in ("cuda:0", "cuda:1", "cuda:0"):
+            qd, kcd, vcd, btd, sld = (t.to(dev) for t in (q, kc, vc, bt, sl))
+            one = torch.ones((), dtype=torch.float32, device=dev)
+            out = torch.full_like(qd, float("nan"))
+            ops.paged_attention_v1(out, qd, kcd, vcd, Hkv, s, btd, sld, BS, max(lens), None, kv,
+                                   one, one, 0, 0, 0, 64, 0)
+            torch.cuda.synchronize(dev)
+            torch.testing.assert_close(out.cpu().float(), want.float(), atol=1e-2, rtol=1e-2)
+    finally:
+        native.set_impl(native.IMPL_AUTO)
+
+
 def test_tail_page_garbage_is_ignored(ops, native, ora):
     """Slots past seq_len in the last page may hold anything, including NaN codes
     (attention_kernels.cuh:415-425 zeroes them)."""

@@ -1177,7 +1177,13 @@ int launch_stream_t(StreamParams& p, int num_sms, int64_t workspace_bytes, cudaS
   constexpr int CES = FP8 ? 1 : 2;
   constexpr int SMEM = NW * STAGES * PPS * 2 * kBS * (FLASH ? D * CES + 16 : D * CES);
   auto kern = paged_attention_stream_kernel<ST, FP8, D, NW, STAGES, PPS, MINB, FLASH, BSZ>;
-  static int ctas_per_sm = 0;  // per instantiation
+  // per instantiation AND per device: the shared-memory opt-in is a per-device function
+  // attribute (a process that drives several GPUs must set it on each)
+  static int ctas_per_sm_of[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64)
+    return set_error(B200PA_ERR_CUDA, "cudaGetDevice failed or device ordinal out of range");
+  int& ctas_per_sm = ctas_per_sm_of[dev];
   if (ctas_per_sm == 0) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
     if (e != cudaSuccess)

@@ -609,7 +609,7 @@ def test_second_device_in_one_process(ops, native, ora, kv):
     """The stream kernel's shared-memory opt-in is a per-device function attribute: a process
     that has already launched on cuda:0 must still be able to launch on cuda:1 (the reference's
     ops run under an OptionalCUDAGuard of the query's device, paged_attention_v1.cu:88)."""
-    B, H, Hkv, D, BS, NB = 3, 16, 2, 128, 16, 80
+    B, H, Hkv, D, BS, NB = 3, 16, 2, 128, 16, 100
     lens = [300, 17, 1000]
     s = D ** -0.5
     q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, NB, lens, torch.bfloat16, seed=21,

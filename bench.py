@@ -293,6 +293,39 @@ def run_ours(args):
 
     for _ in range(3):
         e2e_step()
+    if os.environ.get("B200PA_E2E_BREAKDOWN") == "1" and rank == 0:
+        # development aid: host time of each part of the eager step (median of 30), to stderr
+        parts_us = {"h2d_enqueue": [], "forward": [], "d2h_enqueue": [], "sync": []}
+        for _ in range(30):
+            t0 = time.perf_counter()
+            dbuf.copy_(hbuf, non_blocking=True)
+            t1 = time.perf_counter()
+            impl.forward(layer, dq, dk, dv, w["kv_cache"], meta2, output=out)
+            t2 = time.perf_counter()
+            hout.copy_(out, non_blocking=True)
+            t3 = time.perf_counter()
+            torch.cuda.current_stream().synchronize()
+            t4 = time.perf_counter()
+            for name, dt in zip(parts_us, (t1 - t0, t2 - t1, t3 - t2, t4 - t3)):
+                parts_us[name].append(dt * 1e6)
+        sys.stderr.write("[bench] e2e host time per part, us (median): " + json.dumps(
+            {k: round(sorted(v)[len(v) // 2], 1) for k, v in parts_us.items()}) + "\n")
+        # ... and the device-side segments of the same step (CUDA events between the parts)
+        seg_us = {"h2d": [], "forward": [], "d2h": []}
+        for _ in range(30):
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+            ev[0].record()
+            dbuf.copy_(hbuf, non_blocking=True)
+            ev[1].record()
+            impl.forward(layer, dq, dk, dv, w["kv_cache"], meta2, output=out)
+            ev[2].record()
+            hout.copy_(out, non_blocking=True)
+            ev[3].record()
+            torch.cuda.current_stream().synchronize()
+            for name, i in zip(seg_us, range(3)):
+                seg_us[name].append(ev[i].elapsed_time(ev[i + 1]) * 1e3)
+        sys.stderr.write("[bench] e2e device time per segment, us (median): " + json.dumps(
+            {k: round(sorted(v)[len(v) // 2], 1) for k, v in seg_us.items()}) + "\n")
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -333,10 +366,24 @@ def run_ours(args):
         e1.record()
         barrier()
         ms_e2e_graph = e0.elapsed_time(e1)
+        # the replay must order H2D -> forward -> D2H like the eager step: change the host-side
+        # query, replay, and compare the host-side output with an eager step on the same input
+        hq = seg(hbuf, "q", q2)
+        saved = hq.clone()
+        hq.copy_(-saved)
+        e2e_graph_step()
+        got = hout.clone()
+        e2e_step()
+        if not torch.equal(got.view(torch.uint8), hout.view(torch.uint8)):
+            raise RuntimeError("graph replay and eager step disagree on a changed input")
+        hq.copy_(saved)
+        e2e_step()
     except Exception as exc:   # the eager figure stands; say why there is no replay figure
-        sys.stderr.write(f"[bench] e2e graph replay skipped: {exc}\n")
-        barrier()
-        barrier()
+        sys.stderr.write(f"[bench] e2e graph replay dropped: {exc}\n")
+        if ms_e2e_graph != ms_e2e_graph:   # failed before the timed loop: keep the ranks in step
+            barrier()
+            barrier()
+        ms_e2e_graph = float("nan")
 
     # ---- reduce over ranks ---------------------------------------------------
     my_bytes = kv_bytes(w["lens"], w["Hkv"], kv)

@@ -112,14 +112,15 @@ def _alibi(H):
 @pytest.mark.parametrize("impl", [GENERIC, STREAM])
 @pytest.mark.parametrize("use_alibi", [False, True])
 @pytest.mark.parametrize("heads", [(40, 40), (64, 8)])
-@pytest.mark.parametrize("head_size", [32, 64, 80, 96, 128, 192, 256])
+@pytest.mark.parametrize("head_size", [32, 64, 80, 96, 112, 128, 192, 256])
 @pytest.mark.parametrize("block_size", [16, 32])
 @pytest.mark.parametrize("kv", ["auto", "fp8"])
 def test_paged_attention_sweep(ops, native, ora, version, impl, heads, head_size, block_size,
                                use_alibi, kv):
     H, Hkv = heads
     dtype = torch.bfloat16
-    stream_ok = block_size in (16, 32) and head_size in (32, 64, 96, 128, 192, 256)
+    stream_ok = block_size in (16, 32) and (head_size in (32, 64, 96, 128, 192, 256) or
+                                            (head_size in (80, 112) and kv == "auto"))
     if impl == STREAM and not stream_ok:
         pytest.skip("shape served by the generic kernel")
     if kv == "fp8" and head_size % 16:

@@ -59,6 +59,8 @@ CASES = [
     ("phi_d96_bf16", 6, 32, 32, 96, [1, 16, 17, 999, 2048, 31], torch.bfloat16, "auto", False),
     ("d96_fp8_gqa12", 4, 24, 2, 96, [300, 5000, 12, 640], torch.bfloat16, "fp8", False),
     ("d32_fp8", 4, 8, 8, 32, [300, 1500, 12, 640], torch.float16, "fp8", False),
+    ("neox_d80_f16", 6, 32, 32, 80, [1, 16, 17, 999, 2048, 31], torch.float16, "auto", False),
+    ("d112_bf16_gqa4", 5, 16, 4, 112, [1000, 17, 512, 4100, 3333], torch.bfloat16, "auto", True),
 ]
 
 
@@ -153,7 +155,8 @@ def test_decode_step_equals_write_then_attend(ops, native, ora, case, impl):
 BS32_CASES = [c for c in CASES if c[0] in ("gqa8_fp8_page_edges", "gqa4_bf16_page_edges",
                                             "gqa16_two_tiles_fp8", "mha_f16_d64_alibi",
                                             "gemma_d256_fp8", "gemma_d256_bf16", "d192_f16_fp8",
-                                            "phi_d96_bf16", "many_short_fp8")]
+                                            "phi_d96_bf16", "many_short_fp8", "neox_d80_f16",
+                                            "d112_bf16_gqa4")]
 
 
 @pytest.mark.parametrize("case", BS32_CASES, ids=[c[0] for c in BS32_CASES])

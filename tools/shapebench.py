@@ -25,6 +25,8 @@ SHAPES = [
     ("phi_d96_bf16", 64, 32, 32, 96, 2048, "auto"),
     ("d192_fp8", 64, 24, 8, 192, 8192, "fp8"),
     ("d64_fp8_gqa8", 128, 64, 8, 64, 8192, "fp8"),
+    ("neox_d80_bf16", 64, 32, 32, 80, 2048, "auto"),
+    ("d112_bf16_gqa4", 64, 32, 8, 112, 4096, "auto"),
     # 32-token cache blocks
     ("llama8b_bs32_bf16", 64, 32, 8, 128, 4096, "auto", 32),
     ("llama8b_bs32_fp8", 256, 32, 8, 128, 8192, "fp8", 32),

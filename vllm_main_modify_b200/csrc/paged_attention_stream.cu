@@ -3,7 +3,8 @@
 // Replaces the per-sequence decode kernels of the reference
 // (csrc/attention/attention_kernels.cuh:85-491 through paged_attention_v1_kernel :494-522 and
 // paged_attention_v2_kernel :525-557 + paged_attention_v2_reduce_kernel :560-664, launched from
-// paged_attention_v1.cu:46-125 / paged_attention_v2.cu:47-126) for head_size 32/64/96/128/192/256,
+// paged_attention_v1.cu:46-125 / paged_attention_v2.cu:47-126) for head_size 32/64/96/128/192/256
+// (80 / 112 too with a 16-bit cache),
 // block_size 16/32, bf16/fp16 query and a 16-bit or fp8-e4m3 KV cache -- x-packed layout, or
 // (FLASH, block_size 16, the same head sizes) the token-major layout of reshape_and_cache_flash --
 // with the new token's cache write optionally fused in (decode_step).
@@ -1287,7 +1288,9 @@ int launch_stream_bs32(StreamParams& p, bool fp8, int scalar_type, int head_size
   switch (head_size) {                                                                       \
     case 32:  if (fp8) { STREAM_CALL(ST, true, 32, 4, 3, 2, 2, false, 32); }  else { STREAM_CALL(ST, false, 32, 4, 3, 2, 2, false, 32); }  \
     case 64:  if (fp8) { STREAM_CALL(ST, true, 64, 4, 3, 2, 2, false, 32); }  else { STREAM_CALL(ST, false, 64, 4, 3, 2, 2, false, 32); }  \
+    case 80:  if (!fp8) { STREAM_CALL(ST, false, 80, 4, 3, 2, 2, false, 32); } return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: head size %d needs a 16-bit cache", head_size);  \
     case 96:  if (fp8) { STREAM_CALL(ST, true, 96, 4, 3, 2, 2, false, 32); }  else { STREAM_CALL(ST, false, 96, 4, 3, 2, 1, false, 32); }  \
+    case 112: if (!fp8) { STREAM_CALL(ST, false, 112, 4, 3, 2, 1, false, 32); } return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: head size %d needs a 16-bit cache", head_size); \
     case 128: if (fp8) { STREAM_CALL(ST, true, 128, 8, 3, 2, 1, false, 32); } else { STREAM_CALL(ST, false, 128, 4, 3, 2, 1, false, 32); } \
     case 192: if (fp8) { STREAM_CALL(ST, true, 192, 4, 4, 2, 1, false, 32); } else { STREAM_CALL(ST, false, 192, 4, 2, 2, 1, false, 32); } \
     case 256: if (fp8) { STREAM_CALL(ST, true, 256, 4, 3, 2, 1, false, 32); } else { STREAM_CALL(ST, false, 256, 3, 2, 2, 1, false, 32); } \
@@ -1305,7 +1308,9 @@ int launch_stream_other(StreamParams& p, bool fp8, int scalar_type, int head_siz
   switch (head_size) {                                                                       \
     case 32:  if (fp8) { STREAM_CALL(ST, true, 32, 4, 3, 2, 2); }  else { STREAM_CALL(ST, false, 32, 4, 3, 2, 2); }  \
     case 64:  if (fp8) { STREAM_CALL(ST, true, 64, 4, 3, 2, 2); }  else { STREAM_CALL(ST, false, 64, 4, 3, 2, 2); }  \
+    case 80:  if (!fp8) { STREAM_CALL(ST, false, 80, 4, 3, 2, 2); } return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: head size %d needs a 16-bit cache", head_size);  \
     case 96:  if (fp8) { STREAM_CALL(ST, true, 96, 4, 3, 2, 2); }  else { STREAM_CALL(ST, false, 96, 4, 3, 2, 1); }  \
+    case 112: if (!fp8) { STREAM_CALL(ST, false, 112, 4, 3, 2, 1); } return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: head size %d needs a 16-bit cache", head_size); \
     case 128: if (fp8) { STREAM_CALL(ST, true, 128, 4, 3, 2, 2); } else { STREAM_CALL(ST, false, 128, 4, 4, 1, 1); } \
     case 192: if (fp8) { STREAM_CALL(ST, true, 192, 4, 4, 2, 1); } else { STREAM_CALL(ST, false, 192, 4, 4, 1, 1); } \
     case 256: if (fp8) { STREAM_CALL(ST, true, 256, 4, 3, 2, 1); } else { STREAM_CALL(ST, false, 256, 4, 3, 1, 1); } \
@@ -1329,9 +1334,12 @@ bool stream_supported(const void* query, const void* key_cache, const void* valu
                       int scalar_type, int kv_dtype, int blocksparse_vert_stride) {
   if (blocksparse_vert_stride > 1) return false;
   if (block_size != 16 && block_size != 32) return false;
-  // multiples of 32 of the reference's head sizes (80, 112, 120 stay on the generic kernel)
+  // multiples of 32 of the reference's head sizes; 80 and 112 (multiples of 16) with a 16-bit
+  // cache only -- the fp8 fragments come 32 head elements at a time; 120 stays on the generic kernel
+  const bool mult16_only = head_size == 80 || head_size == 112;
   if (head_size != 32 && head_size != 64 && head_size != 96 && head_size != 128 &&
-      head_size != 192 && head_size != 256) return false;
+      head_size != 192 && head_size != 256 && !(mult16_only && kv_dtype == B200PA_KV_AUTO))
+    return false;
   if (scalar_type != B200PA_BF16 && scalar_type != B200PA_F16) return false;
   if (kv_dtype != B200PA_KV_AUTO && kv_dtype != B200PA_KV_FP8_E4M3) return false;
   if (num_kv_heads <= 0 || num_heads % num_kv_heads != 0) return false;

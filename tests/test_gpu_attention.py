@@ -183,6 +183,33 @@ def test_other_dtypes_and_block_sizes(ops, native, ora, dtype, version, kv, bloc
     _close(got, want, *tol)
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("head_size", [64, 128])
+@pytest.mark.parametrize("version", ["v1", "v2"])
+def test_stream_kernel_serves_fp8_e5m2(ops, native, ora, dtype, head_size, version):
+    """fp8_e5m2 caches (DISPATCH_BY_KV_CACHE_DTYPE, quant_utils.cuh:545-582) on the stream kernel:
+    same tolerance against the oracle as e4m3, and the generic kernel's output beside it."""
+    B, H, Hkv, D, NB = 6, 32, 4, head_size, 700
+    lens = [1, 17, 512, 513, 3000, 4097]
+    s = D ** -0.5
+    q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, 16, NB, lens, dtype, seed=5, kv="fp8",
+                                             lo=-s, hi=s, permute=True)
+    kc, vc = kc & 0xBB, vc & 0xBB          # moderate exponents, no inf / nan codes
+    ks, vs = 0.01, 0.02
+    want = _run_oracle(ora, version, q, kc, vc, Hkv, s, bt, sl, 16, max(lens), None, "fp8_e5m2",
+                       ks, vs)
+    outs = {}
+    for impl in (STREAM, GENERIC):
+        native.set_impl(impl)
+        try:
+            outs[impl], *_ = _run_gpu(ops, version, q, kc, vc, Hkv, s, bt, sl, 16, max(lens), None,
+                                      "fp8_e5m2", ks, vs)
+        finally:
+            native.set_impl(native.IMPL_AUTO)
+        _close(outs[impl], want)
+    _close(outs[STREAM], outs[GENERIC])
+
+
 # ------------------------------------------------------------ golden fixtures
 
 ATTN_GOLDEN = ["attn_gqa_bf16_d128.npz", "attn_mha_bf16_d64_alibi.npz",

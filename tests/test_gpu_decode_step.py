@@ -59,6 +59,9 @@ CASES = [
     ("phi_d96_bf16", 6, 32, 32, 96, [1, 16, 17, 999, 2048, 31], torch.bfloat16, "auto", False),
     ("d96_fp8_gqa12", 4, 24, 2, 96, [300, 5000, 12, 640], torch.bfloat16, "fp8", False),
     ("d32_fp8", 4, 8, 8, 32, [300, 1500, 12, 640], torch.float16, "fp8", False),
+    ("gqa8_e5m2_page_edges", 8, 64, 8, 128, [1, 16, 17, 32, 33, 511, 512, 513], torch.bfloat16, "fp8_e5m2", False),
+    ("gqa4_e5m2_d64_f16_alibi", 7, 32, 8, 64, [_RND.randint(1, 3000) for _ in range(7)], torch.float16, "fp8_e5m2", True),
+    ("e5m2_ragged_long", 4, 16, 2, 128, [40000, 129, 5000, 16384 + 3], torch.bfloat16, "fp8_e5m2", False),
     ("neox_d80_f16", 6, 32, 32, 80, [1, 16, 17, 999, 2048, 31], torch.float16, "auto", False),
     ("d112_bf16_gqa4", 5, 16, 4, 112, [1000, 17, 512, 4100, 3333], torch.bfloat16, "auto", True),
 ]

@@ -152,8 +152,15 @@ __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
   }
   return r;
 }
-// e4m3 x4 (one 32-bit word) -> two f16x2 words: lo = bytes 0,1 ; hi = bytes 2,3
-__device__ __forceinline__ void e4m3x4_to_f16x2x2(uint32_t w, uint32_t& lo, uint32_t& hi) {
+// fp8 x4 (one 32-bit word) -> two f16x2 words: lo = bytes 0,1 ; hi = bytes 2,3.  Exact for both
+// formats; an e5m2 code is the high byte of the f16 with the same value (two byte permutes).
+template <bool E5>
+__device__ __forceinline__ void fp8x4_to_f16x2x2(uint32_t w, uint32_t& lo, uint32_t& hi) {
+  if constexpr (E5) {
+    asm("prmt.b32 %0, %1, 0, 0x1404;" : "=r"(lo) : "r"(w));
+    asm("prmt.b32 %0, %1, 0, 0x3424;" : "=r"(hi) : "r"(w));
+    return;
+  }
   asm("{\n"
       ".reg .b16 l, h;\n"
       "mov.b32 {l, h}, %2;\n"
@@ -324,9 +331,12 @@ __device__ __forceinline__ void store_out(typename Scalar<ST>::type* out_tile,
 // BSZ: tokens per cache block (16 or 32).  The kernel's unit stays the 16-token M tile ("page"
 // below); with BSZ = 32 a cache block is two tiles that arrive in one bulk copy and are addressed
 // inside the block by the layout's strides (K chunk stride BSZ*16 B, V row stride BSZ elements).
-template <int ST, bool FP8, int D, int NW, int STAGES, int PPS, int MINB, bool FLASH, int BSZ>
+// E5: the fp8 codes are e5m2 (kv_cache_dtype "fp8_e5m2") instead of e4m3.
+template <int ST, bool FP8, int D, int NW, int STAGES, int PPS, int MINB, bool FLASH, int BSZ,
+          bool E5>
 __global__ void __launch_bounds__(NW * 32, MINB)
 paged_attention_stream_kernel(const StreamParams p) {
+  static_assert(FP8 || !E5, "E5 selects the fp8 format");
   using T = typename Scalar<ST>::type;
   constexpr bool MMA_BF16 = (!FP8) && (ST == B200PA_BF16);  // fp8 pages compute in f16
   constexpr int CES = FP8 ? 1 : 2;                           // cache element bytes
@@ -697,9 +707,9 @@ paged_attention_stream_kernel(const StreamParams p) {
           if constexpr (FP8) {
             const T* ke = reinterpret_cast<const T*>(&nt_k[j]);
             const T* ve = reinterpret_cast<const T*>(&nt_v[j]);
-            kw = fp8_quant2<B200PA_KV_FP8_E4M3>(Scalar<ST>::to_float(ke[0]),
+            kw = fp8_quant2<(E5 ? B200PA_KV_FP8_E5M2 : B200PA_KV_FP8_E4M3)>(Scalar<ST>::to_float(ke[0]),
                                                 Scalar<ST>::to_float(ke[1]), ks_raw);
-            vw = fp8_quant2<B200PA_KV_FP8_E4M3>(Scalar<ST>::to_float(ve[0]),
+            vw = fp8_quant2<(E5 ? B200PA_KV_FP8_E5M2 : B200PA_KV_FP8_E4M3)>(Scalar<ST>::to_float(ve[0]),
                                                 Scalar<ST>::to_float(ve[1]), out_scale);
           }
           if constexpr (FLASH) {
@@ -748,11 +758,11 @@ paged_attention_stream_kernel(const StreamParams p) {
           for (int c = 0; c < KSTEPS; c += 2) {
             uint32_t w4[4], a[4];
             ldmatrix_x4(w4, kbase + c * (FLASH ? 16 : KCS) + k_lane_off);
-            e4m3x4_to_f16x2x2(w4[0], a[0], a[2]);
-            e4m3x4_to_f16x2x2(w4[1], a[1], a[3]);
+            fp8x4_to_f16x2x2<E5>(w4[0], a[0], a[2]);
+            fp8x4_to_f16x2x2<E5>(w4[1], a[1], a[3]);
             mma16816<false>(sc[g], a, qb[c][0], qb[c][1]);
-            e4m3x4_to_f16x2x2(w4[2], a[0], a[2]);
-            e4m3x4_to_f16x2x2(w4[3], a[1], a[3]);
+            fp8x4_to_f16x2x2<E5>(w4[2], a[0], a[2]);
+            fp8x4_to_f16x2x2<E5>(w4[3], a[1], a[3]);
             mma16816<false>(sb, a, qb[c + 1][0], qb[c + 1][1]);
           }
         } else {
@@ -860,12 +870,12 @@ paged_attention_stream_kernel(const StreamParams p) {
         for (int gg = 0; gg < D / 32; ++gg) {
           uint32_t w4[4], a[4];
           ldmatrix_x4_trans(w4, vbase + gg * 32 + v_lane_off);
-          e4m3x4_to_f16x2x2(prmt<0x6420>(w4[0], w4[1]), a[0], a[2]);
-          e4m3x4_to_f16x2x2(prmt<0x7531>(w4[0], w4[1]), a[1], a[3]);
+          fp8x4_to_f16x2x2<E5>(prmt<0x6420>(w4[0], w4[1]), a[0], a[2]);
+          fp8x4_to_f16x2x2<E5>(prmt<0x7531>(w4[0], w4[1]), a[1], a[3]);
           if constexpr (MASKED) { a[0] &= m01; a[1] &= m01; a[2] &= m23; a[3] &= m23; }
           mma16816<false>(o[2 * gg], a, pb[g][0], pb[g][1]);
-          e4m3x4_to_f16x2x2(prmt<0x6420>(w4[2], w4[3]), a[0], a[2]);
-          e4m3x4_to_f16x2x2(prmt<0x7531>(w4[2], w4[3]), a[1], a[3]);
+          fp8x4_to_f16x2x2<E5>(prmt<0x6420>(w4[2], w4[3]), a[0], a[2]);
+          fp8x4_to_f16x2x2<E5>(prmt<0x7531>(w4[2], w4[3]), a[1], a[3]);
           if constexpr (MASKED) { a[0] &= m01; a[1] &= m01; a[2] &= m23; a[3] &= m23; }
           mma16816<false>(o[2 * gg + 1], a, pb[g][0], pb[g][1]);
         }
@@ -874,12 +884,12 @@ paged_attention_stream_kernel(const StreamParams p) {
         for (int gg = 0; gg < D / 32; ++gg) {
           uint32_t w4[4], a[4];
           ldmatrix_x4(w4, vbase + gg * (32 * VRS) + v_lane_off);
-          e4m3x4_to_f16x2x2(w4[0], a[0], a[2]);
-          e4m3x4_to_f16x2x2(w4[1], a[1], a[3]);
+          fp8x4_to_f16x2x2<E5>(w4[0], a[0], a[2]);
+          fp8x4_to_f16x2x2<E5>(w4[1], a[1], a[3]);
           if constexpr (MASKED) { a[0] &= m01; a[1] &= m01; a[2] &= m23; a[3] &= m23; }
           mma16816<false>(o[2 * gg], a, pb[g][0], pb[g][1]);
-          e4m3x4_to_f16x2x2(w4[2], a[0], a[2]);
-          e4m3x4_to_f16x2x2(w4[3], a[1], a[3]);
+          fp8x4_to_f16x2x2<E5>(w4[2], a[0], a[2]);
+          fp8x4_to_f16x2x2<E5>(w4[3], a[1], a[3]);
           if constexpr (MASKED) { a[0] &= m01; a[1] &= m01; a[2] &= m23; a[3] &= m23; }
           mma16816<false>(o[2 * gg + 1], a, pb[g][0], pb[g][1]);
         }
@@ -1173,11 +1183,11 @@ paged_attention_stream_merge_kernel(const StreamParams p) {
 constexpr int kMaxWarpsPerSm = 16;
 
 template <int ST, bool FP8, int D, int NW, int STAGES, int PPS, int MINB, bool FLASH = false,
-          int BSZ = 16>
+          int BSZ = 16, bool E5 = false>
 int launch_stream_t(StreamParams& p, int num_sms, int64_t workspace_bytes, cudaStream_t stream) {
   constexpr int CES = FP8 ? 1 : 2;
   constexpr int SMEM = NW * STAGES * PPS * 2 * kBS * (FLASH ? D * CES + 16 : D * CES);
-  auto kern = paged_attention_stream_kernel<ST, FP8, D, NW, STAGES, PPS, MINB, FLASH, BSZ>;
+  auto kern = paged_attention_stream_kernel<ST, FP8, D, NW, STAGES, PPS, MINB, FLASH, BSZ, E5>;
   // per instantiation AND per device: the shared-memory opt-in is a per-device function
   // attribute (a process that drives several GPUs must set it on each)
   static int ctas_per_sm_of[64] = {0};
@@ -1257,6 +1267,8 @@ int launch_stream_bs32(StreamParams& p, bool fp8, int scalar_type, int head_size
     int64_t workspace_bytes, cudaStream_t stream);
 int launch_stream_other(StreamParams& p, bool fp8, int scalar_type, int head_size, int num_sms,
     int64_t workspace_bytes, cudaStream_t stream);
+int launch_stream_e5m2(StreamParams& p, int scalar_type, int head_size, int num_sms,
+    int64_t workspace_bytes, cudaStream_t stream);
 
 #define STREAM_CALL(ST, FP8V, DV, NWV, SG, PP, MB, ...) \
   return launch_stream_t<ST, FP8V, DV, NWV, SG, PP, MB, ##__VA_ARGS__>(p, num_sms, workspace_bytes, stream)
@@ -1320,6 +1332,19 @@ int launch_stream_other(StreamParams& p, bool fp8, int scalar_type, int head_siz
   else { STREAM_BY_HEAD_SIZE(B200PA_F16) }
 #undef STREAM_BY_HEAD_SIZE
 }
+// fp8_e5m2 caches (x-packed, 16-token blocks): the default fp8 launch shapes of head sizes 64 / 128
+int launch_stream_e5m2(StreamParams& p, int scalar_type, int head_size, int num_sms,
+    int64_t workspace_bytes, cudaStream_t stream) {
+  if (scalar_type == B200PA_BF16) {
+    if (head_size == 128) { STREAM_CALL(B200PA_BF16, true, 128, 8, 3, 2, 1, false, 16, true); }
+    if (head_size == 64) { STREAM_CALL(B200PA_BF16, true, 64, 4, 3, 2, 2, false, 16, true); }
+  } else {
+    if (head_size == 128) { STREAM_CALL(B200PA_F16, true, 128, 8, 3, 2, 1, false, 16, true); }
+    if (head_size == 64) { STREAM_CALL(B200PA_F16, true, 64, 4, 3, 2, 2, false, 16, true); }
+  }
+  return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: head size %d with an fp8_e5m2 cache",
+                   head_size);
+}
 #else
 // Upper bound of the workspace any stream launch on a device with `num_sms` SMs needs.
 int64_t stream_workspace_bytes(int num_sms, int head_size) {
@@ -1341,7 +1366,11 @@ bool stream_supported(const void* query, const void* key_cache, const void* valu
       head_size != 192 && head_size != 256 && !(mult16_only && kv_dtype == B200PA_KV_AUTO))
     return false;
   if (scalar_type != B200PA_BF16 && scalar_type != B200PA_F16) return false;
-  if (kv_dtype != B200PA_KV_AUTO && kv_dtype != B200PA_KV_FP8_E4M3) return false;
+  if (kv_dtype == B200PA_KV_FP8_E5M2) {   // e5m2: head sizes 64 / 128 on 16-token blocks
+    if (block_size != 16 || (head_size != 64 && head_size != 128)) return false;
+  } else if (kv_dtype != B200PA_KV_AUTO && kv_dtype != B200PA_KV_FP8_E4M3) {
+    return false;
+  }
   if (num_kv_heads <= 0 || num_heads % num_kv_heads != 0) return false;
   const int ces = kv_dtype == B200PA_KV_AUTO ? 2 : 1;
   auto aligned = [](const void* p, uintptr_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; };
@@ -1429,6 +1458,12 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
   p.nw = 0;
   p.scale = scale;
   const bool fp8 = kv_dtype == B200PA_KV_FP8_E4M3;
+  if (kv_dtype == B200PA_KV_FP8_E5M2) {
+    if (flash_token_stride > 0 || block_size != 16)
+      return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: fp8_e5m2 serves the x-packed "
+                       "layout with 16-token blocks");
+    return launch_stream_e5m2(p, scalar_type, head_size, num_sms, workspace_bytes, stream);
+  }
   if (flash_token_stride > 0)
     return launch_stream_flash(p, fp8, scalar_type, head_size, num_sms, workspace_bytes, stream);
   if (block_size == 32)

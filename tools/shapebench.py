@@ -27,6 +27,7 @@ SHAPES = [
     ("d64_fp8_gqa8", 128, 64, 8, 64, 8192, "fp8"),
     ("neox_d80_bf16", 64, 32, 32, 80, 2048, "auto"),
     ("d112_bf16_gqa4", 64, 32, 8, 112, 4096, "auto"),
+    ("llama8b_e5m2", 256, 32, 8, 128, 8192, "fp8_e5m2"),
     # 32-token cache blocks
     ("llama8b_bs32_bf16", 64, 32, 8, 128, 4096, "auto", 32),
     ("llama8b_bs32_fp8", 256, 32, 8, 128, 8192, "fp8", 32),
@@ -53,6 +54,7 @@ def timeit(fn, iters):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--iters", type=int, default=10)
+    ap.add_argument("--only", default="", help="comma-separated shape names (default: all)")
     args = ap.parse_args()
     from vllm_main_modify_b200 import _custom_ops as ops
     from vllm_main_modify_b200 import _native
@@ -65,7 +67,10 @@ def main():
     except Exception as e:  # noqa: BLE001
         print(json.dumps({"ref_cuda": f"unavailable: {e}"}))
     g = torch.Generator(device=DEV).manual_seed(0)
+    only = set(filter(None, args.only.split(",")))
     for name, B, H, Hkv, D, ctx, kv, *rest in SHAPES:
+        if only and name not in only:
+            continue
         BS = rest[0] if rest else 16
         nblk = ctx // BS
         NB = B * nblk

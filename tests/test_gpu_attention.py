@@ -119,8 +119,7 @@ def test_paged_attention_sweep(ops, native, ora, version, impl, heads, head_size
                                use_alibi, kv):
     H, Hkv = heads
     dtype = torch.bfloat16
-    stream_ok = block_size in (16, 32) and (head_size in (32, 64, 96, 128, 192, 256) or
-                                            (head_size in (80, 112) and kv == "auto"))
+    stream_ok = block_size in (16, 32) and head_size in (32, 64, 80, 96, 112, 128, 192, 256)
     if impl == STREAM and not stream_ok:
         pytest.skip("shape served by the generic kernel")
     if kv == "fp8" and head_size % 16:

@@ -62,6 +62,8 @@ CASES = [
     ("gqa8_e5m2_page_edges", 8, 64, 8, 128, [1, 16, 17, 32, 33, 511, 512, 513], torch.bfloat16, "fp8_e5m2", False),
     ("gqa4_e5m2_d64_f16_alibi", 7, 32, 8, 64, [_RND.randint(1, 3000) for _ in range(7)], torch.float16, "fp8_e5m2", True),
     ("e5m2_ragged_long", 4, 16, 2, 128, [40000, 129, 5000, 16384 + 3], torch.bfloat16, "fp8_e5m2", False),
+    ("d80_fp8_f16", 6, 32, 32, 80, [1, 16, 17, 999, 2048, 31], torch.float16, "fp8", False),
+    ("d112_fp8_gqa4", 5, 16, 4, 112, [1000, 17, 512, 4100, 3333], torch.bfloat16, "fp8", True),
     ("neox_d80_f16", 6, 32, 32, 80, [1, 16, 17, 999, 2048, 31], torch.float16, "auto", False),
     ("d112_bf16_gqa4", 5, 16, 4, 112, [1000, 17, 512, 4100, 3333], torch.bfloat16, "auto", True),
 ]
@@ -159,7 +161,7 @@ BS32_CASES = [c for c in CASES if c[0] in ("gqa8_fp8_page_edges", "gqa4_bf16_pag
                                             "gqa16_two_tiles_fp8", "mha_f16_d64_alibi",
                                             "gemma_d256_fp8", "gemma_d256_bf16", "d192_f16_fp8",
                                             "phi_d96_bf16", "many_short_fp8", "neox_d80_f16",
-                                            "d112_bf16_gqa4")]
+                                            "d112_bf16_gqa4", "d80_fp8_f16", "d112_fp8_gqa4")]
 
 
 @pytest.mark.parametrize("case", BS32_CASES, ids=[c[0] for c in BS32_CASES])

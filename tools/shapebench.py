@@ -27,6 +27,8 @@ SHAPES = [
     ("d64_fp8_gqa8", 128, 64, 8, 64, 8192, "fp8"),
     ("neox_d80_bf16", 64, 32, 32, 80, 2048, "auto"),
     ("d112_bf16_gqa4", 64, 32, 8, 112, 4096, "auto"),
+    ("d80_fp8", 64, 32, 32, 80, 4096, "fp8"),
+    ("d112_fp8_gqa4", 64, 32, 8, 112, 8192, "fp8"),
     ("llama8b_e5m2", 256, 32, 8, 128, 8192, "fp8_e5m2"),
     # 32-token cache blocks
     ("llama8b_bs32_bf16", 64, 32, 8, 128, 4096, "auto", 32),

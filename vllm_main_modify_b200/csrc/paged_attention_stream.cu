@@ -4,7 +4,7 @@
 // (csrc/attention/attention_kernels.cuh:85-491 through paged_attention_v1_kernel :494-522 and
 // paged_attention_v2_kernel :525-557 + paged_attention_v2_reduce_kernel :560-664, launched from
 // paged_attention_v1.cu:46-125 / paged_attention_v2.cu:47-126) for head_size 32/64/96/128/192/256
-// (80 / 112 too with a 16-bit cache),
+// and 80 / 112 (x-packed layout),
 // block_size 16/32, bf16/fp16 query and a 16-bit or fp8-e4m3 KV cache -- x-packed layout, or
 // (FLASH, block_size 16, the same head sizes) the token-major layout of reshape_and_cache_flash --
 // with the new token's cache write optionally fused in (decode_step).
@@ -756,14 +756,20 @@ paged_attention_stream_kernel(const StreamParams p) {
         if constexpr (FP8) {
 #pragma unroll
           for (int c = 0; c < KSTEPS; c += 2) {
+            // (odd KSTEPS, D = 80 / 112: the second half of the last x4 reads the first bytes of
+            // the V tile that follows the K tile in the stage -- valid memory, not used)
             uint32_t w4[4], a[4];
             ldmatrix_x4(w4, kbase + c * (FLASH ? 16 : KCS) + k_lane_off);
             fp8x4_to_f16x2x2<E5>(w4[0], a[0], a[2]);
             fp8x4_to_f16x2x2<E5>(w4[1], a[1], a[3]);
             mma16816<false>(sc[g], a, qb[c][0], qb[c][1]);
-            fp8x4_to_f16x2x2<E5>(w4[2], a[0], a[2]);
-            fp8x4_to_f16x2x2<E5>(w4[3], a[1], a[3]);
-            mma16816<false>(sb, a, qb[c + 1][0], qb[c + 1][1]);
+            if (c + 1 < KSTEPS) {
+              constexpr int KL = KSTEPS - 1;
+              const int c1 = c + 1 < KL ? c + 1 : KL;
+              fp8x4_to_f16x2x2<E5>(w4[2], a[0], a[2]);
+              fp8x4_to_f16x2x2<E5>(w4[3], a[1], a[3]);
+              mma16816<false>(sb, a, qb[c1][0], qb[c1][1]);
+            }
           }
         } else {
 #pragma unroll
@@ -881,17 +887,24 @@ paged_attention_stream_kernel(const StreamParams p) {
         }
       } else if constexpr (FP8) {
 #pragma unroll
-        for (int gg = 0; gg < D / 32; ++gg) {
+        for (int gg = 0; gg < (D + 31) / 32; ++gg) {
           uint32_t w4[4], a[4];
-          ldmatrix_x4(w4, vbase + gg * (32 * VRS) + v_lane_off);
+          // D = 80 / 112: the last group has 16 rows; lanes 16-31 re-read rows 0-15 of it (their
+          // matrices are not used) instead of running past the V tile
+          const bool half = 32 * gg + 16 >= D;
+          ldmatrix_x4(w4, vbase + gg * (32 * VRS) + (half ? (lane & 15) * VRS : v_lane_off));
           fp8x4_to_f16x2x2<E5>(w4[0], a[0], a[2]);
           fp8x4_to_f16x2x2<E5>(w4[1], a[1], a[3]);
           if constexpr (MASKED) { a[0] &= m01; a[1] &= m01; a[2] &= m23; a[3] &= m23; }
           mma16816<false>(o[2 * gg], a, pb[g][0], pb[g][1]);
-          fp8x4_to_f16x2x2<E5>(w4[2], a[0], a[2]);
-          fp8x4_to_f16x2x2<E5>(w4[3], a[1], a[3]);
-          if constexpr (MASKED) { a[0] &= m01; a[1] &= m01; a[2] &= m23; a[3] &= m23; }
-          mma16816<false>(o[2 * gg + 1], a, pb[g][0], pb[g][1]);
+          if (!half) {
+            constexpr int ML = MT - 1;
+            const int m1 = 2 * gg + 1 < ML ? 2 * gg + 1 : ML;
+            fp8x4_to_f16x2x2<E5>(w4[2], a[0], a[2]);
+            fp8x4_to_f16x2x2<E5>(w4[3], a[1], a[3]);
+            if constexpr (MASKED) { a[0] &= m01; a[1] &= m01; a[2] &= m23; a[3] &= m23; }
+            mma16816<false>(o[m1], a, pb[g][0], pb[g][1]);
+          }
         }
       } else {
 #pragma unroll
@@ -1300,9 +1313,9 @@ int launch_stream_bs32(StreamParams& p, bool fp8, int scalar_type, int head_size
   switch (head_size) {                                                                       \
     case 32:  if (fp8) { STREAM_CALL(ST, true, 32, 4, 3, 2, 2, false, 32); }  else { STREAM_CALL(ST, false, 32, 4, 3, 2, 2, false, 32); }  \
     case 64:  if (fp8) { STREAM_CALL(ST, true, 64, 4, 3, 2, 2, false, 32); }  else { STREAM_CALL(ST, false, 64, 4, 3, 2, 2, false, 32); }  \
-    case 80:  if (!fp8) { STREAM_CALL(ST, false, 80, 4, 3, 2, 2, false, 32); } return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: head size %d needs a 16-bit cache", head_size);  \
+    case 80:  if (fp8) { STREAM_CALL(ST, true, 80, 4, 3, 2, 2, false, 32); } else { STREAM_CALL(ST, false, 80, 4, 3, 2, 2, false, 32); }  \
     case 96:  if (fp8) { STREAM_CALL(ST, true, 96, 4, 3, 2, 2, false, 32); }  else { STREAM_CALL(ST, false, 96, 4, 3, 2, 1, false, 32); }  \
-    case 112: if (!fp8) { STREAM_CALL(ST, false, 112, 4, 3, 2, 1, false, 32); } return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: head size %d needs a 16-bit cache", head_size); \
+    case 112: if (fp8) { STREAM_CALL(ST, true, 112, 4, 3, 2, 2, false, 32); } else { STREAM_CALL(ST, false, 112, 4, 3, 2, 1, false, 32); } \
     case 128: if (fp8) { STREAM_CALL(ST, true, 128, 8, 3, 2, 1, false, 32); } else { STREAM_CALL(ST, false, 128, 4, 3, 2, 1, false, 32); } \
     case 192: if (fp8) { STREAM_CALL(ST, true, 192, 4, 4, 2, 1, false, 32); } else { STREAM_CALL(ST, false, 192, 4, 2, 2, 1, false, 32); } \
     case 256: if (fp8) { STREAM_CALL(ST, true, 256, 4, 3, 2, 1, false, 32); } else { STREAM_CALL(ST, false, 256, 3, 2, 2, 1, false, 32); } \
@@ -1320,9 +1333,9 @@ int launch_stream_other(StreamParams& p, bool fp8, int scalar_type, int head_siz
   switch (head_size) {                                                                       \
     case 32:  if (fp8) { STREAM_CALL(ST, true, 32, 4, 3, 2, 2); }  else { STREAM_CALL(ST, false, 32, 4, 3, 2, 2); }  \
     case 64:  if (fp8) { STREAM_CALL(ST, true, 64, 4, 3, 2, 2); }  else { STREAM_CALL(ST, false, 64, 4, 3, 2, 2); }  \
-    case 80:  if (!fp8) { STREAM_CALL(ST, false, 80, 4, 3, 2, 2); } return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: head size %d needs a 16-bit cache", head_size);  \
+    case 80:  if (fp8) { STREAM_CALL(ST, true, 80, 4, 3, 2, 2); } else { STREAM_CALL(ST, false, 80, 4, 3, 2, 2); }  \
     case 96:  if (fp8) { STREAM_CALL(ST, true, 96, 4, 3, 2, 2); }  else { STREAM_CALL(ST, false, 96, 4, 3, 2, 1); }  \
-    case 112: if (!fp8) { STREAM_CALL(ST, false, 112, 4, 3, 2, 1); } return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: head size %d needs a 16-bit cache", head_size); \
+    case 112: if (fp8) { STREAM_CALL(ST, true, 112, 4, 3, 2, 2); } else { STREAM_CALL(ST, false, 112, 4, 3, 2, 1); } \
     case 128: if (fp8) { STREAM_CALL(ST, true, 128, 4, 3, 2, 2); } else { STREAM_CALL(ST, false, 128, 4, 4, 1, 1); } \
     case 192: if (fp8) { STREAM_CALL(ST, true, 192, 4, 4, 2, 1); } else { STREAM_CALL(ST, false, 192, 4, 4, 1, 1); } \
     case 256: if (fp8) { STREAM_CALL(ST, true, 256, 4, 3, 2, 1); } else { STREAM_CALL(ST, false, 256, 4, 3, 1, 1); } \
@@ -1359,11 +1372,9 @@ bool stream_supported(const void* query, const void* key_cache, const void* valu
                       int scalar_type, int kv_dtype, int blocksparse_vert_stride) {
   if (blocksparse_vert_stride > 1) return false;
   if (block_size != 16 && block_size != 32) return false;
-  // multiples of 32 of the reference's head sizes; 80 and 112 (multiples of 16) with a 16-bit
-  // cache only -- the fp8 fragments come 32 head elements at a time; 120 stays on the generic kernel
-  const bool mult16_only = head_size == 80 || head_size == 112;
-  if (head_size != 32 && head_size != 64 && head_size != 96 && head_size != 128 &&
-      head_size != 192 && head_size != 256 && !(mult16_only && kv_dtype == B200PA_KV_AUTO))
+  // the reference's head sizes that are multiples of 16 (120 stays on the generic kernel)
+  if (head_size != 32 && head_size != 64 && head_size != 80 && head_size != 96 &&
+      head_size != 112 && head_size != 128 && head_size != 192 && head_size != 256)
     return false;
   if (scalar_type != B200PA_BF16 && scalar_type != B200PA_F16) return false;
   if (kv_dtype == B200PA_KV_FP8_E5M2) {   // e5m2: head sizes 64 / 128 on 16-token blocks

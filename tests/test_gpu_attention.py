@@ -183,7 +183,7 @@ def test_other_dtypes_and_block_sizes(ops, native, ora, dtype, version, kv, bloc
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
-@pytest.mark.parametrize("head_size", [64, 128])
+@pytest.mark.parametrize("head_size", [32, 64, 80, 96, 112, 128, 192, 256])
 @pytest.mark.parametrize("version", ["v1", "v2"])
 def test_stream_kernel_serves_fp8_e5m2(ops, native, ora, dtype, head_size, version):
     """fp8_e5m2 caches (DISPATCH_BY_KV_CACHE_DTYPE, quant_utils.cuh:545-582) on the stream kernel:

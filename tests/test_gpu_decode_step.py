@@ -64,6 +64,8 @@ CASES = [
     ("e5m2_ragged_long", 4, 16, 2, 128, [40000, 129, 5000, 16384 + 3], torch.bfloat16, "fp8_e5m2", False),
     ("d80_fp8_f16", 6, 32, 32, 80, [1, 16, 17, 999, 2048, 31], torch.float16, "fp8", False),
     ("d112_fp8_gqa4", 5, 16, 4, 112, [1000, 17, 512, 4100, 3333], torch.bfloat16, "fp8", True),
+    ("d80_e5m2_f16", 6, 32, 32, 80, [1, 16, 17, 999, 2048, 31], torch.float16, "fp8_e5m2", False),
+    ("d256_e5m2_bf16", 5, 16, 8, 256, [1000, 17, 512, 4100, 3333], torch.bfloat16, "fp8_e5m2", False),
     ("neox_d80_f16", 6, 32, 32, 80, [1, 16, 17, 999, 2048, 31], torch.float16, "auto", False),
     ("d112_bf16_gqa4", 5, 16, 4, 112, [1000, 17, 512, 4100, 3333], torch.bfloat16, "auto", True),
 ]

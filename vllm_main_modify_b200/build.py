@@ -28,7 +28,7 @@ NVCC = os.path.join(CUDA_HOME, "bin", "nvcc")
 # The image exports CC/CXX=/opt/gcc/bin/*, a wrapper without libgomp; pin the system one.
 HOST_CXX = "/usr/bin/g++"
 
-# (source, extra defines, object name): the stream kernel's instantiations are spread over four
+# (source, extra defines, object name): the stream kernel's instantiations are spread over five
 # translation units (STREAM_PART, see the end of paged_attention_stream.cu) to build in parallel
 CU_SOURCES = [("c_abi.cu", [], "c_abi.o"), ("cache_kernels.cu", [], "cache_kernels.o"),
               ("paged_attention_generic.cu", [], "paged_attention_generic.o"),
@@ -36,6 +36,7 @@ CU_SOURCES = [("c_abi.cu", [], "c_abi.o"), ("cache_kernels.cu", [], "cache_kerne
               ("paged_attention_stream.cu", ["-DSTREAM_PART=1"], "paged_attention_stream_flash.o"),
               ("paged_attention_stream.cu", ["-DSTREAM_PART=2"], "paged_attention_stream_bs32.o"),
               ("paged_attention_stream.cu", ["-DSTREAM_PART=3"], "paged_attention_stream_other.o"),
+              ("paged_attention_stream.cu", ["-DSTREAM_PART=4"], "paged_attention_stream_e5m2.o"),
               ("merge_attn_states.cu", [], "merge_attn_states.o"), ("block_ops.cu", [], "block_ops.o")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
               "-Xcompiler", "-fPIC", "-ccbin", HOST_CXX, "--expt-relaxed-constexpr",

@@ -1268,9 +1268,10 @@ int launch_stream_t(StreamParams& p, int num_sms, int64_t workspace_bytes, cudaS
 }  // namespace
 
 // The instantiations are spread over four translation units (this file compiled with
-// -DSTREAM_PART=0..3, see build.py) so that they build in parallel:
+// -DSTREAM_PART=0..4, see build.py) so that they build in parallel:
 //   0: entry point, support queries, the bf16 head-size-128 shapes (with the tuning variants)
 //   1: token-major ("flash") layout     2: 32-token cache blocks     3: the other head sizes
+//   4: fp8_e5m2 caches
 #ifndef STREAM_PART
 #define STREAM_PART 0
 #endif
@@ -1345,18 +1346,26 @@ int launch_stream_other(StreamParams& p, bool fp8, int scalar_type, int head_siz
   else { STREAM_BY_HEAD_SIZE(B200PA_F16) }
 #undef STREAM_BY_HEAD_SIZE
 }
-// fp8_e5m2 caches (x-packed, 16-token blocks): the default fp8 launch shapes of head sizes 64 / 128
+#elif STREAM_PART == 4
+// fp8_e5m2 caches (x-packed, 16-token blocks): the fp8 launch shapes of launch_stream_other
 int launch_stream_e5m2(StreamParams& p, int scalar_type, int head_size, int num_sms,
     int64_t workspace_bytes, cudaStream_t stream) {
-  if (scalar_type == B200PA_BF16) {
-    if (head_size == 128) { STREAM_CALL(B200PA_BF16, true, 128, 8, 3, 2, 1, false, 16, true); }
-    if (head_size == 64) { STREAM_CALL(B200PA_BF16, true, 64, 4, 3, 2, 2, false, 16, true); }
-  } else {
-    if (head_size == 128) { STREAM_CALL(B200PA_F16, true, 128, 8, 3, 2, 1, false, 16, true); }
-    if (head_size == 64) { STREAM_CALL(B200PA_F16, true, 64, 4, 3, 2, 2, false, 16, true); }
+#define STREAM_E5M2_BY_HEAD_SIZE(ST)                                              \
+  switch (head_size) {                                                           \
+    case 32:  STREAM_CALL(ST, true, 32, 4, 3, 2, 2, false, 16, true);            \
+    case 64:  STREAM_CALL(ST, true, 64, 4, 3, 2, 2, false, 16, true);            \
+    case 80:  STREAM_CALL(ST, true, 80, 4, 3, 2, 2, false, 16, true);            \
+    case 96:  STREAM_CALL(ST, true, 96, 4, 3, 2, 2, false, 16, true);            \
+    case 112: STREAM_CALL(ST, true, 112, 4, 3, 2, 2, false, 16, true);           \
+    case 128: STREAM_CALL(ST, true, 128, 8, 3, 2, 1, false, 16, true);           \
+    case 192: STREAM_CALL(ST, true, 192, 4, 4, 2, 1, false, 16, true);           \
+    case 256: STREAM_CALL(ST, true, 256, 4, 3, 2, 1, false, 16, true);           \
+    default: return set_error(B200PA_ERR_UNSUPPORTED,                            \
+                              "stream kernel: head size %d with an fp8_e5m2 cache", head_size); \
   }
-  return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: head size %d with an fp8_e5m2 cache",
-                   head_size);
+  if (scalar_type == B200PA_BF16) { STREAM_E5M2_BY_HEAD_SIZE(B200PA_BF16) }
+  else { STREAM_E5M2_BY_HEAD_SIZE(B200PA_F16) }
+#undef STREAM_E5M2_BY_HEAD_SIZE
 }
 #else
 // Upper bound of the workspace any stream launch on a device with `num_sms` SMs needs.
@@ -1377,8 +1386,8 @@ bool stream_supported(const void* query, const void* key_cache, const void* valu
       head_size != 112 && head_size != 128 && head_size != 192 && head_size != 256)
     return false;
   if (scalar_type != B200PA_BF16 && scalar_type != B200PA_F16) return false;
-  if (kv_dtype == B200PA_KV_FP8_E5M2) {   // e5m2: head sizes 64 / 128 on 16-token blocks
-    if (block_size != 16 || (head_size != 64 && head_size != 128)) return false;
+  if (kv_dtype == B200PA_KV_FP8_E5M2) {   // e5m2: 16-token blocks
+    if (block_size != 16) return false;
   } else if (kv_dtype != B200PA_KV_AUTO && kv_dtype != B200PA_KV_FP8_E4M3) {
     return false;
   }

@@ -15,6 +15,17 @@ attention path.  Rank 0 prints ONE JSON line on stdout.
 `--impl reference` times the reference's own CPU kernels (oracle/_ref, built from
 csrc/cpu/attention.cpp + cache.cpp, unmodified) on the host cores, on a bounded
 sample of the same workload.
+
+Besides the timed legs the line carries
+  parity     -- BEFORE any timing, one step of exactly the tensors that are timed is compared
+                with the reference's own CUDA kernels (oracle/_ref/libvllm_ref_cuda.so =
+                csrc/attention/paged_attention_v2.cu + csrc/cache_kernels.cu compiled unmodified
+                for sm_100a; used ONLY as the checker, never timed here): the whole output of
+                every rank within 1e-2 + 1e-2|ref|, the cache bytes torch.equal; at N > 1 the
+                all-gathered [B,H,D] is also compared with an UNSHARDED reference run on rank 0
+  sustained  -- the same step back to back for >= 3 s with a 100 ms series and the sensors
+                (SM / memory clock, power, GPU / HBM temperature) sampled meanwhile
+  configs    -- the other four BASELINE.json configs, 10 steps each, with their own parity check
 """
 from __future__ import annotations
 
@@ -69,12 +80,14 @@ def kv_bytes(lens, hkv, kv):
 
 
 # ----------------------------------------------------------------------------
-# clocks sampler (nvidia-smi during the timed region)
+# sensors sampler (nvidia-smi during a timed region)
 # ----------------------------------------------------------------------------
 class ClockSampler:
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    FIELDS = ("clocks.sm", "clocks.max.sm", "clocks.mem", "clocks.max.mem", "power.draw",
+              "temperature.gpu", "temperature.memory",
+              "clocks_event_reasons.hw_slowdown", "clocks_event_reasons.hw_thermal_slowdown",
+              "clocks_event_reasons.sw_thermal_slowdown", "clocks_event_reasons.sw_power_cap")
+    REASONS = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
 
     def __init__(self, index: int):
         self.index, self.proc, self.lines = index, None, []
@@ -82,7 +95,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + ",".join(self.FIELDS),
                  "--format=csv,noheader,nounits", "-lms", "100"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
@@ -94,7 +107,14 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.lines.append(line.strip())
 
-    def stop(self):
+    @staticmethod
+    def _num(s):
+        try:
+            return float(s)
+        except ValueError:      # "[N/A]" on parts without that sensor
+            return None
+
+    def stop(self, series: bool = False):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -102,29 +122,66 @@ class ClockSampler:
             self.proc.wait(timeout=2)
         except subprocess.TimeoutExpired:
             self.proc.kill()
-        sm, smax, reasons = [], None, set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        cols = {k: [] for k in ("sm", "mem", "power", "tgpu", "tmem")}
+        smax = mmax = None
+        reasons = set()
         for ln in self.lines:
             p = [x.strip() for x in ln.split(",")]
-            if len(p) < 6:
+            if len(p) < len(self.FIELDS):
                 continue
-            try:
-                sm.append(float(p[0]))
-                smax = float(p[1])
-            except ValueError:
+            sm = self._num(p[0])
+            if sm is None:
                 continue
-            for n, v in zip(names, p[2:6]):
+            cols["sm"].append(sm)
+            smax = self._num(p[1]) or smax
+            mmax = self._num(p[3]) or mmax
+            for key, idx in (("mem", 2), ("power", 4), ("tgpu", 5), ("tmem", 6)):
+                v = self._num(p[idx])
+                if v is not None:
+                    cols[key].append(v)
+            for n, v in zip(self.REASONS, p[7:11]):
                 if v.lower().startswith("active"):
                     reasons.add(n)
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": smax,
-                "reasons": sorted(reasons), "samples": len(sm)}
+
+        def med(v):
+            return sorted(v)[len(v) // 2] if v else None
+
+        out = {"sm_mhz": med(cols["sm"]), "sm_max_mhz": smax, "reasons": sorted(reasons),
+               "samples": len(cols["sm"]), "mem_mhz": med(cols["mem"]), "mem_max_mhz": mmax,
+               "power_w": med(cols["power"]), "temp_gpu_c": med(cols["tgpu"]),
+               "temp_hbm_c": med(cols["tmem"])}
+        if series:
+            # first / last thirds: the sensor that moves over a multi-second run shows here
+            def thirds(v):
+                if len(v) < 3:
+                    return None
+                n = max(1, len(v) // 3)
+                return {"first": round(sum(v[:n]) / n, 1), "last": round(sum(v[-n:]) / n, 1),
+                        "min": min(v), "max": max(v)}
+            out["drift"] = {"sm_mhz": thirds(cols["sm"]), "mem_mhz": thirds(cols["mem"]),
+                            "power_w": thirds(cols["power"]), "temp_gpu_c": thirds(cols["tgpu"]),
+                            "temp_hbm_c": thirds(cols["tmem"])}
+        return out
 
 
 # ----------------------------------------------------------------------------
 # workload
 # ----------------------------------------------------------------------------
-def make_shard(cfg, rank, world, device):
+L2_BYTES = 126 << 20
+
+
+def cache_copies(cfg, world):
+    """Per-GPU KV of a step far above the 126 MB L2: one cache.  Otherwise (cfg1; small shards)
+    the step rotates over enough distinct copies of the cache that a copy is long evicted when
+    its turn comes again (>= 1 GiB in rotation)."""
+    _, B, H, Hkv, ctx, kv, _ = CONFIGS[cfg]
+    per_gpu = kv_bytes(seq_lens_of(cfg), Hkv // world, kv)
+    if per_gpu >= 4 * L2_BYTES:
+        return 1
+    return int(min(32, max(2, -(-(1 << 30) // per_gpu))))
+
+
+def make_shard(cfg, rank, world, device, copies=1):
     """Seeded synthetic tensors of this rank's KV-head shard, resident in HBM."""
     _, B, H, Hkv, ctx, kv, _ = CONFIGS[cfg]
     assert Hkv % world == 0, "tp must divide the KV heads"
@@ -163,9 +220,12 @@ def make_shard(cfg, rank, world, device):
     slots = (bt[torch.arange(B), (last // BS)].long() * BS + (last % BS)).to(torch.int64)
     ks = torch.tensor(s / 1.7 if kv != "auto" else 1.0, dtype=torch.float32, device=device)
     vs = torch.tensor(s / 2.9 if kv != "auto" else 1.0, dtype=torch.float32, device=device)
+    caches = [kv_cache] + [kv_cache.clone() for _ in range(copies - 1)]
+    from vllm_main_modify_b200.paged_attn import PagedAttention
+    views = [PagedAttention.split_kv_cache(c, hkv_loc, D) for c in caches]
     return dict(B=B, H=h_loc, Hkv=hkv_loc, kv=kv, lens=lens, max_len=max(lens), scale=s,
-                q=q, k_new=k_new, v_new=v_new, kv_cache=kv_cache, bt=bt.to(device),
-                sl=sl.to(device), slots=slots.to(device), ks=ks, vs=vs,
+                q=q, k_new=k_new, v_new=v_new, kv_cache=kv_cache, kv_caches=caches, views=views,
+                bt=bt.to(device), sl=sl.to(device), slots=slots.to(device), ks=ks, vs=vs,
                 bt_host=bt, sl_host=sl, slots_host=slots)
 
 
@@ -176,11 +236,263 @@ class Layer:
         self._k_scale, self._v_scale = ks, vs
 
 
+def decode_op(w, out, fused, ci=0):
+    """The device-resident step on copy `ci` of the cache, through the package's public helper
+    (= the reference's PagedAttention.write_to_paged_cache + forward_decode, paged_attn.py:73-198)."""
+    from vllm_main_modify_b200.paged_attn import PagedAttention
+    kc, vc = w["views"][ci]
+    o = out.view(w["B"], w["H"], D)
+    if fused:
+        PagedAttention.write_and_decode(w["q"], w["k_new"], w["v_new"], kc, vc, w["slots"],
+                                        w["bt"], w["sl"], w["max_len"], w["kv"], w["Hkv"],
+                                        w["scale"], None, w["ks"], w["vs"], output=o)
+        return None
+    PagedAttention.write_to_paged_cache(w["k_new"], w["v_new"], kc, vc, w["slots"], w["kv"],
+                                        w["ks"], w["vs"])
+    return lambda: PagedAttention.forward_decode(w["q"], kc, vc, w["bt"], w["sl"], w["max_len"],
+                                                 w["kv"], w["Hkv"], w["scale"], None, w["ks"],
+                                                 w["vs"], output=o)
+
+
+# ----------------------------------------------------------------------------
+# parity of exactly what is timed, against the reference's own CUDA kernels (CHECKER ONLY)
+# ----------------------------------------------------------------------------
+PARITY_ATOL, PARITY_RTOL = 1e-2, 1e-2
+PARITY_AGAINST = ("reference CUDA paged_attention_v2 + reshape_and_cache (csrc/attention/"
+                  "paged_attention_v2.cu, csrc/cache_kernels.cu compiled unmodified for sm_100a: "
+                  "oracle/_ref/libvllm_ref_cuda.so)")
+
+
+def _ref_cuda_step(ref, q, k_new, v_new, kv_cache, hkv, slots, bt, sl, max_len, kv, scale, ks, vs):
+    """reshape_and_cache + paged_attention_v2 of the reference on (a copy of) the cache."""
+    from vllm_main_modify_b200.paged_attn import PagedAttention
+    kc, vc = PagedAttention.split_kv_cache(kv_cache, hkv, D)
+    ref.reshape_and_cache(k_new, v_new, kc, vc, slots, kv, ks, vs)
+    B, H, _ = q.shape
+    P = (max_len + 511) // 512
+    es = torch.empty(B, H, P, dtype=torch.float32, device=q.device)
+    ml = torch.empty_like(es)
+    tmp = torch.empty(B, H, P, D, dtype=q.dtype, device=q.device)
+    want = torch.full_like(q, float("nan"))
+    ref.paged_attention_v2(want, es, ml, tmp, q, kc, vc, hkv, scale, bt, sl, BS, max_len, None, kv,
+                           ks, vs, 0, 0, 0, 64, 0)
+    torch.cuda.synchronize()
+    return want
+
+
+def _diff(got, want):
+    g, r = got.float(), want.float()
+    d = (g - r).abs()
+    viol = d - (PARITY_ATOL + PARITY_RTOL * r.abs())
+    big = r.abs() > PARITY_ATOL
+    max_rel = float((d[big] / r.abs()[big]).max()) if bool(big.any()) else 0.0
+    ok = bool(torch.isfinite(g).all()) and float(viol.max()) <= 0.0
+    return ok, float(d.max()), max_rel
+
+
+def parity_check(cfg, w, out, fused, rank, world, dev):
+    """Runs ONE step of the op that is about to be timed, on the tensors that are about to be
+    timed, and compares output and cache bytes with the reference's CUDA kernels run on a clone
+    of the same cache.  Must be called before any other step touched the cache."""
+    import torch.distributed as dist
+    try:
+        from oracle import ref_cuda as ref     # the checker; the product never loads it
+        if not os.path.exists(ref.LIB_PATH):
+            raise RuntimeError("oracle/_ref/libvllm_ref_cuda.so is not built")
+        ref.load()
+    except Exception as exc:
+        return {"checked": False, "why": str(exc)}
+    res = {"checked": True, "against": PARITY_AGAINST,
+           "gate": f"|out - ref| <= {PARITY_ATOL} + {PARITY_RTOL}|ref| over the whole "
+                   "[B, H/n, D] output of every rank; written cache torch.equal (whole tensor)"}
+    ok_all, max_abs, max_rel, cache_ok = True, 0.0, 0.0, True
+    for ci, kvc in enumerate(w["kv_caches"][:2]):   # the rotation's copies are clones: two suffice
+        ref_cache = kvc.clone()
+        want = _ref_cuda_step(ref, w["q"], w["k_new"], w["v_new"], ref_cache, w["Hkv"], w["slots"],
+                              w["bt"], w["sl"], w["max_len"], w["kv"], w["scale"], w["ks"], w["vs"])
+        out.fill_(float("nan"))
+        attend = decode_op(w, out, fused, ci)
+        if attend is not None:
+            attend()
+        torch.cuda.synchronize()
+        ok, a, r = _diff(out.view_as(want), want)
+        ok_all &= ok
+        max_abs, max_rel = max(max_abs, a), max(max_rel, r)
+        cache_ok &= bool(torch.equal(kvc, ref_cache))
+        del ref_cache
+    flags = torch.tensor([float(ok_all), float(cache_ok), -max_abs, -max_rel], dtype=torch.float64,
+                         device=dev)
+    if world > 1:
+        dist.all_reduce(flags, op=dist.ReduceOp.MIN)
+    ok_all, cache_ok = bool(flags[0] > 0), bool(flags[1] > 0)
+    res.update(ok=ok_all and cache_ok, max_abs=round(-float(flags[2]), 6),
+               max_rel=round(-float(flags[3]), 6), cache_bytes_equal=cache_ok, ranks=world)
+    if world > 1:
+        # the all-gathered [B, H, D] against ONE unsharded reference run on rank 0: rank 0
+        # regenerates every rank's shard (same seeds, same device model) into the full tensors
+        _, B, H, Hkv, _, kv, _ = CONFIGS[cfg]
+        gathered = torch.empty(world, B, w["H"], D, dtype=out.dtype, device=dev)
+        dist.all_gather_into_tensor(gathered, out.view(B, w["H"], D).contiguous())
+        gres = torch.zeros(3, dtype=torch.float64, device=dev)
+        if rank == 0:
+            hkv_loc = Hkv // world
+            full_q = torch.empty(B, H, D, dtype=out.dtype, device=dev)
+            full_k = torch.empty(B, Hkv, D, dtype=out.dtype, device=dev)
+            full_v = torch.empty_like(full_k)
+            NB = w["kv_cache"].shape[1]
+            full_cache = torch.empty(2, NB, Hkv, BS * D, dtype=w["kv_cache"].dtype, device=dev)
+            for r_ in range(world):
+                sh = w if r_ == 0 else make_shard(cfg, r_, world, dev)
+                full_q[:, r_ * w["H"]:(r_ + 1) * w["H"]] = sh["q"]
+                full_k[:, r_ * hkv_loc:(r_ + 1) * hkv_loc] = sh["k_new"]
+                full_v[:, r_ * hkv_loc:(r_ + 1) * hkv_loc] = sh["v_new"]
+                # rank 0's own cache already holds the new token; the reference rewrites it
+                full_cache[:, :, r_ * hkv_loc:(r_ + 1) * hkv_loc] = \
+                    sh["kv_cache"].view(2, NB, hkv_loc, BS * D)
+                del sh
+            want = _ref_cuda_step(ref, full_q, full_k, full_v, full_cache.view(2, NB, -1), Hkv,
+                                  w["slots"], w["bt"], w["sl"], w["max_len"], kv, w["scale"],
+                                  w["ks"], w["vs"])
+            got = gathered.permute(1, 0, 2, 3).reshape(B, H, D)
+            ok, a, r = _diff(got, want)
+            gres = torch.tensor([float(ok), a, r], dtype=torch.float64, device=dev)
+            del full_cache, want
+        dist.broadcast(gres, src=0)
+        res["gathered_vs_unsharded"] = {"ok": bool(gres[0] > 0), "max_abs": round(float(gres[1]), 6),
+                                        "max_rel": round(float(gres[2]), 6),
+                                        "what": f"all-gather of the {world} ranks' [B,H/{world},D] vs "
+                                                "one unsharded reference run (all KV heads) on rank 0"}
+        res["ok"] = res["ok"] and res["gathered_vs_unsharded"]["ok"]
+    torch.cuda.empty_cache()
+    return res
+
+
+def timed_steps(w, out, fused, K, barrier, native, graph=False):
+    """K back-to-back steps, CUDA events around the whole loop and around every attention op.
+    graph=True (steps of tens of microseconds, where the Python caller -- not the GPU -- would
+    set the pace): the K steps are captured into ONE CUDA graph and its replay is timed."""
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n = len(w["kv_caches"])
+    if graph:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        launches0 = native.launch_count()
+        with torch.cuda.stream(side):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=side):
+                for i in range(K):
+                    attend = decode_op(w, out, fused, i % n)
+                    if attend is not None:
+                        attend()
+        launches = native.launch_count() - launches0
+        torch.cuda.current_stream().wait_stream(side)
+        g.replay()                       # warm-up replay
+        barrier()
+        ev0.record()
+        g.replay()
+        ev1.record()
+        barrier()
+        ms = ev0.elapsed_time(ev1)
+        return ms, ms / K, launches
+    a_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            for _ in range(K)]
+    launches0 = native.launch_count()
+    barrier()
+    ev0.record()
+    for i in range(K):
+        if fused:
+            # one launch: the decode kernel also quantises + stores the new token (decode_step)
+            a_ev[i][0].record()
+            decode_op(w, out, True, i % n)
+            a_ev[i][1].record()
+            continue
+        attend = decode_op(w, out, False, i % n)
+        a_ev[i][0].record()
+        attend()
+        a_ev[i][1].record()
+    ev1.record()
+    barrier()
+    launches = native.launch_count() - launches0
+    return ev0.elapsed_time(ev1), sum(a.elapsed_time(b) for a, b in a_ev) / K, launches
+
+
+def sustained_leg(w, out, fused, seconds, ms_step_hint, my_bytes, sampler_index, barrier):
+    """The same step back to back for >= `seconds`, an event every ~100 ms of work."""
+    chunk = max(1, int(round(100.0 / max(ms_step_hint, 1e-3))))
+    n_chunks = max(3, int(seconds * 1e3 / (chunk * ms_step_hint)) + 1)
+    caches = w["kv_caches"]
+    sampler = ClockSampler(sampler_index)
+    sampler.start()
+    time.sleep(0.25)
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(n_chunks + 1)]
+    barrier()
+    evs[0].record()
+    i = 0
+    for c in range(n_chunks):
+        for _ in range(chunk):
+            attend = decode_op(w, out, fused, i % len(caches))
+            if attend is not None:
+                attend()
+            i += 1
+        evs[c + 1].record()
+        if c >= 2:
+            evs[c - 1].synchronize()      # keep the launch queue bounded, never drained
+    barrier()
+    sens = sampler.stop(series=True)
+    per = [evs[c].elapsed_time(evs[c + 1]) / chunk for c in range(n_chunks)]
+    total_ms = evs[0].elapsed_time(evs[-1])
+    return per, total_ms, n_chunks * chunk, chunk, sens
+
+
+def run_side_config(cfg, rank, world, dev, fused, check, barrier, native, peak, steps=10):
+    """One of the other BASELINE configs: parity check, 3 warm-ups, `steps` timed steps."""
+    import torch.distributed as dist
+    _, B, H, Hkv, ctx, kv, _ = CONFIGS[cfg]
+    copies = cache_copies(cfg, world)
+    w = make_shard(cfg, rank, world, dev, copies)
+    out = torch.empty(B, w["H"] * D, dtype=torch.bfloat16, device=dev)
+    par = parity_check(cfg, w, out, fused, rank, world, dev) if check else {"checked": False,
+                                                                            "why": "--no-check"}
+    for i in range(3):
+        attend = decode_op(w, out, fused, i % copies)
+        if attend is not None:
+            attend()
+    # steps shorter than ~0.1 ms: replayed from one CUDA graph (the Python caller would pace them)
+    per_gpu = kv_bytes(w["lens"], w["Hkv"], kv)
+    graph = per_gpu < 512 << 20
+    ms_total, attn_ms, launches = timed_steps(w, out, fused, steps, barrier, native, graph)
+    my_bytes = kv_bytes(w["lens"], w["Hkv"], kv)
+    st = torch.tensor([ms_total, attn_ms], dtype=torch.float64, device=dev)
+    tot = torch.tensor([float(my_bytes)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(st, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    ms_step = float(st[0]) / steps
+    gbs = float(tot[0]) / (ms_step * 1e-3) / 1e9
+    op_gbs = float(tot[0]) / world / (float(st[1]) * 1e-3) / 1e9
+    del w, out
+    torch.cuda.empty_cache()
+    return {"gbs": round(gbs, 1), "ms_per_step": round(ms_step, 4), "steps": steps,
+            "kv_bytes_total": int(tot[0]), "gbs_per_gpu": round(gbs / world, 1),
+            "frac_of_measured_hbm": round(gbs / world / peak, 4),
+            "pct_of_8TBps": round(100.0 * gbs / world / HBM_NOMINAL_GBPS, 2),
+            "attn_op_gbs_per_gpu": round(op_gbs, 1), "launches_per_step": launches / steps,
+            "timing": ("one CUDA graph of the %d steps, events around its replay" % steps) if graph
+                      else "eager launches, events around the loop",
+            "l2": ("one cache, %d MiB per GPU per step" % (int(tot[0]) / world / 2 ** 20)
+                   if copies == 1 else
+                   "%d MiB per GPU per step: rotates over %d copies of the cache (L2 is 126 MB)"
+                   % (int(tot[0]) / world / 2 ** 20, copies)),
+            "tokens_per_s": round(B / (ms_step * 1e-3), 1),
+            "parity": {k: par[k] for k in ("checked", "ok", "max_abs", "max_rel",
+                                           "cache_bytes_equal", "why", "gathered_vs_unsharded")
+                       if k in par}}
+
+
 def run_ours(args):
     import torch.distributed as dist
     from vllm_main_modify_b200 import _native
     from vllm_main_modify_b200.backend import B200PagedAttentionBackend, B200PagedAttentionMetadata
-    from vllm_main_modify_b200.paged_attn import PagedAttention
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -193,9 +505,19 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}"
 
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except OSError:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+
     cfg = args.config
     desc, B, H, Hkv, ctx, kv, _ = CONFIGS[cfg]
-    w = make_shard(cfg, rank, world, dev)
+    copies = cache_copies(cfg, world)
+    w = make_shard(cfg, rank, world, dev, copies)
     impl = B200PagedAttentionBackend.get_impl_cls()(w["H"], D, w["scale"], w["Hkv"], None, None, kv)
     layer = Layer(w["ks"], w["vs"])
     meta = B200PagedAttentionMetadata(num_actual_tokens=B, max_query_len=1, seq_lens=w["sl"],
@@ -204,15 +526,20 @@ def run_ours(args):
     q2 = w["q"].view(B, -1)
     k2, v2 = w["k_new"].view(B, -1), w["v_new"].view(B, -1)
     out = torch.empty_like(q2)
-    key_cache, value_cache = PagedAttention.split_kv_cache(w["kv_cache"], w["Hkv"], D)
-
-    def step():
-        impl.forward(layer, q2, k2, v2, w["kv_cache"], meta, output=out)
+    fused = not args.unfused
+    impl.fused_decode_step = fused
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    # ---- parity of what is about to be timed (outside every timed region) ----
+    parity = (parity_check(cfg, w, out, fused, rank, world, dev) if args.check
+              else {"checked": False, "why": "--no-check"})
+
+    def step():
+        impl.forward(layer, q2, k2, v2, w["kv_cache"], meta, output=out)
 
     for _ in range(max(args.warmup, 3)):
         step()
@@ -223,38 +550,20 @@ def run_ours(args):
     sampler.start()
     time.sleep(0.3)
     K = args.steps
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
-            for _ in range(K)]
-    launches0 = _native.launch_count()
-    barrier()
-    ev0.record()
-    fused = not args.unfused
-    impl.fused_decode_step = fused
-    for i in range(K):
-        # the step, with events around the attention op (the dominant kernel)
-        if fused:
-            # one launch: the decode kernel also quantises + stores the new token (decode_step)
-            a_ev[i][0].record()
-            PagedAttention.write_and_decode(w["q"], w["k_new"], w["v_new"], key_cache, value_cache,
-                                            w["slots"], w["bt"], w["sl"], w["max_len"], kv,
-                                            w["Hkv"], w["scale"], None, w["ks"], w["vs"],
-                                            output=out.view(B, w["H"], D))
-            a_ev[i][1].record()
-            continue
-        PagedAttention.write_to_paged_cache(w["k_new"], w["v_new"], key_cache, value_cache,
-                                            w["slots"], kv, w["ks"], w["vs"])
-        a_ev[i][0].record()
-        PagedAttention.forward_decode(w["q"], key_cache, value_cache, w["bt"], w["sl"],
-                                      w["max_len"], kv, w["Hkv"], w["scale"], None, w["ks"],
-                                      w["vs"], output=out.view(B, w["H"], D))
-        a_ev[i][1].record()
-    ev1.record()
-    barrier()
-    launches = _native.launch_count() - launches0
-    ms_total = ev0.elapsed_time(ev1)
-    attn_ms = sum(a.elapsed_time(b) for a, b in a_ev) / K
+    ms_total, attn_ms, launches = timed_steps(w, out, fused, K, barrier, _native)
     clocks = sampler.stop()
+
+    # ---- sustained leg: the same step for >= args.sustain seconds -----------
+    my_bytes = kv_bytes(w["lens"], w["Hkv"], kv)
+    sustained = None
+    if args.sustain > 0:
+        per, sus_ms, sus_steps, chunk, sens = sustained_leg(w, out, fused, args.sustain,
+                                                            ms_total / K, my_bytes, local_rank,
+                                                            barrier)
+        sus = torch.tensor([sus_ms] + per, dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(sus, op=dist.ReduceOp.MAX)
+        sustained = (sus.tolist(), sus_steps, chunk, sens)
 
     # ---- timed region 2: end to end through AttentionImpl.forward with HOST buffers
     # One pinned staging buffer on the host and its twin on the device hold every per-step input
@@ -284,33 +593,20 @@ def run_ours(args):
                                        slot_mapping=dslots)
     h2d = total   # bytes actually copied (segments padded to 256 B)
     d2h = hout.numel() * hout.element_size()
+    e2e_caches = w["kv_caches"]
+    e2e_i = [0]
 
     def e2e_step():
         dbuf.copy_(hbuf, non_blocking=True)
-        impl.forward(layer, dq, dk, dv, w["kv_cache"], meta2, output=out)
+        impl.forward(layer, dq, dk, dv, e2e_caches[e2e_i[0] % len(e2e_caches)], meta2, output=out)
+        e2e_i[0] += 1
         hout.copy_(out, non_blocking=True)
         torch.cuda.current_stream().synchronize()     # the caller reads the result
 
     for _ in range(3):
         e2e_step()
     if os.environ.get("B200PA_E2E_BREAKDOWN") == "1" and rank == 0:
-        # development aid: host time of each part of the eager step (median of 30), to stderr
-        parts_us = {"h2d_enqueue": [], "forward": [], "d2h_enqueue": [], "sync": []}
-        for _ in range(30):
-            t0 = time.perf_counter()
-            dbuf.copy_(hbuf, non_blocking=True)
-            t1 = time.perf_counter()
-            impl.forward(layer, dq, dk, dv, w["kv_cache"], meta2, output=out)
-            t2 = time.perf_counter()
-            hout.copy_(out, non_blocking=True)
-            t3 = time.perf_counter()
-            torch.cuda.current_stream().synchronize()
-            t4 = time.perf_counter()
-            for name, dt in zip(parts_us, (t1 - t0, t2 - t1, t3 - t2, t4 - t3)):
-                parts_us[name].append(dt * 1e6)
-        sys.stderr.write("[bench] e2e host time per part, us (median): " + json.dumps(
-            {k: round(sorted(v)[len(v) // 2], 1) for k, v in parts_us.items()}) + "\n")
-        # ... and the device-side segments of the same step (CUDA events between the parts)
+        # development aid: device-side segments of the eager step (CUDA events between the parts)
         seg_us = {"h2d": [], "forward": [], "d2h": []}
         for _ in range(30):
             ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
@@ -373,6 +669,7 @@ def run_ours(args):
         hq.copy_(-saved)
         e2e_graph_step()
         got = hout.clone()
+        e2e_i[0] = 0
         e2e_step()
         if not torch.equal(got.view(torch.uint8), hout.view(torch.uint8)):
             raise RuntimeError("graph replay and eager step disagree on a changed input")
@@ -386,7 +683,6 @@ def run_ours(args):
         ms_e2e_graph = float("nan")
 
     # ---- reduce over ranks ---------------------------------------------------
-    my_bytes = kv_bytes(w["lens"], w["Hkv"], kv)
     stats = torch.tensor([ms_total, ms_e2e, attn_ms, ms_e2e_graph], dtype=torch.float64, device=dev)
     tot = torch.tensor([float(my_bytes), float(launches)], dtype=torch.float64, device=dev)
     if world > 1:
@@ -401,22 +697,32 @@ def run_ours(args):
         g1.record()
         torch.cuda.synchronize()
         allgather_ms = g0.elapsed_time(g1)
+        del gathered
     else:
         allgather_ms = None
     ms_total, ms_e2e, attn_ms, ms_e2e_graph = [float(x) for x in stats.tolist()]
     total_bytes, total_launches = tot.tolist()
+
+    # ---- the other BASELINE configs (driver-visible, 10 steps each) ---------
+    del w, impl, meta, meta2, q2, k2, v2, dbuf, dq, dk, dv, dbt, dsl, dslots, e2e_caches
+    torch.cuda.empty_cache()
+    side_configs = {}
+    if args.side_configs:
+        for c in sorted(CONFIGS):
+            if c == cfg or CONFIGS[c][3] % world:
+                continue
+            try:
+                side_configs[c] = run_side_config(c, rank, world, dev, fused, args.check, barrier,
+                                                  _native, peak)
+            except Exception as exc:       # a side config must not take the main line down
+                side_configs[c] = {"error": f"{type(exc).__name__}: {exc}"}
+                barrier()
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_reference_sample(cfg, budget_s=args.cpu_budget)
 
     if rank == 0:
-        peaks = {}
-        try:
-            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-                peaks = json.load(f)
-        except OSError:
-            pass
         # DRAM traffic of the dominant kernel per launch, from the committed ncu --set full
         # capture of this exact workload (profiles/): only quoted for the config it was taken on
         traffic = None
@@ -427,13 +733,12 @@ def run_ours(args):
                 traffic = int(tr["dram_bytes_read"]) + int(tr["dram_bytes_write"])
         except (OSError, ValueError, KeyError):
             pass
-        peak = float(peaks.get("hbm_gbs", 6650.0))
-        peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
         ms_step = ms_total / K
         value = total_bytes / (ms_step * 1e-3) / 1e9
         e2e_val = total_bytes / (ms_e2e / K * 1e-3) / 1e9
         # roofline of the dominant kernel, per GPU: this rank's KV bytes / attention time
         achieved = (total_bytes / world) / (attn_ms * 1e-3) / 1e9
+        per_gpu_mib = int(total_bytes / world) >> 20
         line = {
             "metric": "paged_decode_attn_kv_bandwidth", "value": round(value, 1), "unit": "GB/s",
             "n_gpus": world, "steps": K, "warmup": max(args.warmup, 3),
@@ -446,11 +751,14 @@ def run_ours(args):
                                 "context attended in one launch (= reshape_and_cache + "
                                 "paged_attention)") if fused else
                                "reshape_and_cache (new token K/V) + paged_attention_v2",
-                       "l2": "inputs larger than L2: KV read per GPU per step = "
-                             f"{int(total_bytes / world) >> 20} MiB vs 126 MB L2; no flush"},
+                       "l2": (f"inputs larger than L2: KV read per GPU per step = {per_gpu_mib} MiB "
+                              "vs 126 MB L2; no flush") if copies == 1 else
+                             (f"KV read per GPU per step = {per_gpu_mib} MiB: the step rotates over "
+                              f"{copies} distinct copies of the cache (126 MB L2)")},
             "tokens_per_s": round(B / (ms_step * 1e-3), 1),
             "pct_of_8TBps": round(100.0 * value / world / HBM_NOMINAL_GBPS, 2),
             "pct_of_measured_hbm": round(100.0 * value / world / peak, 2),
+            "parity": parity,
             "e2e": {"value": round(e2e_val, 1), "unit": "GB/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "ms_per_step": round(ms_e2e / K, 4),
                     "tokens_per_s": round(B / (ms_e2e / K * 1e-3), 1),
@@ -466,20 +774,46 @@ def run_ours(args):
             "gpu_launches": int(total_launches),
             "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak,
                          "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic,
-                         "kernel": "paged_attention_stream_kernel (+ its merge launch; CUDA "
-                                   "events around the attention op, in-loop"
+                         "traffic_source": "profiles/ncu_traffic.json (ncu --set full capture of "
+                                           "this workload, committed; not measured in this run)",
+                         "kernel": "paged_attention_stream_kernel (CUDA events around the "
+                                   "attention op, in-loop"
                                    + ("; includes the fused cache write)" if fused else ")"),
                          "kernel_ms": round(attn_ms, 4), "peak_source": peak_src,
                          "bytes": "sum(seq_len) * Hkv_local * D * 2 (K,V) * sizeof(cache_t)"},
             "clocks": clocks,
         }
+        if sustained is not None:
+            vals, sus_steps, chunk, sens = sustained
+            sus_ms, per = vals[0], sorted(vals[1:])
+            series = [round(total_bytes / (m * 1e-3) / 1e9, 1) for m in vals[1:]]
+            line["sustained"] = {
+                "seconds": round(sus_ms / 1e3, 3), "steps": sus_steps,
+                "gbs": round(total_bytes * sus_steps / (sus_ms * 1e-3) / 1e9, 1),
+                "pct_of_8TBps": round(100.0 * total_bytes * sus_steps / (sus_ms * 1e-3) / 1e9
+                                      / world / HBM_NOMINAL_GBPS, 2),
+                "ms_per_step_p50": round(per[len(per) // 2], 4),
+                "ms_per_step_p95": round(per[min(len(per) - 1, int(0.95 * len(per)))], 4),
+                "series_100ms": series, "steps_per_point": chunk,
+                "first_vs_last_third": [round(sum(series[:max(1, len(series) // 3)])
+                                              / max(1, len(series) // 3), 1),
+                                        round(sum(series[-max(1, len(series) // 3):])
+                                              / max(1, len(series) // 3), 1)],
+                "sensors": sens,
+                "what": "the timed step back to back (whole job, max over ranks per point)"}
+        if side_configs:
+            line["configs"] = side_configs
         if allgather_ms is not None:
             line["bench_allgather_ms"] = round(allgather_ms, 4)
         if cpu is not None:
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)
+    bad = parity.get("checked") and not parity.get("ok")
     if world > 1:
         dist.destroy_process_group()
+    if bad:
+        raise SystemExit("bench.py: PARITY FAILED against the reference's CUDA kernels: "
+                         + json.dumps(parity))
 
 
 # ----------------------------------------------------------------------------
@@ -622,6 +956,12 @@ def main():
     ap.add_argument("--unfused", action="store_true",
                     help="step = reshape_and_cache + paged_attention_v2 as two ops (A/B)")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
+    ap.add_argument("--no-check", dest="check", action="store_false",
+                    help="skip the parity check against the reference's CUDA kernels")
+    ap.add_argument("--sustain", type=float, default=3.0,
+                    help="seconds of the back-to-back sustained leg (0 = off)")
+    ap.add_argument("--no-side-configs", dest="side_configs", action="store_false",
+                    help="do not run the other four BASELINE configs after the main one")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -58,7 +58,7 @@
 extern "C" {
 #endif
 
-#define B200PA_ABI_VERSION 6
+#define B200PA_ABI_VERSION 7
 
 /* scalar_t of query / out / key / value (reference: VLLM_DISPATCH_FLOATING_TYPES) */
 enum { B200PA_F32 = 0, B200PA_F16 = 1, B200PA_BF16 = 2 };
@@ -97,11 +97,20 @@ uint64_t b200pa_launch_count(void);
 /*
  * Bytes of device scratch the attention entry points want in `workspace` for head size
  * `head_size` on the current device (a function of the SM count only, about 20 MB on a B200;
- * independent of batch and context).  The workspace needs no initialisation, may be shared by
- * calls on ONE stream, and must be 16-byte aligned.  The torch shim takes it from torch's
- * caching allocator per call (CUDA-graph safe).  workspace == NULL is allowed: the launchers then
- * use the generic SIMT kernel, which needs none (and is several times slower).
+ * independent of batch and context).  Contract (ABI v7):
+ *   - its first B200PA_WORKSPACE_HEADER_BYTES must be ZERO before the first call that uses it
+ *     (cudaMemsetAsync once, at allocation); every call leaves them zero again -- they hold the
+ *     ticket counters with which the decode kernel's CTAs elect the one that merges a sequence
+ *     cut by CTA boundaries (the reference needs a second kernel for that:
+ *     paged_attention_v2_reduce_kernel, attention_kernels.cuh:560-664);
+ *   - the rest needs no initialisation;
+ *   - it may be shared by calls of any shape on ONE stream (calls that may run concurrently
+ *     need one workspace each) and must be 16-byte aligned.
+ * The torch shim keeps one zero-initialised workspace per (device, stream).  workspace == NULL is
+ * allowed: the launchers then use the generic SIMT kernel, which needs none (and is several
+ * times slower).
  */
+#define B200PA_WORKSPACE_HEADER_BYTES 4096
 int64_t b200pa_paged_attention_workspace_bytes(int head_size);
 
 /*

@@ -512,7 +512,8 @@ def test_c_abi_without_workspace_uses_generic_and_stream_needs_one(native):
     lib.b200pa_paged_attention_workspace_bytes.restype = ctypes.c_int64
     need = lib.b200pa_paged_attention_workspace_bytes(D)
     assert 0 < need < (64 << 20)
-    ws = torch.empty(need, dtype=torch.uint8, device=DEV)
+    # ABI v7: the workspace header (ticket counters) is zero before the first use
+    ws = torch.zeros(need, dtype=torch.uint8, device=DEV)
 
     def call(out, wsp, wsn):
         p = lambda t: ctypes.c_void_p(t.data_ptr())
@@ -526,7 +527,9 @@ def test_c_abi_without_workspace_uses_generic_and_stream_needs_one(native):
     out_ws = torch.empty_like(qd)
     n0 = native.launch_count()
     assert call(out_ws, ctypes.c_void_p(ws.data_ptr()), need) == 0
-    assert native.launch_count() - n0 == 2          # stream kernel + merge
+    assert native.launch_count() - n0 == 1          # ONE launch: the merge is inside the kernel
+    torch.cuda.synchronize()
+    assert int(ws[:4096].max()) == 0                # ... and it leaves the header clean
     out_nows = torch.empty_like(qd)
     n0 = native.launch_count()
     assert call(out_nows, None, 0) == 0
@@ -813,7 +816,7 @@ def test_launch_counter_counts_native_launches(ops, native):
     n0 = native.launch_count()
     ops.paged_attention_v1(torch.empty_like(q), q, kc, vc, Hkv, s, bt, sl, BS, max_len, None,
                            "fp8", one, one)
-    assert native.launch_count() == n0 + 2   # stream kernel + merge
+    assert native.launch_count() == n0 + 1   # ONE kernel: the cross-CTA merge is inside it
 
 
 # ------------------------------------------------------ backend (AttentionImpl)
@@ -867,3 +870,66 @@ def test_backend_decode_step_matches_oracle(ora, kv):
     # and the cache bytes are the oracle's
     assert torch.equal(kv_cache[0].cpu().view(torch.uint8), kc_o.reshape(NB, -1).view(torch.uint8))
     assert torch.equal(kv_cache[1].cpu().view(torch.uint8), vc_o.reshape(NB, -1).view(torch.uint8))
+
+
+# ------------------------------------------------- one launch per step, shared workspace
+
+def test_back_to_back_launches_share_the_workspace(ops, native):
+    """ABI v7: the cross-CTA merge is inside the decode kernel (ticket counters in the workspace
+    header, left at zero).  Many launches back to back on one stream -- no host synchronisation,
+    programmatic stream serialisation between them, shapes with different slot sizes sharing
+    the one cached workspace, sequences short enough that a launch lasts microseconds -- must
+    each give exactly what the same call gives alone."""
+    cases = []
+    rnd = random.Random(11)
+    for B, H, Hkv, D, kv, lens in [
+        (40, 16, 2, 128, "fp8", [rnd.randint(1, 32) for _ in range(40)]),       # all <= 32 tokens
+        (3, 8, 1, 64, "auto", [3000, 17, 900]),
+        (1, 8, 1, 128, "fp8", [40000]),                                         # ~all CTAs share one item
+        (7, 32, 8, 256, "fp8", [rnd.randint(1, 3000) for _ in range(7)]),
+        (64, 8, 8, 128, "auto", [rnd.randint(1, 200) for _ in range(64)]),
+    ]:
+        BS = 16
+        NB = sum((L + BS - 1) // BS for L in lens) + 2
+        s = D ** -0.5
+        q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, NB, lens, torch.bfloat16,
+                                                 seed=B + D, kv=kv, lo=-1.0, hi=1.0, permute=True)
+        ks = torch.tensor(1.0 if kv == "auto" else 0.5, device=DEV)
+        vs = torch.tensor(1.0 if kv == "auto" else 1.5, device=DEV)
+        cases.append(dict(q=q.to(DEV), kc=kc.to(DEV), vc=vc.to(DEV), bt=bt.to(DEV), sl=sl.to(DEV),
+                          Hkv=Hkv, s=s, max_len=max(lens), kv=kv, ks=ks, vs=vs))
+
+    def call(c, out):
+        ops.paged_attention_v1(out, c["q"], c["kc"], c["vc"], c["Hkv"], c["s"], c["bt"], c["sl"], 16,
+                               c["max_len"], None, c["kv"], c["ks"], c["vs"])
+
+    native.set_impl(STREAM)
+    try:
+        alone = []
+        for c in cases:
+            o = torch.empty_like(c["q"])
+            call(c, o)
+            torch.cuda.synchronize()
+            alone.append(o)
+        n0 = native.launch_count()
+        outs = [[torch.full_like(c["q"], float("nan")) for c in cases] for _ in range(40)]
+        for rep in range(40):
+            for c, o in zip(cases, outs[rep]):
+                call(c, o)
+        torch.cuda.synchronize()
+        assert native.launch_count() - n0 == 40 * len(cases)       # one kernel per call
+        for rep in range(40):
+            for a, o in zip(alone, outs[rep]):
+                assert torch.equal(a, o), f"repetition {rep} differs from the call alone"
+    finally:
+        native.set_impl(native.IMPL_AUTO)
+    # ... and the stream results are the generic kernel's
+    native.set_impl(GENERIC)
+    try:
+        for c, a in zip(cases, alone):
+            o = torch.empty_like(c["q"])
+            call(c, o)
+            torch.cuda.synchronize()
+            _close(a.cpu(), o.cpu(), atol=ATOL * max(1.0, float(o.float().abs().max())))
+    finally:
+        native.set_impl(native.IMPL_AUTO)

@@ -6,6 +6,7 @@
 #include <cstdio>
 #include <cstdint>
 #include <cstdlib>
+#include <cstring>
 #include <vector>
 #include <algorithm>
 #include <cuda_runtime.h>
@@ -102,11 +103,61 @@ void run_tma(const uint8_t* buf, size_t bytes, int ctas_per_sm, int sms, uint32_
   CK(cudaFree(dperm));
 }
 
-int main() {
+// `bwprobe sustain [seconds]`: the 8-warp 2 KiB TMA ring probe (the decode kernel's traffic without
+// its math) and the plain-load probe back to back for `seconds` each, one line per ~100 ms: does
+// a pure read stream hold its rate for seconds, and at what power / SM clock (sample nvidia-smi
+// beside it)?  The difference to the decode kernel's sustained leg is the cost of the math.
+template <int NW, int STAGES, int RUN>
+void sustain_tma(const uint8_t* buf, size_t bytes, int ctas_per_sm, int sms, uint32_t* sink, double seconds,
+                 const char* name) {
+  const size_t nruns = bytes / RUN;
+  const int workers = sms * ctas_per_sm * NW;
+  int rpw = (int)(nruns / workers); rpw &= ~1;
+  std::vector<int> perm(nruns);
+  for (size_t i = 0; i < nruns; ++i) perm[i] = (int)i;
+  uint64_t st = 88172645463325252ull;
+  for (size_t i = nruns - 1; i > 0; --i) { st ^= st << 13; st ^= st >> 7; st ^= st << 17; std::swap(perm[i], perm[st % (i + 1)]); }
+  int* dperm; CK(cudaMalloc(&dperm, nruns * sizeof(int)));
+  CK(cudaMemcpy(dperm, perm.data(), nruns * sizeof(int), cudaMemcpyHostToDevice));
+  const int smem = NW * STAGES * 2 * RUN;
+  auto k = read_tma<NW, STAGES, RUN>;
+  CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  const double got = (double)workers * rpw * RUN;
+  cudaEvent_t a, b; CK(cudaEventCreate(&a)); CK(cudaEventCreate(&b));
+  double elapsed = 0;
+  while (elapsed < seconds * 1e3) {
+    CK(cudaEventRecord(a));
+    for (int i = 0; i < 80; ++i) k<<<sms * ctas_per_sm, NW * 32, smem>>>(buf, dperm, rpw, sink);
+    CK(cudaEventRecord(b)); CK(cudaEventSynchronize(b));
+    float ms; CK(cudaEventElapsedTime(&ms, a, b));
+    elapsed += ms;
+    printf("{\"probe\": \"%s\", \"t_ms\": %.0f, \"gbs\": %.1f}\n", name, elapsed, 80 * got / ms / 1e6);
+    fflush(stdout);
+  }
+  CK(cudaFree(dperm));
+}
+
+int main(int argc, char** argv) {
   const size_t bytes = (size_t)8 << 30;
   uint8_t* buf; CK(cudaMalloc(&buf, bytes)); CK(cudaMemset(buf, 1, bytes));
   uint32_t* sink; CK(cudaMalloc(&sink, 4));
   int sms = 0; CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0));
+  if (argc > 1 && !strcmp(argv[1], "sustain")) {
+    const double seconds = argc > 2 ? atof(argv[2]) : 4.0;
+    sustain_tma<8, 6, 2048>(buf, bytes, 1, sms, sink, seconds, "sustain_tma_2k_8w_6st");
+    double elapsed = 0;
+    cudaEvent_t a, b; CK(cudaEventCreate(&a)); CK(cudaEventCreate(&b));
+    while (elapsed < seconds * 1e3) {
+      CK(cudaEventRecord(a));
+      for (int i = 0; i < 80; ++i) read_plain<<<sms * 8, 256>>>((const uint4*)buf, bytes / 16, sink);
+      CK(cudaEventRecord(b)); CK(cudaEventSynchronize(b));
+      float ms; CK(cudaEventElapsedTime(&ms, a, b));
+      elapsed += ms;
+      printf("{\"probe\": \"sustain_plain_ld128\", \"t_ms\": %.0f, \"gbs\": %.1f}\n", elapsed, 80.0 * bytes / ms / 1e6);
+      fflush(stdout);
+    }
+    return 0;
+  }
   for (int cps : {4, 8, 16}) {
     float ms = time_ms([&] { read_plain<<<sms * cps, 256>>>((const uint4*)buf, bytes / 16, sink); }, 10);
     printf("{\"probe\": \"plain_ld128\", \"ctas_per_sm\": %d, \"ms\": %.4f, \"gbs\": %.1f}\n", cps, ms, bytes / ms / 1e6);

@@ -23,12 +23,14 @@
 //    A piece that covers its whole (sequence, kv head) is normalised and written straight to
 //    `out`.  A warp has at most two pieces that do not (its first and its last): their
 //    unnormalised fp32 accumulators + (max, sum) go to workspace slots 2w / 2w+1.  At the end of
-//    the kernel -- the only CTA-wide barrier -- each CTA merges the pieces of its own warps:
-//    items that begin and end inside the CTA are finished there, and what is cut by a CTA
-//    boundary (at most two runs per CTA) goes to the CTA's slots.  Only those reach
-//    paged_attention_stream_merge_kernel (one small CTA per boundary between main-kernel CTAs;
-//    ncu showed the per-warp-boundary version instruction-bound at 13-23 us,
-//    profiles/r01_small_shard_launches.csv).
+//    the kernel -- behind its first CTA-wide barrier -- each CTA merges the pieces of its own
+//    warps: items that begin and end inside the CTA are finished there, and what is cut by a CTA
+//    boundary (at most two runs per CTA) goes to the CTA's slots 2c / 2c+1.  The CTAs that share
+//    such an item take a ticket from the item's counter in the workspace; the LAST one to arrive
+//    merges all the item's CTA slots (all its warps, fixed piece order: deterministic whoever is
+//    last), writes `out` and resets the counter -- the job of the reference's
+//    paged_attention_v2_reduce_kernel (attention_kernels.cuh:560-664) without a second launch.
+//    (Round 1 used a separate merge kernel: 7-11 us per step, profiles/r01q_*.)
 //  * LOADS.  For one (page, kv head) the x-packed K sub-block [D/x][16][x] and the V sub-block
 //    [D][16] are each one contiguous run (2 KiB fp8 / 4 KiB 16-bit at D=128): one 1-D TMA bulk
 //    copy each, completing on the stage's mbarrier.  Block-table entries are fetched 32 at a
@@ -179,7 +181,8 @@ struct StreamParams {
   void* out;           // [S,H,D] scalar_t
   float* lse;          // optional: natural-log sum-exp of the scaled logits per (seq, head)
   int64_t lse_seq_stride, lse_head_stride;
-  float* ws;           // workspace: 2 slots per worker, kSlotFloats(D) floats each
+  float* ws;           // workspace slots: 2 per worker + 2 per CTA, slot_floats(D) floats each
+  int* counters;       // workspace header: one ticket counter per CTA, zero between launches
   const void* q;
   const void* k_cache;
   const void* v_cache;
@@ -210,6 +213,10 @@ namespace {
 // workspace slot: O^T fragments [D/16][32 lanes][4] fp32 (unnormalised, v_scale applied),
 // then m[8] (log2 domain), l[8]
 __host__ __device__ constexpr int slot_floats(int d) { return 8 * d + 16; }
+// workspace header: the ticket counters of the cross-CTA merge, one int per CTA.  ZERO before the
+// first launch on a workspace and left zero by every launch; at a fixed offset so that launches
+// of different shapes can share one workspace.
+constexpr int kCounterBytes = 4096;
 
 template <int PPS> __device__ __forceinline__ int stages_of(int len) {
   return len <= 0 ? 0 : (len + kBS * PPS - 1) / (kBS * PPS);
@@ -384,15 +391,21 @@ paged_attention_stream_kernel(const StreamParams p) {
   const long long Ttot = total_stages<PPS>(p.seq_lens, p.num_seqs, lane) * vheads;
   const long long W = min((long long)p.num_workers, Ttot);
   const long long w = (long long)blockIdx.x * NW + warp;
-  // let the merge kernel's CTAs be scheduled as soon as SM resources free up; they block in
-  // griddepcontrol.wait until this grid has completed and flushed
+  // let the next kernel of the stream (the next layer's decode step) be scheduled as soon as SM
+  // resources free up; it blocks in its own griddepcontrol.wait until this grid has completed
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   // what this warp leaves for the in-CTA merge: bit 0 head piece (slot 2w, continues an earlier
   // worker's item), bit 1 the head piece reaches the item's end, bit 2 tail piece (slot 2w+1,
   // from the item's start, continued by a later worker)
-  __shared__ int meta_s[NW][5];   // flags, head (b, vh), tail (b, vh)
+  __shared__ int meta_s[NW][7];   // flags, head (b, vh), tail (b, vh), stages of the head / tail item
+  __shared__ long long ibeg_s[NW][2];  // first flattened stage of the head / tail piece's item
   __shared__ float hdr_s[2 * NW][16];  // per piece (2i head, 2i+1 tail): m[8] (log2), l[8]
-  int mflags = 0, mh_b = 0, mh_vh = 0, mt_b = 0, mt_vh = 0;
+  // what the in-CTA merge leaves for the cross-CTA merge: [0] the run that continues an earlier
+  // CTA's item (CTA slot 2c), [1] the run a later CTA continues (slot 2c+1)
+  __shared__ int pend_s[2][6];    // valid, first CTA of the item, CTAs of the item, b, vh, last?
+  int mflags = 0, mh_b = 0, mh_vh = 0, mt_b = 0, mt_vh = 0, mh_ns = 0, mt_ns = 0;
+  long long mh_ib = 0, mt_ib = 0;
+  if (threadIdx.x < 2) pend_s[threadIdx.x][0] = 0;
   if (w < W) {  // idle warps (fewer stages than warps) go straight to the barrier
   const long long u0 = (w * Ttot) / W, u1 = ((w + 1) * Ttot) / W;
 
@@ -405,6 +418,7 @@ paged_attention_stream_kernel(const StreamParams p) {
   }
   Cursor cc = pc;
   int piece_begin = cc.st;
+  int it = 0;                               // stages consumed
 
   // ---------------------------------------------------------------- ring + barriers
   uint8_t* ring = smem + (size_t)warp * RING_BYTES;
@@ -644,8 +658,10 @@ paged_attention_stream_kernel(const StreamParams p) {
     } else {
       // slot 2w: my first piece, continuing an earlier worker's; slot 2w+1: my last piece,
       // continued by a later worker
-      if (from_start) { mflags |= 4; mt_b = cc.b; mt_vh = cc.vh; }
-      else { mflags |= to_end ? 3 : 1; mh_b = cc.b; mh_vh = cc.vh; }
+      // the item's first flattened stage: this piece ends at stage u0 + it of the span
+      const long long ib = u0 + it - cc.st_end;
+      if (from_start) { mflags |= 4; mt_b = cc.b; mt_vh = cc.vh; mt_ns = cc.ns; mt_ib = ib; }
+      else { mflags |= to_end ? 3 : 1; mh_b = cc.b; mh_vh = cc.vh; mh_ns = cc.ns; mh_ib = ib; }
       float* slot = p.ws + (size_t)(2 * w + (from_start ? 1 : 0)) * slot_floats(D);
 #pragma unroll
       for (int mt = 0; mt < MT; ++mt)
@@ -666,7 +682,8 @@ paged_attention_stream_kernel(const StreamParams p) {
 
   // ---------------------------------------------------------------- main loop
 #pragma unroll 1
-  for (int i = 0;; ++i) {
+  for (;; ++it) {
+    const int i = it;
     if (cc.st == cc.st_end) {
       end_piece();
       if (cc.left == 0) break;
@@ -946,6 +963,18 @@ paged_attention_stream_kernel(const StreamParams p) {
     meta_s[warp][0] = mflags;
     meta_s[warp][1] = mh_b; meta_s[warp][2] = mh_vh;
     meta_s[warp][3] = mt_b; meta_s[warp][4] = mt_vh;
+    meta_s[warp][5] = mh_ns; meta_s[warp][6] = mt_ns;
+    ibeg_s[warp][0] = mh_ib; ibeg_s[warp][1] = mt_ib;
+  }
+  // empty sequences: the reference's v1 kernel yields zeros (no keys, zero accumulators)
+  for (long long b = (long long)blockIdx.x * NW + warp; b < p.num_seqs; b += (long long)gridDim.x * NW) {
+    if (p.seq_lens[b] <= 0) {
+      T* row = reinterpret_cast<T*>(p.out) + b * p.num_heads * D;
+      for (int i = lane; i < p.num_heads * D; i += 32) row[i] = Scalar<ST>::from_float(0.f);
+      if (p.lse != nullptr)
+        for (int i = lane; i < p.num_heads; i += 32)
+          p.lse[b * p.lse_seq_stride + i * p.lse_head_stride] = -INFINITY;
+    }
   }
   __syncthreads();   // also orders the warps' global slot stores before the loads below
   {
@@ -1037,6 +1066,21 @@ paged_attention_stream_kernel(const StreamParams p) {
           *reinterpret_cast<float2*>(dst + 8 * D + 2 * q4) = make_float2(mx0, mx1);
           *reinterpret_cast<float2*>(dst + 8 * D + 8 + 2 * q4) = make_float2(l0, l1);
         }
+        __threadfence();   // the slot is visible device-wide before this CTA takes its ticket
+        if (lane == 0) {
+          // the CTAs that hold a piece of this item: those of the workers of its first and last
+          // stage (worker of stage s = the largest x with (x * Ttot) / W <= s)
+          const int i0 = ps >> 1, hk = ps & 1;
+          const long long ib = ibeg_s[i0][hk], ie = ib + meta_s[i0][5 + hk];
+          const long long c_first = (((ib + 1) * W - 1) / Ttot) / NW;
+          const long long c_last = ((ie * W - 1) / Ttot) / NW;
+          int* pd = pend_s[from_start ? 1 : 0];
+          pd[1] = (int)c_first;
+          pd[2] = (int)(c_last - c_first) + 1;
+          pd[3] = meta_s[i0][hk ? 3 : 1];
+          pd[4] = meta_s[i0][hk ? 4 : 2];
+          pd[0] = 1;
+        }
       }
     };
     int ps = -1;
@@ -1051,144 +1095,114 @@ paged_attention_stream_kernel(const StreamParams p) {
     }
     if (ps >= 0) emit(ps, 2 * NW - 1, false);
   }
-}
 
-// ---------------------------------------------------------------------------------------
-// Merge of the pieces of every (sequence, head tile) that a boundary between two CTAs of the
-// main kernel cut (the job of the reference's paged_attention_v2_reduce_kernel,
-// attention_kernels.cuh:560-664: weights l_j * exp(m_j - m), 1e-6 in the denominator).  The main
-// kernel has already merged inside each CTA, so a "worker" here is a main-kernel CTA c with span
-// [cta_begin(c), cta_begin(c+1)) and CTA slots 2c (continues an earlier CTA's item) / 2c+1
-// (continued by a later CTA).  One CTA per boundary c-1 | c; the CTA that owns the FIRST boundary
-// inside an item merges all its pieces: slot 2(c-1)+1 and slots 2c' of every later CTA whose span
-// starts inside the item (2-3 pieces typically, ~150 for a lone 131072-token sequence on one kv
-// head).  Pieces are dealt round-robin to the warps, which accumulate whole slots with 16-byte
-// loads and meet in shared memory in a fixed order (deterministic).  The CTA is small enough
-// (4 warps, 16.6 KiB) to become resident beside a main-kernel CTA: launched with programmatic
-// stream serialisation, everything up to griddepcontrol.wait overlaps the main kernel.
-constexpr int kMergeWarps = 4;
-
-template <int ST, int D, int PPS, bool DPERM>
-__global__ void __launch_bounds__(32 * kMergeWarps)
-paged_attention_stream_merge_kernel(const StreamParams p) {
-  using T = typename Scalar<ST>::type;
-  constexpr int MT = D / 16;
-  __shared__ float4 acc_s[kMergeWarps][MT][32];
-  __shared__ float lsum_s[kMergeWarps][8];
-  const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
-  const int r = lane >> 2, q4 = lane & 3;
-  const int vheads = p.num_kv_heads * p.h_tiles;
-  const long long c = (long long)blockIdx.x + 1;
-  // empty sequences: the reference's v1 kernel yields zeros (no keys, zero accumulators)
-  for (long long b = blockIdx.x; b < p.num_seqs; b += gridDim.x) {
-    if (p.seq_lens[b] <= 0) {
-      T* row = reinterpret_cast<T*>(p.out) + b * p.num_heads * D;
-      for (int i = threadIdx.x; i < p.num_heads * D; i += blockDim.x)
-        row[i] = Scalar<ST>::from_float(0.f);
-      if (p.lse != nullptr)
-        for (int i = threadIdx.x; i < p.num_heads; i += blockDim.x)
-          p.lse[b * p.lse_seq_stride + i * p.lse_head_stride] = -INFINITY;
-    }
-  }
-  const long long Ttot = total_stages<PPS>(p.seq_lens, p.num_seqs, lane) * vheads;
-  const long long W = min((long long)p.num_workers, Ttot);
-  const long long NW = p.nw;
-  if (c * NW >= W) return;                         // main-kernel CTA c had no work
-  // first stage of main-kernel CTA x (its first warp is worker x * NW)
-  auto cta_begin = [&](long long x) { return (min(x * NW, W) * Ttot) / W; };
-  const long long s = cta_begin(c);
-  const Loc loc = locate_stage<PPS>(p.seq_lens, p.num_seqs, vheads, s, lane);
-  if (loc.st == 0) return;                         // the boundary is not inside a (seq, head)
-  const long long item_begin = s - loc.st, item_end = item_begin + loc.ns;
-  if (cta_begin(c - 1) > item_begin) return;       // an earlier boundary owns this one
-  // pieces: CTAs c-1 .. c_last (the CTA of the worker that holds the last stage of the item)
-  const long long c_last = min(W - 1, (item_end * W - 1) / Ttot) / NW;
-  const int n = (int)(c_last - (c - 1)) + 1;
-  const size_t SF = slot_floats(D);
-  const float* const cta_slots = p.ws + (size_t)2 * p.num_workers * SF;
-  // piece k: slot 2(c-1)+1 for k = 0, else 2(c-1+k)
-  auto slot_of = [&](int k) { return cta_slots + (size_t)(2 * (c - 1 + k) + (k == 0 ? 1 : 0)) * SF; };
-
-  asm volatile("griddepcontrol.wait;" ::: "memory");  // the main kernel's stores are visible
-
-  // pass 1: per-head maximum of the pieces' references (lanes stride over pieces)
-  float mx8[8];
-#pragma unroll
-  for (int h = 0; h < 8; ++h) mx8[h] = -INFINITY;
-  for (int k = lane; k < n; k += 32) {
-    const float4* m = reinterpret_cast<const float4*>(slot_of(k) + 8 * D);
-    const float4 a = m[0], b = m[1];
-    mx8[0] = fmaxf(mx8[0], a.x); mx8[1] = fmaxf(mx8[1], a.y);
-    mx8[2] = fmaxf(mx8[2], a.z); mx8[3] = fmaxf(mx8[3], a.w);
-    mx8[4] = fmaxf(mx8[4], b.x); mx8[5] = fmaxf(mx8[5], b.y);
-    mx8[6] = fmaxf(mx8[6], b.z); mx8[7] = fmaxf(mx8[7], b.w);
-  }
-#pragma unroll
-  for (int h = 0; h < 8; ++h) mx8[h] = warp_max(mx8[h]);
-  float mx[2];
-#pragma unroll
-  for (int h = 0; h < 8; ++h) {   // select heads 2q4, 2q4+1 without dynamic register indexing
-    if (h == 2 * q4) mx[0] = mx8[h];
-    if (h == 2 * q4 + 1) mx[1] = mx8[h];
-  }
-  // pass 2: warp wv sums pieces wv, wv + kMergeWarps, ... (whole slots)
-  float4 acc[MT];
-#pragma unroll
-  for (int mt = 0; mt < MT; ++mt) acc[mt] = make_float4(0.f, 0.f, 0.f, 0.f);
-  float lsum[2] = {0.f, 0.f};
-#pragma unroll 2
-  for (int k = wv; k < n; k += kMergeWarps) {
-    const float* slot = slot_of(k);
-    const float2 m = *reinterpret_cast<const float2*>(slot + 8 * D + 2 * q4);
-    const float2 l = *reinterpret_cast<const float2*>(slot + 8 * D + 8 + 2 * q4);
-    float4 v[MT];
-#pragma unroll
-    for (int mt = 0; mt < MT; ++mt) v[mt] = reinterpret_cast<const float4*>(slot)[mt * 32 + lane];
-    const float f0 = ex2(m.x - mx[0]), f1 = ex2(m.y - mx[1]);
-    lsum[0] += l.x * f0;
-    lsum[1] += l.y * f1;
-#pragma unroll
-    for (int mt = 0; mt < MT; ++mt) {
-      acc[mt].x += v[mt].x * f0; acc[mt].y += v[mt].y * f1;
-      acc[mt].z += v[mt].z * f0; acc[mt].w += v[mt].w * f1;
-    }
-  }
-#pragma unroll
-  for (int mt = 0; mt < MT; ++mt) acc_s[wv][mt][lane] = acc[mt];
-  if (r == 0) {
-    lsum_s[wv][2 * q4] = lsum[0];
-    lsum_s[wv][2 * q4 + 1] = lsum[1];
+  // ---------------------------------------------------------------- cross-CTA merge
+  // An item that CTA boundaries cut has one piece per CTA it touches: slot 2c+1 of its first CTA,
+  // slot 2c of every later one.  Each of those CTAs takes a ticket from the counter of the item's
+  // first CTA; the last to arrive sums the pieces with the reference's weights l_j * 2^(m_j - m)
+  // (attention_kernels.cuh:560-664) -- pieces dealt round-robin to the warps, which meet in
+  // shared memory (the ring is free by now) in warp order -- and leaves the counter at zero.
+  __syncthreads();
+  if (threadIdx.x < 2 && pend_s[threadIdx.x][0]) {
+    int* pd = pend_s[threadIdx.x];
+    const int ticket = atomicAdd(p.counters + pd[1], 1);
+    pd[5] = ticket == pd[2] - 1;
+    if (pd[5]) atomicExch(p.counters + pd[1], 0);
   }
   __syncthreads();
-  // final: warp wv adds the warps' sums of m-tiles wv, wv + kMergeWarps, ... in warp order
-  float lt[2] = {0.f, 0.f};
+#pragma unroll 1
+  for (int k = 0; k < 2; ++k) {
+    if (!pend_s[k][0] || !pend_s[k][5]) continue;     // CTA-uniform
+    __threadfence();                                   // the other CTAs' slots, fenced before their tickets
+    constexpr int SF = slot_floats(D);
+    const int c_first = pend_s[k][1], n = pend_s[k][2], b = pend_s[k][3], vh = pend_s[k][4];
+    const float* const cta_slots = p.ws + (size_t)2 * p.num_workers * SF;
+    // piece j: slot 2 c_first + 1 for j = 0, else 2 (c_first + j)
+    auto slot_of = [&](int j) {
+      return cta_slots + (size_t)(2 * (c_first + j) + (j == 0 ? 1 : 0)) * SF;
+    };
+    float4* acc_s = reinterpret_cast<float4*>(smem);          // [NW][MT][32]
+    float* lsum_s = reinterpret_cast<float*>(smem + (size_t)NW * MT * 32 * sizeof(float4));  // [NW][8]
+    // pass 1: per-head maximum of the pieces' references (lanes stride over pieces)
+    float mx8[8];
 #pragma unroll
-  for (int g = 0; g < kMergeWarps; ++g) {
-    lt[0] += lsum_s[g][2 * q4];
-    lt[1] += lsum_s[g][2 * q4 + 1];
-  }
-  const int kvh = loc.vh / p.h_tiles;
-  const int tile = loc.vh - kvh * p.h_tiles;
-  const int head0 = kvh * p.group + tile * 8;
-  const int heads_valid = min(8, p.group - tile * 8);
-  const float inv0 = __fdividef(1.f, lt[0] + 1e-6f);
-  const float inv1 = __fdividef(1.f, lt[1] + 1e-6f);
-  for (int mt = wv; mt < MT; mt += kMergeWarps) {
-    float o[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-    for (int g = 0; g < kMergeWarps; ++g) {
-      const float4 v = acc_s[g][mt][lane];
-      o[0] += v.x; o[1] += v.y; o[2] += v.z; o[3] += v.w;
+    for (int h = 0; h < 8; ++h) mx8[h] = -INFINITY;
+    for (int j = lane; j < n; j += 32) {
+      const float4* m = reinterpret_cast<const float4*>(slot_of(j) + 8 * D);
+      const float4 a = __ldcg(m), bb = __ldcg(m + 1);
+      mx8[0] = fmaxf(mx8[0], a.x); mx8[1] = fmaxf(mx8[1], a.y);
+      mx8[2] = fmaxf(mx8[2], a.z); mx8[3] = fmaxf(mx8[3], a.w);
+      mx8[4] = fmaxf(mx8[4], bb.x); mx8[5] = fmaxf(mx8[5], bb.y);
+      mx8[6] = fmaxf(mx8[6], bb.z); mx8[7] = fmaxf(mx8[7], bb.w);
     }
-    store_out_tile<ST, D, DPERM>(reinterpret_cast<T*>(p.out) + ((int64_t)loc.b * p.num_heads + head0) * D,
-                          mt, o, inv0, inv1, heads_valid, r, q4);
-  }
-  if (p.lse != nullptr && wv == 0 && r == 0) {
 #pragma unroll
-    for (int h = 0; h < 2; ++h)
-      if (2 * q4 + h < heads_valid)
-        p.lse[loc.b * p.lse_seq_stride + (head0 + 2 * q4 + h) * p.lse_head_stride] =
-            (mx[h] + __log2f(lt[h])) * kLn2;
+    for (int h = 0; h < 8; ++h) mx8[h] = warp_max(mx8[h]);
+    float mx[2];
+#pragma unroll
+    for (int h = 0; h < 8; ++h) {   // select heads 2q4, 2q4+1 without dynamic register indexing
+      if (h == 2 * q4) mx[0] = mx8[h];
+      if (h == 2 * q4 + 1) mx[1] = mx8[h];
+    }
+    // pass 2: warp `warp` sums pieces warp, warp + NW, ... (whole slots)
+    float4 acc[MT];
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt) acc[mt] = make_float4(0.f, 0.f, 0.f, 0.f);
+    float ls[2] = {0.f, 0.f};
+#pragma unroll 1
+    for (int j = warp; j < n; j += NW) {
+      const float* slot = slot_of(j);
+      const float2 m = __ldcg(reinterpret_cast<const float2*>(slot + 8 * D + 2 * q4));
+      const float2 l = __ldcg(reinterpret_cast<const float2*>(slot + 8 * D + 8 + 2 * q4));
+      float4 v[MT];
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt) v[mt] = __ldcg(reinterpret_cast<const float4*>(slot) + mt * 32 + lane);
+      const float f0 = ex2(m.x - mx[0]), f1 = ex2(m.y - mx[1]);
+      ls[0] += l.x * f0;
+      ls[1] += l.y * f1;
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt) {
+        acc[mt].x += v[mt].x * f0; acc[mt].y += v[mt].y * f1;
+        acc[mt].z += v[mt].z * f0; acc[mt].w += v[mt].w * f1;
+      }
+    }
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt) acc_s[(warp * MT + mt) * 32 + lane] = acc[mt];
+    if (r == 0) {
+      lsum_s[warp * 8 + 2 * q4] = ls[0];
+      lsum_s[warp * 8 + 2 * q4 + 1] = ls[1];
+    }
+    __syncthreads();
+    // final: warp `warp` adds the warps' sums of m-tiles warp, warp + NW, ... in warp order
+    float lt[2] = {0.f, 0.f};
+#pragma unroll
+    for (int g = 0; g < NW; ++g) {
+      lt[0] += lsum_s[g * 8 + 2 * q4];
+      lt[1] += lsum_s[g * 8 + 2 * q4 + 1];
+    }
+    const int kvh = vh / p.h_tiles;
+    const int tile = vh - kvh * p.h_tiles;
+    const int hd0 = kvh * p.group + tile * 8;
+    const int hv = min(8, p.group - tile * 8);
+    const float inv0 = __fdividef(1.f, lt[0] + 1e-6f);
+    const float inv1 = __fdividef(1.f, lt[1] + 1e-6f);
+    for (int mt = warp; mt < MT; mt += NW) {
+      float o4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int g = 0; g < NW; ++g) {
+        const float4 v = acc_s[(g * MT + mt) * 32 + lane];
+        o4[0] += v.x; o4[1] += v.y; o4[2] += v.z; o4[3] += v.w;
+      }
+      store_out_tile<ST, D, DPERM>(reinterpret_cast<T*>(p.out) + ((int64_t)b * p.num_heads + hd0) * D,
+                                   mt, o4, inv0, inv1, hv, r, q4);
+    }
+    if (p.lse != nullptr && warp == 0 && r == 0) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h)
+        if (2 * q4 + h < hv)
+          p.lse[b * p.lse_seq_stride + (hd0 + 2 * q4 + h) * p.lse_head_stride] =
+              (mx[h] + __log2f(lt[h])) * kLn2;
+    }
+    __syncthreads();   // acc_s is reused by the CTA's other pending item
   }
 }
 
@@ -1221,8 +1235,12 @@ int launch_stream_t(StreamParams& p, int num_sms, int64_t workspace_bytes, cudaS
   const int ctas = num_sms * ctas_per_sm;
   p.num_workers = ctas * NW;
   p.nw = NW;
-  // 2 slots per warp (pieces) + 2 per CTA (what the in-CTA merge leaves for the merge kernel)
-  const int64_t need = (int64_t)2 * (p.num_workers + ctas) * slot_floats(D) * (int64_t)sizeof(float);
+  if (ctas * (int)sizeof(int) > kCounterBytes)
+    return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: %d CTAs exceed the workspace header", ctas);
+  // header (ticket counters) + 2 slots per warp (pieces) + 2 per CTA (what the in-CTA merge
+  // leaves for the cross-CTA merge)
+  const int64_t need = kCounterBytes +
+      (int64_t)2 * (p.num_workers + ctas) * slot_floats(D) * (int64_t)sizeof(float);
   if (workspace_bytes < need)
     return set_error(B200PA_ERR_INVALID, "workspace too small: %lld bytes, need %lld "
                      "(b200pa_paged_attention_workspace_bytes)", (long long)workspace_bytes,
@@ -1243,26 +1261,7 @@ int launch_stream_t(StreamParams& p, int num_sms, int64_t workspace_bytes, cudaS
       return set_error(B200PA_ERR_CUDA, "stream kernel launch: %s", cudaGetErrorString(e));
   }
   count_launch();
-  int rc = check_launch("paged_attention (stream)");
-  if (rc) return rc;
-  if (ctas > 1) {
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(ctas - 1);            // boundaries between main-kernel CTAs c-1 | c
-    cfg.blockDim = dim3(32 * kMergeWarps);
-    cfg.dynamicSmemBytes = 0;
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(
-        &cfg, paged_attention_stream_merge_kernel<ST, D, PPS, FLASH && FP8>, p);
-    if (e != cudaSuccess)
-      return set_error(B200PA_ERR_CUDA, "stream merge launch: %s", cudaGetErrorString(e));
-    count_launch();
-  }
-  return check_launch("paged_attention (stream merge)");
+  return check_launch("paged_attention (stream)");
 }
 
 }  // namespace
@@ -1371,8 +1370,8 @@ int launch_stream_e5m2(StreamParams& p, int scalar_type, int head_size, int num_
 // Upper bound of the workspace any stream launch on a device with `num_sms` SMs needs.
 int64_t stream_workspace_bytes(int num_sms, int head_size) {
   // warps per SM + (at most 4) CTAs per SM, two slots each
-  return (int64_t)2 * num_sms * (kMaxWarpsPerSm + 4) * slot_floats(head_size) *
-         (int64_t)sizeof(float);
+  return kCounterBytes + (int64_t)2 * num_sms * (kMaxWarpsPerSm + 4) * slot_floats(head_size) *
+                             (int64_t)sizeof(float);
 }
 
 bool stream_supported(const void* query, const void* key_cache, const void* value_cache,
@@ -1450,7 +1449,8 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
   p.lse = lse;
   p.lse_seq_stride = lse_seq_stride;
   p.lse_head_stride = lse_head_stride;
-  p.ws = reinterpret_cast<float*>(workspace);
+  p.counters = reinterpret_cast<int*>(workspace);
+  p.ws = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + kCounterBytes);
   p.q = query;
   p.k_cache = key_cache;
   p.v_cache = value_cache;

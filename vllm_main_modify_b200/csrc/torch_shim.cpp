@@ -21,6 +21,8 @@
 
 #include <memory>
 #include <optional>
+#include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -59,12 +61,30 @@ void check_cache_dtype(const torch::Tensor& cache, const torch::Tensor& ref, int
   }
 }
 
-// Scratch of the stream kernel, from torch's caching allocator: stream-ordered reuse and
-// CUDA-graph capture (private pool) are handled by the allocator.
+// Scratch of the stream kernel: ONE workspace per (device, stream), allocated on first use,
+// zero-filled once (the ticket counters in its header, include/b200_paged_attn.h) and kept -- no
+// allocator round trip per call, and a CUDA-graph capture sees the same pointer in every replay.
+// A call on another stream (a capture stream included) gets its own workspace, so concurrent
+// streams never share counters or slots.  Sized for the largest head size (256), so every shape
+// can use it.
+torch::Tensor cached_workspace(const torch::Tensor& query) {
+  static std::mutex mu;
+  static std::map<std::pair<int, cudaStream_t>, torch::Tensor> cache;
+  const int dev = query.get_device();
+  const cudaStream_t stream = at::cuda::getCurrentCUDAStream(dev);
+  std::lock_guard<std::mutex> lock(mu);
+  auto it = cache.find({dev, stream});
+  if (it != cache.end()) return it->second;
+  const at::cuda::OptionalCUDAGuard guard(device_of(query));
+  const int64_t bytes = b200pa_paged_attention_workspace_bytes(256);
+  torch::Tensor ws = at::zeros({bytes}, query.options().dtype(at::kByte));
+  cache.emplace(std::make_pair(dev, stream), ws);
+  return ws;
+}
+
 torch::Tensor attention_workspace(const torch::Tensor& query) {
   if (b200pa_get_impl() == B200PA_IMPL_GENERIC) return torch::Tensor();
-  const int64_t bytes = b200pa_paged_attention_workspace_bytes((int)query.size(2));
-  return at::empty({bytes}, query.options().dtype(at::kByte));
+  return cached_workspace(query);
 }
 
 void paged_attention_v1(torch::Tensor& out, torch::Tensor& query, torch::Tensor& key_cache,
@@ -305,8 +325,7 @@ void paged_attention_flash(torch::Tensor& out, const std::optional<torch::Tensor
   const at::cuda::OptionalCUDAGuard device_guard(device_of(query));
   const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
   const float* alibi = alibi_slopes ? reinterpret_cast<const float*>(alibi_slopes->data_ptr()) : nullptr;
-  const int64_t ws_bytes = b200pa_paged_attention_workspace_bytes((int)query.size(2));
-  const torch::Tensor ws = at::empty({ws_bytes}, query.options().dtype(at::kByte));
+  const torch::Tensor ws = cached_workspace(query);
   check_status(b200pa_paged_attention_flash(
       out.data_ptr(), lse_ptr, ls0, ls1, query.data_ptr(), kp, vp, kst, vst, sp,
       key_cache.data_ptr(), value_cache.data_ptr(), (int)query.size(0), (int)query.size(1),

@@ -72,15 +72,6 @@ enum {
   B200PA_ERR_CUDA = 3         /* CUDA runtime error (no device, launch failure) */
 };
 
-/* which kernel family b200pa_paged_attention_v1/v2 may use (tests, A/B runs) */
-enum {
-  B200PA_IMPL_AUTO = 0,    /* stream kernel when the shape is covered and a workspace is given,
-                              else generic */
-  B200PA_IMPL_GENERIC = 1, /* SIMT kernel, whole reference domain, no workspace */
-  B200PA_IMPL_STREAM = 2   /* persistent stream-K tensor-core kernel (v1 and v2); error if the
-                              shape is not covered or no workspace is given */
-};
-
 int b200pa_abi_version(void);
 const char* b200pa_last_error(void);
 
@@ -88,9 +79,9 @@ const char* b200pa_last_error(void);
  * (DISPATCH_BY_KV_CACHE_DTYPE, quant_utils.cuh:545-582). */
 int b200pa_kv_dtype_from_string(const char* kv_cache_dtype);
 
-/* Process-wide override of the kernel family (default B200PA_IMPL_AUTO). */
-void b200pa_set_impl(int impl);
-int b200pa_get_impl(void);
+/* (The process-wide test hooks -- kernel-family override, tuning variant, in-kernel trace --
+ * are NOT part of this ABI: include/b200_paged_attn_testing.h, compiled in only with
+ * -DB200PA_TESTING=1.) */
 /* Number of kernels launched by this library so far in this process. */
 uint64_t b200pa_launch_count(void);
 

@@ -12,8 +12,11 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 HEADER = os.path.join(ROOT, "include", "b200_paged_attn.h")
 
 
-def _declared_symbols():
-    src = open(HEADER).read()
+TESTING_HEADER = os.path.join(ROOT, "include", "b200_paged_attn_testing.h")
+
+
+def _declared_symbols(header=HEADER):
+    src = open(header).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
     return sorted(set(re.findall(r"\b(b200pa_[a-z0-9_]+)\s*\(", src)))
 
@@ -29,6 +32,13 @@ def test_library_loads_and_exports_every_declared_symbol():
     assert sorted(_native.C_ABI_SYMBOLS) == declared
     m = re.search(r"#define B200PA_ABI_VERSION (\d+)", open(HEADER).read())
     assert lib.b200pa_abi_version() == int(m.group(1))
+    # the test hooks live in their own header, outside the product ABI
+    hooks = _declared_symbols(TESTING_HEADER)
+    assert sorted(_native.TESTING_SYMBOLS) == hooks
+    assert not set(hooks) & set(declared)
+    if _native.has_testing_hooks():
+        for sym in hooks:
+            assert hasattr(lib, sym), sym
 
 
 def test_host_only_entry_points_work_without_a_gpu():
@@ -39,7 +49,7 @@ def test_host_only_entry_points_work_without_a_gpu():
     assert f(b"int8") == -1
     lib.b200pa_paged_attention_workspace_bytes.restype = ctypes.c_int64
     assert lib.b200pa_paged_attention_workspace_bytes(128) > 0
-    assert lib.b200pa_get_impl() == _native.IMPL_AUTO
+    assert _native.get_impl() == _native.IMPL_AUTO
     assert isinstance(_native.launch_count(), int)
 
 

@@ -12,7 +12,7 @@ SHIM_PATH = os.path.join(_HERE, "_b200pa_torch.so")
 # every symbol include/b200_paged_attn.h declares
 C_ABI_SYMBOLS = (
     "b200pa_abi_version", "b200pa_last_error", "b200pa_kv_dtype_from_string",
-    "b200pa_set_impl", "b200pa_get_impl", "b200pa_launch_count",
+    "b200pa_launch_count",
     "b200pa_paged_attention_workspace_bytes",
     "b200pa_paged_attention_v1", "b200pa_paged_attention_v2", "b200pa_paged_attention_lse",
     "b200pa_decode_step", "b200pa_paged_attention_flash",
@@ -23,6 +23,10 @@ C_ABI_SYMBOLS = (
     "b200pa_convert_fp8",
     "b200pa_get_max_shared_memory_per_block_device_attribute",
 )
+
+# test hooks (include/b200_paged_attn_testing.h): present when built with -DB200PA_TESTING=1
+TESTING_SYMBOLS = ("b200pa_set_impl", "b200pa_get_impl", "b200pa_testing_set_stream_tune",
+                   "b200pa_testing_set_trace")
 
 IMPL_AUTO, IMPL_GENERIC, IMPL_STREAM = 0, 1, 2
 
@@ -81,12 +85,29 @@ def load(register_vllm_namespaces: bool = True):
     return torch.ops.b200pa
 
 
+def has_testing_hooks() -> bool:
+    return hasattr(c_lib(), "b200pa_set_impl")
+
+
 def set_impl(impl: int) -> None:
+    """Test hook: force one kernel family (needs a -DB200PA_TESTING=1 build)."""
     c_lib().b200pa_set_impl(int(impl))
 
 
 def get_impl() -> int:
-    return int(c_lib().b200pa_get_impl())
+    return int(c_lib().b200pa_get_impl()) if has_testing_hooks() else IMPL_AUTO
+
+
+def set_stream_tune(tune: int) -> None:
+    """Test hook: alternative launch shape of the stream kernel (0 = default)."""
+    c_lib().b200pa_testing_set_stream_tune(int(tune))
+
+
+def set_trace(device_ptr: int, nbytes: int) -> None:
+    """Test hook: arm (or, with 0, disarm) the in-kernel phase trace of the stream kernel."""
+    lib = c_lib()
+    lib.b200pa_testing_set_trace.argtypes = [ctypes.c_void_p, ctypes.c_int64]
+    lib.b200pa_testing_set_trace(ctypes.c_void_p(device_ptr or None), int(nbytes))
 
 
 def launch_count() -> int:

@@ -38,9 +38,11 @@ CU_SOURCES = [("c_abi.cu", [], "c_abi.o"), ("cache_kernels.cu", [], "cache_kerne
               ("paged_attention_stream.cu", ["-DSTREAM_PART=3"], "paged_attention_stream_other.o"),
               ("paged_attention_stream.cu", ["-DSTREAM_PART=4"], "paged_attention_stream_e5m2.o"),
               ("merge_attn_states.cu", [], "merge_attn_states.o"), ("block_ops.cu", [], "block_ops.o")]
+# test hooks of include/b200_paged_attn_testing.h: compiled in unless B200PA_TESTING=0 is set
+TESTING = "-DB200PA_TESTING=" + ("0" if os.environ.get("B200PA_TESTING") == "0" else "1")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
               "-Xcompiler", "-fPIC", "-ccbin", HOST_CXX, "--expt-relaxed-constexpr",
-              "-Xptxas", "-v", "-Wno-deprecated-gpu-targets"]
+              "-Xptxas", "-v", "-Wno-deprecated-gpu-targets", TESTING]
 
 
 def _digest(paths, extra=""):
@@ -54,6 +56,7 @@ def _digest(paths, extra=""):
 def _headers():
     hs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
     hs.append(os.path.join(ROOT, "include", "b200_paged_attn.h"))
+    hs.append(os.path.join(ROOT, "include", "b200_paged_attn_testing.h"))
     return hs
 
 
@@ -104,12 +107,12 @@ def build_shim(verbose: bool = False) -> str:
     tdir = os.path.dirname(torch.__file__)
     src = os.path.join(CSRC, "torch_shim.cpp")
     os.makedirs(BUILD, exist_ok=True)
-    key = _digest([src] + _headers(), torch.__version__)
+    key = _digest([src] + _headers(), torch.__version__ + TESTING)
     stamp = os.path.join(BUILD, "shim.sha1")
     if os.path.exists(SHIM) and os.path.exists(stamp) and open(stamp).read() == key:
         return SHIM
     abi = int(torch._C._GLIBCXX_USE_CXX11_ABI)
-    cmd = [HOST_CXX, "-O2", "-std=c++17", "-fPIC", "-shared", "-w",
+    cmd = [HOST_CXX, "-O2", "-std=c++17", "-fPIC", "-shared", "-w", TESTING,
            f"-D_GLIBCXX_USE_CXX11_ABI={abi}",
            f"-I{tdir}/include", f"-I{tdir}/include/torch/csrc/api/include",
            f"-I{sysconfig.get_paths()['include']}", f"-I{CUDA_HOME}/include",

@@ -52,7 +52,6 @@ int launch_cp_gather_cache(const void*, void*, const int32_t*, const int32_t*, i
                            cudaStream_t);
 
 static thread_local char g_err[512] = "";
-static std::atomic<int> g_impl{B200PA_IMPL_AUTO};
 static std::atomic<uint64_t> g_launches{0};
 
 int set_error(int code, const char* fmt, ...) {
@@ -72,30 +71,42 @@ int check_launch(const char* what) {
 
 void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
 
+// SM count of the CURRENT device (the persistent grid is sized from it), cached per ordinal.
 static int num_sms() {
-  static int cached = 0;
-  if (cached == 0) {
-    int dev = 0, n = 0;
-    if (cudaGetDevice(&dev) == cudaSuccess &&
-        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
-      cached = n;
-    else
+  static std::atomic<int> cached[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  int n = cached[dev].load(std::memory_order_relaxed);
+  if (n == 0) {
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
       return 148;
+    cached[dev].store(n, std::memory_order_relaxed);
   }
-  return cached;
+  return n;
 }
 
-// development knob: B200PA_STREAM_TUNE=<n> selects an alternative (stages, pages/stage,
-// CTAs/SM) instantiation of the stream kernel (see launch_stream)
+// test hooks (include/b200_paged_attn_testing.h); constants in a build without them
+#if B200PA_TESTING
+static std::atomic<int> g_impl{B200PA_IMPL_AUTO};
+static std::atomic<int> g_tune{-1};
+static std::atomic<void*> g_trace{nullptr};
+static int current_impl() { return g_impl.load(std::memory_order_relaxed); }
 static int stream_tune() {
-  static int cached = -1;
-  if (cached < 0) {
+  int t = g_tune.load(std::memory_order_relaxed);
+  if (t < 0) {
     const char* e = getenv("B200PA_STREAM_TUNE");
-    cached = e ? atoi(e) : 0;
-    if (cached < 0) cached = 0;
+    t = e ? atoi(e) : 0;
+    if (t < 0) t = 0;
+    g_tune.store(t, std::memory_order_relaxed);
   }
-  return cached;
+  return t;
 }
+void* testing_trace_buffer() { return g_trace.load(std::memory_order_relaxed); }
+#else
+static int current_impl() { return B200PA_IMPL_AUTO; }
+static int stream_tune() { return 0; }
+void* testing_trace_buffer() { return nullptr; }
+#endif
 
 static bool head_size_ok(int h) {
   switch (h) {  // paged_attention_v1.cu:90-124 of the reference
@@ -159,7 +170,7 @@ static int paged_attention_common(
   if (bsp.enabled && bs_block_size <= 0)
     return set_error(B200PA_ERR_INVALID, "blocksparse_block_size must be positive");
 
-  const int impl = g_impl.load();
+  const int impl = current_impl();
   const bool stream_ok =
       stream_supported(query, key_cache, value_cache, num_heads, num_kv_heads, head_size,
                        block_size, q_stride, kv_block_stride, kv_head_stride, scalar_type,
@@ -217,8 +228,14 @@ int b200pa_kv_dtype_from_string(const char* s) {
   return -1;
 }
 
+#if B200PA_TESTING
 void b200pa_set_impl(int impl) { g_impl.store(impl); }
 int b200pa_get_impl(void) { return g_impl.load(); }
+void b200pa_testing_set_stream_tune(int tune) { g_tune.store(tune < 0 ? 0 : tune); }
+void b200pa_testing_set_trace(void* device_buffer, int64_t bytes) {
+  g_trace.store(bytes >= 256 ? device_buffer : nullptr);
+}
+#endif
 uint64_t b200pa_launch_count(void) { return g_launches.load(); }
 
 int64_t b200pa_paged_attention_workspace_bytes(int head_size) {

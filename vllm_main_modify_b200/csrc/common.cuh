@@ -11,6 +11,11 @@
 #include <type_traits>
 
 #include "../../include/b200_paged_attn.h"
+#include "../../include/b200_paged_attn_testing.h"
+
+#ifndef B200PA_TESTING
+#define B200PA_TESTING 0
+#endif
 
 namespace b200pa {
 
@@ -129,4 +134,5 @@ namespace b200pa {
 int set_error(int code, const char* fmt, ...);
 int check_launch(const char* what);
 void count_launch(int n = 1);
+void* testing_trace_buffer();   // nullptr unless b200pa_testing_set_trace armed one
 }  // namespace b200pa

@@ -44,6 +44,13 @@
 //    steady state has no shuffles, only a warp vote.
 #include "common.cuh"
 
+// Development builds only (tools/ablate.sh): B200PA_ABLATE removes one ingredient of the main loop
+// so that its share of the step's time and POWER can be measured (results are then wrong):
+// 1 no fp8 -> f16 conversion, 2 no MMA, 4 no ldmatrix, 8 no exp2.  0 in every product build.
+#ifndef B200PA_ABLATE
+#define B200PA_ABLATE 0
+#endif
+
 namespace b200pa {
 
 namespace {
@@ -102,9 +109,13 @@ __device__ __forceinline__ void cp_async_mbar_arrive(uint32_t bar) {
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], uint32_t addr) {
+#if B200PA_ABLATE & 4
+  r[0] = addr; r[1] = addr + 1; r[2] = addr + 2; r[3] = addr + 3;
+#else
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
                : "r"(addr));
+#endif
 }
 __device__ __forceinline__ void ldmatrix_x4_trans(uint32_t (&r)[4], uint32_t addr) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
@@ -125,6 +136,11 @@ __device__ __forceinline__ uint32_t movmatrix_trans(uint32_t a) {
 template <bool BF16>
 __device__ __forceinline__ void mma16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0,
                                          uint32_t b1) {
+#if B200PA_ABLATE & 2
+  asm volatile("" ::"r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  d[0] += 1.f;
+  return;
+#endif
   if constexpr (BF16) {
     asm volatile(
         "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, "
@@ -140,9 +156,17 @@ __device__ __forceinline__ void mma16816(float (&d)[4], const uint32_t (&a)[4], 
   }
 }
 __device__ __forceinline__ float ex2(float x) {
+#if B200PA_ABLATE & 8
+  return x;
+#endif
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
 }
 template <bool BF16>
 __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
@@ -163,6 +187,10 @@ __device__ __forceinline__ void fp8x4_to_f16x2x2(uint32_t w, uint32_t& lo, uint3
     asm("prmt.b32 %0, %1, 0, 0x3424;" : "=r"(hi) : "r"(w));
     return;
   }
+#if B200PA_ABLATE & 1
+  lo = w; hi = w;
+  return;
+#endif
   asm("{\n"
       ".reg .b16 l, h;\n"
       "mov.b32 {l, h}, %2;\n"
@@ -183,6 +211,11 @@ struct StreamParams {
   int64_t lse_seq_stride, lse_head_stride;
   float* ws;           // workspace slots: 2 per worker + 2 per CTA, slot_floats(D) floats each
   int* counters;       // workspace header: one ticket counter per CTA, zero between launches
+  // development aid (b200pa_testing_set_trace, nullptr otherwise): 32 %globaltimer stamps per CTA
+  // -- 0 entry, 1 dependency wait over, 2 stage count known, 3 span located, 4 first copies
+  // issued, 5 query loaded, 8+w first stage landed (warp w), 16+w main loop over (warp w),
+  // 24 every warp over, 25 in-CTA merge over, 26 ticket taken, 27 exit
+  unsigned long long* trace;
   const void* q;
   const void* k_cache;
   const void* v_cache;
@@ -380,15 +413,22 @@ paged_attention_stream_kernel(const StreamParams p) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int r = lane >> 2, q4 = lane & 3;
   const int vheads = p.num_kv_heads * p.h_tiles;
+#define TRACE(k) do { if (p.trace != nullptr && threadIdx.x == 0) \
+    p.trace[(size_t)blockIdx.x * 32 + (k)] = globaltimer_ns(); } while (0)
+#define TRACE_W(k) do { if (p.trace != nullptr && lane == 0) \
+    p.trace[(size_t)blockIdx.x * 32 + (k) + warp] = globaltimer_ns(); } while (0)
+  TRACE(0);
 
   // Launched with programmatic stream serialisation: this CTA may have been scheduled while the
   // previous kernel of the stream (typically reshape_and_cache writing this step's token) was
   // still running.  Nothing produced by earlier kernels -- seq_lens, q, the cache -- is read
   // before this wait; what overlaps is the launch itself.
   asm volatile("griddepcontrol.wait;" ::: "memory");
+  TRACE(1);
 
   // ---------------------------------------------------------------- my span
   const long long Ttot = total_stages<PPS>(p.seq_lens, p.num_seqs, lane) * vheads;
+  TRACE(2);
   const long long W = min((long long)p.num_workers, Ttot);
   const long long w = (long long)blockIdx.x * NW + warp;
   // let the next kernel of the stream (the next layer's decode step) be scheduled as soon as SM
@@ -416,6 +456,7 @@ paged_attention_stream_kernel(const StreamParams p) {
     pc.left = (int)(u1 - u0);
     cursor_open(pc, loc.st);
   }
+  TRACE(3);
   Cursor cc = pc;
   int piece_begin = cc.st;
   int it = 0;                               // stages consumed
@@ -513,6 +554,7 @@ paged_attention_stream_kernel(const StreamParams p) {
   };
 #pragma unroll 1
   for (int i = 0; i < STAGES && producing; ++i) produce();
+  TRACE(4);
 
   // ---------------------------------------------------------------- consumer state
   uint32_t qb[KSTEPS][2];       // Q^T B-fragments: head r, k-step ks
@@ -679,6 +721,7 @@ paged_attention_stream_kernel(const StreamParams p) {
   };
 
   begin_piece();
+  TRACE(5);
 
   // ---------------------------------------------------------------- main loop
 #pragma unroll 1
@@ -696,6 +739,7 @@ paged_attention_stream_kernel(const StreamParams p) {
     const int s = i % STAGES;
     const uint32_t sbase = ring_u32 + s * STAGE_BYTES;
     mbar_wait(bar0 + 8 * s, (i / STAGES) & 1);
+    if (i == 0) TRACE_W(8);
 
     // ---- fused cache write: the stage that ends the sequence holds position len - 1, whose
     // K/V come from this step's key/value rows (in registers since begin_piece, quantised here
@@ -948,6 +992,7 @@ paged_attention_stream_kernel(const StreamParams p) {
     __syncwarp();
     if (producing) produce();
   }
+  TRACE_W(16);
   }  // w < W
 
   // ---------------------------------------------------------------- in-CTA merge
@@ -977,6 +1022,7 @@ paged_attention_stream_kernel(const StreamParams p) {
     }
   }
   __syncthreads();   // also orders the warps' global slot stores before the loads below
+  TRACE(24);
   {
     constexpr int SF = slot_floats(D);
     const float* const my_slots = p.ws + (size_t)2 * ((size_t)blockIdx.x * NW) * SF;
@@ -1103,6 +1149,7 @@ paged_attention_stream_kernel(const StreamParams p) {
   // (attention_kernels.cuh:560-664) -- pieces dealt round-robin to the warps, which meet in
   // shared memory (the ring is free by now) in warp order -- and leaves the counter at zero.
   __syncthreads();
+  TRACE(25);
   if (threadIdx.x < 2 && pend_s[threadIdx.x][0]) {
     int* pd = pend_s[threadIdx.x];
     const int ticket = atomicAdd(p.counters + pd[1], 1);
@@ -1110,6 +1157,7 @@ paged_attention_stream_kernel(const StreamParams p) {
     if (pd[5]) atomicExch(p.counters + pd[1], 0);
   }
   __syncthreads();
+  TRACE(26);
 #pragma unroll 1
   for (int k = 0; k < 2; ++k) {
     if (!pend_s[k][0] || !pend_s[k][5]) continue;     // CTA-uniform
@@ -1204,6 +1252,9 @@ paged_attention_stream_kernel(const StreamParams p) {
     }
     __syncthreads();   // acc_s is reused by the CTA's other pending item
   }
+  TRACE(27);
+#undef TRACE
+#undef TRACE_W
 }
 
 // ---------------------------------------------------------------------------------------
@@ -1450,6 +1501,7 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
   p.lse_seq_stride = lse_seq_stride;
   p.lse_head_stride = lse_head_stride;
   p.counters = reinterpret_cast<int*>(workspace);
+  p.trace = reinterpret_cast<unsigned long long*>(testing_trace_buffer());
   p.ws = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + kCounterBytes);
   p.q = query;
   p.k_cache = key_cache;

@@ -1,14 +1,14 @@
 set -u
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -x -q 2>&1 | tail -15 > gpurun_out/r02d_pytest.txt; cat gpurun_out/r02d_pytest.txt
-python tools/ktrace.py --configs cfg1,cfg2 --tp 1 > gpurun_out/r02d_ktrace_tp1.jsonl 2> gpurun_out/r02d_ktrace.err
-python tools/ktrace.py --configs cfg5,cfg4 --tp 8 >> gpurun_out/r02d_ktrace_tp8.jsonl 2>> gpurun_out/r02d_ktrace.err
-tail -3 gpurun_out/r02d_ktrace.err
-for v in tree no_cvt no_mma no_ldmatrix no_exp only_copy; do
-  if [ $v = tree ]; then unset B200PA_PKG_ROOT; else export B200PA_PKG_ROOT=_ab/$v; fi
-  B200PA_AB_LABEL=$v python tools/powerprobe.py --config cfg4 --seconds 4 >> gpurun_out/r02d_powerprobe.jsonl 2>> gpurun_out/r02d_powerprobe.err
-  sleep 3
+T=r02e
+python -m pytest tests -m gpu -x -q 2>&1 | tail -15 > gpurun_out/${T}_pytest.txt; cat gpurun_out/${T}_pytest.txt
+tools/gpu_job.sh $T smoke
+python bench.py > gpurun_out/${T}_bench_cfg4.json 2> gpurun_out/${T}_bench_cfg4.err; echo "bench rc=$?"; tail -3 gpurun_out/${T}_bench_cfg4.err; cut -c1-3000 gpurun_out/${T}_bench_cfg4.json
+python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${T}_bench_reference_arm.json 2>> gpurun_out/${T}_bench_cfg4.err; cut -c1-600 gpurun_out/${T}_bench_reference_arm.json
+for t in 0 1 2 3 4 5 6 7; do
+  python tools/powerprobe.py --config cfg4 --seconds 3 --tune $t >> gpurun_out/${T}_powerprobe_tunes.jsonl 2>> gpurun_out/${T}_powerprobe.err
+  sleep 2
 done
-unset B200PA_PKG_ROOT
-cut -c1-420 gpurun_out/r02d_powerprobe.jsonl
-tail -3 gpurun_out/r02d_powerprobe.err
+cut -c1-330 gpurun_out/${T}_powerprobe_tunes.jsonl
+tail -3 gpurun_out/${T}_powerprobe.err
+tools/gpu_job.sh $T list cfg4

@@ -26,6 +26,9 @@
  *   b200pa_merge_attn_states        csrc/attention/merge_attn_states.cu:172-180
  *                                   (launcher :131-170; schema csrc/torch_bindings.cpp:80-87)
  *   b200pa_correct_attn_out         vllm/attention/ops/common.py:86-116 (Triton kernel :9-68)
+ *   b200pa_prefill_attention        flash_attn_varlen_func with block_table as called by
+ *                                   vllm/v1/attention/backends/cpu_attn.py:584-612; Triton
+ *                                   context_attention_fwd (vllm/attention/ops/paged_attn.py:200-242)
  *   b200pa_paged_attention_lse      no reference kernel: decode + log-sum-exp, what
  *                                   AttentionImpl.can_return_lse_for_decode
  *                                   (vllm/attention/backends/abstract.py:115-138) asks of a
@@ -58,7 +61,7 @@
 extern "C" {
 #endif
 
-#define B200PA_ABI_VERSION 7
+#define B200PA_ABI_VERSION 8
 
 /* scalar_t of query / out / key / value (reference: VLLM_DISPATCH_FLOATING_TYPES) */
 enum { B200PA_F32 = 0, B200PA_F16 = 1, B200PA_BF16 = 2 };
@@ -221,6 +224,33 @@ int b200pa_paged_attention_flash(
     int64_t q_stride, int64_t block_stride, int64_t page_stride, int64_t head_stride,
     int scalar_type, int kv_dtype, const float* k_scale, const float* v_scale,
     void* workspace, int64_t workspace_bytes, void* stream);
+
+/*
+ * Causal attention of query CHUNKS over the paged cache -- prefill, chunked prefill and
+ * multi-token (speculative) decode; the second kernel the reference's paged backends hand every
+ * batch with more than one query token per sequence to: flash_attn_varlen_func(out, query,
+ * key_cache, value_cache, cu_seqlens_q, cu_seqlens_kv, ..., causal, block_table, alibi_slopes) in
+ * vllm/v1/attention/backends/cpu_attn.py:584-612, context_attention_fwd behind
+ * PagedAttention.forward_prefix (vllm/attention/ops/paged_attn.py:200-242).
+ *   query, out [num_tokens, num_heads, head_size] scalar_t (token strides q_stride / out_stride,
+ *   heads dense); lse [num_tokens, num_heads] fp32 natural-log sum-exp or NULL;
+ *   query_start_loc[num_seqs + 1] int32 (tokens of sequence b: [qsl[b], qsl[b+1]));
+ *   seq_lens[num_seqs] int32 = context + new tokens; the K/V of the new tokens are already in the
+ *   cache (write it first: b200pa_reshape_and_cache).  Query token i of sequence b sits at
+ *   position ctx + i, ctx = seq_lens[b] - q_len, and attends cache positions [0, ctx + i].
+ *   key_cache / value_cache: the x-packed layout of b200pa_paged_attention_v1.
+ *   heads_per_tile: query heads of one kv head stacked per token in a 64-row tile (must divide
+ *   num_heads / num_kv_heads); 0 = choose (the whole group when max_query_len < 64, else 1).
+ * Domain: head_size 32 / 64 / 96 / 128 / 192 / 256, block_size 16 / 32, f16 / bf16, kv auto /
+ * fp8_e4m3 / fp8_e5m2; 16-byte aligned query rows.  No workspace.
+ */
+int b200pa_prefill_attention(
+    void* out, float* lse, const void* query, const void* key_cache, const void* value_cache,
+    int num_seqs, int num_heads, int num_kv_heads, int head_size, int block_size, float scale,
+    const int32_t* block_tables, int max_num_blocks_per_seq, const int32_t* query_start_loc,
+    const int32_t* seq_lens, int max_query_len, const float* alibi_slopes, int64_t q_stride,
+    int64_t out_stride, int64_t kv_block_stride, int64_t kv_head_stride, int scalar_type,
+    int kv_dtype, const float* k_scale, const float* v_scale, int heads_per_tile, void* stream);
 
 /*
  * output, prefix_output, suffix_output [num_tokens, num_heads, head_size] scalar_t, dense,

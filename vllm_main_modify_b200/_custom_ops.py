@@ -176,6 +176,34 @@ def paged_attention_flash(
         block_tables, seq_lens, max_seq_len, alibi_slopes, kv_cache_dtype, k_scale, v_scale)
 
 
+def prefill_attention(
+    out: torch.Tensor,
+    lse: Optional[torch.Tensor],
+    query: torch.Tensor,
+    key_cache: torch.Tensor,
+    value_cache: torch.Tensor,
+    scale: float,
+    block_tables: torch.Tensor,
+    query_start_loc: torch.Tensor,
+    seq_lens: torch.Tensor,
+    max_query_len: int,
+    alibi_slopes: Optional[torch.Tensor],
+    kv_cache_dtype: str,
+    k_scale: torch.Tensor,
+    v_scale: torch.Tensor,
+    heads_per_tile: int = 0,
+) -> None:
+    """Causal attention of query chunks (prefill / chunked prefill / multi-token decode) over the
+    paged cache, whose K/V already hold the chunk -- what the reference's paged backends call
+    ``flash_attn_varlen_func(..., block_table)`` for (``cpu_attn.py:584-612``).  ``query`` /
+    ``out`` ``[num_tokens, num_heads, head_size]``, ``query_start_loc`` ``[num_seqs + 1]`` int32,
+    ``seq_lens`` ``[num_seqs]`` int32 (context + new tokens), ``lse`` optional
+    ``[num_tokens, num_heads]`` fp32."""
+    _ops.prefill_attention(out, lse, query, key_cache, value_cache, scale, block_tables,
+                           query_start_loc, seq_lens, max_query_len, alibi_slopes,
+                           kv_cache_dtype, k_scale, v_scale, heads_per_tile)
+
+
 def correct_attn_out(out: torch.Tensor, lses: torch.Tensor, cp_rank: int,
                      ctx=None) -> "tuple[torch.Tensor, torch.Tensor]":
     """``vllm/attention/ops/common.py:86-116`` (``ctx`` is the reference's Triton cache, unused):

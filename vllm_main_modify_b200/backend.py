@@ -9,13 +9,18 @@ meaning and error behaviour, so that registering this class as
 (``vllm/attention/layer.py:101,184-192``) or through a platform plugin's
 ``get_attn_backend_cls`` is a pure wiring change.
 
-It is deliberately free of ``import vllm``: the classes below are structural
-twins of the ABCs, not subclasses, so the package works (and is tested) without
-the reference installed.  Scope: decode (one query token per sequence).  Batches
-with longer queries (prefill / chunked prefill / mixed), which the reference's
-paged-attention backends hand to a second kernel (``cpu_attn.py:584-612``), are
-served by the same decode kernel, one single-query attention per token
-(:func:`expand_queries_to_sequences`): correct, O(T x context) -- SURVEY.md 8(f) row 1.
+It is deliberately free of ``import vllm`` at import time: the classes below are structural
+twins of the ABCs, so the package works (and is tested) without the reference installed;
+:func:`bind_abcs` / :func:`bind_vllm` return real subclasses of ``AttentionBackend`` /
+``AttentionImpl`` when the reference's (or an installed vLLM's) ``abstract`` module is
+importable.  Batches are split like the reference's paged backends split them
+(``cpu_attn.py:584-638``): single-token sequences go to the decode kernel
+(``decode_step`` / ``paged_attention_v1``), sequences with longer queries (prefill, chunked
+prefill) to the causal chunk kernel over the paged cache (``ops.prefill_attention``,
+csrc/paged_prefill.cu); the metadata builder reorders the batch decode-first
+(``reorder_batch``, ``v1/attention/backends/utils.py:774-834``) and records the split.
+Head sizes / block sizes the chunk kernel does not serve fall back to one single-query
+attention per token (:func:`expand_queries_to_sequences`): correct, O(T x context).
 """
 from __future__ import annotations
 
@@ -51,10 +56,19 @@ class B200PagedAttentionMetadata:
     block_table: torch.Tensor         # [num_seqs, max_blocks_per_seq] int32
     slot_mapping: torch.Tensor        # [num_actual_tokens] int64, <0 = skip
     query_start_loc: Optional[torch.Tensor] = None  # [num_seqs + 1] int32
+    # the decode-first split of a reordered batch (``split_decodes_and_prefills``,
+    # v1/attention/backends/utils.py:721-771): sequences [0, num_decodes) have one query token
+    # each, the remaining num_prefills longer chunks.  None: unknown (not reordered).
+    num_decodes: Optional[int] = None
+    num_prefills: Optional[int] = None
+    num_prefill_tokens: Optional[int] = None
+    max_decode_seq_len: Optional[int] = None        # host copy of seq_lens[:num_decodes].max()
 
     @property
     def num_decode_tokens(self) -> int:
-        return self.num_actual_tokens if self.max_query_len <= 1 else 0
+        if self.max_query_len <= 1:
+            return self.num_actual_tokens
+        return self.num_decodes if self.num_decodes is not None else 0
 
 
 def expand_queries_to_sequences(meta: "B200PagedAttentionMetadata"):
@@ -98,14 +112,31 @@ class B200PagedAttentionMetadataBuilder:
         self.vllm_config = vllm_config
         self.device = device
 
+    def reorder_batch(self, input_batch: Any, scheduler_output: Any) -> bool:
+        """Decode-first order with the fewest swaps: what the runner does for a builder with a
+        ``reorder_batch_threshold`` (``reorder_batch_to_split_decodes_and_prefills``,
+        ``v1/attention/backends/utils.py:774-834``; the CPU backend's own ``reorder_batch``,
+        ``cpu_attn.py:346-388``, is the mirror image).  A request is a decode when it has at most
+        ``reorder_batch_threshold`` scheduled tokens.  Returns True if anything moved."""
+        sched = scheduler_output.num_scheduled_tokens
+        is_decode = [sched[rid] <= self.reorder_batch_threshold for rid in input_batch.req_ids]
+        num_decodes = sum(is_decode)
+        # decodes sitting behind the decode region, last first / prefills inside it, first first
+        late_decodes = [i for i in range(len(is_decode) - 1, num_decodes - 1, -1) if is_decode[i]]
+        early_prefills = [i for i in range(num_decodes) if not is_decode[i]]
+        assert len(late_decodes) == len(early_prefills)
+        for src, dst in zip(late_decodes, early_prefills):
+            input_batch.swap_states(dst, src)
+        return bool(late_decodes)
+
     def build(self, common_prefix_len: int, common_attn_metadata: Any,
               fast_build: bool = False) -> B200PagedAttentionMetadata:
         m = common_attn_metadata
         max_seq_len = getattr(m, "max_seq_len", None)
+        seq_lens_cpu = getattr(m, "seq_lens_cpu", None)
         if max_seq_len is None:
-            cpu = getattr(m, "seq_lens_cpu", None)
-            max_seq_len = int(cpu.max()) if cpu is not None else int(m.seq_lens.max())
-        return B200PagedAttentionMetadata(
+            max_seq_len = int(seq_lens_cpu.max()) if seq_lens_cpu is not None else int(m.seq_lens.max())
+        meta = B200PagedAttentionMetadata(
             num_actual_tokens=int(m.num_actual_tokens),
             max_query_len=int(m.max_query_len),
             seq_lens=m.seq_lens,
@@ -114,6 +145,20 @@ class B200PagedAttentionMetadataBuilder:
             slot_mapping=m.slot_mapping,
             query_start_loc=getattr(m, "query_start_loc", None),
         )
+        qsl_cpu = getattr(m, "query_start_loc_cpu", None)
+        if meta.max_query_len > 1 and qsl_cpu is not None:
+            # split_decodes_and_prefills (utils.py:721-771) on the host copy: the leading run of
+            # single-token sequences is the decode part
+            qlens = (qsl_cpu[1:] - qsl_cpu[:-1]).tolist()
+            nd = 0
+            while nd < len(qlens) and qlens[nd] <= self.reorder_batch_threshold:
+                nd += 1
+            meta.num_decodes = nd
+            meta.num_prefills = len(qlens) - nd
+            meta.num_prefill_tokens = meta.num_actual_tokens - int(qsl_cpu[nd])
+            if nd and seq_lens_cpu is not None:
+                meta.max_decode_seq_len = int(seq_lens_cpu[:nd].max())
+        return meta
 
     def build_for_cudagraph_capture(self, common_attn_metadata: Any) -> B200PagedAttentionMetadata:
         return self.build(0, common_attn_metadata)
@@ -237,11 +282,22 @@ class B200PagedAttentionImpl:
             self.alibi_slopes, layer._k_scale, layer._v_scale, output=out[:n])
         return output
 
+    # shapes the chunk kernel (csrc/paged_prefill.cu) serves; others fall back to the expansion
+    _PREFILL_HEAD_SIZES = (32, 64, 96, 128, 192, 256)
+
+    def _chunk_kernel_serves(self, query: torch.Tensor, block_size: int) -> bool:
+        return (self.head_size in self._PREFILL_HEAD_SIZES and block_size in (16, 32)
+                and query.dtype in (torch.float16, torch.bfloat16))
+
     def _forward_multi_query(self, layer, query, key, value, kv_cache, attn_metadata, output):
-        """Batches with more than one query token per sequence (prefill, chunked prefill, mixed):
-        write every new token, then one single-query attention per token (see
-        :func:`expand_queries_to_sequences`)."""
-        n = attn_metadata.num_actual_tokens
+        """Batches with more than one query token per sequence (prefill, chunked prefill, mixed),
+        split the way the reference's paged backends split them (``cpu_attn.py:584-638``): write
+        every new token, then the leading single-token sequences (a decode-first batch,
+        :meth:`B200PagedAttentionMetadataBuilder.reorder_batch`) on the decode kernel and the
+        chunks on the causal chunk kernel over the paged cache.  Without the split (a batch that
+        was not reordered) the chunk kernel takes every sequence: it is correct for any mix."""
+        m = attn_metadata
+        n = m.num_actual_tokens
         q = query.view(-1, self.num_heads, self.head_size)
         out = output.view(-1, self.num_heads, self.head_size)
         key_cache, value_cache = PagedAttention.split_kv_cache(kv_cache, self.num_kv_heads,
@@ -250,14 +306,34 @@ class B200PagedAttentionImpl:
             PagedAttention.write_to_paged_cache(
                 key.view(-1, self.num_kv_heads, self.head_size),
                 value.view(-1, self.num_kv_heads, self.head_size), key_cache, value_cache,
-                attn_metadata.slot_mapping, self.kv_cache_dtype, layer._k_scale, layer._v_scale)
+                m.slot_mapping, self.kv_cache_dtype, layer._k_scale, layer._v_scale)
         if self.alibi_slopes is not None and self.alibi_slopes.device != q.device:
             self.alibi_slopes = self.alibi_slopes.to(q.device)
-        bt_tok, sl_tok = expand_queries_to_sequences(attn_metadata)
-        PagedAttention.forward_decode(
-            q[:n], key_cache, value_cache, bt_tok, sl_tok, attn_metadata.max_seq_len,
-            self.kv_cache_dtype, self.num_kv_heads, self.scale, self.alibi_slopes,
-            layer._k_scale, layer._v_scale, output=out[:n])
+        if m.query_start_loc is None:
+            raise ValueError("batches with max_query_len > 1 need attn_metadata.query_start_loc")
+        if not self._chunk_kernel_serves(q, value_cache.shape[3]):
+            bt_tok, sl_tok = expand_queries_to_sequences(m)
+            PagedAttention.forward_decode(
+                q[:n], key_cache, value_cache, bt_tok, sl_tok, m.max_seq_len,
+                self.kv_cache_dtype, self.num_kv_heads, self.scale, self.alibi_slopes,
+                layer._k_scale, layer._v_scale, output=out[:n])
+            return output
+        num_seqs = m.query_start_loc.shape[0] - 1
+        nd = m.num_decodes or 0
+        if nd > 0:
+            # decode part: sequence b < nd is token b (a decode-first batch)
+            PagedAttention.forward_decode(
+                q[:nd], key_cache, value_cache, m.block_table[:nd], m.seq_lens[:nd],
+                m.max_decode_seq_len or m.max_seq_len, self.kv_cache_dtype, self.num_kv_heads,
+                self.scale, self.alibi_slopes, layer._k_scale, layer._v_scale, output=out[:nd])
+        if nd < num_seqs:
+            # chunk part: the kernel indexes tokens through query_start_loc, so the whole q / out
+            # go in with the tail of the per-sequence tensors (views, no copies)
+            from . import _custom_ops as ops
+            ops.prefill_attention(out[:n], None, q[:n], key_cache, value_cache, self.scale,
+                                  m.block_table[nd:], m.query_start_loc[nd:],
+                                  m.seq_lens[nd:num_seqs], m.max_query_len, self.alibi_slopes,
+                                  self.kv_cache_dtype, layer._k_scale, layer._v_scale)
         return output
 
     def fused_output_quant_supported(self, quant_key: Any) -> bool:
@@ -297,7 +373,8 @@ class B200PagedAttentionBackend:
 
     @staticmethod
     def get_kv_cache_stride_order() -> Tuple[int, ...]:
-        raise NotImplementedError
+        # (2, num_blocks, block_size * num_kv_heads * head_size) is allocated as it is indexed
+        return (0, 1, 2)
 
     @classmethod
     def full_cls_name(cls) -> Tuple[str, str]:
@@ -417,3 +494,33 @@ class B200FlashLayoutAttentionBackend(B200PagedAttentionBackend):
     @classmethod
     def get_supported_dtypes(cls) -> List[torch.dtype]:
         return [torch.float16, torch.bfloat16]
+
+
+# --------------------------------------------------------------------------------------------
+# Real subclasses of the reference's ABCs, on demand
+# --------------------------------------------------------------------------------------------
+def bind_abcs(abstract_module: Any, flash_layout: bool = False):
+    """``(Backend, Impl)`` as subclasses of ``abstract_module.AttentionBackend`` /
+    ``.AttentionImpl`` -- the reference's ``vllm/attention/backends/abstract.py:27-181`` (or an
+    installed vLLM's equivalent): what ``Attention(..., attn_backend=Backend)``
+    (``vllm/attention/layer.py:101,184-198``) and ``get_attn_backend_cls`` expect to receive.
+    The twins above implement every abstract method, so the subclasses add nothing but the base."""
+    backend_twin = B200FlashLayoutAttentionBackend if flash_layout else B200PagedAttentionBackend
+    impl_twin = backend_twin.get_impl_cls()
+    impl = type(impl_twin.__name__ + "Bound", (impl_twin, abstract_module.AttentionImpl), {})
+    backend = type(backend_twin.__name__ + "Bound", (backend_twin, abstract_module.AttentionBackend),
+                   {"get_impl_cls": staticmethod(lambda: impl)})
+    return backend, impl
+
+
+def bind_vllm(flash_layout: bool = False):
+    """:func:`bind_abcs` on whichever vLLM is importable: the reference's module path first, then
+    the one newer releases moved the ABCs to.  Raises ImportError when there is none."""
+    import importlib
+    err: Optional[Exception] = None
+    for name in ("vllm.attention.backends.abstract", "vllm.v1.attention.backend"):
+        try:
+            return bind_abcs(importlib.import_module(name), flash_layout)
+        except ImportError as exc:      # try the next layout
+            err = exc
+    raise ImportError(f"no vLLM attention ABCs importable: {err}")

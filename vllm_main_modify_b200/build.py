@@ -37,6 +37,10 @@ CU_SOURCES = [("c_abi.cu", [], "c_abi.o"), ("cache_kernels.cu", [], "cache_kerne
               ("paged_attention_stream.cu", ["-DSTREAM_PART=2"], "paged_attention_stream_bs32.o"),
               ("paged_attention_stream.cu", ["-DSTREAM_PART=3"], "paged_attention_stream_other.o"),
               ("paged_attention_stream.cu", ["-DSTREAM_PART=4"], "paged_attention_stream_e5m2.o"),
+              ("paged_prefill.cu", ["-DPREFILL_PART=0"], "paged_prefill.o"),
+              ("paged_prefill.cu", ["-DPREFILL_PART=1"], "paged_prefill_small.o"),
+              ("paged_prefill.cu", ["-DPREFILL_PART=2"], "paged_prefill_mid.o"),
+              ("paged_prefill.cu", ["-DPREFILL_PART=3"], "paged_prefill_256.o"),
               ("merge_attn_states.cu", [], "merge_attn_states.o"), ("block_ops.cu", [], "block_ops.o")]
 # test hooks of include/b200_paged_attn_testing.h: compiled in unless B200PA_TESTING=0 is set
 TESTING = "-DB200PA_TESTING=" + ("0" if os.environ.get("B200PA_TESTING") == "0" else "1")

@@ -346,6 +346,57 @@ void paged_attention_flash(torch::Tensor& out, const std::optional<torch::Tensor
 }
 
 // csrc/attention/merge_attn_states.cu:131-180 of the reference (same checks, same messages)
+// Causal attention of query chunks over the paged cache (b200pa_prefill_attention): what the
+// reference's paged backends call flash_attn_varlen_func(..., block_table) / context_attention_fwd
+// for (cpu_attn.py:584-612, paged_attn.py:200-242).  heads_per_tile = 0: the library chooses.
+void prefill_attention(torch::Tensor& out, const std::optional<torch::Tensor>& lse,
+                       torch::Tensor& query, torch::Tensor& key_cache, torch::Tensor& value_cache,
+                       double scale, torch::Tensor& block_tables, torch::Tensor& query_start_loc,
+                       torch::Tensor& seq_lens, int64_t max_query_len,
+                       const std::optional<torch::Tensor>& alibi_slopes,
+                       const std::string& kv_cache_dtype, torch::Tensor& k_scale,
+                       torch::Tensor& v_scale, int64_t heads_per_tile) {
+  check_cuda(query, "query");
+  const int kv = kv_code(kv_cache_dtype);
+  const int st = scalar_code(query.scalar_type());
+  check_cache_dtype(key_cache, query, kv, "key_cache");
+  TORCH_CHECK(query.dim() == 3 && out.dim() == 3, "query / out must be [num_tokens, num_heads, head_size]");
+  TORCH_CHECK(out.scalar_type() == query.scalar_type() && out.sizes() == query.sizes(),
+              "out must have query's type and shape");
+  TORCH_CHECK(key_cache.dim() == 5 && value_cache.dim() == 4,
+              "key_cache [blocks, kv_heads, head_size/x, block_size, x], value_cache [blocks, "
+              "kv_heads, head_size, block_size]");
+  TORCH_CHECK(block_tables.scalar_type() == at::ScalarType::Int, "block_tables must be int32");
+  TORCH_CHECK(seq_lens.scalar_type() == at::ScalarType::Int, "seq_lens must be int32");
+  TORCH_CHECK(query_start_loc.scalar_type() == at::ScalarType::Int, "query_start_loc must be int32");
+  TORCH_CHECK(query_start_loc.is_contiguous() && seq_lens.is_contiguous() &&
+              block_tables.stride(1) == 1, "metadata tensors must be contiguous");
+  TORCH_CHECK(query_start_loc.numel() == seq_lens.numel() + 1,
+              "query_start_loc must have num_seqs + 1 entries");
+  TORCH_CHECK(block_tables.size(0) >= seq_lens.numel(), "block_tables has fewer rows than seq_lens");
+  TORCH_CHECK(query.stride(2) == 1 && query.stride(1) == query.size(2),
+              "query heads must be densely packed");
+  TORCH_CHECK(out.stride(2) == 1 && out.stride(1) == out.size(2), "out heads must be densely packed");
+  float* lse_ptr = nullptr;
+  if (lse) {
+    TORCH_CHECK(lse->scalar_type() == at::ScalarType::Float && lse->is_contiguous() &&
+                lse->dim() == 2 && lse->size(0) == query.size(0) && lse->size(1) == query.size(1),
+                "lse must be a contiguous float32 [num_tokens, num_heads]");
+    lse_ptr = lse->data_ptr<float>();
+  }
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(query));
+  const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  const float* alibi = alibi_slopes ? reinterpret_cast<const float*>(alibi_slopes->data_ptr()) : nullptr;
+  check_status(b200pa_prefill_attention(
+      out.data_ptr(), lse_ptr, query.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(),
+      (int)seq_lens.numel(), (int)query.size(1), (int)key_cache.size(1), (int)query.size(2),
+      (int)key_cache.size(3), (float)scale, block_tables.data_ptr<int>(),
+      (int)block_tables.stride(0), query_start_loc.data_ptr<int>(), seq_lens.data_ptr<int>(),
+      (int)max_query_len, alibi, query.stride(0), out.stride(0), key_cache.stride(0),
+      key_cache.stride(1), st, kv, reinterpret_cast<const float*>(k_scale.data_ptr()),
+      reinterpret_cast<const float*>(v_scale.data_ptr()), (int)heads_per_tile, stream));
+}
+
 void merge_attn_states(torch::Tensor& output, std::optional<torch::Tensor> output_lse,
                        const torch::Tensor& prefix_output, const torch::Tensor& prefix_lse,
                        const torch::Tensor& suffix_output, const torch::Tensor& suffix_lse) {
@@ -654,6 +705,12 @@ constexpr const char* kSchemaFlash =
     "    Tensor! key_cache, Tensor! value_cache, Tensor? slot_mapping, float scale,"
     "    Tensor block_tables, Tensor seq_lens, int max_seq_len, Tensor? alibi_slopes,"
     "    str kv_cache_dtype, Tensor k_scale, Tensor v_scale) -> ()";
+constexpr const char* kSchemaPrefill =
+    "prefill_attention("
+    "    Tensor! out, Tensor!? lse, Tensor query, Tensor key_cache, Tensor value_cache,"
+    "    float scale, Tensor block_tables, Tensor query_start_loc, Tensor seq_lens,"
+    "    int max_query_len, Tensor? alibi_slopes, str kv_cache_dtype,"
+    "    Tensor k_scale, Tensor v_scale, int heads_per_tile=0) -> ()";
 constexpr const char* kSchemaCorrect =
     "correct_attn_out(Tensor! out, Tensor lses, int cp_rank) -> Tensor";
 constexpr const char* kSchemaReshape =
@@ -689,6 +746,8 @@ void define_extras(torch::Library& ops) {
   ops.impl("decode_step", torch::kCUDA, &decode_step);
   ops.def(kSchemaFlash);
   ops.impl("paged_attention_flash", torch::kCUDA, &paged_attention_flash);
+  ops.def(kSchemaPrefill);
+  ops.impl("prefill_attention", torch::kCUDA, &prefill_attention);
   ops.def(kSchemaCorrect);
   ops.impl("correct_attn_out", torch::kCUDA, &correct_attn_out);
 }

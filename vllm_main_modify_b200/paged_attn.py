@@ -148,6 +148,44 @@ class PagedAttention:
         return output
 
     @staticmethod
+    def forward_prefix(
+        query: torch.Tensor,
+        key: Optional[torch.Tensor],
+        value: Optional[torch.Tensor],
+        kv_cache_dtype: str,
+        key_cache: torch.Tensor,
+        value_cache: torch.Tensor,
+        block_tables: torch.Tensor,
+        query_start_loc: torch.Tensor,
+        seq_lens_tensor: torch.Tensor,
+        max_query_len: int,
+        alibi_slopes: Optional[torch.Tensor],
+        sliding_window: Optional[int],
+        k_scale: torch.Tensor,
+        v_scale: torch.Tensor,
+        scale: Optional[float] = None,
+        output: Optional[torch.Tensor] = None,
+        lse: Optional[torch.Tensor] = None,
+    ) -> torch.Tensor:
+        """``PagedAttention.forward_prefix`` (:200-242 of the reference's ``paged_attn.py``):
+        attention of each sequence's new tokens over its context AND the new tokens, causal.
+        The reference's Triton kernel takes the new tokens' K/V from ``key`` / ``value`` and the
+        context from the cache; here everything is read from the cache, which the backends have
+        written before this call (``cpu_attn.py:548-612`` does the same with its
+        ``flash_attn_varlen_func``) -- ``key`` / ``value`` are accepted for signature parity and
+        not read.  ``scale`` defaults to ``head_size ** -0.5`` like the Triton kernel's."""
+        if sliding_window is not None and sliding_window > 0:
+            raise NotImplementedError("sliding_window is not supported by the paged_attention ops")
+        if output is None:
+            output = torch.empty_like(query)
+        if scale is None:
+            scale = float(query.shape[-1]) ** -0.5
+        ops.prefill_attention(output, lse, query, key_cache, value_cache, scale, block_tables,
+                              query_start_loc.to(torch.int32), seq_lens_tensor.to(torch.int32),
+                              max_query_len, alibi_slopes, kv_cache_dtype, k_scale, v_scale)
+        return output
+
+    @staticmethod
     def forward_decode_with_lse(
         query: torch.Tensor,
         key_cache: torch.Tensor,

@@ -1,6 +1,7 @@
 """Prefill / chunked-prefill / mixed batches through ``AttentionImpl.forward``:
-the backend writes every new token and runs one single-query attention per token on the decode
-kernel (``backend.expand_queries_to_sequences``).  Checked against an independent fp64 causal
+the backend writes every new token, runs the leading single-token sequences of a decode-first
+batch on the decode kernel and the chunks on the causal chunk kernel (``ops.prefill_attention``);
+the token-major backend still expands per token (``backend.expand_queries_to_sequences``).  Checked against an independent fp64 causal
 attention over the logical token order (no paging, no expansion): new K/V are appended to each
 sequence's history and token j of the query attends to history + new[:j+1].
 """
@@ -102,3 +103,80 @@ def test_mixed_prefill_and_decode_batch(which):
         kd = co.xpacked_to_flash(kd.view(kc.shape), kv_cache[1].cpu().view(vc.shape))[0]
     flat = kd.reshape(NB * BS, Hkv, D)
     assert torch.equal(flat[torch.tensor(slots)], new_k)
+
+
+class _Common:
+    pass
+
+
+@pytest.mark.parametrize("kv", ["auto", "fp8"])
+def test_decode_first_batch_through_the_builder(kv):
+    """A batch as the runner hands it over after ``reorder_batch``: decodes first, then chunks;
+    ``build`` records the split, ``forward`` runs the two kernels.  Checked against the chunk
+    oracle on the cache as the backend itself wrote it (bit-exact bytes are the cache tests'
+    business) and, for the 16-bit cache, against the independent fp64 reference above."""
+    from oracle import oracle as ora
+    from oracle import prefill_oracle as po
+    from oracle import cache_ops_oracle as co
+    from vllm_main_modify_b200 import backend as be
+    H, Hkv, D = 16, 2, 128
+    G = H // Hkv
+    dt = torch.bfloat16
+    s = D ** -0.5
+    hist = [300, 37, 1000, 0, 500, 16]
+    qlens = [1, 1, 1, 70, 20, 3]
+    B, T = len(hist), sum(qlens)
+    lens = [h + ql for h, ql in zip(hist, qlens)]
+    NB = sum((L + BS - 1) // BS for L in lens) + 3
+    g = torch.Generator().manual_seed(7)
+    _, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, NB, lens, dt, seed=32, kv=kv,
+                                             lo=-1.0, hi=1.0, permute=True)
+    q = (torch.rand(T, H, D, generator=g) * 2 - 1).to(dt)
+    new_k = (torch.rand(T, Hkv, D, generator=g) * 2 - 1).to(dt)
+    new_v = (torch.rand(T, Hkv, D, generator=g) * 2 - 1).to(dt)
+    slots, qsl = [], [0]
+    for b in range(B):
+        for j in range(qlens[b]):
+            p = hist[b] + j
+            slots.append(int(bt[b, p // BS]) * BS + p % BS)
+        qsl.append(qsl[-1] + qlens[b])
+    ks, vs = (1.0, 1.0) if kv == "auto" else (0.02, 0.03)
+    c = _Common()
+    c.num_actual_tokens, c.max_query_len, c.num_reqs = T, max(qlens), B
+    c.seq_lens, c.seq_lens_cpu, c.max_seq_len = sl.to(DEV), sl, max(lens)
+    c.block_table_tensor = bt.to(DEV)
+    c.slot_mapping = torch.tensor(slots, dtype=torch.int64, device=DEV)
+    c.query_start_loc_cpu = torch.tensor(qsl, dtype=torch.int32)
+    c.query_start_loc = c.query_start_loc_cpu.to(DEV)
+    meta = be.B200PagedAttentionMetadataBuilder().build(0, c)
+    assert (meta.num_decodes, meta.num_prefills) == (3, 3)
+    backend = be.B200PagedAttentionBackend
+    kv_cache = torch.empty(backend.get_kv_cache_shape(NB, BS, Hkv, D), dtype=kc.dtype, device=DEV)
+    kv_cache[0] = kc.reshape(NB, -1).to(DEV)
+    kv_cache[1] = vc.reshape(NB, -1).to(DEV)
+    layer = _Layer()
+    layer._k_scale = torch.tensor(ks, device=DEV)
+    layer._v_scale = torch.tensor(vs, device=DEV)
+    impl = backend.get_impl_cls()(H, D, s, Hkv, None, None, kv)
+    out = impl.forward(layer, q.to(DEV).view(T, H * D), new_k.to(DEV).view(T, Hkv * D),
+                       new_v.to(DEV).view(T, Hkv * D), kv_cache, meta)
+    torch.cuda.synchronize()
+    got = out.view(T, H, D).cpu().float()
+    # the cache as the oracle's reshape_and_cache writes it == what the backend wrote
+    kc_o, vc_o = kc.clone(), vc.clone()
+    ora.reshape_and_cache(new_k, new_v, kc_o, vc_o, torch.tensor(slots), kv, torch.tensor(ks),
+                          torch.tensor(vs))
+    assert torch.equal(kv_cache[0].cpu().view(kc.shape).view(torch.uint8), kc_o.view(torch.uint8))
+    assert torch.equal(kv_cache[1].cpu().view(vc.shape).view(torch.uint8), vc_o.view(torch.uint8))
+    want = po.prefill_attention(q, kc_o, vc_o, bt, qsl, lens, s, None, kv, ks, vs)
+    torch.testing.assert_close(got, want, atol=1e-2, rtol=1e-2)
+    if kv == "auto":
+        kf, vf = co.xpacked_to_flash(kc, vc)
+        hist_k, hist_v = [], []
+        for b in range(B):
+            nb = (hist[b] + BS - 1) // BS
+            blocks = bt[b, :nb].long()
+            hist_k.append(kf[blocks].reshape(nb * BS, Hkv, D)[:hist[b]])
+            hist_v.append(vf[blocks].reshape(nb * BS, Hkv, D)[:hist[b]])
+        ref = _causal_reference(q, hist_k, hist_v, new_k, new_v, qlens, s, G)
+        torch.testing.assert_close(got, ref.float(), atol=1e-2, rtol=1e-2)

@@ -256,3 +256,64 @@ def test_error_convention(ops):
     with pytest.raises(RuntimeError):
         ops.convert_fp8(torch.empty(4, dtype=torch.uint8, device=DEV),
                         torch.empty(4, dtype=torch.bfloat16, device=DEV), 1.0, "auto")
+
+
+@pytest.mark.parametrize("kv", ["auto", "fp8", "fp8_e5m2"])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("head_size,block_size", [(128, 16), (64, 32), (256, 16), (128, 8), (80, 16),
+                                                  (256, 32)])
+def test_reshape_and_cache_prefill_sized_batches_bit_exact(ops, ora, kv, dtype, head_size,
+                                                           block_size):
+    """>= 1024 tokens take the tile kernel (64 tokens x one kv head per CTA, V rows staged in
+    shared memory and stored by 16-byte groups when the tile is a run of consecutive positions):
+    prefill chunks at every slot offset, decode tokens, padding slots and sequence boundaries
+    inside a tile -- the same bytes as the reference's per-token kernel
+    (csrc/cache_kernels.cu:212-264)."""
+    x = 16 // (1 if kv != "auto" else 2)
+    if head_size % x:
+        pytest.skip("head_size not divisible by x")
+    Hkv = 3
+    rnd = random.Random(head_size + block_size)
+    # (kind, length, first position): chunks start at arbitrary positions of their sequence
+    parts = [("chunk", 300, 0), ("chunk", 77, 5), ("decode", 10, 0), ("chunk", 500, block_size - 1),
+             ("pad", 7, 0), ("chunk", 64, 64), ("chunk", 129, 9), ("decode", 3, 0), ("chunk", 200, 3)]
+    slots, nblocks = [], 0
+    for kind, n, first in parts:
+        if kind == "pad":
+            slots += [-1] * n
+        elif kind == "decode":
+            for _ in range(n):
+                slots.append(nblocks * block_size + rnd.randrange(block_size))
+                nblocks += 1
+        else:
+            nb = (first + n + block_size - 1) // block_size
+            blocks = list(range(nblocks, nblocks + nb))
+            rnd.shuffle(blocks)                      # physical blocks in any order
+            nblocks += nb
+            slots += [blocks[p // block_size] * block_size + p % block_size
+                      for p in range(first, first + n)]
+    T, NB = len(slots), nblocks + 1
+    assert T >= 1024
+    g = torch.Generator().manual_seed(3)
+    qkv = torch.randn(T, 3, Hkv, head_size, generator=g).to(dtype)
+    key, value = qkv[:, 1], qkv[:, 2]
+    slots = torch.tensor(slots, dtype=torch.int64)
+    if kv == "auto":
+        kc0 = torch.zeros(NB, Hkv, head_size // x, block_size, x, dtype=dtype)
+        vc0 = torch.zeros(NB, Hkv, head_size, block_size, dtype=dtype)
+    else:
+        g2 = torch.Generator().manual_seed(1)
+        kc0 = torch.randint(0, 255, (NB, Hkv, head_size // x, block_size, x), generator=g2,
+                            dtype=torch.uint8)
+        vc0 = torch.randint(0, 255, (NB, Hkv, head_size, block_size), generator=g2,
+                            dtype=torch.uint8)
+    ks, vs = _scales(key, value, kv)
+    kc_o, vc_o = kc0.clone(), vc0.clone()
+    ora.reshape_and_cache(key, value, kc_o, vc_o, slots, kv, ks, vs)
+    qkv_d = qkv.to(DEV)
+    kc_d, vc_d = kc0.to(DEV), vc0.to(DEV)
+    ops.reshape_and_cache(qkv_d[:, 1], qkv_d[:, 2], kc_d, vc_d, slots.to(DEV), kv,
+                          ks.to(DEV), vs.to(DEV))
+    torch.cuda.synchronize()
+    assert torch.equal(_bytes(kc_d), _bytes(kc_o))
+    assert torch.equal(_bytes(vc_d), _bytes(vc_o))

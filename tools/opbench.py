@@ -75,23 +75,33 @@ def main():
 
     # ---------------------------------------------------------------- cache write
     Hkv, D, BS = 8, 128, 16
-    for T, tag in ((128, "decode step, 128 tokens (latency-bound)"), (16384, "16384 tokens")):
+    for T, tag in ((128, "decode step, 128 tokens (latency-bound)"),
+                   (16384, "16384 tokens, random slots"),
+                   (16384, "16384 tokens, prefill: 8 chunks of 2048 consecutive positions from "
+                           "position 5, physical blocks permuted")):
         NB = max(T // BS + 64, 2048)
         key = torch.randn(T, Hkv, D, device=DEV, generator=g).to(torch.bfloat16)
         val = torch.randn(T, Hkv, D, device=DEV, generator=g).to(torch.bfloat16)
-        slots = torch.randperm(NB * BS, device=DEV, generator=g)[:T].to(torch.int64)
+        if "prefill" in tag:
+            per = T // 8
+            nb = (5 + per + BS - 1) // BS
+            perm = torch.randperm(NB, device=DEV, generator=g)[:8 * nb].view(8, nb)
+            pos = torch.arange(5, 5 + per, device=DEV)
+            slots = (perm[:, pos // BS] * BS + pos % BS).reshape(-1).to(torch.int64)
+        else:
+            slots = torch.randperm(NB * BS, device=DEV, generator=g)[:T].to(torch.int64)
         sc = torch.tensor(0.05, device=DEV)
         for kv, cdt, ces in (("fp8", torch.uint8, 1), ("auto", torch.bfloat16, 2)):
             x = 16 // ces
             kc = torch.zeros(NB, Hkv, D // x, BS, x, dtype=cdt, device=DEV)
             vc = torch.zeros(NB, Hkv, D, BS, dtype=cdt, device=DEV)
             nbytes = 2 * T * Hkv * D * (2 + ces)
-            both(f"reshape_and_cache {kv} T={T}", nbytes,
+            both(f"reshape_and_cache {kv} T={T}" + (" prefill" if "prefill" in tag else ""), nbytes,
                  lambda: ops.reshape_and_cache(key, val, kc, vc, slots, kv, sc, sc),
                  (lambda: ref.reshape_and_cache(key, val, kc, vc, slots, kv, sc, sc)) if ref else None, tag)
             kf = torch.zeros(NB, BS, Hkv, D, dtype=cdt, device=DEV)
             vf = torch.zeros_like(kf)
-            both(f"reshape_and_cache_flash NHD {kv} T={T}", nbytes,
+            both(f"reshape_and_cache_flash NHD {kv} T={T}" + (" prefill" if "prefill" in tag else ""), nbytes,
                  lambda: ops.reshape_and_cache_flash(key, val, kf, vf, slots, kv, sc, sc),
                  (lambda: ref.reshape_and_cache_flash(key, val, kf, vf, slots, kv, sc, sc)) if ref else None, tag)
             del kc, vc, kf, vf

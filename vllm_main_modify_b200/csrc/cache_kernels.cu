@@ -109,6 +109,161 @@ __global__ void reshape_and_cache_kernel(
 }
 
 // ---------------------------------------------------------------------------
+// reshape_and_cache for prefill-sized batches: one CTA per (tile of kRunTokens consecutive
+// tokens, kv head).  Same bytes as the kernel above.  When the tile's tokens are consecutive
+// positions of one sequence (slot offsets advance by one, a new physical block at every multiple
+// of block_size) -- the shape of every prefill chunk -- the V rows of the tile are staged in
+// shared memory TRANSPOSED, laid out exactly as the cache rows they go to ([d][block j][token],
+// the first token at its slot offset), and copied out with 16-byte stores: the cache's
+// [D][block_size] plane of a full block is one contiguous run.  The per-token kernel writes the
+// same plane one 1-2 byte element at a stride of block_size (cache_kernels.cu:254-262 of the
+// reference does too).  Tiles that are not such a run (decode tokens, a sequence boundary, a
+// padding slot) take the per-element path inside this kernel.
+// ---------------------------------------------------------------------------
+constexpr int kRunTokens = 64;
+constexpr int kRunThreads = 256;
+constexpr int kRunMinTokens = 1024;    // below this the per-token kernel has more CTAs in flight
+
+template <int ST, int KV>
+__global__ void __launch_bounds__(kRunThreads)
+reshape_and_cache_run_kernel(
+    const typename Scalar<ST>::type* __restrict__ key,
+    const typename Scalar<ST>::type* __restrict__ value, void* __restrict__ key_cache,
+    void* __restrict__ value_cache, const int64_t* __restrict__ slot_mapping, int num_tokens,
+    int64_t key_stride, int64_t value_stride, int num_heads, int head_size, int block_size,
+    const float* __restrict__ k_scale, const float* __restrict__ v_scale) {
+  using T = typename Scalar<ST>::type;
+  static_assert(ST != B200PA_F32, "16-bit sources");
+  constexpr int CES = KV == B200PA_KV_AUTO ? 2 : 1;     // cache element bytes
+  constexpr int X = 16 / CES;                            // elements per 16-byte K chunk
+  extern __shared__ __align__(16) uint8_t vs_smem[];     // [head_size][pitch] cache elements
+  __shared__ int64_t slots_s[kRunTokens];
+  __shared__ int run_s;
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  const int t0 = blockIdx.x * kRunTokens;
+  const int head = blockIdx.y;
+  const int nt = min(kRunTokens, num_tokens - t0);
+  if (threadIdx.x < kRunTokens)
+    slots_s[threadIdx.x] = threadIdx.x < nt ? slot_mapping[t0 + threadIdx.x] : -1;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    // a run: every slot valid; offsets advance by one; inside a block the slot itself does too
+    bool ok = true;
+    for (int i = threadIdx.x; i < nt; i += 32) {
+      const int64_t sl = slots_s[i];
+      ok = ok && sl >= 0;
+      if (i > 0) {
+        const int64_t pv = slots_s[i - 1];
+        const int off = (int)(sl % block_size);
+        ok = ok && (off == (int)((pv + 1) % block_size)) && (off == 0 || sl == pv + 1);
+      }
+    }
+    ok = __all_sync(0xffffffffu, ok);
+    if (threadIdx.x == 0) run_s = ok ? 1 : 0;
+  }
+  __syncthreads();
+  const bool run = run_s != 0;
+  float ks = 1.f, vs = 1.f;
+  if constexpr (KV != B200PA_KV_AUTO) { ks = *k_scale; vs = *v_scale; }
+  const int64_t blk_elems = (int64_t)num_heads * head_size * block_size;
+  const int64_t head_elems = (int64_t)head * head_size * block_size;
+
+  // ---- K: one 16-byte cache chunk per (token, chunk), as in the per-token kernel
+  const int cph = head_size / X;
+  for (int idx = threadIdx.x; idx < nt * cph; idx += kRunThreads) {
+    const int i = idx / cph, xi = idx - i * cph;
+    const int64_t slot = slots_s[i];
+    if (slot < 0) continue;
+    const T* src = key + (int64_t)(t0 + i) * key_stride + head * head_size + xi * X;
+    const int64_t dst = (slot / block_size) * blk_elems + head_elems +
+                        (int64_t)xi * block_size * X + (slot % block_size) * X;
+    if constexpr (KV == B200PA_KV_AUTO) {
+      *reinterpret_cast<uint4*>(reinterpret_cast<T*>(key_cache) + dst) =
+          *reinterpret_cast<const uint4*>(src);
+    } else {
+      uint4 raw[2];
+      raw[0] = reinterpret_cast<const uint4*>(src)[0];
+      raw[1] = reinterpret_cast<const uint4*>(src)[1];
+      const T* e = reinterpret_cast<const T*>(raw);
+      uint32_t w[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const uint32_t lo = fp8_quant2<KV>(Scalar<ST>::to_float(e[4 * k + 0]),
+                                           Scalar<ST>::to_float(e[4 * k + 1]), ks);
+        const uint32_t hi = fp8_quant2<KV>(Scalar<ST>::to_float(e[4 * k + 2]),
+                                           Scalar<ST>::to_float(e[4 * k + 3]), ks);
+        w[k] = lo | (hi << 16);
+      }
+      *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(key_cache) + dst) =
+          make_uint4(w[0], w[1], w[2], w[3]);
+    }
+  }
+
+  // ---- V
+  const int d8n = head_size / 8;                       // 16-byte groups of a source row
+  if (!run) {
+    // per element, stride block_size (coalesced loads of the token row, scattered stores)
+    for (int idx = threadIdx.x; idx < nt * head_size; idx += kRunThreads) {
+      const int i = idx / head_size, d = idx - i * head_size;
+      const int64_t slot = slots_s[i];
+      if (slot < 0) continue;
+      const T v = value[(int64_t)(t0 + i) * value_stride + head * head_size + d];
+      const int64_t dst = (slot / block_size) * blk_elems + head_elems +
+                          (int64_t)d * block_size + slot % block_size;
+      if constexpr (KV == B200PA_KV_AUTO) reinterpret_cast<T*>(value_cache)[dst] = v;
+      else reinterpret_cast<uint8_t*>(value_cache)[dst] = fp8_quant<KV>(Scalar<ST>::to_float(v), vs);
+    }
+    return;
+  }
+  const int a = (int)(slots_s[0] % block_size);        // slot offset of the tile's first token
+  const int nblk_max = kRunTokens / block_size + 1;
+  const int pitch = nblk_max * block_size * CES;       // bytes per staged row (16-byte multiple)
+  // stage: lanes along the tokens (conflict-free 1-2 byte shared stores), 8 head elements each
+  for (int idx = threadIdx.x; idx < d8n * kRunTokens; idx += kRunThreads) {
+    const int i = idx % kRunTokens, d8 = idx / kRunTokens;
+    if (i >= nt) continue;
+    const uint4 raw = __ldg(reinterpret_cast<const uint4*>(
+        value + (int64_t)(t0 + i) * value_stride + head * head_size + d8 * 8));
+    const T* e = reinterpret_cast<const T*>(&raw);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      uint8_t* dst = vs_smem + (size_t)(d8 * 8 + k) * pitch + (a + i) * CES;
+      if constexpr (KV == B200PA_KV_AUTO) *reinterpret_cast<T*>(dst) = e[k];
+      else *dst = fp8_quant<KV>(Scalar<ST>::to_float(e[k]), vs);
+    }
+  }
+  __syncthreads();
+  // copy out: (block j, row d, 16-byte group g) -- for a full block the rows of one head are one
+  // contiguous run of head_size * block_size elements
+  const int gpb = block_size * CES / 16 > 0 ? block_size * CES / 16 : 1;   // groups per block row
+  const int gbytes = block_size * CES < 16 ? block_size * CES : 16;          // (block_size 8, fp8: 8)
+  const int nblk = (a + nt + block_size - 1) / block_size;
+  const int lo_b = a * CES, hi_b = (a + nt) * CES;     // valid byte range of a staged row
+  for (int idx = threadIdx.x; idx < nblk * head_size * gpb; idx += kRunThreads) {
+    const int j = idx / (head_size * gpb);
+    const int rem = idx - j * head_size * gpb;
+    const int d = rem / gpb, g = rem - d * gpb;
+    const int tok = max(0, j * block_size - a);        // first token of the tile in block j
+    const int64_t phys = slots_s[tok] / block_size;
+    const int b0 = j * block_size * CES + g * gbytes;  // byte offset in the staged row
+    const uint8_t* src = vs_smem + (size_t)d * pitch + b0;
+    uint8_t* dst = reinterpret_cast<uint8_t*>(value_cache) +
+                   (phys * blk_elems + head_elems + (int64_t)d * block_size) * CES +
+                   g * gbytes;
+    if (gbytes == 16 && b0 >= lo_b && b0 + 16 <= hi_b) {
+      *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
+    } else {
+      for (int k = 0; k < gbytes; k += CES) {
+        if (b0 + k >= lo_b && b0 + k < hi_b) {
+          if constexpr (CES == 2) *reinterpret_cast<uint16_t*>(dst + k) = *reinterpret_cast<const uint16_t*>(src + k);
+          else dst[k] = src[k];
+        }
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
 // reshape_and_cache_flash: NHD / HND, addressed by strides.  One CTA per token;
 // each thread moves 8 consecutive elements of one head (16-byte load).
 // ---------------------------------------------------------------------------
@@ -242,6 +397,35 @@ int launch_reshape_and_cache(const void* key, const void* value, void* key_cache
   const bool vec = (x * cache_es == 16) && aligned16(key) && aligned16(key_cache) &&
                    ((key_stride * es) % 16 == 0) && ((head_size * es) % 16 == 0) &&
                    ((x * es) % 16 == 0) && (scalar_type != B200PA_F32 || kv_dtype == B200PA_KV_AUTO);
+  // prefill-sized batches: token tiles x kv heads, V staged and stored by rows (see the kernel)
+  const bool run_ok = vec && num_tokens >= kRunMinTokens && scalar_type != B200PA_F32 &&
+                      aligned16(value) && aligned16(value_cache) &&
+                      ((value_stride * es) % 16 == 0) && head_size % 8 == 0 &&
+                      (block_size == 8 || block_size == 16 || block_size == 32) &&
+                      num_heads <= 65535 &&
+                      head_size * (kRunTokens / block_size + 1) * block_size * cache_es <= 40960;
+  if (run_ok) {
+    const int pitch = (kRunTokens / block_size + 1) * block_size * cache_es;
+    const int smem = head_size * pitch;
+    dim3 grid((num_tokens + kRunTokens - 1) / kRunTokens, num_heads);
+#define RUN_CASE(ST_, KV_)                                                                     \
+    reshape_and_cache_run_kernel<ST_, KV_><<<grid, kRunThreads, smem, stream>>>(               \
+        (const typename Scalar<ST_>::type*)key, (const typename Scalar<ST_>::type*)value,      \
+        key_cache, value_cache, slot_mapping, num_tokens, key_stride, value_stride, num_heads, \
+        head_size, block_size, k_scale, v_scale)
+    if (scalar_type == B200PA_BF16) {
+      if (kv_dtype == B200PA_KV_AUTO) RUN_CASE(B200PA_BF16, B200PA_KV_AUTO);
+      else if (kv_dtype == B200PA_KV_FP8_E4M3) RUN_CASE(B200PA_BF16, B200PA_KV_FP8_E4M3);
+      else RUN_CASE(B200PA_BF16, B200PA_KV_FP8_E5M2);
+    } else {
+      if (kv_dtype == B200PA_KV_AUTO) RUN_CASE(B200PA_F16, B200PA_KV_AUTO);
+      else if (kv_dtype == B200PA_KV_FP8_E4M3) RUN_CASE(B200PA_F16, B200PA_KV_FP8_E4M3);
+      else RUN_CASE(B200PA_F16, B200PA_KV_FP8_E5M2);
+    }
+#undef RUN_CASE
+    count_launch();
+    return check_launch("reshape_and_cache");
+  }
   const int threads = min(max(num_heads * head_size / 4, 64), 512);
   dim3 grid(num_tokens), block((threads + 31) / 32 * 32);
   B200PA_DISPATCH_ST_KV(scalar_type, kv_dtype, {

@@ -71,11 +71,6 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
                : "memory");
 }
-// transaction bytes without an arrival / the arrival that closes a split expectation (EARLYK)
-__device__ __forceinline__ void mbar_expect_tx_only(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(bytes)
-               : "memory");
-}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   asm volatile(
       "{\n"
@@ -377,15 +372,11 @@ __device__ __forceinline__ void store_out(typename Scalar<ST>::type* out_tile,
 // below); with BSZ = 32 a cache block is two tiles that arrive in one bulk copy and are addressed
 // inside the block by the layout's strides (K chunk stride BSZ*16 B, V row stride BSZ elements).
 // E5: the fp8 codes are e5m2 (kv_cache_dtype "fp8_e5m2") instead of e4m3.
-// EARLYK: the K half of a stage is refilled as soon as the stage's QK^T is done (its bytes are
-// expected on the stage's barrier without an arrival), the V half after PV (with the arrival):
-// the K copy of stage i + STAGES gets the softmax + PV time of stage i as extra lead.
 template <int ST, bool FP8, int D, int NW, int STAGES, int PPS, int MINB, bool FLASH, int BSZ,
-          bool E5, bool EARLYK>
+          bool E5>
 __global__ void __launch_bounds__(NW * 32, MINB)
 paged_attention_stream_kernel(const StreamParams p) {
   static_assert(FP8 || !E5, "E5 selects the fp8 format");
-  static_assert(!(EARLYK && FLASH), "the split refill serves the bulk-copy path");
   using T = typename Scalar<ST>::type;
   constexpr bool MMA_BF16 = (!FP8) && (ST == B200PA_BF16);  // fp8 pages compute in f16
   constexpr int CES = FP8 ? 1 : 2;                           // cache element bytes
@@ -489,28 +480,6 @@ paged_attention_stream_kernel(const StreamParams p) {
   int bt_reg = 0, bt_b = -1, bt_win = -1;  // 32 block-table entries of (bt_b, window bt_win)
   bool producing = true;
   int ip = 0;                               // stages issued
-  // EARLYK: what produce(K half) leaves for the V half of the same stage
-  int pv_phys[PPS / (BSZ / kBS)];
-  int pv_nblk = 0, pv_kvh = 0;
-  bool pending_v = false;
-  auto produce_v = [&]() {
-    if constexpr (EARLYK) {
-      if (lane == 0) {
-        const int s = ip % STAGES;
-        const uint32_t bar = bar0 + 8 * s;
-        const uint32_t dst = ring_u32 + s * STAGE_BYTES;
-        const uint8_t* vc = reinterpret_cast<const uint8_t*>(p.v_cache) + pv_kvh * head_stride_bytes;
-        mbar_expect_tx(bar, pv_nblk * BLOCK_BYTES);
-#pragma unroll
-        for (int g = 0; g < BPS; ++g)
-          if (g < pv_nblk)
-            tma_load_1d(dst + g * 2 * BLOCK_BYTES + BLOCK_BYTES,
-                        vc + (int64_t)pv_phys[g] * blk_stride_bytes, BLOCK_BYTES, bar, policy);
-      }
-      pending_v = false;
-      ++ip;
-    }
-  };
   auto produce = [&]() {
     if (pc.st == pc.st_end) {
       if (pc.left == 0) { producing = false; return; }
@@ -563,26 +532,6 @@ paged_attention_stream_kernel(const StreamParams p) {
         }
       }
       cp_async_mbar_arrive(bar);
-    } else if constexpr (EARLYK) {
-      // K half now (bytes expected, no arrival yet); produce_v() closes the expectation
-      pv_kvh = pc.vh / p.h_tiles;
-      pv_nblk = nblk;
-#pragma unroll
-      for (int g = 0; g < BPS; ++g) pv_phys[g] = phys[g];
-      if (lane == 0) {
-        const int s = ip % STAGES;
-        const uint32_t bar = bar0 + 8 * s;
-        const uint32_t dst = ring_u32 + s * STAGE_BYTES;
-        const uint8_t* kc = reinterpret_cast<const uint8_t*>(p.k_cache) + pv_kvh * head_stride_bytes;
-        mbar_expect_tx_only(bar, nblk * BLOCK_BYTES);
-#pragma unroll
-        for (int g = 0; g < BPS; ++g)
-          if (g < nblk)
-            tma_load_1d(dst + g * 2 * BLOCK_BYTES, kc + (int64_t)phys[g] * blk_stride_bytes,
-                        BLOCK_BYTES, bar, policy);
-      }
-      pending_v = true;
-      return;     // ip advances with the V half
     } else if (lane == 0) {
       const int s = ip % STAGES;
       const uint32_t bar = bar0 + 8 * s;
@@ -604,10 +553,7 @@ paged_attention_stream_kernel(const StreamParams p) {
     ++ip;
   };
 #pragma unroll 1
-  for (int i = 0; i < STAGES && producing; ++i) {
-    produce();
-    if (pending_v) produce_v();
-  }
+  for (int i = 0; i < STAGES && producing; ++i) produce();
   TRACE(4);
 
   // ---------------------------------------------------------------- consumer state
@@ -900,12 +846,6 @@ paged_attention_stream_kernel(const StreamParams p) {
       }
     }
 
-    if constexpr (EARLYK) {
-      // every lane is past its last read of the stage's K half
-      __syncwarp();
-      if (producing) produce();
-    }
-
     // ---- online softmax.  d[g][j]: j = 0,1 token tokA heads 2q,2q+1 ; j = 2,3 token tokB
     const int tok0 = page0 * kBS;
     float d[PPS][4];
@@ -1050,11 +990,7 @@ paged_attention_stream_kernel(const StreamParams p) {
 
     // ---- refill this stage (all lanes are past their last read of it)
     __syncwarp();
-    if constexpr (EARLYK) {
-      if (pending_v) produce_v();
-    } else {
-      if (producing) produce();
-    }
+    if (producing) produce();
   }
   TRACE_W(16);
   }  // w < W
@@ -1325,11 +1261,11 @@ paged_attention_stream_kernel(const StreamParams p) {
 constexpr int kMaxWarpsPerSm = 16;
 
 template <int ST, bool FP8, int D, int NW, int STAGES, int PPS, int MINB, bool FLASH = false,
-          int BSZ = 16, bool E5 = false, bool EARLYK = false>
+          int BSZ = 16, bool E5 = false>
 int launch_stream_t(StreamParams& p, int num_sms, int64_t workspace_bytes, cudaStream_t stream) {
   constexpr int CES = FP8 ? 1 : 2;
   constexpr int SMEM = NW * STAGES * PPS * 2 * kBS * (FLASH ? D * CES + 16 : D * CES);
-  auto kern = paged_attention_stream_kernel<ST, FP8, D, NW, STAGES, PPS, MINB, FLASH, BSZ, E5, EARLYK>;
+  auto kern = paged_attention_stream_kernel<ST, FP8, D, NW, STAGES, PPS, MINB, FLASH, BSZ, E5>;
   // per instantiation AND per device: the shared-memory opt-in is a per-device function
   // attribute (a process that drives several GPUs must set it on each)
   static int ctas_per_sm_of[64] = {0};
@@ -1431,7 +1367,7 @@ int launch_stream_bs32(StreamParams& p, bool fp8, int scalar_type, int head_size
     case 80:  if (fp8) { STREAM_CALL(ST, true, 80, 4, 3, 2, 2, false, 32); } else { STREAM_CALL(ST, false, 80, 4, 3, 2, 2, false, 32); }  \
     case 96:  if (fp8) { STREAM_CALL(ST, true, 96, 4, 3, 2, 2, false, 32); }  else { STREAM_CALL(ST, false, 96, 4, 3, 2, 1, false, 32); }  \
     case 112: if (fp8) { STREAM_CALL(ST, true, 112, 4, 3, 2, 2, false, 32); } else { STREAM_CALL(ST, false, 112, 4, 3, 2, 1, false, 32); } \
-    case 128: if (fp8) { STREAM_CALL(ST, true, 128, 8, 3, 2, 1, false, 32); } else { STREAM_CALL(ST, false, 128, 4, 3, 2, 1, false, 32); } \
+    case 128: if (fp8) { STREAM_CALL(ST, true, 128, 6, 2, 2, 2, false, 32); } else { STREAM_CALL(ST, false, 128, 4, 3, 2, 1, false, 32); } \
     case 192: if (fp8) { STREAM_CALL(ST, true, 192, 4, 4, 2, 1, false, 32); } else { STREAM_CALL(ST, false, 192, 4, 2, 2, 1, false, 32); } \
     case 256: if (fp8) { STREAM_CALL(ST, true, 256, 4, 3, 2, 1, false, 32); } else { STREAM_CALL(ST, false, 256, 3, 2, 2, 1, false, 32); } \
     default: return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: head size %d", head_size);  \
@@ -1471,7 +1407,7 @@ int launch_stream_e5m2(StreamParams& p, int scalar_type, int head_size, int num_
     case 80:  STREAM_CALL(ST, true, 80, 4, 3, 2, 2, false, 16, true);            \
     case 96:  STREAM_CALL(ST, true, 96, 4, 3, 2, 2, false, 16, true);            \
     case 112: STREAM_CALL(ST, true, 112, 4, 3, 2, 2, false, 16, true);           \
-    case 128: STREAM_CALL(ST, true, 128, 8, 3, 2, 1, false, 16, true);           \
+    case 128: STREAM_CALL(ST, true, 128, 6, 2, 2, 2, false, 16, true);           \
     case 192: STREAM_CALL(ST, true, 192, 4, 4, 2, 1, false, 16, true);           \
     case 256: STREAM_CALL(ST, true, 256, 4, 3, 2, 1, false, 16, true);           \
     default: return set_error(B200PA_ERR_UNSUPPORTED,                            \
@@ -1604,7 +1540,13 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
     return launch_stream_flash(p, fp8, scalar_type, head_size, num_sms, workspace_bytes, stream);
   if (block_size == 32)
     return launch_stream_bs32(p, fp8, scalar_type, head_size, num_sms, workspace_bytes, stream);
-  // <ST, FP8, D, NW, STAGES, PPS, MINB>: fp8 stage = PPS x 4 KiB, 16-bit stage = PPS x 8 KiB (D=128)
+  // <ST, FP8, D, NW, STAGES, PPS, MINB>: fp8 stage = PPS x 4 KiB, 16-bit stage = PPS x 8 KiB (D=128).
+  // Defaults (tune 0) by the SUSTAINED rate: seconds of back-to-back steps run under the 1 kW
+  // power cap at 1.4-1.7 GHz, where 12 warps x 2 stages (fp8) hold 6.4-6.6 TB/s and the former
+  // default, 8 warps x 3 stages (tune 8), falls from 6.9 TB/s (first 50 ms) to 5.7-5.9; for 16-bit
+  // caches 8 warps x 2 stages beat 4 x 4 (tune 10) in both regimes
+  // (profiles/r02e_powerprobe_tunes.jsonl, r02f_powerprobe_cfg{2,3,4}.jsonl -- tune numbers there
+  // are those of commit e162116).
 #define STREAM_TUNE_FP8(ST, DV)                                        \
   switch (tune) {                                                      \
     case 1: STREAM_CALL(ST, true, DV, 4, 4, 2, 1);                     \
@@ -1614,14 +1556,13 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
     case 5: STREAM_CALL(ST, true, DV, 4, 2, 2, 3);                     \
     case 6: STREAM_CALL(ST, true, DV, 5, 4, 2, 1);                     \
     case 7: STREAM_CALL(ST, true, DV, 6, 3, 2, 1);                     \
-    case 8: STREAM_CALL(ST, true, DV, 6, 2, 2, 2);                     \
+    case 8: STREAM_CALL(ST, true, DV, 8, 3, 2, 1);                     \
     case 9: STREAM_CALL(ST, true, DV, 12, 2, 2, 1);                    \
-    case 10: STREAM_CALL(ST, true, DV, 4, 2, 2, 3, false, 16, false, true);  \
-    case 11: STREAM_CALL(ST, true, DV, 8, 3, 2, 1, false, 16, false, true);  \
-    case 12: STREAM_CALL(ST, true, DV, 5, 2, 2, 2);                    \
-    case 13: STREAM_CALL(ST, true, DV, 3, 2, 2, 4);                    \
-    case 14: STREAM_CALL(ST, true, DV, 6, 2, 2, 2, false, 16, false, true);  \
-    default: STREAM_CALL(ST, true, DV, 8, 3, 2, 1);                    \
+    case 10: STREAM_CALL(ST, true, DV, 5, 2, 2, 2);                    \
+    case 11: STREAM_CALL(ST, true, DV, 3, 2, 2, 4);                    \
+    case 12: STREAM_CALL(ST, true, DV, 10, 2, 2, 1);                   \
+    case 13: STREAM_CALL(ST, true, DV, 8, 2, 2, 1);                    \
+    default: STREAM_CALL(ST, true, DV, 6, 2, 2, 2);                    \
   }
 #define STREAM_TUNE_16(ST, DV)                                         \
   switch (tune) {                                                      \
@@ -1634,12 +1575,11 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
     case 7: STREAM_CALL(ST, false, DV, 5, 4, 1, 1);                    \
     case 8: STREAM_CALL(ST, false, DV, 12, 2, 1, 1);                   \
     case 9: STREAM_CALL(ST, false, DV, 6, 2, 1, 2);                    \
-    case 10: STREAM_CALL(ST, false, DV, 4, 2, 1, 3, false, 16, false, true); \
-    case 11: STREAM_CALL(ST, false, DV, 4, 4, 1, 1, false, 16, false, true); \
-    case 12: STREAM_CALL(ST, false, DV, 8, 2, 1, 1);                   \
-    case 13: STREAM_CALL(ST, false, DV, 6, 2, 1, 2, false, 16, false, true); \
-    case 14: STREAM_CALL(ST, false, DV, 8, 3, 1, 1, false, 16, false, true); \
-    default: STREAM_CALL(ST, false, DV, 4, 4, 1, 1);                   \
+    case 10: STREAM_CALL(ST, false, DV, 4, 4, 1, 1);                   \
+    case 11: STREAM_CALL(ST, false, DV, 10, 2, 1, 1);                  \
+    case 12: STREAM_CALL(ST, false, DV, 4, 2, 1, 2);                   \
+    case 13: STREAM_CALL(ST, false, DV, 9, 2, 1, 1);                   \
+    default: STREAM_CALL(ST, false, DV, 8, 2, 1, 1);                   \
   }
   if (scalar_type == B200PA_BF16 && head_size == 128) {
     if (fp8) { STREAM_TUNE_FP8(B200PA_BF16, 128) } else { STREAM_TUNE_16(B200PA_BF16, 128) }

@@ -8,9 +8,12 @@ Nothing here is imported by the product.  Everything runs on CPU torch tensors i
                           (tests/kernels/attention/test_merge_attn_states.py:16-46), and on the
                           GPU box by the reference CUDA kernel itself (oracle/_ref).
 * ``correct_attn_out``    vllm/attention/ops/common.py:9-68 (Triton kernel) and :86-116 (wrapper).
-                          The Triton kernel cannot run without a GPU and /root/reference does not
-                          travel; pinned through the property it exists for (the sum over ranks of
-                          the corrected partial outputs is the full attention output, :119-140).
+                          Pinned by tests/golden/correct_*.npz: the reference's kernel SOURCE,
+                          extracted and executed per (batch, head) against a torch implementation
+                          of the tl. primitives it uses (tests/golden/make_correct_golden.py;
+                          Triton itself needs a GPU), inf / nan / all -inf rows included -- and
+                          through the property it exists for (the sum over ranks of the corrected
+                          partial outputs is the full attention output, :119-140).
 * ``paged_attention_lse`` no reference op.  LSE of the scaled logits from the oracle's own v2
                           partials (attention_kernels.cuh:337-341 exp_sums / max_logits):
                           lse = log(sum_j exp_sums[j] * exp(max_logits[j] - m)) + m.

@@ -587,18 +587,22 @@ def test_strided_query_and_padded_cache(ops, ora, version, kv):
     _close(out.cpu(), want)
 
 
-@pytest.mark.parametrize("impl", [GENERIC])
-def test_v2_scratch_contract(ops, native, impl):
+@pytest.mark.parametrize("mode", ["generic", "env"])
+def test_v2_scratch_contract(ops, native, mode, monkeypatch):
     """After paged_attention_v2 through the generic kernel the scratch buffers hold the
     reference's partials: merging them with the reference's reduce formula
-    (attention_kernels.cuh:560-664) reproduces `out`.  (The stream kernel keeps its partials
-    in its own workspace and leaves the caller's scratch untouched.)"""
+    (attention_kernels.cuh:560-664) reproduces `out`.  The default (stream) path keeps its
+    partials in its own workspace and leaves the caller's scratch untouched; a caller that reads
+    the scratch sets B200PA_V2_REFERENCE_SCRATCH=1 (mode "env": no test hook involved)."""
     B, H, Hkv, D, BS, NB = 4, 16, 4, 128, 16, 600
     lens = [4096, 513, 100, 2049]
     s = D ** -0.5
     q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, NB, lens, torch.bfloat16, seed=6,
                                              lo=-s, hi=s)
-    native.set_impl(impl)
+    if mode == "env":
+        monkeypatch.setenv("B200PA_V2_REFERENCE_SCRATCH", "1")
+    else:
+        native.set_impl(GENERIC)
     try:
         out, es, ml, tmp = _run_gpu(ops, "v2", q, kc, vc, Hkv, s, bt, sl, BS, 4096, None, "auto",
                                     1.0, 1.0)
@@ -721,7 +725,9 @@ def test_opcheck_schemas(ops):
     q, kc, vc, bt, sl, Hkv, s, BS, max_len = _small_device_case()
     one = torch.tensor(0.02, device=DEV)
     out = torch.empty_like(q)
-    utils = ("test_schema", "test_faketensor")
+    # ALL_OPCHECK_TEST_UTILS of the reference (tests/kernels/utils.py:33-38)
+    utils = ("test_schema", "test_autograd_registration", "test_faketensor",
+             "test_aot_dispatch_dynamic")
     for ns in (torch.ops.b200pa, torch.ops._C):
         torch.library.opcheck(ns.paged_attention_v1,
                               (out, q, kc, vc, Hkv, s, bt, sl, BS, max_len, None, "fp8", one, one,

@@ -283,3 +283,21 @@ def test_opcheck_lse_ops(ops):
     lses = torch.randn(2, n, h, device=DEV)
     torch.library.opcheck(torch.ops.b200pa.correct_attn_out, (o.clone(), lses, 1),
                           test_utils=("test_schema",))
+
+
+@pytest.mark.parametrize("name", ["correct_f32_n4.npz", "correct_bf16_n8.npz", "correct_f16_n2.npz"])
+def test_correct_attn_out_matches_the_reference_kernel_golden(ops, name):
+    """Outputs of the reference's Triton kernel source (vllm/attention/ops/common.py:9-68) run at
+    fixture-generation time (tests/golden/make_correct_golden.py), inf / nan / all -inf rows
+    included: same values, NaN in the same places."""
+    from tests.test_lse_oracle import load_correct_case
+    out, lses, rank, want, want_lse, dt = load_correct_case(name)
+    got, got_lse = ops.correct_attn_out(out.clone().to(DEV), lses.to(DEV), rank)
+    got, got_lse = got.cpu(), got_lse.cpu()
+    assert torch.equal(torch.isnan(got_lse), torch.isnan(want_lse))
+    fin = ~torch.isnan(want_lse)
+    torch.testing.assert_close(got_lse[fin], want_lse[fin], atol=1e-5, rtol=1e-5)
+    assert torch.equal(torch.isnan(got.float()), torch.isnan(want.float()))
+    ok = ~torch.isnan(want.float())
+    torch.testing.assert_close(got.float()[ok], want.float()[ok], atol=1e-6,
+                               rtol=2 ** -7 if dt != torch.float32 else 1e-5)

@@ -113,3 +113,29 @@ def test_correct_attn_out_sums_to_full_attention(n_ranks):
     torch.testing.assert_close(total.double(), full, atol=1e-4, rtol=1e-4)
     want_lse = _fp64_attention_lse(q, kc, vc, bt, sl, scale, Hkv)
     torch.testing.assert_close(lse_tot.double(), want_lse, atol=1e-5, rtol=1e-5)
+
+
+CORRECT_CASES = ["correct_f32_n4.npz", "correct_bf16_n8.npz", "correct_f16_n2.npz"]
+
+
+def load_correct_case(name):
+    g = hp.load_golden(name)
+    dt = hp.golden_dtype(g)
+    return (hp.from_bits(g["out"], dt), torch.from_numpy(g["lses"].copy()), int(g["rank"]),
+            hp.from_bits(g["out_ref"], dt), torch.from_numpy(g["lse_ref"].copy()), dt)
+
+
+@pytest.mark.parametrize("name", CORRECT_CASES)
+def test_correct_attn_out_oracle_matches_the_reference_kernel(name):
+    """tests/golden/correct_*.npz: the reference's Triton kernel source
+    (vllm/attention/ops/common.py:9-68) executed per (batch, head) at fixture-generation time
+    (tests/golden/make_correct_golden.py), inf / nan / all -inf rows included."""
+    out, lses, rank, want, want_lse, dt = load_correct_case(name)
+    got, got_lse = lse_oracle.correct_attn_out(out.clone(), lses, rank)
+    assert torch.equal(torch.isnan(got_lse), torch.isnan(want_lse))
+    fin = ~torch.isnan(want_lse)
+    torch.testing.assert_close(got_lse[fin], want_lse[fin], atol=1e-6, rtol=1e-6)
+    assert torch.equal(torch.isnan(got.float()), torch.isnan(want.float()))
+    ok = ~torch.isnan(want.float())
+    torch.testing.assert_close(got.float()[ok], want.float()[ok], atol=1e-7,
+                               rtol=2 ** -8 if dt != torch.float32 else 1e-6)

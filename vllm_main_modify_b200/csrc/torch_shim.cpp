@@ -14,6 +14,7 @@
 // `_C_cache_ops::*`, `_C_cuda_utils::*` (when the reference's own extension is
 // not loaded in the process) so that an unmodified `vllm/_custom_ops.py` resolves
 // `torch.ops._C.paged_attention_v1` etc. to this library.
+#include <cstdlib>
 #include <ATen/cuda/CUDAContext.h>
 #include <c10/cuda/CUDAGuard.h>
 #include <torch/all.h>
@@ -159,7 +160,18 @@ void paged_attention_v2(torch::Tensor& out, torch::Tensor& exp_sums, torch::Tens
   const at::cuda::OptionalCUDAGuard device_guard(device_of(query));
   const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
   const float* alibi = alibi_slopes ? reinterpret_cast<const float*>(alibi_slopes->data_ptr()) : nullptr;
-  const torch::Tensor ws = attention_workspace(query);
+  // The stream kernel splits the context by its own schedule and keeps its partials in the
+  // workspace: exp_sums / max_logits / tmp_out stay untouched (the reference's callers treat them
+  // as scratch, paged_attn.py:163-173).  B200PA_V2_REFERENCE_SCRATCH=1 serves a caller that reads
+  // them: the call then takes the generic kernel, which leaves the reference's per-partition
+  // partials (attention_kernels.cuh:345-351, 487) in them.
+  const char* ref_scratch = std::getenv("B200PA_V2_REFERENCE_SCRATCH");
+  const bool want_ref_scratch = ref_scratch != nullptr && ref_scratch[0] == '1';
+  const torch::Tensor ws = want_ref_scratch ? torch::Tensor() : attention_workspace(query);
+  if (ws.defined())
+    TORCH_WARN_ONCE("b200pa paged_attention_v2: exp_sums / max_logits / tmp_out are scratch and "
+                    "are left untouched by the stream kernel; set B200PA_V2_REFERENCE_SCRATCH=1 "
+                    "if a caller reads the reference's per-partition partials from them");
   check_status(b200pa_paged_attention_v2(
       out.data_ptr(), exp_sums.data_ptr<float>(), max_logits.data_ptr<float>(), tmp_out.data_ptr(),
       query.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(), (int)query.size(0),

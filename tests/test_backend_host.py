@@ -52,8 +52,9 @@ def test_backend_twins_static_contract():
     assert flash.get_name() == "B200_PAGED_ATTN_FLASH_LAYOUT"
     assert paged.get_kv_cache_shape(10, 16, 8, 128) == (2, 10, 16 * 8 * 128)   # paged_attn.py:48-54
     assert flash.get_kv_cache_shape(10, 16, 8, 128) == (2, 10, 16, 8, 128)
+    assert flash.get_kv_cache_shape(10, 32, 8, 128) == (2, 10, 32, 8, 128)
     with pytest.raises(ValueError):
-        flash.get_kv_cache_shape(10, 32, 8, 128)
+        flash.get_kv_cache_shape(10, 8, 8, 128)
     assert flash.get_impl_cls() is be.B200FlashLayoutAttentionImpl
     assert issubclass(flash.get_impl_cls(), paged.get_impl_cls())
     assert paged.get_builder_cls() is flash.get_builder_cls()
@@ -61,8 +62,8 @@ def test_backend_twins_static_contract():
         assert cls.accept_output_buffer and not cls.use_cascade_attention()
         assert torch.bfloat16 in cls.get_supported_dtypes()
         cls.validate_head_size(128)
-    with pytest.raises(ValueError, match="Head size 80"):
-        flash.validate_head_size(80)
+    with pytest.raises(ValueError, match="Head size 120"):
+        flash.validate_head_size(120)
     mod, name = flash.full_cls_name()
     assert (mod, name) == ("vllm_main_modify_b200.backend", "B200FlashLayoutAttentionBackend")
 

@@ -185,24 +185,25 @@ def test_other_dtypes_and_block_sizes(ops, native, ora, dtype, version, kv, bloc
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
 @pytest.mark.parametrize("head_size", [32, 64, 80, 96, 112, 128, 192, 256])
 @pytest.mark.parametrize("version", ["v1", "v2"])
-def test_stream_kernel_serves_fp8_e5m2(ops, native, ora, dtype, head_size, version):
+@pytest.mark.parametrize("block_size", [16, 32])
+def test_stream_kernel_serves_fp8_e5m2(ops, native, ora, dtype, head_size, version, block_size):
     """fp8_e5m2 caches (DISPATCH_BY_KV_CACHE_DTYPE, quant_utils.cuh:545-582) on the stream kernel:
     same tolerance against the oracle as e4m3, and the generic kernel's output beside it."""
     B, H, Hkv, D, NB = 6, 32, 4, head_size, 700
     lens = [1, 17, 512, 513, 3000, 4097]
     s = D ** -0.5
-    q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, 16, NB, lens, dtype, seed=5, kv="fp8",
-                                             lo=-s, hi=s, permute=True)
+    q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, block_size, NB, lens, dtype, seed=5,
+                                             kv="fp8", lo=-s, hi=s, permute=True)
     kc, vc = kc & 0xBB, vc & 0xBB          # moderate exponents, no inf / nan codes
     ks, vs = 0.01, 0.02
-    want = _run_oracle(ora, version, q, kc, vc, Hkv, s, bt, sl, 16, max(lens), None, "fp8_e5m2",
-                       ks, vs)
+    want = _run_oracle(ora, version, q, kc, vc, Hkv, s, bt, sl, block_size, max(lens), None,
+                       "fp8_e5m2", ks, vs)
     outs = {}
     for impl in (STREAM, GENERIC):
         native.set_impl(impl)
         try:
-            outs[impl], *_ = _run_gpu(ops, version, q, kc, vc, Hkv, s, bt, sl, 16, max(lens), None,
-                                      "fp8_e5m2", ks, vs)
+            outs[impl], *_ = _run_gpu(ops, version, q, kc, vc, Hkv, s, bt, sl, block_size,
+                                      max(lens), None, "fp8_e5m2", ks, vs)
         finally:
             native.set_impl(native.IMPL_AUTO)
         _close(outs[impl], want)
@@ -706,6 +707,36 @@ def test_blocksparse_matches_oracle(ops, ora):
         want = _run_oracle(ora, version, q, kc, vc, Hkv, s, bt, sl, BS, 1200, None, "auto", 1.0,
                            1.0, extra=extra)
         _close(got, want)
+
+
+@pytest.mark.parametrize("kv", ["auto", "fp8"])
+@pytest.mark.parametrize("block_size", [16, 32])
+@pytest.mark.parametrize("extra", [
+    (0, 2, 3, 32, 1),      # tp_rank, local_blocks, vert_stride, blocksparse_block_size, step
+    (1, 4, 8, 64, 1),      # the reference's default sparse block, stripes slide with the q head
+    (1, 1, 4, 64, -1),     # ... with the kv head (negative step, attention_kernels.cuh:216-220)
+    (0, 16, 5, 16, 2),
+])
+def test_blocksparse_on_the_stream_kernel(ops, native, ora, kv, block_size, extra):
+    """Block-sparse attention (attention_kernels.cuh:207-251): the stream kernel streams every
+    block and masks per (head, block); the reference skips -- same numbers."""
+    B, H, Hkv, D, NB = 4, 16, 4, 128, 400
+    lens = [300, 513, 2500, 64]
+    s = D ** -0.5
+    q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, block_size, NB, lens, torch.bfloat16,
+                                             seed=7, kv=kv, lo=-s, hi=s, permute=True)
+    ks, vs = (1.0, 1.0) if kv == "auto" else (s / 2, s / 3)
+    want = _run_oracle(ora, "v1", q, kc, vc, Hkv, s, bt, sl, block_size, max(lens), None, kv, ks,
+                       vs, extra=extra)
+    for version in ("v1", "v2"):
+        for impl in (STREAM, GENERIC):
+            native.set_impl(impl)
+            try:
+                got, *_ = _run_gpu(ops, version, q, kc, vc, Hkv, s, bt, sl, block_size, max(lens),
+                                   None, kv, ks, vs, extra=extra)
+            finally:
+                native.set_impl(native.IMPL_AUTO)
+            _close(got, want)
 
 
 # ----------------------------------------------------------- boundary contract

@@ -72,7 +72,26 @@ CASES = [
     ("d96_fp8_gqa12", 4, 24, 2, 96, [300, 5000, 12, 640], torch.bfloat16, "fp8", False),
     ("d32_fp8", 4, 8, 8, 32, [300, 1500, 12, 640], torch.float16, "fp8", False),
     ("d32_bf16", 4, 8, 2, 32, [300, 5000, 12, 640], torch.bfloat16, "auto", False),
+    # head sizes 80 / 112 (rows padded to an odd number of 16-byte units), fp8_e5m2, and -- tenth
+    # field -- 32-token cache blocks (reshape_and_cache_flash writes all of these,
+    # csrc/cache_kernels.cu:280-353 of the reference)
+    ("neox_d80_bf16", 4, 8, 8, 80, [300, 1500, 12, 640], torch.bfloat16, "auto", False),
+    ("d80_fp8", 4, 8, 8, 80, [300, 1500, 12, 640], torch.bfloat16, "fp8", False),
+    ("d112_f16_gqa4", 4, 16, 4, 112, [1, 16, 17, 2049], torch.float16, "auto", False),
+    ("d112_fp8_gqa4", 4, 16, 4, 112, [300, 5000, 12, 640], torch.bfloat16, "fp8", False),
+    ("e5m2_d128_gqa4", 5, 32, 8, 128, [1, 16, 17, 999, 2048], torch.bfloat16, "fp8_e5m2", False),
+    ("e5m2_d64_f16", 4, 8, 8, 64, [300, 1500, 12, 640], torch.float16, "fp8_e5m2", False),
+    ("bs32_fp8_gqa8", 6, 16, 2, 128, [1, 16, 32, 33, 1000, 4097], torch.bfloat16, "fp8", False, 32),
+    ("bs32_bf16_gqa4", 6, 16, 4, 128, [1, 16, 32, 33, 1000, 4097], torch.bfloat16, "auto", False, 32),
+    ("bs32_d64_f16_alibi", 5, 8, 8, 64, [31, 64, 65, 700, 3000], torch.float16, "auto", True, 32),
+    ("bs32_d256_fp8", 4, 16, 8, 256, [1000, 17, 512, 4100], torch.bfloat16, "fp8", False, 32),
+    ("bs32_d80_e5m2", 4, 8, 8, 80, [300, 1500, 12, 640], torch.bfloat16, "fp8_e5m2", False, 32),
 ]
+
+
+def _unpack(case):
+    name, B, H, Hkv, D, lens, dtype, kv, use_alibi, *rest = case
+    return name, B, H, Hkv, D, lens, dtype, kv, use_alibi, (rest[0] if rest else BS)
 
 
 def _layout(t, layout):
@@ -82,10 +101,12 @@ def _layout(t, layout):
     return t.permute(0, 2, 1, 3).contiguous().permute(0, 2, 1, 3)
 
 
-def _inputs(co, B, H, Hkv, D, lens, dtype, kv, seed=17):
+def _inputs(co, B, H, Hkv, D, lens, dtype, kv, seed=17, bs=BS):
     s = D ** -0.5
-    NB = sum((L + BS - 1) // BS for L in lens) + 5
-    q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, NB, lens, dtype, seed=seed, kv=kv,
+    NB = sum((L + bs - 1) // bs for L in lens) + 5
+    # (the generator's fp8 codes, magnitudes below 0x48, are finite in e4m3 and in e5m2)
+    q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, bs, NB, lens, dtype, seed=seed,
+                                             kv="auto" if kv == "auto" else "fp8",
                                              lo=-1.0, hi=1.0, permute=True)
     kf, vf = co.xpacked_to_flash(kc, vc)
     return s, q, kc, vc, kf, vf, bt, sl
@@ -98,8 +119,8 @@ def _scales(kv):
 @pytest.mark.parametrize("layout", ["NHD", "HND"])
 @pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
 def test_flash_layout_attention(ops, native, ora, co, case, layout):
-    name, B, H, Hkv, D, lens, dtype, kv, use_alibi = case
-    s, q, kc, vc, kf, vf, bt, sl = _inputs(co, B, H, Hkv, D, lens, dtype, kv)
+    name, B, H, Hkv, D, lens, dtype, kv, use_alibi, bs = _unpack(case)
+    s, q, kc, vc, kf, vf, bt, sl = _inputs(co, B, H, Hkv, D, lens, dtype, kv, bs=bs)
     ks, vs = _scales(kv)
     alibi = None
     if use_alibi:
@@ -121,7 +142,7 @@ def test_flash_layout_attention(ops, native, ora, co, case, layout):
     try:
         ref = torch.full_like(qd, float("nan"))
         ref_lse = torch.full_like(lse, float("nan"))
-        ops.paged_attention_lse(ref, ref_lse, qd, d(kc), d(vc), Hkv, s, btd, sld, BS, max_len, ald,
+        ops.paged_attention_lse(ref, ref_lse, qd, d(kc), d(vc), Hkv, s, btd, sld, bs, max_len, ald,
                                 kv, ksd, vsd)
         torch.cuda.synchronize()
     finally:
@@ -141,7 +162,7 @@ def test_flash_layout_attention(ops, native, ora, co, case, layout):
         assert bool(torch.isinf(lse[~live]).all())
     if sum(lens) * H <= 64 * 140000:
         want = torch.empty_like(q)
-        ora.paged_attention_v1(want, q, kc, vc, Hkv, s, bt, sl, BS, max_len, alibi, kv,
+        ora.paged_attention_v1(want, q, kc, vc, Hkv, s, bt, sl, bs, max_len, alibi, kv,
                                torch.tensor(ks), torch.tensor(vs))
         atol = ATOL * max(1.0, float(want[live].float().abs().max()))
         torch.testing.assert_close(got[live].float(), want[live].float(), atol=atol, rtol=RTOL)
@@ -152,8 +173,8 @@ def test_flash_layout_attention(ops, native, ora, co, case, layout):
                          ids=[c[0] for c in CASES if min(c[5]) >= 1])
 def test_flash_layout_fused_write(ops, native, ora, co, case, layout):
     """key / value / slot_mapping given: reshape_and_cache_flash + attention in one launch."""
-    name, B, H, Hkv, D, lens, dtype, kv, use_alibi = case
-    s, q, kc, vc, kf, vf, bt, sl = _inputs(co, B, H, Hkv, D, lens, dtype, kv)
+    name, B, H, Hkv, D, lens, dtype, kv, use_alibi, bs = _unpack(case)
+    s, q, kc, vc, kf, vf, bt, sl = _inputs(co, B, H, Hkv, D, lens, dtype, kv, bs=bs)
     ks, vs = _scales(kv)
     alibi = None
     if use_alibi:
@@ -162,10 +183,10 @@ def test_flash_layout_fused_write(ops, native, ora, co, case, layout):
     g = torch.Generator().manual_seed(4)
     key = (torch.rand(B, Hkv, D, generator=g) * 2 - 1).to(dtype)
     value = (torch.rand(B, Hkv, D, generator=g) * 2 - 1).to(dtype)
-    slots = torch.tensor([int(bt[b, (L - 1) // BS]) * BS + (L - 1) % BS
+    slots = torch.tensor([int(bt[b, (L - 1) // bs]) * bs + (L - 1) % bs
                           for b, L in enumerate(lens)], dtype=torch.int64)
     # poison the slots about to be written (NaN codes)
-    blk, off = slots // BS, slots % BS
+    blk, off = slots // bs, slots % bs
     if kv == "auto":
         kf[blk, off] = float("nan")
         vf[blk, off] = float("nan")
@@ -206,7 +227,7 @@ def test_flash_layout_error_convention(ops):
     one = torch.tensor(1.0, device=DEV)
     bt = torch.zeros(B, 2, dtype=torch.int32, device=DEV)
     sl = torch.tensor([5, 20], dtype=torch.int32, device=DEV)
-    for D, bs, dt in ((80, 16, torch.bfloat16), (128, 32, torch.bfloat16), (128, 16, torch.float32)):
+    for D, bs, dt in ((120, 16, torch.bfloat16), (128, 8, torch.bfloat16), (128, 16, torch.float32)):
         q = torch.zeros(B, H, D, dtype=dt, device=DEV)
         kc = torch.zeros(NB, bs, Hkv, D, dtype=dt, device=DEV)
         with pytest.raises(RuntimeError, match="Unsupported|needs a 16-bit query"):

@@ -1,37 +1,30 @@
 set -u
 mkdir -p gpurun_out
-T=r02g
-python -m pytest tests -m gpu -x -q 2>&1 | tail -15 > gpurun_out/${T}_pytest.txt; cat gpurun_out/${T}_pytest.txt
-tools/gpu_job.sh $T smoke
-python bench.py > gpurun_out/${T}_bench_cfg4.json 2> gpurun_out/${T}_bench_cfg4.err; echo "bench rc=$?"; tail -3 gpurun_out/${T}_bench_cfg4.err
-python - <<'PY'
-import json
-d=json.load(open('gpurun_out/r02g_bench_cfg4.json'))
-print('value',d['value'],'ms',d['ms_per_step'],'e2e',d['e2e']['value'],'sustained',d['sustained']['gbs'],'frac',d['roofline']['frac'],'parity',d['parity']['ok'])
-print({k:(v['gbs'],v['ms_per_step'],v['parity'].get('ok')) for k,v in d['configs'].items()})
-PY
-python tools/opbench.py > gpurun_out/${T}_opbench.jsonl 2> gpurun_out/${T}_opbench.err; tail -2 gpurun_out/${T}_opbench.err; grep reshape_and_cache gpurun_out/${T}_opbench.jsonl | cut -c1-260
-for t in 0 5 8 9 11; do
-  B200PA_STREAM_TUNE=$t python tools/kbench.py --configs cfg5,cfg4 --tp 8 --ops fstep --iters 30 >> gpurun_out/${T}_kbench_small.jsonl 2>> gpurun_out/${T}_kbench.err
-done
-for t in 0 1 8 9 10 12; do
-  B200PA_STREAM_TUNE=$t python tools/kbench.py --configs cfg1,cfg2 --tp 1 --ops fstep --iters 30 >> gpurun_out/${T}_kbench_small.jsonl 2>> gpurun_out/${T}_kbench.err
-done
-cut -c1-230 gpurun_out/${T}_kbench_small.jsonl; tail -2 gpurun_out/${T}_kbench.err
-# ---- ncu --set full captures (each only after the same command exited 0 without ncu)
-cap() {  # name, kernel regex, skip, command...
-  local name=$1 rx=$2 skip=$3; shift 3
+T=r02h
+python -m pytest tests -m gpu -q 2>&1 | tail -40 > gpurun_out/${T}_pytest.txt; tail -25 gpurun_out/${T}_pytest.txt
+python tools/opbench.py 2> gpurun_out/${T}_opbench.err | grep reshape_and_cache > gpurun_out/${T}_opbench_cache.jsonl; grep '"reshape_and_cache ' gpurun_out/${T}_opbench_cache.jsonl | grep 16384 | cut -c1-200
+# ---- ncu --set full captures (each only after the same command exited 0 without ncu); the
+# reports are exported to CSV on the box (gpurun_out is capped at 64 MiB)
+cap() {  # name, kernel regex, skip, keep-report(0/1), command...
+  local name=$1 rx=$2 skip=$3 keep=$4; shift 4
   "$@" > gpurun_out/${T}_${name}_plain.log 2>&1 &&
   ncu --set full --clock-control none --import-source on -k regex:"$rx" -s $skip -c 1 -f \
       -o gpurun_out/${T}_${name} "$@" > gpurun_out/${T}_${name}_ncu.log 2>&1
   echo "cap $name rc=$?"
+  if [ -f gpurun_out/${T}_${name}.ncu-rep ]; then
+    ncu -i gpurun_out/${T}_${name}.ncu-rep --page raw --csv > gpurun_out/${T}_${name}_raw.csv 2>/dev/null
+    python tools/ncu_summary.py gpurun_out/${T}_${name}_raw.csv > gpurun_out/${T}_${name}_summary.txt 2>&1
+    if [ $keep = 0 ]; then rm -f gpurun_out/${T}_${name}.ncu-rep; fi
+  fi
+  rm -f gpurun_out/${T}_${name}_plain.log
 }
-cap cfg4_stream paged_attention_stream_kernel 4 python bench.py --config cfg4 --steps 3 --warmup 3 --no-cpu-baseline --no-check --sustain 0 --no-side-configs
-cap cfg2_stream paged_attention_stream_kernel 4 python bench.py --config cfg2 --steps 3 --warmup 3 --no-cpu-baseline --no-check --sustain 0 --no-side-configs
-cap d192_fp8 paged_attention_stream_kernel 3 python tools/shapebench.py --only d192_fp8 --iters 2
-cap d64_fp8_gqa8 paged_attention_stream_kernel 3 python tools/shapebench.py --only d64_fp8_gqa8 --iters 2
-cap d112_fp8_gqa4 paged_attention_stream_kernel 3 python tools/shapebench.py --only d112_fp8_gqa4 --iters 2
-cap flash_nhd paged_attention_stream_kernel 3 python tools/kbench.py --configs cfg3 --ops flash_nhd --iters 3
-cap prefill_fp8 paged_prefill_kernel 2 python tools/prefillbench.py --cases chunk2k_ctx6k_fp8 --iters 2
-cap prefill_bf16 paged_prefill_kernel 2 python tools/prefillbench.py --cases chunk2k_ctx6k_bf16 --iters 2
-ls -la gpurun_out/*.ncu-rep | awk '{print $5, $9}'
+cap cfg4_stream paged_attention_stream_kernel 4 1 python bench.py --config cfg4 --steps 3 --warmup 3 --no-cpu-baseline --no-check --sustain 0 --no-side-configs
+cap cfg2_stream paged_attention_stream_kernel 4 0 python bench.py --config cfg2 --steps 3 --warmup 3 --no-cpu-baseline --no-check --sustain 0 --no-side-configs
+cap d192_fp8 paged_attention_stream_kernel 3 0 python tools/shapebench.py --only d192_fp8 --iters 2
+cap d64_fp8_gqa8 paged_attention_stream_kernel 3 0 python tools/shapebench.py --only d64_fp8_gqa8 --iters 2
+cap d112_fp8_gqa4 paged_attention_stream_kernel 3 0 python tools/shapebench.py --only d112_fp8_gqa4 --iters 2
+cap flash_nhd paged_attention_stream_kernel 3 0 python tools/kbench.py --configs cfg3 --ops flash_nhd --iters 3
+cap prefill_fp8 paged_prefill_kernel 2 1 python tools/prefillbench.py --cases chunk2k_ctx6k_fp8 --iters 2
+cap prefill_bf16 paged_prefill_kernel 2 0 python tools/prefillbench.py --cases chunk2k_ctx6k_bf16 --iters 2
+cap cache_run reshape_and_cache_run_kernel 3 0 python tools/opbench.py --iters 3
+du -sh gpurun_out; ls gpurun_out | head -50

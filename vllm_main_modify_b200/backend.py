@@ -478,8 +478,8 @@ class B200FlashLayoutAttentionBackend(B200PagedAttentionBackend):
     @staticmethod
     def get_kv_cache_shape(num_blocks: int, block_size: int, num_kv_heads: int,
                            head_size: int, cache_dtype_str: str = "auto") -> Tuple[int, ...]:
-        if block_size != 16:
-            raise ValueError("B200_PAGED_ATTN_FLASH_LAYOUT serves block_size 16")
+        if block_size not in (16, 32):
+            raise ValueError("B200_PAGED_ATTN_FLASH_LAYOUT serves block_size 16 and 32")
         return (2, num_blocks, block_size, num_kv_heads, head_size)
 
     @staticmethod
@@ -489,7 +489,7 @@ class B200FlashLayoutAttentionBackend(B200PagedAttentionBackend):
 
     @staticmethod
     def get_supported_head_sizes() -> List[int]:
-        return [32, 64, 96, 128, 192, 256]
+        return [32, 64, 80, 96, 112, 128, 192, 256]
 
     @classmethod
     def get_supported_dtypes(cls) -> List[torch.dtype]:

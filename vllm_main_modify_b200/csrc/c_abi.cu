@@ -32,8 +32,8 @@ bool stream_supported(const void*, const void*, const void*, int, int, int, int,
                       int64_t, int, int, int);
 int launch_stream(void*, float*, int64_t, int64_t, void*, int64_t, const void*, const void*, const void*, int, int, int, int,
                   float, const int32_t*, int, const int32_t*, const float*, int64_t, int64_t,
-                  int64_t, int, int, const float*, const float*, const FusedWrite*, int64_t, int,
-                  int, int, cudaStream_t);
+                  int64_t, int, int, const float*, const float*, const FusedWrite*,
+                  const BlockSparse*, int64_t, int, int, int, cudaStream_t);
 bool stream_flash_supported(const void*, const void*, const void*, int, int, int, int, int64_t,
                             int64_t, int64_t, int64_t, int, int);
 bool stream_fused_supported(const FusedWrite&, int);
@@ -196,7 +196,7 @@ static int paged_attention_common(
                          num_heads, num_kv_heads, head_size, scale, block_tables,
                          max_num_blocks_per_seq, seq_lens, alibi_slopes, q_stride,
                          kv_block_stride, kv_head_stride, scalar_type, kv_dtype, k_scale, v_scale,
-                         fused, 0, block_size, num_sms(), stream_tune(), stream);
+                         fused, &bsp, 0, block_size, num_sms(), stream_tune(), stream);
   }
   int rc = launch_generic(out, lse, lse_seq_stride, lse_head_stride, exp_sums, max_logits, tmp_out, query, key_cache, value_cache,
                           num_seqs, num_heads, num_kv_heads, head_size, block_size, scale,
@@ -341,18 +341,19 @@ int b200pa_paged_attention_flash(
                      num_heads, num_kv_heads);
   if (kv_dtype != B200PA_KV_AUTO && (!k_scale || !v_scale))
     return set_error(B200PA_ERR_INVALID, "fp8 kv cache needs k_scale and v_scale");
-  if (head_size != 32 && head_size != 64 && head_size != 96 && head_size != 128 &&
-      head_size != 192 && head_size != 256)
+  if (head_size != 32 && head_size != 64 && head_size != 80 && head_size != 96 &&
+      head_size != 112 && head_size != 128 && head_size != 192 && head_size != 256)
     return set_error(B200PA_ERR_UNSUPPORTED,
-                     "Unsupported head size: %d (flash layout: 32, 64, 96, 128, 192, 256)", head_size);
-  if (block_size != 16)
-    return set_error(B200PA_ERR_UNSUPPORTED, "Unsupported block size: %d (flash layout: 16)",
+                     "Unsupported head size: %d (flash layout: 32, 64, 80, 96, 112, 128, 192, 256)",
+                     head_size);
+  if (block_size != 16 && block_size != 32)
+    return set_error(B200PA_ERR_UNSUPPORTED, "Unsupported block size: %d (flash layout: 16, 32)",
                      block_size);
   if (!stream_flash_supported(query, key_cache, value_cache, num_heads, num_kv_heads, head_size,
                               block_size, q_stride, block_stride, page_stride, head_stride,
                               scalar_type, kv_dtype))
     return set_error(B200PA_ERR_UNSUPPORTED,
-                     "paged_attention_flash: needs a 16-bit query, an auto or fp8_e4m3 cache and "
+                     "paged_attention_flash: needs a 16-bit query, an auto or fp8 cache and "
                      "16-byte aligned cache rows");
   const bool want_write = key || value || slot_mapping;
   if (want_write && (!key || !value || !slot_mapping))
@@ -374,7 +375,7 @@ int b200pa_paged_attention_flash(
                        key_cache, value_cache, num_seqs, num_heads, num_kv_heads, head_size, scale,
                        block_tables, max_num_blocks_per_seq, seq_lens, alibi_slopes, q_stride,
                        block_stride, head_stride, scalar_type, kv_dtype, k_scale, v_scale, fused,
-                       page_stride, block_size, num_sms(), 0, stream);
+                       nullptr, page_stride, block_size, num_sms(), 0, stream);
 }
 
 int b200pa_merge_attn_states(void* output, float* output_lse, const void* prefix_output,

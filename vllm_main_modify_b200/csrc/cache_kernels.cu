@@ -136,120 +136,123 @@ reshape_and_cache_run_kernel(
   static_assert(ST != B200PA_F32, "16-bit sources");
   constexpr int CES = KV == B200PA_KV_AUTO ? 2 : 1;     // cache element bytes
   constexpr int X = 16 / CES;                            // elements per 16-byte K chunk
-  extern __shared__ __align__(16) uint8_t vs_smem[];     // [head_size][pitch] cache elements
-  __shared__ int64_t slots_s[kRunTokens];
+  // [head_size][pitch] V rows laid out as in the cache, then [kRunTokens][head_size * CES + 16] K
+  extern __shared__ __align__(16) uint8_t run_smem[];
+  __shared__ int blk_s[kRunTokens];    // physical block of the token, -1: padding slot
+  __shared__ int off_s[kRunTokens];    // slot offset in its block
   __shared__ int run_s;
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int t0 = blockIdx.x * kRunTokens;
   const int head = blockIdx.y;
   const int nt = min(kRunTokens, num_tokens - t0);
-  if (threadIdx.x < kRunTokens)
-    slots_s[threadIdx.x] = threadIdx.x < nt ? slot_mapping[t0 + threadIdx.x] : -1;
+  if (threadIdx.x < kRunTokens) {
+    const int64_t sl = threadIdx.x < nt ? slot_mapping[t0 + threadIdx.x] : -1;
+    blk_s[threadIdx.x] = sl < 0 ? -1 : (int)(sl / block_size);
+    off_s[threadIdx.x] = sl < 0 ? 0 : (int)(sl % block_size);
+  }
   __syncthreads();
   if (threadIdx.x < 32) {
-    // a run: every slot valid; offsets advance by one; inside a block the slot itself does too
+    // a run: every slot valid; offsets advance by one; inside a block the block stays the same
     bool ok = true;
     for (int i = threadIdx.x; i < nt; i += 32) {
-      const int64_t sl = slots_s[i];
-      ok = ok && sl >= 0;
+      ok = ok && blk_s[i] >= 0;
       if (i > 0) {
-        const int64_t pv = slots_s[i - 1];
-        const int off = (int)(sl % block_size);
-        ok = ok && (off == (int)((pv + 1) % block_size)) && (off == 0 || sl == pv + 1);
+        const int want = off_s[i - 1] + 1 == block_size ? 0 : off_s[i - 1] + 1;
+        ok = ok && off_s[i] == want && (want == 0 || blk_s[i] == blk_s[i - 1]);
       }
     }
     ok = __all_sync(0xffffffffu, ok);
     if (threadIdx.x == 0) run_s = ok ? 1 : 0;
   }
-  __syncthreads();
-  const bool run = run_s != 0;
   float ks = 1.f, vs = 1.f;
   if constexpr (KV != B200PA_KV_AUTO) { ks = *k_scale; vs = *v_scale; }
-  const int64_t blk_elems = (int64_t)num_heads * head_size * block_size;
-  const int64_t head_elems = (int64_t)head * head_size * block_size;
+  const int64_t blk_bytes = (int64_t)num_heads * head_size * block_size * CES;
+  const int64_t head_bytes = (int64_t)head * head_size * block_size * CES;
+  const int a = off_s[0];                               // slot offset of the tile's first token
+  const int pitch = (kRunTokens / block_size + 1) * block_size * CES;   // staged V row, bytes
+  uint8_t* const vs_smem = run_smem;
+  const int krow = head_size * CES + 16;                // staged K row (odd 16-byte units)
+  uint8_t* const ks_smem = run_smem + (size_t)head_size * pitch;
+  const int d8n = head_size / 8;                        // 16-byte groups of a source row
 
-  // ---- K: one 16-byte cache chunk per (token, chunk), as in the per-token kernel
-  const int cph = head_size / X;
-  for (int idx = threadIdx.x; idx < nt * cph; idx += kRunThreads) {
-    const int i = idx / cph, xi = idx - i * cph;
-    const int64_t slot = slots_s[i];
-    if (slot < 0) continue;
-    const T* src = key + (int64_t)(t0 + i) * key_stride + head * head_size + xi * X;
-    const int64_t dst = (slot / block_size) * blk_elems + head_elems +
-                        (int64_t)xi * block_size * X + (slot % block_size) * X;
+  // ---- stage K (token-major, cache bytes) and V (transposed: [d][slot offset]); the loads of
+  // one token's row are coalesced, lanes along the head elements
+  for (int idx = threadIdx.x; idx < nt * d8n; idx += kRunThreads) {
+    const int i = idx / d8n, d8 = idx - i * d8n;
+    const uint4 kraw = __ldg(reinterpret_cast<const uint4*>(
+        key + (int64_t)(t0 + i) * key_stride + head * head_size + d8 * 8));
+    const uint4 vraw = __ldg(reinterpret_cast<const uint4*>(
+        value + (int64_t)(t0 + i) * value_stride + head * head_size + d8 * 8));
+    const T* ke = reinterpret_cast<const T*>(&kraw);
+    const T* ve = reinterpret_cast<const T*>(&vraw);
     if constexpr (KV == B200PA_KV_AUTO) {
-      *reinterpret_cast<uint4*>(reinterpret_cast<T*>(key_cache) + dst) =
-          *reinterpret_cast<const uint4*>(src);
+      *reinterpret_cast<uint4*>(ks_smem + (size_t)i * krow + d8 * 16) = kraw;
     } else {
-      uint4 raw[2];
-      raw[0] = reinterpret_cast<const uint4*>(src)[0];
-      raw[1] = reinterpret_cast<const uint4*>(src)[1];
-      const T* e = reinterpret_cast<const T*>(raw);
-      uint32_t w[4];
+      uint32_t w[2];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const uint32_t lo = fp8_quant2<KV>(Scalar<ST>::to_float(e[4 * k + 0]),
-                                           Scalar<ST>::to_float(e[4 * k + 1]), ks);
-        const uint32_t hi = fp8_quant2<KV>(Scalar<ST>::to_float(e[4 * k + 2]),
-                                           Scalar<ST>::to_float(e[4 * k + 3]), ks);
+      for (int k = 0; k < 2; ++k) {
+        const uint32_t lo = fp8_quant2<KV>(Scalar<ST>::to_float(ke[4 * k + 0]),
+                                           Scalar<ST>::to_float(ke[4 * k + 1]), ks);
+        const uint32_t hi = fp8_quant2<KV>(Scalar<ST>::to_float(ke[4 * k + 2]),
+                                           Scalar<ST>::to_float(ke[4 * k + 3]), ks);
         w[k] = lo | (hi << 16);
       }
-      *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(key_cache) + dst) =
-          make_uint4(w[0], w[1], w[2], w[3]);
+      *reinterpret_cast<uint2*>(ks_smem + (size_t)i * krow + d8 * 8) = make_uint2(w[0], w[1]);
     }
-  }
-
-  // ---- V
-  const int d8n = head_size / 8;                       // 16-byte groups of a source row
-  if (!run) {
-    // per element, stride block_size (coalesced loads of the token row, scattered stores)
-    for (int idx = threadIdx.x; idx < nt * head_size; idx += kRunThreads) {
-      const int i = idx / head_size, d = idx - i * head_size;
-      const int64_t slot = slots_s[i];
-      if (slot < 0) continue;
-      const T v = value[(int64_t)(t0 + i) * value_stride + head * head_size + d];
-      const int64_t dst = (slot / block_size) * blk_elems + head_elems +
-                          (int64_t)d * block_size + slot % block_size;
-      if constexpr (KV == B200PA_KV_AUTO) reinterpret_cast<T*>(value_cache)[dst] = v;
-      else reinterpret_cast<uint8_t*>(value_cache)[dst] = fp8_quant<KV>(Scalar<ST>::to_float(v), vs);
-    }
-    return;
-  }
-  const int a = (int)(slots_s[0] % block_size);        // slot offset of the tile's first token
-  const int nblk_max = kRunTokens / block_size + 1;
-  const int pitch = nblk_max * block_size * CES;       // bytes per staged row (16-byte multiple)
-  // stage: lanes along the tokens (conflict-free 1-2 byte shared stores), 8 head elements each
-  for (int idx = threadIdx.x; idx < d8n * kRunTokens; idx += kRunThreads) {
-    const int i = idx % kRunTokens, d8 = idx / kRunTokens;
-    if (i >= nt) continue;
-    const uint4 raw = __ldg(reinterpret_cast<const uint4*>(
-        value + (int64_t)(t0 + i) * value_stride + head * head_size + d8 * 8));
-    const T* e = reinterpret_cast<const T*>(&raw);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       uint8_t* dst = vs_smem + (size_t)(d8 * 8 + k) * pitch + (a + i) * CES;
-      if constexpr (KV == B200PA_KV_AUTO) *reinterpret_cast<T*>(dst) = e[k];
-      else *dst = fp8_quant<KV>(Scalar<ST>::to_float(e[k]), vs);
+      if constexpr (KV == B200PA_KV_AUTO) *reinterpret_cast<T*>(dst) = ve[k];
+      else *dst = fp8_quant<KV>(Scalar<ST>::to_float(ve[k]), vs);
     }
   }
   __syncthreads();
+  const bool run = run_s != 0;
+
+  // ---- K: one 16-byte cache chunk per (chunk, token), lanes along the tokens: the 16 tokens
+  // of a block are one contiguous 256-byte run per chunk
+  const int cph = head_size / X;
+  for (int idx = threadIdx.x; idx < nt * cph; idx += kRunThreads) {
+    const int xi = idx / nt, i = idx - xi * nt;
+    const int blk = blk_s[i];
+    if (blk < 0) continue;
+    const uint4 v = *reinterpret_cast<const uint4*>(ks_smem + (size_t)i * krow + xi * 16);
+    *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(key_cache) + blk * blk_bytes + head_bytes +
+                              ((int64_t)xi * block_size + off_s[i]) * 16) = v;
+  }
+
+  // ---- V
+  if (!run) {
+    // per element at a stride of block_size (lanes along the tokens: neighbours in one block
+    // share sectors); the staged row of head element d holds token i at (a + i)
+    for (int idx = threadIdx.x; idx < nt * head_size; idx += kRunThreads) {
+      const int d = idx / nt, i = idx - d * nt;
+      const int blk = blk_s[i];
+      if (blk < 0) continue;
+      const uint8_t* src = vs_smem + (size_t)d * pitch + (a + i) * CES;
+      uint8_t* dst = reinterpret_cast<uint8_t*>(value_cache) + blk * blk_bytes + head_bytes +
+                     ((int64_t)d * block_size + off_s[i]) * CES;
+      if constexpr (CES == 2) *reinterpret_cast<uint16_t*>(dst) = *reinterpret_cast<const uint16_t*>(src);
+      else *dst = *src;
+    }
+    return;
+  }
   // copy out: (block j, row d, 16-byte group g) -- for a full block the rows of one head are one
   // contiguous run of head_size * block_size elements
   const int gpb = block_size * CES / 16 > 0 ? block_size * CES / 16 : 1;   // groups per block row
   const int gbytes = block_size * CES < 16 ? block_size * CES : 16;          // (block_size 8, fp8: 8)
   const int nblk = (a + nt + block_size - 1) / block_size;
   const int lo_b = a * CES, hi_b = (a + nt) * CES;     // valid byte range of a staged row
-  for (int idx = threadIdx.x; idx < nblk * head_size * gpb; idx += kRunThreads) {
-    const int j = idx / (head_size * gpb);
-    const int rem = idx - j * head_size * gpb;
+  const int per_blk = head_size * gpb;
+  for (int idx = threadIdx.x; idx < nblk * per_blk; idx += kRunThreads) {
+    const int j = idx / per_blk;
+    const int rem = idx - j * per_blk;
     const int d = rem / gpb, g = rem - d * gpb;
     const int tok = max(0, j * block_size - a);        // first token of the tile in block j
-    const int64_t phys = slots_s[tok] / block_size;
     const int b0 = j * block_size * CES + g * gbytes;  // byte offset in the staged row
     const uint8_t* src = vs_smem + (size_t)d * pitch + b0;
-    uint8_t* dst = reinterpret_cast<uint8_t*>(value_cache) +
-                   (phys * blk_elems + head_elems + (int64_t)d * block_size) * CES +
-                   g * gbytes;
+    uint8_t* dst = reinterpret_cast<uint8_t*>(value_cache) + blk_s[tok] * blk_bytes + head_bytes +
+                   (int64_t)d * block_size * CES + g * gbytes;
     if (gbytes == 16 && b0 >= lo_b && b0 + 16 <= hi_b) {
       *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
     } else {
@@ -403,10 +406,11 @@ int launch_reshape_and_cache(const void* key, const void* value, void* key_cache
                       ((value_stride * es) % 16 == 0) && head_size % 8 == 0 &&
                       (block_size == 8 || block_size == 16 || block_size == 32) &&
                       num_heads <= 65535 &&
-                      head_size * (kRunTokens / block_size + 1) * block_size * cache_es <= 40960;
+                      head_size * (kRunTokens / block_size + 1) * block_size * cache_es +
+                              kRunTokens * (head_size * cache_es + 16) <= 47104;
   if (run_ok) {
     const int pitch = (kRunTokens / block_size + 1) * block_size * cache_es;
-    const int smem = head_size * pitch;
+    const int smem = head_size * pitch + kRunTokens * (head_size * cache_es + 16);
     dim3 grid((num_tokens + kRunTokens - 1) / kRunTokens, num_heads);
 #define RUN_CASE(ST_, KV_)                                                                     \
     reshape_and_cache_run_kernel<ST_, KV_><<<grid, kRunThreads, smem, stream>>>(               \

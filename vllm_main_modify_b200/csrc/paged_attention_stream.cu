@@ -236,6 +236,8 @@ struct StreamParams {
   int num_seqs, num_heads, num_kv_heads, group;       // group = num_heads / num_kv_heads
   int h_tiles;                                         // ceil(group / 8)
   int max_num_blocks_per_seq;
+  // block-sparse attention (attention_kernels.cuh:207-251 of the reference); vert_stride <= 1: off
+  int bs_vert_stride, bs_local_blocks, bs_block_size, bs_head_sliding_step, bs_tp_rank;
   int num_workers;                                     // gridDim.x * NW of the main kernel
   int nw;                                              // NW: warps per CTA of the main kernel
   float scale;
@@ -250,6 +252,13 @@ __host__ __device__ constexpr int slot_floats(int d) { return 8 * d + 16; }
 // first launch on a workspace and left zero by every launch; at a fixed offset so that launches
 // of different shapes can share one workspace.
 constexpr int kCounterBytes = 4096;
+
+// flash layout: bytes of a token row of one head in shared memory -- its data plus at least 16
+// bytes, an ODD number of 16-byte units so that the 8 rows of an ldmatrix fall into 8 different
+// bank groups
+__host__ __device__ constexpr int flash_row_bytes(int row_data) {
+  return ((row_data + 16) / 16) % 2 ? row_data + 16 : row_data + 32;
+}
 
 template <int PPS> __device__ __forceinline__ int stages_of(int len) {
   return len <= 0 ? 0 : (len + kBS * PPS - 1) / (kBS * PPS);
@@ -382,7 +391,7 @@ paged_attention_stream_kernel(const StreamParams p) {
   constexpr int CES = FP8 ? 1 : 2;                           // cache element bytes
   constexpr int PAGE_BYTES = D * kBS * CES;                  // one K (or V) page of one kv head
   constexpr int ROW_DATA = D * CES;                          // flash: one token row of one head
-  constexpr int ROWB = ROW_DATA + 16;                        // ... and its padded shared-memory row
+  constexpr int ROWB = flash_row_bytes(ROW_DATA);            // ... and its padded shared-memory row
   constexpr int PAGE_SMEM = FLASH ? kBS * ROWB : PAGE_BYTES; // shared-memory footprint of a page
   constexpr int STAGE_BYTES = PPS * 2 * PAGE_SMEM;
   constexpr bool DPERM = FLASH && FP8;                       // see store_out_tile
@@ -394,11 +403,14 @@ paged_attention_stream_kernel(const StreamParams p) {
   constexpr int VRS = BSZ * CES;                             // x-packed V: bytes per head-element row
   static_assert(BSZ == 16 || BSZ == 32, "block size");
   static_assert(PPS % TPB == 0 && 32 % BPS == 0, "a stage holds whole cache blocks");
-  static_assert(!FLASH || BSZ == 16, "the flash-layout variant serves block size 16");
-  // tile g of a stage: block g / TPB, half g % TPB
-  auto k_tile = [](int g) { return (g / TPB) * 2 * BLOCK_SMEM + (g % TPB) * (FLASH ? 0 : kBS * 16); };
+  // tile g of a stage: block g / TPB, half g % TPB (x-packed: inside the block's K / V run;
+  // flash layout: every 16-token tile has its own K and V region of padded rows)
+  auto k_tile = [](int g) {
+    return FLASH ? g * 2 * PAGE_SMEM : (g / TPB) * 2 * BLOCK_SMEM + (g % TPB) * (kBS * 16);
+  };
   auto v_tile = [](int g) {
-    return (g / TPB) * 2 * BLOCK_SMEM + BLOCK_SMEM + (g % TPB) * (FLASH ? 0 : kBS * CES);
+    return FLASH ? g * 2 * PAGE_SMEM + PAGE_SMEM
+                 : (g / TPB) * 2 * BLOCK_SMEM + BLOCK_SMEM + (g % TPB) * (kBS * CES);
   };
   constexpr int KSTEPS = D / 16;                             // QK k-steps
   constexpr int MT = D / 16;                                 // PV m-tiles (16 head elements each)
@@ -508,7 +520,7 @@ paged_attention_stream_kernel(const StreamParams p) {
       // dealt to the lanes so that a warp instruction covers whole rows; every lane arrives
       // once per stage on the stage's mbarrier (expected count 32).
       constexpr int GR = ROW_DATA / 16;            // granules per token row
-      constexpr int PER_LANE = kBS * GR / 32;      // granules per lane per K (or V) page
+      constexpr int PER_LANE = (kBS * GR + 31) / 32;   // granules per lane per K (or V) page
       const int s = ip % STAGES;
       const uint32_t bar = bar0 + 8 * s;
       const int kvh = pc.vh / p.h_tiles;
@@ -519,15 +531,18 @@ paged_attention_stream_kernel(const StreamParams p) {
 #pragma unroll
       for (int g = 0; g < PPS; ++g) {
         if (g < npg) {
-          const int64_t boff = (int64_t)phys[g] * blk_stride_bytes;
+          // tile g: block g / TPB of the stage, tokens (g % TPB) * 16 .. + 15 of it
+          const int64_t boff = (int64_t)phys[g / TPB] * blk_stride_bytes + (g % TPB) * kBS * tsb;
 #pragma unroll
           for (int i = 0; i < PER_LANE; ++i) {
             const int idx = i * 32 + lane;
-            const int row = idx / GR, col = idx % GR;
-            const int64_t goff = boff + row * tsb + col * 16;
-            const uint32_t soff = g * 2 * PAGE_SMEM + row * ROWB + col * 16;
-            cp_async_16(dst + soff, kc + goff, policy);
-            cp_async_16(dst + soff + PAGE_SMEM, vc + goff, policy);
+            if ((kBS * GR) % 32 == 0 || idx < kBS * GR) {
+              const int row = idx / GR, col = idx % GR;
+              const int64_t goff = boff + row * tsb + col * 16;
+              const uint32_t soff = g * 2 * PAGE_SMEM + row * ROWB + col * 16;
+              cp_async_16(dst + soff, kc + goff, policy);
+              cp_async_16(dst + soff + PAGE_SMEM, vc + goff, policy);
+            }
           }
         }
       }
@@ -563,6 +578,9 @@ paged_attention_stream_kernel(const StreamParams p) {
   float slope_l2[2];
   int head0 = 0, heads_valid = 0;
   const bool has_alibi = p.alibi_slopes != nullptr;
+  // block-sparse: per query head the offset of its vertical stripes, per piece the query's block
+  const bool block_sparse = p.bs_vert_stride > 1;
+  int bs_off[2] = {0, 0}, bs_qblk = 0;
   float sl2 = p.scale * kLog2e;
   float out_scale = 1.f;
   float ks_raw = 1.f;           // k_scale itself (the fused cache write quantises with it)
@@ -672,6 +690,15 @@ paged_attention_stream_kernel(const StreamParams p) {
       msub[h] = -INFINITY;
       lsum[h] = 0.f;
     }
+    if (block_sparse) {
+      // attention_kernels.cuh:209-220: stripes slide with the query head (step >= 0) or the kv head
+      bs_qblk = (cc.len - 1) / p.bs_block_size;
+#pragma unroll
+      for (int h = 0; h < 2; ++h)
+        bs_off[h] = p.bs_head_sliding_step >= 0
+            ? (p.bs_tp_rank * p.num_heads + head0 + 2 * q4 + h) * p.bs_head_sliding_step + 1
+            : (p.bs_tp_rank * p.num_kv_heads + kvh) * (-p.bs_head_sliding_step) + 1;
+    }
 #pragma unroll
     for (int mt = 0; mt < MT; ++mt) o[mt][0] = o[mt][1] = o[mt][2] = o[mt][3] = 0.f;
   };
@@ -747,8 +774,11 @@ paged_attention_stream_kernel(const StreamParams p) {
     if (p.new_key != nullptr && cc.st == cc.ns && nt_slot >= 0) {
       constexpr int X = 16 / CES;       // elements per 16-byte chunk of the x-packed K layout
       const int t = cc.len - 1 - page0 * kBS;
-      uint8_t* pg = ring + s * STAGE_BYTES + ((t >> 4) / TPB) * (2 * BLOCK_SMEM);   // the block
-      const int tt = t & (BSZ - 1);                                                 // token in it
+      // x-packed: the token's cache block in the stage and its offset in it; flash: its 16-token
+      // tile and its row in it
+      uint8_t* pg = ring + s * STAGE_BYTES +
+                    (FLASH ? (t >> 4) * (2 * PAGE_SMEM) : ((t >> 4) / TPB) * (2 * BLOCK_SMEM));
+      const int tt = FLASH ? (t & (kBS - 1)) : (t & (BSZ - 1));
       const int kvh = cc.vh / p.h_tiles;
       const bool to_global = cc.vh == kvh * p.h_tiles;
       const int64_t goff = (nt_slot / BSZ) * blk_stride_bytes + kvh * head_stride_bytes;
@@ -853,12 +883,22 @@ paged_attention_stream_kernel(const StreamParams p) {
 #pragma unroll
       for (int g = 0; g < PPS; ++g) {
         const int nv = cc.len - (tok0 + g * kBS);  // valid tokens of the page (<= 0: absent)
+        bool seen[2] = {true, true};
+        if (block_sparse) {
+          // attention_kernels.cuh:234-240: a cache block is attended by a head if it is one of
+          // the last local blocks or on one of the head's vertical stripes.  (The reference skips
+          // the other blocks; here they are streamed and masked -- same result.)
+          const int kb = ((page0 + g) / TPB) * BSZ / p.bs_block_size;
+          const bool local = kb > bs_qblk - p.bs_local_blocks;
+          seen[0] = local || ((kb + bs_off[0]) % p.bs_vert_stride == 0);
+          seen[1] = local || ((kb + bs_off[1]) % p.bs_vert_stride == 0);
+        }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const int tk = (j & 2) ? tokB : tokA;
           float t = fmaf(sc[g][j], sl2, (j & 1) ? neg1 : neg0);
           if (has_alibi) t += slope_l2[j & 1] * (float)(tok0 + g * kBS + tk - cc.len + 1);
-          d[g][j] = (g < npg && tk < nv) ? t : -INFINITY;
+          d[g][j] = (g < npg && tk < nv && seen[j & 1]) ? t : -INFINITY;
         }
       }
     };
@@ -934,17 +974,21 @@ paged_attention_stream_kernel(const StreamParams p) {
         // first 16 d, w4[1] the same for tokens + 8, w4[2], w4[3] for the next 16 d.  Rows of
         // the m-tile are assigned d = 2r (a[0], a[2]) and d = 2r + 1 (a[1], a[3]): DPERM.
 #pragma unroll
-        for (int gg = 0; gg < D / 32; ++gg) {
+        for (int gg = 0; gg < (D + 31) / 32; ++gg) {
+          // (D = 80 / 112: the last group has 16 head elements; the second half of its x4 reads
+          // the row's 16 bytes of padding -- valid memory, not used)
           uint32_t w4[4], a[4];
           ldmatrix_x4_trans(w4, vbase + gg * 32 + v_lane_off);
           fp8x4_to_f16x2x2<E5>(prmt<0x6420>(w4[0], w4[1]), a[0], a[2]);
           fp8x4_to_f16x2x2<E5>(prmt<0x7531>(w4[0], w4[1]), a[1], a[3]);
           if constexpr (MASKED) { a[0] &= m01; a[1] &= m01; a[2] &= m23; a[3] &= m23; }
           mma16816<false>(o[2 * gg], a, pb[g][0], pb[g][1]);
-          fp8x4_to_f16x2x2<E5>(prmt<0x6420>(w4[2], w4[3]), a[0], a[2]);
-          fp8x4_to_f16x2x2<E5>(prmt<0x7531>(w4[2], w4[3]), a[1], a[3]);
-          if constexpr (MASKED) { a[0] &= m01; a[1] &= m01; a[2] &= m23; a[3] &= m23; }
-          mma16816<false>(o[2 * gg + 1], a, pb[g][0], pb[g][1]);
+          if (32 * gg + 16 < D) {
+            fp8x4_to_f16x2x2<E5>(prmt<0x6420>(w4[2], w4[3]), a[0], a[2]);
+            fp8x4_to_f16x2x2<E5>(prmt<0x7531>(w4[2], w4[3]), a[1], a[3]);
+            if constexpr (MASKED) { a[0] &= m01; a[1] &= m01; a[2] &= m23; a[3] &= m23; }
+            mma16816<false>(o[2 * gg + 1 < MT ? 2 * gg + 1 : MT - 1], a, pb[g][0], pb[g][1]);
+          }
         }
       } else if constexpr (FP8) {
 #pragma unroll
@@ -1264,7 +1308,7 @@ template <int ST, bool FP8, int D, int NW, int STAGES, int PPS, int MINB, bool F
           int BSZ = 16, bool E5 = false>
 int launch_stream_t(StreamParams& p, int num_sms, int64_t workspace_bytes, cudaStream_t stream) {
   constexpr int CES = FP8 ? 1 : 2;
-  constexpr int SMEM = NW * STAGES * PPS * 2 * kBS * (FLASH ? D * CES + 16 : D * CES);
+  constexpr int SMEM = NW * STAGES * PPS * 2 * kBS * (FLASH ? flash_row_bytes(D * CES) : D * CES);
   auto kern = paged_attention_stream_kernel<ST, FP8, D, NW, STAGES, PPS, MINB, FLASH, BSZ, E5>;
   // per instantiation AND per device: the shared-memory opt-in is a per-device function
   // attribute (a process that drives several GPUs must set it on each)
@@ -1325,35 +1369,46 @@ int launch_stream_t(StreamParams& p, int num_sms, int64_t workspace_bytes, cudaS
 #ifndef STREAM_PART
 #define STREAM_PART 0
 #endif
-int launch_stream_flash(StreamParams& p, bool fp8, int scalar_type, int head_size, int num_sms,
-    int64_t workspace_bytes, cudaStream_t stream);
+int launch_stream_flash(StreamParams& p, bool fp8, int scalar_type, int head_size, int block_size,
+    int num_sms, int64_t workspace_bytes, cudaStream_t stream);
 int launch_stream_bs32(StreamParams& p, bool fp8, int scalar_type, int head_size, int num_sms,
     int64_t workspace_bytes, cudaStream_t stream);
 int launch_stream_other(StreamParams& p, bool fp8, int scalar_type, int head_size, int num_sms,
     int64_t workspace_bytes, cudaStream_t stream);
-int launch_stream_e5m2(StreamParams& p, int scalar_type, int head_size, int num_sms,
-    int64_t workspace_bytes, cudaStream_t stream);
+int launch_stream_e5m2(StreamParams& p, int scalar_type, int head_size, bool flash, int block_size,
+    int num_sms, int64_t workspace_bytes, cudaStream_t stream);
+int launch_stream_e5m2_wide(StreamParams& p, int scalar_type, int head_size, bool flash,
+    int block_size, int num_sms, int64_t workspace_bytes, cudaStream_t stream);
 
 #define STREAM_CALL(ST, FP8V, DV, NWV, SG, PP, MB, ...) \
   return launch_stream_t<ST, FP8V, DV, NWV, SG, PP, MB, ##__VA_ARGS__>(p, num_sms, workspace_bytes, stream)
 
 #if STREAM_PART == 1
-int launch_stream_flash(StreamParams& p, bool fp8, int scalar_type, int head_size, int num_sms,
-    int64_t workspace_bytes, cudaStream_t stream) {
-    // one instantiation per (scalar_t, cache type, head size): the default shapes of the
-    // x-packed kernel (the padded rows make the fp8 D=128 ring 216 KiB)
-#define STREAM_FLASH_BY_HEAD_SIZE(ST, NW128)                                                  \
+int launch_stream_flash(StreamParams& p, bool fp8, int scalar_type, int head_size, int block_size,
+    int num_sms, int64_t workspace_bytes, cudaStream_t stream) {
+    // one instantiation per (scalar_t, cache type, head size, block size): the shapes of the
+    // x-packed kernel where the padded rows fit (fp8 D=128: 8 warps x 3 stages = 216 KiB)
+#define STREAM_FLASH_BY_HEAD_SIZE(ST, BSV, NW128, S128, P128, S192, P192, NW256, S256, P256)             \
   switch (head_size) {                                                                       \
-    case 32:  if (fp8) { STREAM_CALL(ST, true, 32, 4, 3, 2, 2, true); }  else { STREAM_CALL(ST, false, 32, 4, 3, 2, 2, true); }  \
-    case 64:  if (fp8) { STREAM_CALL(ST, true, 64, 4, 3, 2, 2, true); }  else { STREAM_CALL(ST, false, 64, 4, 3, 2, 2, true); }  \
-    case 96:  if (fp8) { STREAM_CALL(ST, true, 96, 4, 3, 2, 2, true); }  else { STREAM_CALL(ST, false, 96, 4, 3, 2, 1, true); }  \
-    case 128: if (fp8) { STREAM_CALL(ST, true, 128, NW128, 3, 2, 1, true); } else { STREAM_CALL(ST, false, 128, 4, 4, 1, 1, true); } \
-    case 192: if (fp8) { STREAM_CALL(ST, true, 192, 4, 4, 2, 1, true); } else { STREAM_CALL(ST, false, 192, 4, 4, 1, 1, true); } \
-    case 256: if (fp8) { STREAM_CALL(ST, true, 256, 4, 3, 2, 1, true); } else { STREAM_CALL(ST, false, 256, 4, 3, 1, 1, true); } \
+    case 32:  if (fp8) { STREAM_CALL(ST, true, 32, 4, 3, 2, 2, true, BSV); }  else { STREAM_CALL(ST, false, 32, 4, 3, 2, 2, true, BSV); }  \
+    case 64:  if (fp8) { STREAM_CALL(ST, true, 64, 4, 3, 2, 2, true, BSV); }  else { STREAM_CALL(ST, false, 64, 4, 3, 2, 2, true, BSV); }  \
+    case 80:  if (fp8) { STREAM_CALL(ST, true, 80, 4, 3, 2, 2, true, BSV); }  else { STREAM_CALL(ST, false, 80, 4, 3, 2, 2, true, BSV); }  \
+    case 96:  if (fp8) { STREAM_CALL(ST, true, 96, 4, 3, 2, 2, true, BSV); }  else { STREAM_CALL(ST, false, 96, 4, 3, 2, 1, true, BSV); }  \
+    case 112: if (fp8) { STREAM_CALL(ST, true, 112, 4, 3, 2, 2, true, BSV); } else { STREAM_CALL(ST, false, 112, 4, 3, 2, 1, true, BSV); } \
+    case 128: if (fp8) { STREAM_CALL(ST, true, 128, 8, 3, 2, 1, true, BSV); } else { STREAM_CALL(ST, false, 128, NW128, S128, P128, 1, true, BSV); } \
+    case 192: if (fp8) { STREAM_CALL(ST, true, 192, 4, 4, 2, 1, true, BSV); } else { STREAM_CALL(ST, false, 192, 4, S192, P192, 1, true, BSV); } \
+    case 256: if (fp8) { STREAM_CALL(ST, true, 256, 4, 3, 2, 1, true, BSV); } else { STREAM_CALL(ST, false, 256, NW256, S256, P256, 1, true, BSV); } \
     default: return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: head size %d", head_size);  \
   }
-    if (scalar_type == B200PA_BF16) { STREAM_FLASH_BY_HEAD_SIZE(B200PA_BF16, 8) }
-    else { STREAM_FLASH_BY_HEAD_SIZE(B200PA_F16, 8) }
+    // 16-bit caches at head sizes >= 128: the launch shapes of the x-packed kernel for the same
+    // block size (same spans, same merge order: bitwise the same output); a stage holds whole
+    // cache blocks, so two tiles per stage with 32-token blocks
+    if (block_size == 32) {
+      if (scalar_type == B200PA_BF16) { STREAM_FLASH_BY_HEAD_SIZE(B200PA_BF16, 32, 4, 3, 2, 2, 2, 3, 2, 2) }
+      else { STREAM_FLASH_BY_HEAD_SIZE(B200PA_F16, 32, 4, 3, 2, 2, 2, 3, 2, 2) }
+    }
+    if (scalar_type == B200PA_BF16) { STREAM_FLASH_BY_HEAD_SIZE(B200PA_BF16, 16, 8, 2, 1, 4, 1, 4, 3, 1) }
+    else { STREAM_FLASH_BY_HEAD_SIZE(B200PA_F16, 16, 8, 2, 1, 4, 1, 4, 3, 1) }
 #undef STREAM_FLASH_BY_HEAD_SIZE
 }
 #elif STREAM_PART == 2
@@ -1387,7 +1442,7 @@ int launch_stream_other(StreamParams& p, bool fp8, int scalar_type, int head_siz
     case 80:  if (fp8) { STREAM_CALL(ST, true, 80, 4, 3, 2, 2); } else { STREAM_CALL(ST, false, 80, 4, 3, 2, 2); }  \
     case 96:  if (fp8) { STREAM_CALL(ST, true, 96, 4, 3, 2, 2); }  else { STREAM_CALL(ST, false, 96, 4, 3, 2, 1); }  \
     case 112: if (fp8) { STREAM_CALL(ST, true, 112, 4, 3, 2, 2); } else { STREAM_CALL(ST, false, 112, 4, 3, 2, 1); } \
-    case 128: if (fp8) { STREAM_CALL(ST, true, 128, 4, 3, 2, 2); } else { STREAM_CALL(ST, false, 128, 4, 4, 1, 1); } \
+    case 128: if (fp8) { STREAM_CALL(ST, true, 128, 6, 2, 2, 2); } else { STREAM_CALL(ST, false, 128, 8, 2, 1, 1); } \
     case 192: if (fp8) { STREAM_CALL(ST, true, 192, 4, 4, 2, 1); } else { STREAM_CALL(ST, false, 192, 4, 4, 1, 1); } \
     case 256: if (fp8) { STREAM_CALL(ST, true, 256, 4, 3, 2, 1); } else { STREAM_CALL(ST, false, 256, 4, 3, 1, 1); } \
     default: return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: head size %d", head_size);  \
@@ -1396,27 +1451,47 @@ int launch_stream_other(StreamParams& p, bool fp8, int scalar_type, int head_siz
   else { STREAM_BY_HEAD_SIZE(B200PA_F16) }
 #undef STREAM_BY_HEAD_SIZE
 }
-#elif STREAM_PART == 4
-// fp8_e5m2 caches (x-packed, 16-token blocks): the fp8 launch shapes of launch_stream_other
-int launch_stream_e5m2(StreamParams& p, int scalar_type, int head_size, int num_sms,
-    int64_t workspace_bytes, cudaStream_t stream) {
-#define STREAM_E5M2_BY_HEAD_SIZE(ST)                                              \
+#elif STREAM_PART == 4 || STREAM_PART == 5
+// fp8_e5m2 caches: the fp8 launch shapes of launch_stream_other / _bs32 / _flash.  Part 4: the
+// x-packed layout, part 5: the token-major layout.
+#define STREAM_E5M2_BY_HEAD_SIZE(ST, FL, BSV)                                     \
   switch (head_size) {                                                           \
-    case 32:  STREAM_CALL(ST, true, 32, 4, 3, 2, 2, false, 16, true);            \
-    case 64:  STREAM_CALL(ST, true, 64, 4, 3, 2, 2, false, 16, true);            \
-    case 80:  STREAM_CALL(ST, true, 80, 4, 3, 2, 2, false, 16, true);            \
-    case 96:  STREAM_CALL(ST, true, 96, 4, 3, 2, 2, false, 16, true);            \
-    case 112: STREAM_CALL(ST, true, 112, 4, 3, 2, 2, false, 16, true);           \
-    case 128: STREAM_CALL(ST, true, 128, 6, 2, 2, 2, false, 16, true);           \
-    case 192: STREAM_CALL(ST, true, 192, 4, 4, 2, 1, false, 16, true);           \
-    case 256: STREAM_CALL(ST, true, 256, 4, 3, 2, 1, false, 16, true);           \
+    case 32:  STREAM_CALL(ST, true, 32, 4, 3, 2, 2, FL, BSV, true);              \
+    case 64:  STREAM_CALL(ST, true, 64, 4, 3, 2, 2, FL, BSV, true);              \
+    case 80:  STREAM_CALL(ST, true, 80, 4, 3, 2, 2, FL, BSV, true);              \
+    case 96:  STREAM_CALL(ST, true, 96, 4, 3, 2, 2, FL, BSV, true);              \
+    case 112: STREAM_CALL(ST, true, 112, 4, 3, 2, 2, FL, BSV, true);             \
+    case 128: STREAM_CALL(ST, true, 128, (FL ? 8 : 6), (FL ? 3 : 2), 2, (FL ? 1 : 2), FL, BSV, true); \
+    case 192: STREAM_CALL(ST, true, 192, 4, 4, 2, 1, FL, BSV, true);             \
+    case 256: STREAM_CALL(ST, true, 256, 4, 3, 2, 1, FL, BSV, true);             \
     default: return set_error(B200PA_ERR_UNSUPPORTED,                            \
                               "stream kernel: head size %d with an fp8_e5m2 cache", head_size); \
   }
-  if (scalar_type == B200PA_BF16) { STREAM_E5M2_BY_HEAD_SIZE(B200PA_BF16) }
-  else { STREAM_E5M2_BY_HEAD_SIZE(B200PA_F16) }
-#undef STREAM_E5M2_BY_HEAD_SIZE
+#if STREAM_PART == 4
+int launch_stream_e5m2(StreamParams& p, int scalar_type, int head_size, bool flash, int block_size,
+    int num_sms, int64_t workspace_bytes, cudaStream_t stream) {
+  if (flash)
+    return launch_stream_e5m2_wide(p, scalar_type, head_size, flash, block_size, num_sms,
+                                   workspace_bytes, stream);
+  if (block_size == 32) {
+    if (scalar_type == B200PA_BF16) { STREAM_E5M2_BY_HEAD_SIZE(B200PA_BF16, false, 32) }
+    else { STREAM_E5M2_BY_HEAD_SIZE(B200PA_F16, false, 32) }
+  }
+  if (scalar_type == B200PA_BF16) { STREAM_E5M2_BY_HEAD_SIZE(B200PA_BF16, false, 16) }
+  else { STREAM_E5M2_BY_HEAD_SIZE(B200PA_F16, false, 16) }
 }
+#else
+int launch_stream_e5m2_wide(StreamParams& p, int scalar_type, int head_size, bool flash,
+    int block_size, int num_sms, int64_t workspace_bytes, cudaStream_t stream) {
+  if (block_size == 32) {
+    if (scalar_type == B200PA_BF16) { STREAM_E5M2_BY_HEAD_SIZE(B200PA_BF16, true, 32) }
+    else { STREAM_E5M2_BY_HEAD_SIZE(B200PA_F16, true, 32) }
+  }
+  if (scalar_type == B200PA_BF16) { STREAM_E5M2_BY_HEAD_SIZE(B200PA_BF16, true, 16) }
+  else { STREAM_E5M2_BY_HEAD_SIZE(B200PA_F16, true, 16) }
+}
+#endif
+#undef STREAM_E5M2_BY_HEAD_SIZE
 #else
 // Upper bound of the workspace any stream launch on a device with `num_sms` SMs needs.
 int64_t stream_workspace_bytes(int num_sms, int head_size) {
@@ -1429,18 +1504,16 @@ bool stream_supported(const void* query, const void* key_cache, const void* valu
                       int num_heads, int num_kv_heads, int head_size, int block_size,
                       int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
                       int scalar_type, int kv_dtype, int blocksparse_vert_stride) {
-  if (blocksparse_vert_stride > 1) return false;
+  (void)blocksparse_vert_stride;   // block-sparse attention is served (masked, not skipped)
   if (block_size != 16 && block_size != 32) return false;
   // the reference's head sizes that are multiples of 16 (120 stays on the generic kernel)
   if (head_size != 32 && head_size != 64 && head_size != 80 && head_size != 96 &&
       head_size != 112 && head_size != 128 && head_size != 192 && head_size != 256)
     return false;
   if (scalar_type != B200PA_BF16 && scalar_type != B200PA_F16) return false;
-  if (kv_dtype == B200PA_KV_FP8_E5M2) {   // e5m2: 16-token blocks
-    if (block_size != 16) return false;
-  } else if (kv_dtype != B200PA_KV_AUTO && kv_dtype != B200PA_KV_FP8_E4M3) {
+  if (kv_dtype != B200PA_KV_AUTO && kv_dtype != B200PA_KV_FP8_E4M3 &&
+      kv_dtype != B200PA_KV_FP8_E5M2)
     return false;
-  }
   if (num_kv_heads <= 0 || num_heads % num_kv_heads != 0) return false;
   const int ces = kv_dtype == B200PA_KV_AUTO ? 2 : 1;
   auto aligned = [](const void* p, uintptr_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; };
@@ -1457,11 +1530,12 @@ bool stream_flash_supported(const void* query, const void* key_cache, const void
                             int num_heads, int num_kv_heads, int head_size, int block_size,
                             int64_t q_stride, int64_t block_stride, int64_t token_stride,
                             int64_t head_stride, int scalar_type, int kv_dtype) {
-  if (block_size != kBS) return false;
-  if (head_size != 32 && head_size != 64 && head_size != 96 && head_size != 128 &&
-      head_size != 192 && head_size != 256) return false;
+  if (block_size != 16 && block_size != 32) return false;
+  if (head_size != 32 && head_size != 64 && head_size != 80 && head_size != 96 &&
+      head_size != 112 && head_size != 128 && head_size != 192 && head_size != 256) return false;
   if (scalar_type != B200PA_BF16 && scalar_type != B200PA_F16) return false;
-  if (kv_dtype != B200PA_KV_AUTO && kv_dtype != B200PA_KV_FP8_E4M3) return false;
+  if (kv_dtype != B200PA_KV_AUTO && kv_dtype != B200PA_KV_FP8_E4M3 &&
+      kv_dtype != B200PA_KV_FP8_E5M2) return false;
   if (num_kv_heads <= 0 || num_heads % num_kv_heads != 0) return false;
   const int ces = kv_dtype == B200PA_KV_AUTO ? 2 : 1;
   auto aligned = [](const void* p, uintptr_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; };
@@ -1488,8 +1562,8 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
                   int max_num_blocks_per_seq, const int32_t* seq_lens, const float* alibi_slopes,
                   int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
                   int scalar_type, int kv_dtype, const float* k_scale, const float* v_scale,
-                  const FusedWrite* fused, int64_t flash_token_stride, int block_size, int num_sms,
-                  int tune, cudaStream_t stream) {
+                  const FusedWrite* fused, const BlockSparse* bsp, int64_t flash_token_stride,
+                  int block_size, int num_sms, int tune, cudaStream_t stream) {
   // flash_token_stride > 0: token-major cache (kv_block_stride / flash_token_stride /
   // kv_head_stride are the strides of [block][token][head][D]); 0: the x-packed layout
   if (!workspace || (reinterpret_cast<uintptr_t>(workspace) & 15u))
@@ -1526,18 +1600,22 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
   p.group = num_heads / num_kv_heads;
   p.h_tiles = (p.group + 7) / 8;
   p.max_num_blocks_per_seq = max_num_blocks_per_seq;
+  const bool sparse = bsp != nullptr && bsp->enabled;
+  p.bs_vert_stride = sparse ? bsp->vert_stride : 0;
+  p.bs_local_blocks = sparse ? bsp->local_blocks : 0;
+  p.bs_block_size = sparse ? bsp->block_size : 1;
+  p.bs_head_sliding_step = sparse ? bsp->head_sliding_step : 0;
+  p.bs_tp_rank = sparse ? bsp->tp_rank : 0;
   p.num_workers = 0;
   p.nw = 0;
   p.scale = scale;
   const bool fp8 = kv_dtype == B200PA_KV_FP8_E4M3;
-  if (kv_dtype == B200PA_KV_FP8_E5M2) {
-    if (flash_token_stride > 0 || block_size != 16)
-      return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: fp8_e5m2 serves the x-packed "
-                       "layout with 16-token blocks");
-    return launch_stream_e5m2(p, scalar_type, head_size, num_sms, workspace_bytes, stream);
-  }
+  if (kv_dtype == B200PA_KV_FP8_E5M2)
+    return launch_stream_e5m2(p, scalar_type, head_size, flash_token_stride > 0, block_size, num_sms,
+                              workspace_bytes, stream);
   if (flash_token_stride > 0)
-    return launch_stream_flash(p, fp8, scalar_type, head_size, num_sms, workspace_bytes, stream);
+    return launch_stream_flash(p, fp8, scalar_type, head_size, block_size, num_sms, workspace_bytes,
+                               stream);
   if (block_size == 32)
     return launch_stream_bs32(p, fp8, scalar_type, head_size, num_sms, workspace_bytes, stream);
   // <ST, FP8, D, NW, STAGES, PPS, MINB>: fp8 stage = PPS x 4 KiB, 16-bit stage = PPS x 8 KiB (D=128).

@@ -30,6 +30,9 @@ SHAPES = [
     ("d80_fp8", 64, 32, 32, 80, 4096, "fp8"),
     ("d112_fp8_gqa4", 64, 32, 8, 112, 8192, "fp8"),
     ("llama8b_e5m2", 256, 32, 8, 128, 8192, "fp8_e5m2"),
+    ("d192_bf16", 64, 24, 8, 192, 4096, "auto"),
+    ("d96_fp8", 64, 32, 8, 96, 8192, "fp8"),
+    ("d64_bf16_gqa8", 128, 64, 8, 64, 4096, "auto"),
     # 32-token cache blocks
     ("llama8b_bs32_bf16", 64, 32, 8, 128, 4096, "auto", 32),
     ("llama8b_bs32_fp8", 256, 32, 8, 128, 8192, "fp8", 32),
@@ -57,6 +60,11 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--only", default="", help="comma-separated shape names (default: all)")
+    ap.add_argument("--tune", type=int, default=0, help="launch-shape candidate (test hook)")
+    ap.add_argument("--sustain", type=float, default=0.0,
+                    help="also run the stream kernel back to back for this many seconds and "
+                         "report the rate of the last third (the power-capped regime)")
+    ap.add_argument("--stream-only", action="store_true")
     args = ap.parse_args()
     from vllm_main_modify_b200 import _custom_ops as ops
     from vllm_main_modify_b200 import _native
@@ -107,15 +115,32 @@ def main():
                                    one, one, 0, 0, 0, 64, 0)
 
         outs = {}
+        _native.set_stream_tune(args.tune)
         for impl, label in ((_native.IMPL_STREAM, "stream"), (_native.IMPL_GENERIC, "generic")):
+            if args.stream_only and label != "stream":
+                continue
             _native.set_impl(impl)
             ms = timeit(ours, args.iters)
             outs[label] = out.clone()
-            print(json.dumps({"shape": name, "B": B, "H": H, "Hkv": Hkv, "D": D, "ctx": ctx,
-                              "block_size": BS, "kv": kv, "impl": label, "ms": round(ms, 4),
-                              "gbs": round(nbytes / ms / 1e6, 1)}), flush=True)
+            rec = {"shape": name, "B": B, "H": H, "Hkv": Hkv, "D": D, "ctx": ctx,
+                   "block_size": BS, "kv": kv, "impl": label, "tune": args.tune,
+                   "ms": round(ms, 4), "gbs": round(nbytes / ms / 1e6, 1)}
+            if label == "stream" and args.sustain > 0:
+                n = max(30, int(args.sustain * 1e3 / ms))
+                marks = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+                marks[0].record()
+                for k in range(3):
+                    for _ in range(n // 3):
+                        ours()
+                    marks[k + 1].record()
+                torch.cuda.synchronize()
+                last = marks[2].elapsed_time(marks[3]) / (n // 3)
+                first = marks[0].elapsed_time(marks[1]) / (n // 3)
+                rec["sustained_first_third_gbs"] = round(nbytes / first / 1e6, 1)
+                rec["sustained_last_third_gbs"] = round(nbytes / last / 1e6, 1)
+            print(json.dumps(rec), flush=True)
         _native.set_impl(_native.IMPL_AUTO)
-        if ref is not None:
+        if ref is not None and not args.stream_only:
             ms = timeit(theirs, args.iters)
             err = float((out.float() - outs["stream"].float()).abs().max())
             print(json.dumps({"shape": name, "impl": "reference_cuda", "ms": round(ms, 4),

@@ -136,8 +136,7 @@ reshape_and_cache_run_kernel(
   static_assert(ST != B200PA_F32, "16-bit sources");
   constexpr int CES = KV == B200PA_KV_AUTO ? 2 : 1;     // cache element bytes
   constexpr int X = 16 / CES;                            // elements per 16-byte K chunk
-  // [head_size][pitch] V rows laid out as in the cache, then [kRunTokens][head_size * CES + 16] K
-  extern __shared__ __align__(16) uint8_t run_smem[];
+  extern __shared__ __align__(16) uint8_t vs_smem[];     // [head_size][pitch] V rows as in the cache
   __shared__ int blk_s[kRunTokens];    // physical block of the token, -1: padding slot
   __shared__ int off_s[kRunTokens];    // slot offset in its block
   __shared__ int run_s;
@@ -164,79 +163,93 @@ reshape_and_cache_run_kernel(
     ok = __all_sync(0xffffffffu, ok);
     if (threadIdx.x == 0) run_s = ok ? 1 : 0;
   }
+  __syncthreads();
+  const bool run = run_s != 0;
   float ks = 1.f, vs = 1.f;
   if constexpr (KV != B200PA_KV_AUTO) { ks = *k_scale; vs = *v_scale; }
   const int64_t blk_bytes = (int64_t)num_heads * head_size * block_size * CES;
   const int64_t head_bytes = (int64_t)head * head_size * block_size * CES;
-  const int a = off_s[0];                               // slot offset of the tile's first token
-  const int pitch = (kRunTokens / block_size + 1) * block_size * CES;   // staged V row, bytes
-  uint8_t* const vs_smem = run_smem;
-  const int krow = head_size * CES + 16;                // staged K row (odd 16-byte units)
-  uint8_t* const ks_smem = run_smem + (size_t)head_size * pitch;
-  const int d8n = head_size / 8;                        // 16-byte groups of a source row
 
-  // ---- stage K (token-major, cache bytes) and V (transposed: [d][slot offset]); the loads of
-  // one token's row are coalesced, lanes along the head elements
-  for (int idx = threadIdx.x; idx < nt * d8n; idx += kRunThreads) {
-    const int i = idx / d8n, d8 = idx - i * d8n;
-    const uint4 kraw = __ldg(reinterpret_cast<const uint4*>(
-        key + (int64_t)(t0 + i) * key_stride + head * head_size + d8 * 8));
-    const uint4 vraw = __ldg(reinterpret_cast<const uint4*>(
-        value + (int64_t)(t0 + i) * value_stride + head * head_size + d8 * 8));
-    const T* ke = reinterpret_cast<const T*>(&kraw);
-    const T* ve = reinterpret_cast<const T*>(&vraw);
-    if constexpr (KV == B200PA_KV_AUTO) {
-      *reinterpret_cast<uint4*>(ks_smem + (size_t)i * krow + d8 * 16) = kraw;
-    } else {
-      uint32_t w[2];
-#pragma unroll
-      for (int k = 0; k < 2; ++k) {
-        const uint32_t lo = fp8_quant2<KV>(Scalar<ST>::to_float(ke[4 * k + 0]),
-                                           Scalar<ST>::to_float(ke[4 * k + 1]), ks);
-        const uint32_t hi = fp8_quant2<KV>(Scalar<ST>::to_float(ke[4 * k + 2]),
-                                           Scalar<ST>::to_float(ke[4 * k + 3]), ks);
-        w[k] = lo | (hi << 16);
-      }
-      *reinterpret_cast<uint2*>(ks_smem + (size_t)i * krow + d8 * 8) = make_uint2(w[0], w[1]);
-    }
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      uint8_t* dst = vs_smem + (size_t)(d8 * 8 + k) * pitch + (a + i) * CES;
-      if constexpr (KV == B200PA_KV_AUTO) *reinterpret_cast<T*>(dst) = ve[k];
-      else *dst = fp8_quant<KV>(Scalar<ST>::to_float(ve[k]), vs);
-    }
-  }
-  __syncthreads();
-  const bool run = run_s != 0;
-
-  // ---- K: one 16-byte cache chunk per (chunk, token), lanes along the tokens: the 16 tokens
-  // of a block are one contiguous 256-byte run per chunk
+  // ---- K: one 16-byte cache chunk per (token, chunk), lanes along the chunks of a token row
   const int cph = head_size / X;
+#pragma unroll 2
   for (int idx = threadIdx.x; idx < nt * cph; idx += kRunThreads) {
-    const int xi = idx / nt, i = idx - xi * nt;
+    const int i = idx / cph, xi = idx - i * cph;
     const int blk = blk_s[i];
     if (blk < 0) continue;
-    const uint4 v = *reinterpret_cast<const uint4*>(ks_smem + (size_t)i * krow + xi * 16);
-    *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(key_cache) + blk * blk_bytes + head_bytes +
-                              ((int64_t)xi * block_size + off_s[i]) * 16) = v;
+    const T* src = key + (int64_t)(t0 + i) * key_stride + head * head_size + xi * X;
+    uint8_t* dst = reinterpret_cast<uint8_t*>(key_cache) + blk * blk_bytes + head_bytes +
+                   ((int64_t)xi * block_size + off_s[i]) * 16;
+    if constexpr (KV == B200PA_KV_AUTO) {
+      *reinterpret_cast<uint4*>(dst) = __ldg(reinterpret_cast<const uint4*>(src));
+    } else {
+      uint4 raw[2];
+      raw[0] = __ldg(reinterpret_cast<const uint4*>(src));
+      raw[1] = __ldg(reinterpret_cast<const uint4*>(src) + 1);
+      const T* e = reinterpret_cast<const T*>(raw);
+      uint32_t w[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const uint32_t lo = fp8_quant2<KV>(Scalar<ST>::to_float(e[4 * k + 0]),
+                                           Scalar<ST>::to_float(e[4 * k + 1]), ks);
+        const uint32_t hi = fp8_quant2<KV>(Scalar<ST>::to_float(e[4 * k + 2]),
+                                           Scalar<ST>::to_float(e[4 * k + 3]), ks);
+        w[k] = lo | (hi << 16);
+      }
+      *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
   }
 
   // ---- V
+  const int d8n = head_size / 8;                       // 16-byte groups of a source row
   if (!run) {
-    // per element at a stride of block_size (lanes along the tokens: neighbours in one block
-    // share sectors); the staged row of head element d holds token i at (a + i)
-    for (int idx = threadIdx.x; idx < nt * head_size; idx += kRunThreads) {
-      const int d = idx / nt, i = idx - d * nt;
-      const int blk = blk_s[i];
-      if (blk < 0) continue;
-      const uint8_t* src = vs_smem + (size_t)d * pitch + (a + i) * CES;
-      uint8_t* dst = reinterpret_cast<uint8_t*>(value_cache) + blk * blk_bytes + head_bytes +
-                     ((int64_t)d * block_size + off_s[i]) * CES;
-      if constexpr (CES == 2) *reinterpret_cast<uint16_t*>(dst) = *reinterpret_cast<const uint16_t*>(src);
-      else *dst = *src;
+    // no run of positions: the per-token kernel's pattern -- lanes along the head elements
+    // (coalesced loads; a warp's stores fall into 8 cache lines), four passes in flight
+    const int total = nt * head_size;
+    for (int base = 0; base < total; base += 4 * kRunThreads) {
+      T v[4];
+      int64_t dsto[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int idx = base + u * kRunThreads + threadIdx.x;
+        dsto[u] = -1;
+        if (idx < total) {
+          const int i = idx / head_size, d = idx - i * head_size;
+          const int blk = blk_s[i];
+          if (blk >= 0) {
+            v[u] = value[(int64_t)(t0 + i) * value_stride + head * head_size + d];
+            dsto[u] = blk * blk_bytes + head_bytes + ((int64_t)d * block_size + off_s[i]) * CES;
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (dsto[u] >= 0) {
+          uint8_t* dst = reinterpret_cast<uint8_t*>(value_cache) + dsto[u];
+          if constexpr (KV == B200PA_KV_AUTO) *reinterpret_cast<T*>(dst) = v[u];
+          else *dst = fp8_quant<KV>(Scalar<ST>::to_float(v[u]), vs);
+        }
+      }
     }
     return;
   }
+  const int a = off_s[0];                              // slot offset of the tile's first token
+  const int pitch = (kRunTokens / block_size + 1) * block_size * CES;   // staged row, bytes
+  // stage: lanes along the tokens (conflict-free 1-2 byte shared stores), 8 head elements each
+  for (int idx = threadIdx.x; idx < d8n * kRunTokens; idx += kRunThreads) {
+    const int i = idx % kRunTokens, d8 = idx / kRunTokens;
+    if (i >= nt) continue;
+    const uint4 raw = __ldg(reinterpret_cast<const uint4*>(
+        value + (int64_t)(t0 + i) * value_stride + head * head_size + d8 * 8));
+    const T* e = reinterpret_cast<const T*>(&raw);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      uint8_t* dst = vs_smem + (size_t)(d8 * 8 + k) * pitch + (a + i) * CES;
+      if constexpr (KV == B200PA_KV_AUTO) *reinterpret_cast<T*>(dst) = e[k];
+      else *dst = fp8_quant<KV>(Scalar<ST>::to_float(e[k]), vs);
+    }
+  }
+  __syncthreads();
   // copy out: (block j, row d, 16-byte group g) -- for a full block the rows of one head are one
   // contiguous run of head_size * block_size elements
   const int gpb = block_size * CES / 16 > 0 ? block_size * CES / 16 : 1;   // groups per block row
@@ -406,11 +419,10 @@ int launch_reshape_and_cache(const void* key, const void* value, void* key_cache
                       ((value_stride * es) % 16 == 0) && head_size % 8 == 0 &&
                       (block_size == 8 || block_size == 16 || block_size == 32) &&
                       num_heads <= 65535 &&
-                      head_size * (kRunTokens / block_size + 1) * block_size * cache_es +
-                              kRunTokens * (head_size * cache_es + 16) <= 47104;
+                      head_size * (kRunTokens / block_size + 1) * block_size * cache_es <= 47104;
   if (run_ok) {
     const int pitch = (kRunTokens / block_size + 1) * block_size * cache_es;
-    const int smem = head_size * pitch + kRunTokens * (head_size * cache_es + 16);
+    const int smem = head_size * pitch;
     dim3 grid((num_tokens + kRunTokens - 1) / kRunTokens, num_heads);
 #define RUN_CASE(ST_, KV_)                                                                     \
     reshape_and_cache_run_kernel<ST_, KV_><<<grid, kRunThreads, smem, stream>>>(               \

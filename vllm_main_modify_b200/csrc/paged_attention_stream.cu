@@ -163,6 +163,12 @@ __device__ __forceinline__ float ex2(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// weight 2^(m - mx) of a partial whose reference is m: a piece that saw no key at all for a head
+// (block-sparse attention: every block of the piece masked) has m = -inf and weight 0, also when
+// the whole run is like that (mx = -inf)
+__device__ __forceinline__ float piece_weight(float m, float mx) {
+  return m == -INFINITY ? 0.f : ex2(m - mx);
+}
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -1109,7 +1115,7 @@ paged_attention_stream_kernel(const StreamParams p) {
           for (int mt = 0; mt < MT; ++mt) vb[mt] = sb[mt * 32 + lane];
         }
         const float* ha = hdr_s[pa];
-        const float fa0 = ex2(ha[2 * q4] - mx0), fa1 = ex2(ha[2 * q4 + 1] - mx1);
+        const float fa0 = piece_weight(ha[2 * q4], mx0), fa1 = piece_weight(ha[2 * q4 + 1], mx1);
         l0 += ha[8 + 2 * q4] * fa0;
         l1 += ha[8 + 2 * q4 + 1] * fa1;
 #pragma unroll
@@ -1119,7 +1125,7 @@ paged_attention_stream_kernel(const StreamParams p) {
         }
         if (two) {
           const float* hb = hdr_s[pb];
-          const float fb0 = ex2(hb[2 * q4] - mx0), fb1 = ex2(hb[2 * q4 + 1] - mx1);
+          const float fb0 = piece_weight(hb[2 * q4], mx0), fb1 = piece_weight(hb[2 * q4 + 1], mx1);
           l0 += hb[8 + 2 * q4] * fb0;
           l1 += hb[8 + 2 * q4 + 1] * fb1;
 #pragma unroll
@@ -1248,7 +1254,7 @@ paged_attention_stream_kernel(const StreamParams p) {
       float4 v[MT];
 #pragma unroll
       for (int mt = 0; mt < MT; ++mt) v[mt] = __ldcg(reinterpret_cast<const float4*>(slot) + mt * 32 + lane);
-      const float f0 = ex2(m.x - mx[0]), f1 = ex2(m.y - mx[1]);
+      const float f0 = piece_weight(m.x, mx[0]), f1 = piece_weight(m.y, mx[1]);
       ls[0] += l.x * f0;
       ls[1] += l.y * f1;
 #pragma unroll
@@ -1373,8 +1379,8 @@ int launch_stream_flash(StreamParams& p, bool fp8, int scalar_type, int head_siz
     int num_sms, int64_t workspace_bytes, cudaStream_t stream);
 int launch_stream_bs32(StreamParams& p, bool fp8, int scalar_type, int head_size, int num_sms,
     int64_t workspace_bytes, cudaStream_t stream);
-int launch_stream_other(StreamParams& p, bool fp8, int scalar_type, int head_size, int num_sms,
-    int64_t workspace_bytes, cudaStream_t stream);
+int launch_stream_other(StreamParams& p, bool fp8, int scalar_type, int head_size, int tune,
+    int num_sms, int64_t workspace_bytes, cudaStream_t stream);
 int launch_stream_e5m2(StreamParams& p, int scalar_type, int head_size, bool flash, int block_size,
     int num_sms, int64_t workspace_bytes, cudaStream_t stream);
 int launch_stream_e5m2_wide(StreamParams& p, int scalar_type, int head_size, bool flash,
@@ -1392,9 +1398,9 @@ int launch_stream_flash(StreamParams& p, bool fp8, int scalar_type, int head_siz
   switch (head_size) {                                                                       \
     case 32:  if (fp8) { STREAM_CALL(ST, true, 32, 4, 3, 2, 2, true, BSV); }  else { STREAM_CALL(ST, false, 32, 4, 3, 2, 2, true, BSV); }  \
     case 64:  if (fp8) { STREAM_CALL(ST, true, 64, 4, 3, 2, 2, true, BSV); }  else { STREAM_CALL(ST, false, 64, 4, 3, 2, 2, true, BSV); }  \
-    case 80:  if (fp8) { STREAM_CALL(ST, true, 80, 4, 3, 2, 2, true, BSV); }  else { STREAM_CALL(ST, false, 80, 4, 3, 2, 2, true, BSV); }  \
-    case 96:  if (fp8) { STREAM_CALL(ST, true, 96, 4, 3, 2, 2, true, BSV); }  else { STREAM_CALL(ST, false, 96, 4, 3, 2, 1, true, BSV); }  \
-    case 112: if (fp8) { STREAM_CALL(ST, true, 112, 4, 3, 2, 2, true, BSV); } else { STREAM_CALL(ST, false, 112, 4, 3, 2, 1, true, BSV); } \
+    case 80:  if (fp8) { STREAM_CALL(ST, true, 80, 4, 3, 2, 2, true, BSV); }  else { STREAM_CALL(ST, false, 80, (BSV == 16 ? 8 : 4), (BSV == 16 ? 2 : 3), 2, (BSV == 16 ? 1 : 2), true, BSV); }  \
+    case 96:  if (fp8) { STREAM_CALL(ST, true, 96, 4, 3, 2, 2, true, BSV); }  else { STREAM_CALL(ST, false, 96, (BSV == 16 ? 8 : 4), (BSV == 16 ? 2 : 3), 2, 1, true, BSV); }  \
+    case 112: if (fp8) { STREAM_CALL(ST, true, 112, 4, 3, 2, 2, true, BSV); } else { STREAM_CALL(ST, false, 112, (BSV == 16 ? 6 : 4), (BSV == 16 ? 2 : 3), 2, 1, true, BSV); } \
     case 128: if (fp8) { STREAM_CALL(ST, true, 128, 8, 3, 2, 1, true, BSV); } else { STREAM_CALL(ST, false, 128, NW128, S128, P128, 1, true, BSV); } \
     case 192: if (fp8) { STREAM_CALL(ST, true, 192, 4, 4, 2, 1, true, BSV); } else { STREAM_CALL(ST, false, 192, 4, S192, P192, 1, true, BSV); } \
     case 256: if (fp8) { STREAM_CALL(ST, true, 256, 4, 3, 2, 1, true, BSV); } else { STREAM_CALL(ST, false, 256, NW256, S256, P256, 1, true, BSV); } \
@@ -1407,8 +1413,8 @@ int launch_stream_flash(StreamParams& p, bool fp8, int scalar_type, int head_siz
       if (scalar_type == B200PA_BF16) { STREAM_FLASH_BY_HEAD_SIZE(B200PA_BF16, 32, 4, 3, 2, 2, 2, 3, 2, 2) }
       else { STREAM_FLASH_BY_HEAD_SIZE(B200PA_F16, 32, 4, 3, 2, 2, 2, 3, 2, 2) }
     }
-    if (scalar_type == B200PA_BF16) { STREAM_FLASH_BY_HEAD_SIZE(B200PA_BF16, 16, 8, 2, 1, 4, 1, 4, 3, 1) }
-    else { STREAM_FLASH_BY_HEAD_SIZE(B200PA_F16, 16, 8, 2, 1, 4, 1, 4, 3, 1) }
+    if (scalar_type == B200PA_BF16) { STREAM_FLASH_BY_HEAD_SIZE(B200PA_BF16, 16, 8, 2, 1, 4, 1, 4, 2, 1) }
+    else { STREAM_FLASH_BY_HEAD_SIZE(B200PA_F16, 16, 8, 2, 1, 4, 1, 4, 2, 1) }
 #undef STREAM_FLASH_BY_HEAD_SIZE
 }
 #elif STREAM_PART == 2
@@ -1432,21 +1438,44 @@ int launch_stream_bs32(StreamParams& p, bool fp8, int scalar_type, int head_size
 #undef STREAM_BY_HEAD_SIZE_32
 }
 #elif STREAM_PART == 3
-int launch_stream_other(StreamParams& p, bool fp8, int scalar_type, int head_size, int num_sms,
-    int64_t workspace_bytes, cudaStream_t stream) {
+int launch_stream_other(StreamParams& p, bool fp8, int scalar_type, int head_size, int tune,
+    int num_sms, int64_t workspace_bytes, cudaStream_t stream) {
   // the other head sizes (and f16 at 128): one shape each.  192 / 256: 12-16 KiB stages, 4 warps.
 #define STREAM_BY_HEAD_SIZE(ST)                                                              \
   switch (head_size) {                                                                       \
     case 32:  if (fp8) { STREAM_CALL(ST, true, 32, 4, 3, 2, 2); }  else { STREAM_CALL(ST, false, 32, 4, 3, 2, 2); }  \
-    case 64:  if (fp8) { STREAM_CALL(ST, true, 64, 4, 3, 2, 2); }  else { STREAM_CALL(ST, false, 64, 4, 3, 2, 2); }  \
-    case 80:  if (fp8) { STREAM_CALL(ST, true, 80, 4, 3, 2, 2); } else { STREAM_CALL(ST, false, 80, 4, 3, 2, 2); }  \
-    case 96:  if (fp8) { STREAM_CALL(ST, true, 96, 4, 3, 2, 2); }  else { STREAM_CALL(ST, false, 96, 4, 3, 2, 1); }  \
-    case 112: if (fp8) { STREAM_CALL(ST, true, 112, 4, 3, 2, 2); } else { STREAM_CALL(ST, false, 112, 4, 3, 2, 1); } \
+    case 64:  if (fp8) { STREAM_CALL(ST, true, 64, 6, 2, 4, 2); }  else { STREAM_CALL(ST, false, 64, 4, 3, 2, 2); }  \
+    case 80:  if (fp8) { STREAM_CALL(ST, true, 80, 4, 3, 2, 2); } else { STREAM_CALL(ST, false, 80, 8, 2, 2, 1); }  \
+    case 96:  if (fp8) { STREAM_CALL(ST, true, 96, 4, 3, 2, 2); }  else { STREAM_CALL(ST, false, 96, 8, 2, 2, 1); }  \
+    case 112: if (fp8) { STREAM_CALL(ST, true, 112, 6, 2, 2, 2); } else { STREAM_CALL(ST, false, 112, 6, 2, 2, 1); } \
     case 128: if (fp8) { STREAM_CALL(ST, true, 128, 6, 2, 2, 2); } else { STREAM_CALL(ST, false, 128, 8, 2, 1, 1); } \
-    case 192: if (fp8) { STREAM_CALL(ST, true, 192, 4, 4, 2, 1); } else { STREAM_CALL(ST, false, 192, 4, 4, 1, 1); } \
-    case 256: if (fp8) { STREAM_CALL(ST, true, 256, 4, 3, 2, 1); } else { STREAM_CALL(ST, false, 256, 4, 3, 1, 1); } \
+    case 192: if (fp8) { STREAM_CALL(ST, true, 192, 8, 2, 2, 1); } else { STREAM_CALL(ST, false, 192, 4, 4, 1, 1); } \
+    case 256: if (fp8) { STREAM_CALL(ST, true, 256, 6, 2, 2, 1); } else { STREAM_CALL(ST, false, 256, 4, 2, 1, 1); } \
     default: return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: head size %d", head_size);  \
   }
+#if B200PA_TESTING
+  // candidate shapes behind the tuning hook (bf16 queries): more warps, two stages -- what won at
+  // head size 128 under the power cap (tools/shapebench.py --sustain)
+  if (tune == 1 && scalar_type == B200PA_BF16) {
+    switch (head_size) {
+      case 64:  if (fp8) { STREAM_CALL(B200PA_BF16, true, 64, 4, 2, 4, 3); }  else { STREAM_CALL(B200PA_BF16, false, 64, 6, 2, 2, 2); }
+      case 80:  if (fp8) { STREAM_CALL(B200PA_BF16, true, 80, 6, 2, 2, 2); }  else break;
+      case 96:  if (fp8) { STREAM_CALL(B200PA_BF16, true, 96, 6, 2, 2, 2); }  else break;
+      case 192: if (fp8) break; else { STREAM_CALL(B200PA_BF16, false, 192, 8, 2, 1, 1); }
+      default: break;
+    }
+  }
+  if (tune == 2 && scalar_type == B200PA_BF16) {
+    switch (head_size) {
+      case 64:  if (fp8) { STREAM_CALL(B200PA_BF16, true, 64, 8, 2, 4, 1); }  else { STREAM_CALL(B200PA_BF16, false, 64, 8, 3, 2, 1); }
+      case 96:  if (fp8) { STREAM_CALL(B200PA_BF16, true, 96, 4, 2, 2, 3); }  else break;
+      case 192: if (fp8) break; else { STREAM_CALL(B200PA_BF16, false, 192, 4, 2, 1, 1); }
+      default: break;
+    }
+  }
+#else
+  (void)tune;
+#endif
   if (scalar_type == B200PA_BF16) { STREAM_BY_HEAD_SIZE(B200PA_BF16) }
   else { STREAM_BY_HEAD_SIZE(B200PA_F16) }
 #undef STREAM_BY_HEAD_SIZE
@@ -1457,13 +1486,13 @@ int launch_stream_other(StreamParams& p, bool fp8, int scalar_type, int head_siz
 #define STREAM_E5M2_BY_HEAD_SIZE(ST, FL, BSV)                                     \
   switch (head_size) {                                                           \
     case 32:  STREAM_CALL(ST, true, 32, 4, 3, 2, 2, FL, BSV, true);              \
-    case 64:  STREAM_CALL(ST, true, 64, 4, 3, 2, 2, FL, BSV, true);              \
+    case 64:  STREAM_CALL(ST, true, 64, ((FL || BSV == 32) ? 4 : 6), ((FL || BSV == 32) ? 3 : 2), ((FL || BSV == 32) ? 2 : 4), 2, FL, BSV, true); \
     case 80:  STREAM_CALL(ST, true, 80, 4, 3, 2, 2, FL, BSV, true);              \
     case 96:  STREAM_CALL(ST, true, 96, 4, 3, 2, 2, FL, BSV, true);              \
-    case 112: STREAM_CALL(ST, true, 112, 4, 3, 2, 2, FL, BSV, true);             \
+    case 112: STREAM_CALL(ST, true, 112, ((FL || BSV == 32) ? 4 : 6), ((FL || BSV == 32) ? 3 : 2), 2, 2, FL, BSV, true); \
     case 128: STREAM_CALL(ST, true, 128, (FL ? 8 : 6), (FL ? 3 : 2), 2, (FL ? 1 : 2), FL, BSV, true); \
-    case 192: STREAM_CALL(ST, true, 192, 4, 4, 2, 1, FL, BSV, true);             \
-    case 256: STREAM_CALL(ST, true, 256, 4, 3, 2, 1, FL, BSV, true);             \
+    case 192: STREAM_CALL(ST, true, 192, ((FL || BSV == 32) ? 4 : 8), ((FL || BSV == 32) ? 4 : 2), 2, 1, FL, BSV, true); \
+    case 256: STREAM_CALL(ST, true, 256, ((FL || BSV == 32) ? 4 : 6), ((FL || BSV == 32) ? 3 : 2), 2, 1, FL, BSV, true); \
     default: return set_error(B200PA_ERR_UNSUPPORTED,                            \
                               "stream kernel: head size %d with an fp8_e5m2 cache", head_size); \
   }
@@ -1664,7 +1693,7 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
   }
 #undef STREAM_TUNE_FP8
 #undef STREAM_TUNE_16
-  return launch_stream_other(p, fp8, scalar_type, head_size, num_sms, workspace_bytes, stream);
+  return launch_stream_other(p, fp8, scalar_type, head_size, tune, num_sms, workspace_bytes, stream);
 }
 #endif
 #undef STREAM_CALL

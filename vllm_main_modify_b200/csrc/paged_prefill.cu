@@ -360,6 +360,12 @@ paged_prefill_kernel(const PrefillParams p) {
     if (warp == 0 && j + STAGES - 1 < n_tiles) produce(j + STAGES - 1);
     const int s = j % STAGES;
     mbar_wait(full0 + 8 * s, (j / STAGES) & 1);
+    if (16 * warp >= rows_valid) {
+      // all 16 rows of this warp are padding (a short chunk): keep in step, compute nothing
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty0 + 8 * s);
+      continue;
+    }
     const uint32_t sb = ring_u32 + s * STAGE_BYTES;
     const int npg = min(PPT, total_pages - j * PPT);   // pages of the stage that were loaded
 

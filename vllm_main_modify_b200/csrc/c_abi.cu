@@ -37,6 +37,7 @@ int launch_stream(void*, float*, int64_t, int64_t, void*, int64_t, const void*, 
 bool stream_flash_supported(const void*, const void*, const void*, int, int, int, int, int64_t,
                             int64_t, int64_t, int64_t, int, int);
 bool stream_fused_supported(const FusedWrite&, int);
+bool stream_nhd_eligible(int, int, int, int, int64_t, int64_t, int);
 int64_t stream_workspace_bytes(int, int);
 int launch_merge_attn_states(void*, float*, const void*, const float*, const void*, const float*,
                              int64_t, int, int, int, cudaStream_t);
@@ -361,8 +362,12 @@ int b200pa_paged_attention_flash(
   if (num_seqs == 0) return B200PA_OK;
   FusedWrite fw{key, value, key_stride, value_stride, slot_mapping};
   const FusedWrite* fused = want_write ? &fw : nullptr;
-  if (fused && !stream_fused_supported(fw, scalar_type)) {
-    // rows the fused path cannot load: the write it stands for, as its own launch
+  const bool nhd = stream_tune() != 99 &&
+                   stream_nhd_eligible(num_heads, num_kv_heads, head_size, block_size, page_stride,
+                                       head_stride, kv_dtype);
+  if (fused && (nhd || !stream_fused_supported(fw, scalar_type))) {
+    // rows the fused path cannot load, or the whole-block NHD kernel (which has no fused write):
+    // the write it stands for, as its own launch
     int rc = launch_reshape_and_cache_flash(key, value, key_cache, value_cache, slot_mapping,
                                             num_seqs, key_stride, value_stride, block_stride,
                                             page_stride, head_stride, num_kv_heads, head_size,
@@ -375,7 +380,7 @@ int b200pa_paged_attention_flash(
                        key_cache, value_cache, num_seqs, num_heads, num_kv_heads, head_size, scale,
                        block_tables, max_num_blocks_per_seq, seq_lens, alibi_slopes, q_stride,
                        block_stride, head_stride, scalar_type, kv_dtype, k_scale, v_scale, fused,
-                       nullptr, page_stride, block_size, num_sms(), 0, stream);
+                       nullptr, page_stride, block_size, num_sms(), stream_tune(), stream);
 }
 
 int b200pa_merge_attn_states(void* output, float* output_lse, const void* prefix_output,

@@ -42,6 +42,8 @@
 //    exact) and multiplied in f16, k_scale folded into the softmax scale and v_scale into the
 //    output scale.  Online softmax in the log2 domain with a lazily moved reference: the
 //    steady state has no shuffles, only a warp vote.
+#include <cuda.h>   // CUtensorMap (types only; the encoder is fetched through the runtime)
+
 #include "common.cuh"
 
 // Development builds only (tools/ablate.sh): B200PA_ABLATE removes one ingredient of the main loop
@@ -1308,6 +1310,10 @@ paged_attention_stream_kernel(const StreamParams p) {
 }
 
 // ---------------------------------------------------------------------------------------
+#if STREAM_PART == 6
+#include "paged_attention_nhd.cuh"
+#endif
+
 constexpr int kMaxWarpsPerSm = 16;
 
 template <int ST, bool FP8, int D, int NW, int STAGES, int PPS, int MINB, bool FLASH = false,
@@ -1385,6 +1391,10 @@ int launch_stream_e5m2(StreamParams& p, int scalar_type, int head_size, bool fla
     int num_sms, int64_t workspace_bytes, cudaStream_t stream);
 int launch_stream_e5m2_wide(StreamParams& p, int scalar_type, int head_size, bool flash,
     int block_size, int num_sms, int64_t workspace_bytes, cudaStream_t stream);
+// NHD caches with 2 / 4 / 8 kv heads per GPU (paged_attention_nhd.cuh); -1: not taken (the caller
+// goes on with the stream kernel's FLASH path)
+int launch_stream_nhd(const StreamParams& p, bool fp8, int scalar_type, int head_size,
+    void* workspace, int64_t workspace_bytes, int num_sms, cudaStream_t stream);
 
 #define STREAM_CALL(ST, FP8V, DV, NWV, SG, PP, MB, ...) \
   return launch_stream_t<ST, FP8V, DV, NWV, SG, PP, MB, ##__VA_ARGS__>(p, num_sms, workspace_bytes, stream)
@@ -1413,8 +1423,8 @@ int launch_stream_flash(StreamParams& p, bool fp8, int scalar_type, int head_siz
       if (scalar_type == B200PA_BF16) { STREAM_FLASH_BY_HEAD_SIZE(B200PA_BF16, 32, 4, 3, 2, 2, 2, 3, 2, 2) }
       else { STREAM_FLASH_BY_HEAD_SIZE(B200PA_F16, 32, 4, 3, 2, 2, 2, 3, 2, 2) }
     }
-    if (scalar_type == B200PA_BF16) { STREAM_FLASH_BY_HEAD_SIZE(B200PA_BF16, 16, 8, 2, 1, 4, 1, 4, 2, 1) }
-    else { STREAM_FLASH_BY_HEAD_SIZE(B200PA_F16, 16, 8, 2, 1, 4, 1, 4, 2, 1) }
+    if (scalar_type == B200PA_BF16) { STREAM_FLASH_BY_HEAD_SIZE(B200PA_BF16, 16, 8, 2, 1, 2, 1, 4, 2, 1) }
+    else { STREAM_FLASH_BY_HEAD_SIZE(B200PA_F16, 16, 8, 2, 1, 2, 1, 4, 2, 1) }
 #undef STREAM_FLASH_BY_HEAD_SIZE
 }
 #elif STREAM_PART == 2
@@ -1449,7 +1459,7 @@ int launch_stream_other(StreamParams& p, bool fp8, int scalar_type, int head_siz
     case 96:  if (fp8) { STREAM_CALL(ST, true, 96, 4, 3, 2, 2); }  else { STREAM_CALL(ST, false, 96, 8, 2, 2, 1); }  \
     case 112: if (fp8) { STREAM_CALL(ST, true, 112, 6, 2, 2, 2); } else { STREAM_CALL(ST, false, 112, 6, 2, 2, 1); } \
     case 128: if (fp8) { STREAM_CALL(ST, true, 128, 6, 2, 2, 2); } else { STREAM_CALL(ST, false, 128, 8, 2, 1, 1); } \
-    case 192: if (fp8) { STREAM_CALL(ST, true, 192, 8, 2, 2, 1); } else { STREAM_CALL(ST, false, 192, 4, 4, 1, 1); } \
+    case 192: if (fp8) { STREAM_CALL(ST, true, 192, 8, 2, 2, 1); } else { STREAM_CALL(ST, false, 192, 4, 2, 1, 1); } \
     case 256: if (fp8) { STREAM_CALL(ST, true, 256, 6, 2, 2, 1); } else { STREAM_CALL(ST, false, 256, 4, 2, 1, 1); } \
     default: return set_error(B200PA_ERR_UNSUPPORTED, "stream kernel: head size %d", head_size);  \
   }
@@ -1521,6 +1531,47 @@ int launch_stream_e5m2_wide(StreamParams& p, int scalar_type, int head_size, boo
 }
 #endif
 #undef STREAM_E5M2_BY_HEAD_SIZE
+#elif STREAM_PART == 6
+int launch_stream_nhd(const StreamParams& sp, bool fp8, int scalar_type, int head_size,
+    void* workspace, int64_t workspace_bytes, int num_sms, cudaStream_t stream) {
+  if (head_size != 128 || sp.group > 8 || sp.h_tiles != 1) return -1;
+  if (sp.num_kv_heads != 2 && sp.num_kv_heads != 4 && sp.num_kv_heads != 8) return -1;
+  if (sp.new_key != nullptr || sp.bs_vert_stride > 1) return -1;
+  NhdParams p;
+  p.out = sp.out;
+  p.lse = sp.lse;
+  p.lse_seq_stride = sp.lse_seq_stride;
+  p.lse_head_stride = sp.lse_head_stride;
+  p.ws = nullptr;
+  p.counters = nullptr;
+  p.q = sp.q;
+  p.block_tables = sp.block_tables;
+  p.seq_lens = sp.seq_lens;
+  p.alibi_slopes = sp.alibi_slopes;
+  p.k_scale = sp.k_scale;
+  p.v_scale = sp.v_scale;
+  p.q_stride = sp.q_stride;
+  p.num_seqs = sp.num_seqs;
+  p.num_heads = sp.num_heads;
+  p.num_kv_heads = sp.num_kv_heads;
+  p.group = sp.group;
+  p.max_num_blocks_per_seq = sp.max_num_blocks_per_seq;
+  p.scale = sp.scale;
+#define NHD_CALL(ST, FP8V, NWV, SG, BP)                                                         \
+  return launch_nhd_t<ST, FP8V, false, 128, NWV, SG, BP>(p, sp.k_cache, sp.v_cache,             \
+      sp.kv_block_stride, sp.kv_token_stride, sp.kv_head_stride, workspace, workspace_bytes,   \
+      num_sms, stream)
+#define NHD_BY_HEADS(ST)                                                                        \
+  switch (sp.num_kv_heads) {                                                                    \
+    case 8: if (fp8) { NHD_CALL(ST, true, 8, 3, 2); } else { NHD_CALL(ST, false, 8, 3, 1); }     \
+    case 4: if (fp8) { NHD_CALL(ST, true, 4, 3, 2); } else { NHD_CALL(ST, false, 4, 3, 1); }     \
+    default: if (fp8) { NHD_CALL(ST, true, 2, 3, 2); } else { NHD_CALL(ST, false, 2, 3, 1); }    \
+  }
+  if (scalar_type == B200PA_BF16) { NHD_BY_HEADS(B200PA_BF16) }
+  else { NHD_BY_HEADS(B200PA_F16) }
+#undef NHD_BY_HEADS
+#undef NHD_CALL
+}
 #else
 // Upper bound of the workspace any stream launch on a device with `num_sms` SMs needs.
 int64_t stream_workspace_bytes(int num_sms, int head_size) {
@@ -1574,6 +1625,18 @@ bool stream_flash_supported(const void* query, const void* key_cache, const void
   if (token_stride <= 0 || head_stride < head_size) return false;
   if (q_stride % 4 != 0) return false;
   return true;
+}
+
+// Token-major caches the whole-block kernel (paged_attention_nhd.cuh) takes: NHD order with 2 / 4
+// / 8 kv heads, head size 128, 16-token blocks, group <= 8, auto / fp8_e4m3.  It has no fused
+// cache write: the entry point writes first (reshape_and_cache_flash) and attends second.
+bool stream_nhd_eligible(int num_heads, int num_kv_heads, int head_size, int block_size,
+                         int64_t token_stride, int64_t head_stride, int kv_dtype) {
+  if (head_size != 128 || block_size != 16) return false;
+  if (num_kv_heads != 2 && num_kv_heads != 4 && num_kv_heads != 8) return false;
+  if (num_heads % num_kv_heads != 0 || num_heads / num_kv_heads > 8) return false;
+  if (kv_dtype != B200PA_KV_AUTO && kv_dtype != B200PA_KV_FP8_E4M3) return false;
+  return head_stride < token_stride;
 }
 
 // The fused write reads the new key/value rows with 4-byte loads (pairs of 16-bit elements).
@@ -1642,9 +1705,19 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
   if (kv_dtype == B200PA_KV_FP8_E5M2)
     return launch_stream_e5m2(p, scalar_type, head_size, flash_token_stride > 0, block_size, num_sms,
                               workspace_bytes, stream);
-  if (flash_token_stride > 0)
+  if (flash_token_stride > 0) {
+    // several kv heads per GPU in NHD order (a token's heads are adjacent, the tokens of one head
+    // are not): whole-block stages through tensor-map TMA, one warp per head
+    // (paged_attention_nhd.cuh).  tune 99 (test hook) keeps the row copies of the FLASH path.
+    if (block_size == 16 && kv_head_stride < flash_token_stride && tune != 99 &&
+        (kv_dtype == B200PA_KV_AUTO || kv_dtype == B200PA_KV_FP8_E4M3)) {
+      const int rc = launch_stream_nhd(p, fp8, scalar_type, head_size, workspace, workspace_bytes,
+                                       num_sms, stream);
+      if (rc >= 0) return rc;
+    }
     return launch_stream_flash(p, fp8, scalar_type, head_size, block_size, num_sms, workspace_bytes,
                                stream);
+  }
   if (block_size == 32)
     return launch_stream_bs32(p, fp8, scalar_type, head_size, num_sms, workspace_bytes, stream);
   // <ST, FP8, D, NW, STAGES, PPS, MINB>: fp8 stage = PPS x 4 KiB, 16-bit stage = PPS x 8 KiB (D=128).

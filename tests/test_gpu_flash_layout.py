@@ -96,8 +96,10 @@ CASES = [
 
 
 def _takes_block_kernel(layout, H, Hkv, D, kv, bs):
-    """b200pa's stream_nhd_eligible: NHD order, 2 / 4 / 8 kv heads, head size 128, 16-token blocks."""
-    return (layout == "NHD" and D == 128 and bs == 16 and Hkv in (2, 4, 8) and H // Hkv <= 8
+    """2 / 4 / 8 kv heads, head size 128, 16-token blocks, group <= 8: the x-packed cache (the
+    comparison's other side) and the NHD cache take the whole-block kernel, the HND cache the
+    per-warp kernel -- other span cuts, hence another merge order: no bitwise equality."""
+    return (D == 128 and bs == 16 and Hkv in (2, 4, 8) and H // Hkv <= 8
             and kv in ("auto", "fp8"))
 
 

@@ -1,6 +1,6 @@
-"""Every launch shape of the stream kernel behind the tuning hook (B200PA_TESTING builds:
-warps x stages x pages per stage x CTAs per SM, with and without the split K / V refill) gives
-the default shape's result: attention within rounding of it and of the oracle, fused cache bytes
+"""Every launch shape of the decode kernels behind the tuning hook (B200PA_TESTING builds: the
+whole-block kernel's heads per CTA x stages x CTAs per SM, the per-warp stream kernel's warps x
+stages x pages per stage x CTAs per SM) gives the default shape's result: attention within rounding of it and of the oracle, fused cache bytes
 bit-exact.  The shapes only differ in how the flattened stages are cut into spans."""
 import pytest
 import torch
@@ -21,7 +21,9 @@ def native():
 
 
 @pytest.mark.parametrize("kv", ["auto", "fp8"])
-@pytest.mark.parametrize("tune", list(range(1, 15)))
+# 20-24: launch shapes of the whole-block kernel (csrc/paged_attention_nhd.cuh); 100 + i: the
+# per-warp stream kernel with its launch shape i
+@pytest.mark.parametrize("tune", [20, 21, 22, 23, 24] + [100 + i for i in range(0, 14)])
 def test_tune_variant_matches_default_and_oracle(native, tune, kv):
     from oracle import oracle as ora
     from vllm_main_modify_b200 import _custom_ops as ops

@@ -71,6 +71,9 @@ def main():
     ap.add_argument("--series", action="store_true", help="also print the per-launch times in order")
     ap.add_argument("--graph", action="store_true",
                     help="time CUDA-graph replays of each op instead of eager launches")
+    ap.add_argument("--sustain", type=float, default=0.0,
+                    help="also run each op back to back for this many seconds and report the "
+                         "rate of the first and the last third (the power-capped regime)")
     ap.add_argument("--ref-cuda", action="store_true",
                     help="time the reference's own CUDA kernels (oracle/_ref/libvllm_ref_cuda.so) "
                          "on the same tensors instead of this repo's")
@@ -169,6 +172,19 @@ def main():
                 line.update(kv_gib=round(nbytes / 2**30, 3), gbs=round(gbs, 1),
                             frac_measured=round(gbs / peak, 4), pct_8tb=round(gbs / 80.0, 2),
                             heuristic_v1=PagedAttention.use_v1(w["max_len"], B, w["H"]))
+            if args.sustain > 0 and name != "reshape_and_cache":
+                n = max(30, int(args.sustain * 1e3 / med))
+                marks = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+                marks[0].record()
+                for k in range(3):
+                    for _ in range(n // 3):
+                        fn()
+                    marks[k + 1].record()
+                torch.cuda.synchronize()
+                first = marks[0].elapsed_time(marks[1]) / (n // 3)
+                last = marks[2].elapsed_time(marks[3]) / (n // 3)
+                line["sustained_first_third_gbs"] = round(nbytes / (first * 1e-3) / 1e9, 1)
+                line["sustained_last_third_gbs"] = round(nbytes / (last * 1e-3) / 1e9, 1)
             if args.series:
                 line["series_us"] = [round(t * 1e3, 1) for t in time_op.last_series]
             print(json.dumps(line), flush=True)

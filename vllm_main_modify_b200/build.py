@@ -38,7 +38,8 @@ CU_SOURCES = [("c_abi.cu", [], "c_abi.o"), ("cache_kernels.cu", [], "cache_kerne
               ("paged_attention_stream.cu", ["-DSTREAM_PART=3"], "paged_attention_stream_other.o"),
               ("paged_attention_stream.cu", ["-DSTREAM_PART=4"], "paged_attention_stream_e5m2.o"),
               ("paged_attention_stream.cu", ["-DSTREAM_PART=5"], "paged_attention_stream_e5m2_flash.o"),
-              ("paged_attention_stream.cu", ["-DSTREAM_PART=6"], "paged_attention_stream_nhd.o"),
+              ("paged_attention_stream.cu", ["-DSTREAM_PART=6"], "paged_attention_stream_block_xp.o"),
+              ("paged_attention_stream.cu", ["-DSTREAM_PART=7"], "paged_attention_stream_block_nhd.o"),
               ("paged_prefill.cu", ["-DPREFILL_PART=0"], "paged_prefill.o"),
               ("paged_prefill.cu", ["-DPREFILL_PART=1"], "paged_prefill_small.o"),
               ("paged_prefill.cu", ["-DPREFILL_PART=2"], "paged_prefill_mid.o"),

@@ -362,12 +362,8 @@ int b200pa_paged_attention_flash(
   if (num_seqs == 0) return B200PA_OK;
   FusedWrite fw{key, value, key_stride, value_stride, slot_mapping};
   const FusedWrite* fused = want_write ? &fw : nullptr;
-  const bool nhd = stream_tune() != 99 &&
-                   stream_nhd_eligible(num_heads, num_kv_heads, head_size, block_size, page_stride,
-                                       head_stride, kv_dtype);
-  if (fused && (nhd || !stream_fused_supported(fw, scalar_type))) {
-    // rows the fused path cannot load, or the whole-block NHD kernel (which has no fused write):
-    // the write it stands for, as its own launch
+  if (fused && !stream_fused_supported(fw, scalar_type)) {
+    // rows the fused path cannot load: the write it stands for, as its own launch
     int rc = launch_reshape_and_cache_flash(key, value, key_cache, value_cache, slot_mapping,
                                             num_seqs, key_stride, value_stride, block_stride,
                                             page_stride, head_stride, num_kv_heads, head_size,

@@ -29,12 +29,20 @@ struct NhdParams {
   float* ws;           // 2 * NW slots per CTA, slot_floats(D) floats each
   int* counters;       // workspace header: one ticket counter per CTA, zero between launches
   const void* q;
+  const void* k_cache;        // x-packed layout: the bulk copies' source; both: the fused write's target
+  const void* v_cache;
   const int32_t* block_tables;
   const int32_t* seq_lens;
   const float* alibi_slopes;
   const float* k_scale;
   const float* v_scale;
+  // fused cache write (decode_step), new_key == nullptr: plain attention
+  const void* new_key;
+  const void* new_value;
+  const int64_t* slot_mapping;
+  int64_t new_key_stride, new_value_stride;           // elements per token
   int64_t q_stride;
+  int64_t kv_block_stride, kv_token_stride, kv_head_stride;   // elements (token: NHD layout only)
   int num_seqs, num_heads, num_kv_heads, group;
   int max_num_blocks_per_seq;
   float scale;
@@ -54,30 +62,38 @@ __device__ __forceinline__ void mbar_arrive_plain(uint32_t bar) {
 
 // ST: scalar type of query / out.  FP8 / E5: cache format.  NW: kv heads per GPU = warps per CTA.
 // BPS: cache blocks (16 tokens, all heads) per pipeline stage.
-template <int ST, bool FP8, bool E5, int D, int NW, int STAGES, int BPS>
-__global__ void __launch_bounds__(NW * 32, 1)
+// XP: the cache is x-packed (key_cache [block][head][D/x][16][x], value_cache [block][head][D][16],
+// heads dense): K and V of one block, ALL heads, are one contiguous run each -- one 1-D bulk copy
+// each, and every warp finds its head's page at warp * PAGE_BYTES in the stream kernel's format.
+// NW: kv heads per CTA (= warps); the kv heads of a GPU are cut into num_kv_heads / NW groups and
+// an item is one (sequence, head group).  MINB: CTAs per SM the launch counts on.
+template <int ST, bool FP8, bool E5, int D, int NW, int STAGES, int BPS, bool XP, int MINB>
+__global__ void __launch_bounds__(NW * 32, MINB)
 paged_attention_nhd_kernel(const __grid_constant__ CUtensorMap map_k,
                            const __grid_constant__ CUtensorMap map_v, const NhdParams p) {
   using T = typename Scalar<ST>::type;
   constexpr bool MMA_BF16 = (!FP8) && (ST == B200PA_BF16);
   constexpr int CES = FP8 ? 1 : 2;
   constexpr int ROW = D * CES;                   // bytes of one token row of one head
-  constexpr int NCH = ROW / 128;                 // 128-byte boxes per row
-  static_assert(ROW % 128 == 0 && NCH >= 1 && NCH <= 2, "head rows of 128 or 256 bytes");
-  constexpr int BOX_BYTES = 128 * kBS * NW;      // one box: [head][token][128 B]
-  constexpr int HEAD_BYTES = 128 * kBS;          // one head's 16 rows inside a box
-  constexpr int KBLK = NCH * BOX_BYTES;          // K (or V) of one block
+  constexpr int NCH = XP ? 1 : ROW / 128;        // NHD: 128-byte boxes per row
+  static_assert(XP || (ROW % 128 == 0 && NCH >= 1 && NCH <= 2), "head rows of 128 or 256 bytes");
+  constexpr int BOX_BYTES = 128 * kBS * NW;      // NHD: one box, [head][token][128 B]
+  constexpr int HEAD_BYTES = 128 * kBS;          // NHD: one head's 16 rows inside a box
+  constexpr int PAGE_BYTES = ROW * kBS;          // x-packed: one head's K (or V) page
+  constexpr int KBLK = ROW * kBS * NW;           // K (or V) of one block, all heads
   constexpr int STAGE_BYTES = BPS * 2 * KBLK;
+  constexpr int KCS = kBS * 16;                  // x-packed K: bytes between 16-byte chunks
+  constexpr int VRS = kBS * CES;                 // x-packed V: bytes per head-element row
   constexpr int KSTEPS = D / 16;
   constexpr int MT = D / 16;
-  constexpr bool DPERM = FP8;                    // see store_out_tile
+  constexpr bool DPERM = FP8 && !XP;             // see store_out_tile
   constexpr float OFF = MMA_BF16 ? 0.f : 6.f;
   constexpr float CAP = MMA_BF16 ? 8.f : 14.f;
   constexpr int SF = slot_floats(D);
 
   extern __shared__ __align__(1024) uint8_t smem[];
   __shared__ __align__(8) uint64_t bars[2 * STAGES];   // full[STAGES], empty[STAGES]
-  __shared__ int pend_s[2][5];    // valid, first CTA of the item, CTAs of the item, b, last?
+  __shared__ int pend_s[2][6];    // valid, first CTA of the item, CTAs of the item, b, last?, head group
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int r = lane >> 2, q4 = lane & 3;
@@ -85,7 +101,8 @@ paged_attention_nhd_kernel(const __grid_constant__ CUtensorMap map_k,
   asm volatile("griddepcontrol.wait;" ::: "memory");
 
   // ---------------------------------------------------------------- the CTA's span
-  const long long Ttot = total_stages<BPS>(p.seq_lens, p.num_seqs, lane);
+  const int groups = p.num_kv_heads / NW;
+  const long long Ttot = total_stages<BPS>(p.seq_lens, p.num_seqs, lane) * groups;
   const long long W = min((long long)gridDim.x, Ttot);
   const long long w = blockIdx.x;
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
@@ -103,15 +120,15 @@ paged_attention_nhd_kernel(const __grid_constant__ CUtensorMap map_k,
   }
   __syncthreads();
   int mflags = 0;            // bit 0: head piece left in slot 0, bit 2: tail piece in slot 1
-  int mh_b = 0, mt_b = 0, mh_ns = 0, mt_ns = 0;
+  int mh_b = 0, mt_b = 0, mh_ns = 0, mt_ns = 0, mh_vh = 0, mt_vh = 0;
   long long mh_ib = 0, mt_ib = 0;
   float* const my_slots = p.ws + (size_t)2 * blockIdx.x * NW * SF;   // [kind][warp]
   if (w < W) {
   const long long u0 = (w * Ttot) / W, u1 = ((w + 1) * Ttot) / W;
   Cursor pc;
   {
-    const Loc loc = locate_stage<BPS>(p.seq_lens, p.num_seqs, 1, u0, lane);
-    pc.b = loc.b; pc.vh = 0; pc.len = loc.len; pc.ns = loc.ns;
+    const Loc loc = locate_stage<BPS>(p.seq_lens, p.num_seqs, groups, u0, lane);
+    pc.b = loc.b; pc.vh = loc.vh; pc.len = loc.len; pc.ns = loc.ns;
     pc.left = (int)(u1 - u0);
     cursor_open(pc, loc.st);
   }
@@ -127,8 +144,7 @@ paged_attention_nhd_kernel(const __grid_constant__ CUtensorMap map_k,
   auto produce = [&]() {   // every lane of warp 0
     if (pc.st == pc.st_end) {
       if (pc.left == 0) { producing = false; return; }
-      cursor_next_piece<BPS>(pc, p.seq_lens, 1);
-      pc.vh = 0;
+      cursor_next_piece<BPS>(pc, p.seq_lens, groups);
     }
     const int blk0 = pc.st * BPS;
     const int nblk = min(BPS, (pc.len + kBS - 1) / kBS - blk0);
@@ -153,13 +169,22 @@ paged_attention_nhd_kernel(const __grid_constant__ CUtensorMap map_k,
 #pragma unroll
       for (int g = 0; g < BPS; ++g) {
         if (g < nblk) {
+          if constexpr (XP) {
+            const int64_t boff = ((int64_t)phys[g] * p.kv_block_stride +
+                                  (int64_t)pc.vh * NW * p.kv_head_stride) * CES;
+            tma_load_1d(dst + g * 2 * KBLK, reinterpret_cast<const uint8_t*>(p.k_cache) + boff, KBLK,
+                        bar, policy);
+            tma_load_1d(dst + g * 2 * KBLK + KBLK,
+                        reinterpret_cast<const uint8_t*>(p.v_cache) + boff, KBLK, bar, policy);
+            continue;
+          }
 #pragma unroll
           for (int h = 0; h < NCH; ++h) {
             // box h of the block: elements [h * 128 / CES, + 128 / CES) of D, 16 tokens, NW heads
-            tma_load_4d(dst + g * 2 * KBLK + h * BOX_BYTES, &map_k, h * (128 / CES), 0, 0, phys[g],
-                        bar, policy);
-            tma_load_4d(dst + g * 2 * KBLK + KBLK + h * BOX_BYTES, &map_v, h * (128 / CES), 0, 0,
+            tma_load_4d(dst + g * 2 * KBLK + h * BOX_BYTES, &map_k, h * (128 / CES), 0, pc.vh * NW,
                         phys[g], bar, policy);
+            tma_load_4d(dst + g * 2 * KBLK + KBLK + h * BOX_BYTES, &map_v, h * (128 / CES), 0,
+                        pc.vh * NW, phys[g], bar, policy);
           }
         }
       }
@@ -177,28 +202,75 @@ paged_attention_nhd_kernel(const __grid_constant__ CUtensorMap map_k,
   float o[MT][4];
   float msub[2], lsum[2], slope_l2[2];
   const bool has_alibi = p.alibi_slopes != nullptr;
-  const int head0 = warp * p.group;
+  int head0 = 0;                               // first query head of this warp's kv head
   const int heads_valid = p.group;            // <= 8
   float sl2 = p.scale * kLog2e, out_scale = 1.f;
   if constexpr (FP8) {
     sl2 *= *p.k_scale;
     out_scale = *p.v_scale;
   }
-  // ldmatrix lane addressing inside a head's [16 tokens][128 B] tile, 128-byte swizzle: chunk c of
-  // row t sits at t * 128 + ((c ^ (t & 7)) << 4); every lane's row has (t & 7) == mi.
+  // NHD: ldmatrix lane addressing inside a head's [16 tokens][128 B] tile, 128-byte swizzle:
+  // chunk c of row t sits at t * 128 + ((c ^ (t & 7)) << 4); every lane's row has (t & 7) == mi.
   // K x4 = {tok 0-7, chunk c | tok 8-15, chunk c | tok 0-7, chunk c+1 | tok 8-15, chunk c+1}
-  const uint32_t k_row_off = warp * HEAD_BYTES + ((mat & 1) * 8 + mi) * 128;
-  const int k_ch = mat >> 1;
   // V x4 (transposing): fp8 like K; 16-bit {tok 0-7, ch c | tok 0-7, ch c+1 | tok 8-15, ch c | ..}
-  const uint32_t v_row_off = FP8 ? k_row_off : warp * HEAD_BYTES + ((mat >> 1) * 8 + mi) * 128;
-  const int v_ch = FP8 ? (mat >> 1) : (mat & 1);
-  auto swz = [&](int cg) {   // chunk cg (0 .. ROW/16) of this lane's row -> byte offset in the K/V block
+  // x-packed: the stream kernel's addressing inside the head's page (see there).
+  uint32_t k_row_off, v_row_off;
+  int k_ch = 0, v_ch = 0, tokA, tokB;
+  if constexpr (XP) {
+    if constexpr (FP8) {
+      const int sig0 = 4 * (mi >> 1) + (mi & 1) + ((mi >= 4) ? 2 : 0);
+      const int tok = (mat & 1) ? (sig0 ^ 2) : sig0;
+      k_row_off = warp * PAGE_BYTES + (mat >> 1) * KCS + tok * 16;
+      v_row_off = warp * PAGE_BYTES + lane * VRS;
+      tokA = 4 * (r >> 1) + (r & 1) + ((r >= 4) ? 2 : 0);
+      tokB = tokA ^ 2;
+    } else {
+      k_row_off = warp * PAGE_BYTES + (mat >> 1) * KCS + ((mat & 1) * 8 + mi) * 16;
+      v_row_off = warp * PAGE_BYTES + ((mat & 1) * 8 + mi) * VRS + (mat >> 1) * 16;
+      tokA = r;
+      tokB = r + 8;
+    }
+  } else {
+    k_row_off = warp * HEAD_BYTES + ((mat & 1) * 8 + mi) * 128;
+    k_ch = mat >> 1;
+    v_row_off = FP8 ? k_row_off : warp * HEAD_BYTES + ((mat >> 1) * 8 + mi) * 128;
+    v_ch = FP8 ? (mat >> 1) : (mat & 1);
+    tokA = r;
+    tokB = r + 8;
+  }
+  auto swz = [&](int cg) {   // NHD: chunk cg (0 .. ROW/16) of this lane's row -> byte offset in the block
     return (cg >> 3) * BOX_BYTES + (((cg & 7) ^ mi) << 4);
   };
-  const int tokA = r, tokB = r + 8;
+  // fused cache write: this lane's pairs of head elements (2(lane + 32j), +1) of the new token
+  constexpr int NP = (D / 2 + 31) / 32;
+  uint32_t nt_k[NP], nt_v[NP];
+  int64_t nt_slot = -1;
+  float ks_raw = 1.f;
+  if constexpr (FP8) ks_raw = *p.k_scale;
 
   auto begin_piece = [&]() {
     piece_begin = cc.st;
+    const int kvh = cc.vh * NW + warp;
+    head0 = kvh * p.group;
+    if (p.new_key != nullptr) {
+      nt_slot = -1;
+      if (cc.st_end == cc.ns) {     // this piece reaches the end of the sequence
+        nt_slot = p.slot_mapping[cc.b];
+        const uint32_t* kn = reinterpret_cast<const uint32_t*>(
+            reinterpret_cast<const T*>(p.new_key) + (int64_t)cc.b * p.new_key_stride + (int64_t)kvh * D);
+        const uint32_t* vn = reinterpret_cast<const uint32_t*>(
+            reinterpret_cast<const T*>(p.new_value) + (int64_t)cc.b * p.new_value_stride + (int64_t)kvh * D);
+#pragma unroll
+        for (int j = 0; j < NP; ++j) {
+          const int pi = lane + 32 * j;
+          nt_k[j] = nt_v[j] = 0u;
+          if (pi < D / 2) {
+            nt_k[j] = kn[pi];
+            nt_v[j] = vn[pi];
+          }
+        }
+      }
+    }
     const T* qrow = reinterpret_cast<const T*>(p.q) + (int64_t)cc.b * p.q_stride +
                     (int64_t)(head0 + r) * D;
 #pragma unroll
@@ -258,8 +330,8 @@ paged_attention_nhd_kernel(const __grid_constant__ CUtensorMap map_k,
       }
     } else {
       const long long ib = u0 + it - cc.st_end;   // the sequence's first flattened stage
-      if (from_start) { mflags |= 4; mt_b = cc.b; mt_ns = cc.ns; mt_ib = ib; }
-      else { mflags |= 1; mh_b = cc.b; mh_ns = cc.ns; mh_ib = ib; }
+      if (from_start) { mflags |= 4; mt_b = cc.b; mt_vh = cc.vh; mt_ns = cc.ns; mt_ib = ib; }
+      else { mflags |= 1; mh_b = cc.b; mh_vh = cc.vh; mh_ns = cc.ns; mh_ib = ib; }
       float* slot = my_slots + (size_t)((from_start ? NW : 0) + warp) * SF;
 #pragma unroll
       for (int mt = 0; mt < MT; ++mt)
@@ -280,8 +352,7 @@ paged_attention_nhd_kernel(const __grid_constant__ CUtensorMap map_k,
     if (cc.st == cc.st_end) {
       end_piece();
       if (cc.left == 0) break;
-      cursor_next_piece<BPS>(cc, p.seq_lens, 1);
-      cc.vh = 0;
+      cursor_next_piece<BPS>(cc, p.seq_lens, groups);
       begin_piece();
     }
     if (warp == 0 && producing) produce();   // the stage the previous iteration released
@@ -292,6 +363,69 @@ paged_attention_nhd_kernel(const __grid_constant__ CUtensorMap map_k,
     const uint32_t sbase = ring_u32 + s * STAGE_BYTES;
     mbar_wait(full0 + 8 * s, (it / STAGES) & 1);
 
+    // ---- fused cache write: the stage that ends the sequence holds position len - 1, whose K/V
+    // come from this step's key / value rows (quantised exactly as reshape_and_cache does), not
+    // from the bytes the copy found in the cache.  Every warp patches its own head only.
+    if (p.new_key != nullptr && cc.st == cc.ns && nt_slot >= 0) {
+      const int t = cc.len - 1 - page0 * kBS;
+      const int g = t >> 4, tt = t & (kBS - 1);
+      uint8_t* const stage = smem + (ring_u32 - smem_u32(smem)) + s * STAGE_BYTES + g * 2 * KBLK;
+      const int64_t blk = nt_slot / kBS;
+      const int off = (int)(nt_slot % kBS);
+      uint8_t* const kg = reinterpret_cast<uint8_t*>(const_cast<void*>(p.k_cache)) +
+                          (blk * p.kv_block_stride + (int64_t)(cc.vh * NW + warp) * p.kv_head_stride) * CES;
+      uint8_t* const vg = reinterpret_cast<uint8_t*>(const_cast<void*>(p.v_cache)) +
+                          (blk * p.kv_block_stride + (int64_t)(cc.vh * NW + warp) * p.kv_head_stride) * CES;
+      auto put = [&](uint8_t* dst, uint32_t wv) {
+        if constexpr (FP8) *reinterpret_cast<uint16_t*>(dst) = (uint16_t)wv;
+        else *reinterpret_cast<uint32_t*>(dst) = wv;
+      };
+#pragma unroll
+      for (int j = 0; j < NP; ++j) {
+        const int e0 = 2 * (lane + 32 * j);
+        if (e0 < D) {
+          uint32_t kw = nt_k[j], vw = nt_v[j];
+          if constexpr (FP8) {
+            const T* ke = reinterpret_cast<const T*>(&nt_k[j]);
+            const T* ve = reinterpret_cast<const T*>(&nt_v[j]);
+            kw = fp8_quant2<(E5 ? B200PA_KV_FP8_E5M2 : B200PA_KV_FP8_E4M3)>(
+                Scalar<ST>::to_float(ke[0]), Scalar<ST>::to_float(ke[1]), ks_raw);
+            vw = fp8_quant2<(E5 ? B200PA_KV_FP8_E5M2 : B200PA_KV_FP8_E4M3)>(
+                Scalar<ST>::to_float(ve[0]), Scalar<ST>::to_float(ve[1]), out_scale);
+          }
+          if constexpr (XP) {
+            constexpr int X = 16 / CES;
+            const int kchunk = (e0 / X) * KCS + (e0 % X) * CES;
+            put(stage + warp * PAGE_BYTES + kchunk + tt * 16, kw);
+            put(kg + kchunk + off * 16, kw);
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {   // V [D][16]: one element per head-element row
+              if constexpr (FP8) {
+                const uint8_t b8 = (uint8_t)(vw >> (8 * i));
+                stage[KBLK + warp * PAGE_BYTES + (e0 + i) * kBS + tt] = b8;
+                vg[(e0 + i) * kBS + off] = b8;
+              } else {
+                const uint16_t v16 = (uint16_t)(vw >> (16 * i));
+                reinterpret_cast<uint16_t*>(stage + KBLK + warp * PAGE_BYTES)[(e0 + i) * kBS + tt] = v16;
+                reinterpret_cast<uint16_t*>(vg)[(e0 + i) * kBS + off] = v16;
+              }
+            }
+          } else {
+            // token-major rows: chunk (e0 * CES) / 16 of row tt, swizzled in shared memory
+            const int byte = e0 * CES, cg = byte >> 4;
+            const int soff = (cg >> 3) * BOX_BYTES + warp * HEAD_BYTES + tt * 128 +
+                             (((cg & 7) ^ (tt & 7)) << 4) + (byte & 15);
+            put(stage + soff, kw);
+            put(stage + KBLK + soff, vw);
+            put(kg + (int64_t)off * p.kv_token_stride * CES + byte, kw);
+            put(vg + (int64_t)off * p.kv_token_stride * CES + byte, vw);
+          }
+        }
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncwarp();
+    }
+
     // ---- S^T = K Q^T
     float sc[BPS][4];
 #pragma unroll
@@ -300,7 +434,27 @@ paged_attention_nhd_kernel(const __grid_constant__ CUtensorMap map_k,
       if (g < npg) {
         const uint32_t kbase = sbase + g * 2 * KBLK + k_row_off;
         float sb[4] = {0.f, 0.f, 0.f, 0.f};
-        if constexpr (FP8) {
+        if constexpr (XP && FP8) {
+#pragma unroll
+          for (int c = 0; c < KSTEPS; c += 2) {
+            uint32_t w4[4], a[4];
+            ldmatrix_x4(w4, kbase + c * KCS);
+            fp8x4_to_f16x2x2<E5>(w4[0], a[0], a[2]);
+            fp8x4_to_f16x2x2<E5>(w4[1], a[1], a[3]);
+            mma16816<false>(sc[g], a, qb[c][0], qb[c][1]);
+            fp8x4_to_f16x2x2<E5>(w4[2], a[0], a[2]);
+            fp8x4_to_f16x2x2<E5>(w4[3], a[1], a[3]);
+            mma16816<false>(sb, a, qb[c + 1][0], qb[c + 1][1]);
+          }
+        } else if constexpr (XP) {
+#pragma unroll
+          for (int ks = 0; ks < KSTEPS; ++ks) {
+            uint32_t a[4];
+            ldmatrix_x4(a, kbase + ks * 2 * KCS);
+            if (ks & 1) mma16816<MMA_BF16>(sb, a, qb[ks][0], qb[ks][1]);
+            else mma16816<MMA_BF16>(sc[g], a, qb[ks][0], qb[ks][1]);
+          }
+        } else if constexpr (FP8) {
 #pragma unroll
           for (int c = 0; c < KSTEPS; c += 2) {
             uint32_t w4[4], a[4];
@@ -382,8 +536,15 @@ paged_attention_nhd_kernel(const __grid_constant__ CUtensorMap map_k,
       for (int j = 0; j < 4; ++j) pr[j] = ex2(d[g][j]);
       lsum[0] += pr[0] + pr[2];
       lsum[1] += pr[1] + pr[3];
-      pb[g][0] = movmatrix_trans(pack2<MMA_BF16>(pr[0], pr[1]));
-      pb[g][1] = movmatrix_trans(pack2<MMA_BF16>(pr[2], pr[3]));
+      const uint32_t ta = movmatrix_trans(pack2<MMA_BF16>(pr[0], pr[1]));
+      const uint32_t tb = movmatrix_trans(pack2<MMA_BF16>(pr[2], pr[3]));
+      if constexpr (XP && FP8) {     // see the stream kernel: b0 / b1 swapped for q >= 2
+        pb[g][0] = (q4 >= 2) ? tb : ta;
+        pb[g][1] = (q4 >= 2) ? ta : tb;
+      } else {
+        pb[g][0] = ta;
+        pb[g][1] = tb;
+      }
     }
 
     // ---- O^T += V^T P^T
@@ -395,11 +556,34 @@ paged_attention_nhd_kernel(const __grid_constant__ CUtensorMap map_k,
         const int nv = cc.len - (tok0 + g * kBS);
         uint32_t m01 = 0xffffffffu, m23 = 0xffffffffu;
         if (nv < kBS) {
-          const int t01 = 2 * q4, t23 = 2 * q4 + 8;
+          const int t01 = (XP && FP8) ? 4 * q4 : 2 * q4;
+          const int t23 = (XP && FP8) ? 4 * q4 + 2 : 2 * q4 + 8;
           m01 = (t01 < nv ? 0x0000ffffu : 0u) | (t01 + 1 < nv ? 0xffff0000u : 0u);
           m23 = (t23 < nv ? 0x0000ffffu : 0u) | (t23 + 1 < nv ? 0xffff0000u : 0u);
         }
-        if constexpr (FP8) {
+        if constexpr (XP && FP8) {
+#pragma unroll
+          for (int gg = 0; gg < D / 32; ++gg) {
+            uint32_t w4[4], a[4];
+            ldmatrix_x4(w4, vbase + gg * (32 * VRS));
+            fp8x4_to_f16x2x2<E5>(w4[0], a[0], a[2]);
+            fp8x4_to_f16x2x2<E5>(w4[1], a[1], a[3]);
+            a[0] &= m01; a[1] &= m01; a[2] &= m23; a[3] &= m23;
+            mma16816<false>(o[2 * gg], a, pb[g][0], pb[g][1]);
+            fp8x4_to_f16x2x2<E5>(w4[2], a[0], a[2]);
+            fp8x4_to_f16x2x2<E5>(w4[3], a[1], a[3]);
+            a[0] &= m01; a[1] &= m01; a[2] &= m23; a[3] &= m23;
+            mma16816<false>(o[2 * gg + 1], a, pb[g][0], pb[g][1]);
+          }
+        } else if constexpr (XP) {
+#pragma unroll
+          for (int mt = 0; mt < MT; ++mt) {
+            uint32_t a[4];
+            ldmatrix_x4(a, vbase + mt * (16 * VRS));
+            a[0] &= m01; a[1] &= m01; a[2] &= m23; a[3] &= m23;
+            mma16816<MMA_BF16>(o[mt], a, pb[g][0], pb[g][1]);
+          }
+        } else if constexpr (FP8) {
 #pragma unroll
           for (int gg = 0; gg < D / 32; ++gg) {
             uint32_t w4[4], a[4];
@@ -465,6 +649,7 @@ paged_attention_nhd_kernel(const __grid_constant__ CUtensorMap map_k,
       pend_s[k][2] = n;
       pend_s[k][3] = k ? mt_b : mh_b;
       pend_s[k][4] = last;
+      pend_s[k][5] = k ? mt_vh : mh_vh;
       pend_s[k][0] = 1;
     }
   }
@@ -520,7 +705,7 @@ paged_attention_nhd_kernel(const __grid_constant__ CUtensorMap map_k,
       }
     }
     const float inv0 = __fdividef(1.f, ls[0] + 1e-6f), inv1 = __fdividef(1.f, ls[1] + 1e-6f);
-    const int hd0 = warp * p.group, hv = p.group;
+    const int hd0 = (pend_s[k][5] * NW + warp) * p.group, hv = p.group;
     T* dst = reinterpret_cast<T*>(p.out) + ((int64_t)b * p.num_heads + hd0) * D;
 #pragma unroll
     for (int mt = 0; mt < MT; ++mt) {
@@ -559,11 +744,12 @@ inline EncodeTiledFn encode_tiled_fn() {
 // Tensor map of one cache: dimensions listed as (D, token, head, block) -- whatever their order
 // in memory (NHD or HND: the strides say) -- and a box of (128 bytes of D, 16 tokens, NW heads),
 // which therefore lands in shared memory as [head][token][128 B], 128-byte swizzled.
-inline bool make_cache_map(CUtensorMap* map, const void* cache, int ces, int head_size, int nw,
-                           int64_t block_stride, int64_t token_stride, int64_t head_stride) {
+inline bool make_cache_map(CUtensorMap* map, const void* cache, int ces, int head_size,
+                           int num_kv_heads, int nw, int64_t block_stride, int64_t token_stride,
+                           int64_t head_stride) {
   EncodeTiledFn fn = encode_tiled_fn();
   if (fn == nullptr) return false;
-  const cuuint64_t dims[4] = {(cuuint64_t)head_size, (cuuint64_t)kBS, (cuuint64_t)nw,
+  const cuuint64_t dims[4] = {(cuuint64_t)head_size, (cuuint64_t)kBS, (cuuint64_t)num_kv_heads,
                               (cuuint64_t)1 << 31};
   const cuuint64_t strides[3] = {(cuuint64_t)token_stride * ces, (cuuint64_t)head_stride * ces,
                                  (cuuint64_t)block_stride * ces};
@@ -576,13 +762,13 @@ inline bool make_cache_map(CUtensorMap* map, const void* cache, int ces, int hea
   return rc == CUDA_SUCCESS;
 }
 
-template <int ST, bool FP8, bool E5, int D, int NW, int STAGES, int BPS>
-int launch_nhd_t(const NhdParams& p_in, const void* key_cache, const void* value_cache,
-                 int64_t block_stride, int64_t token_stride, int64_t head_stride, void* workspace,
-                 int64_t workspace_bytes, int num_sms, cudaStream_t stream) {
+template <int ST, bool FP8, bool E5, int D, int NW, int STAGES, int BPS, bool XP, int MINB>
+int launch_nhd_t(const NhdParams& p_in, void* workspace, int64_t workspace_bytes, int num_sms,
+                 cudaStream_t stream) {
   constexpr int CES = FP8 ? 1 : 2;
-  constexpr int SMEM = STAGES * BPS * 2 * (D * CES / 128) * (128 * kBS * NW) + 1024;
-  auto kern = paged_attention_nhd_kernel<ST, FP8, E5, D, NW, STAGES, BPS>;
+  constexpr int SMEM = STAGES * BPS * 2 * (D * CES * kBS * NW) + 1024;
+  auto kern = paged_attention_nhd_kernel<ST, FP8, E5, D, NW, STAGES, BPS, XP, MINB>;
+  static_assert(MINB * (SMEM + 2048) <= 232448, "the ring of MINB CTAs fits one SM");
   static bool attr_set[64] = {false};
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64)
@@ -593,7 +779,7 @@ int launch_nhd_t(const NhdParams& p_in, const void* key_cache, const void* value
       return set_error(B200PA_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     attr_set[dev] = true;
   }
-  const int ctas = num_sms * (8 / NW);      // 8 warps per SM
+  const int ctas = num_sms * MINB;
   if (ctas * (int)sizeof(int) > kCounterBytes)
     return set_error(B200PA_ERR_UNSUPPORTED, "nhd kernel: %d CTAs exceed the workspace header", ctas);
   const int64_t need = kCounterBytes + (int64_t)2 * ctas * NW * slot_floats(D) * (int64_t)sizeof(float);
@@ -601,9 +787,15 @@ int launch_nhd_t(const NhdParams& p_in, const void* key_cache, const void* value
     return set_error(B200PA_ERR_INVALID, "workspace too small: %lld bytes, need %lld",
                      (long long)workspace_bytes, (long long)need);
   CUtensorMap map_k, map_v;
-  if (!make_cache_map(&map_k, key_cache, CES, D, NW, block_stride, token_stride, head_stride) ||
-      !make_cache_map(&map_v, value_cache, CES, D, NW, block_stride, token_stride, head_stride))
-    return -1;     // the caller falls back to the stream kernel's row copies
+  memset(&map_k, 0, sizeof(map_k));
+  memset(&map_v, 0, sizeof(map_v));
+  if constexpr (!XP) {
+    if (!make_cache_map(&map_k, p_in.k_cache, CES, D, p_in.num_kv_heads, NW, p_in.kv_block_stride,
+                        p_in.kv_token_stride, p_in.kv_head_stride) ||
+        !make_cache_map(&map_v, p_in.v_cache, CES, D, p_in.num_kv_heads, NW, p_in.kv_block_stride,
+                        p_in.kv_token_stride, p_in.kv_head_stride))
+      return -1;     // the caller falls back to the stream kernel's row copies
+  }
   NhdParams p = p_in;
   p.counters = reinterpret_cast<int*>(workspace);
   p.ws = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + kCounterBytes);

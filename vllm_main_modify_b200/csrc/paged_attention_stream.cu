@@ -1310,7 +1310,7 @@ paged_attention_stream_kernel(const StreamParams p) {
 }
 
 // ---------------------------------------------------------------------------------------
-#if STREAM_PART == 6
+#if STREAM_PART == 6 || STREAM_PART == 7
 #include "paged_attention_nhd.cuh"
 #endif
 
@@ -1393,8 +1393,10 @@ int launch_stream_e5m2_wide(StreamParams& p, int scalar_type, int head_size, boo
     int block_size, int num_sms, int64_t workspace_bytes, cudaStream_t stream);
 // NHD caches with 2 / 4 / 8 kv heads per GPU (paged_attention_nhd.cuh); -1: not taken (the caller
 // goes on with the stream kernel's FLASH path)
-int launch_stream_nhd(const StreamParams& p, bool fp8, int scalar_type, int head_size,
-    void* workspace, int64_t workspace_bytes, int num_sms, cudaStream_t stream);
+int launch_stream_block_xp(const StreamParams& p, bool fp8, int scalar_type, int head_size,
+    int tune, void* workspace, int64_t workspace_bytes, int num_sms, cudaStream_t stream);
+int launch_stream_block_nhd(const StreamParams& p, bool fp8, int scalar_type, int head_size,
+    int tune, void* workspace, int64_t workspace_bytes, int num_sms, cudaStream_t stream);
 
 #define STREAM_CALL(ST, FP8V, DV, NWV, SG, PP, MB, ...) \
   return launch_stream_t<ST, FP8V, DV, NWV, SG, PP, MB, ##__VA_ARGS__>(p, num_sms, workspace_bytes, stream)
@@ -1531,12 +1533,14 @@ int launch_stream_e5m2_wide(StreamParams& p, int scalar_type, int head_size, boo
 }
 #endif
 #undef STREAM_E5M2_BY_HEAD_SIZE
-#elif STREAM_PART == 6
-int launch_stream_nhd(const StreamParams& sp, bool fp8, int scalar_type, int head_size,
-    void* workspace, int64_t workspace_bytes, int num_sms, cudaStream_t stream) {
+#elif STREAM_PART == 6 || STREAM_PART == 7
+// part 6: the x-packed layout, part 7: the token-major NHD layout
+static int launch_block_kernel(const StreamParams& sp, bool fp8, int scalar_type, int head_size,
+    int tune, void* workspace, int64_t workspace_bytes, int num_sms, cudaStream_t stream) {
+  constexpr bool XPV = STREAM_PART == 6;
   if (head_size != 128 || sp.group > 8 || sp.h_tiles != 1) return -1;
   if (sp.num_kv_heads != 2 && sp.num_kv_heads != 4 && sp.num_kv_heads != 8) return -1;
-  if (sp.new_key != nullptr || sp.bs_vert_stride > 1) return -1;
+  if (sp.bs_vert_stride > 1) return -1;
   NhdParams p;
   p.out = sp.out;
   p.lse = sp.lse;
@@ -1545,33 +1549,63 @@ int launch_stream_nhd(const StreamParams& sp, bool fp8, int scalar_type, int hea
   p.ws = nullptr;
   p.counters = nullptr;
   p.q = sp.q;
+  p.k_cache = sp.k_cache;
+  p.v_cache = sp.v_cache;
   p.block_tables = sp.block_tables;
   p.seq_lens = sp.seq_lens;
   p.alibi_slopes = sp.alibi_slopes;
   p.k_scale = sp.k_scale;
   p.v_scale = sp.v_scale;
+  p.new_key = sp.new_key;
+  p.new_value = sp.new_value;
+  p.slot_mapping = sp.slot_mapping;
+  p.new_key_stride = sp.new_key_stride;
+  p.new_value_stride = sp.new_value_stride;
   p.q_stride = sp.q_stride;
+  p.kv_block_stride = sp.kv_block_stride;
+  p.kv_token_stride = sp.kv_token_stride;
+  p.kv_head_stride = sp.kv_head_stride;
   p.num_seqs = sp.num_seqs;
   p.num_heads = sp.num_heads;
   p.num_kv_heads = sp.num_kv_heads;
   p.group = sp.group;
   p.max_num_blocks_per_seq = sp.max_num_blocks_per_seq;
   p.scale = sp.scale;
-#define NHD_CALL(ST, FP8V, NWV, SG, BP)                                                         \
-  return launch_nhd_t<ST, FP8V, false, 128, NWV, SG, BP>(p, sp.k_cache, sp.v_cache,             \
-      sp.kv_block_stride, sp.kv_token_stride, sp.kv_head_stride, workspace, workspace_bytes,   \
-      num_sms, stream)
-#define NHD_BY_HEADS(ST)                                                                        \
-  switch (sp.num_kv_heads) {                                                                    \
-    case 8: if (fp8) { NHD_CALL(ST, true, 8, 3, 2); } else { NHD_CALL(ST, false, 8, 3, 1); }     \
-    case 4: if (fp8) { NHD_CALL(ST, true, 4, 3, 2); } else { NHD_CALL(ST, false, 4, 3, 1); }     \
-    default: if (fp8) { NHD_CALL(ST, true, 2, 3, 2); } else { NHD_CALL(ST, false, 2, 3, 1); }    \
+  // launch shapes (kv heads per CTA x stages x blocks per stage x CTAs per SM), tune 20 + i:
+  //   0: 8 x 3 x (2 | 1) x 1    1: 4 x 2 x (2 | 1) x 3    2: 4 x 3 x (2 | 1) x 2
+  //   3: 2 x 2 x (2 | 1) x 6    4: 8 x 2 x (2 | 1) x 1        (fp8 | 16-bit blocks per stage)
+  int v = (tune >= 20 && tune <= 24) ? tune - 20 : 1;
+  const int nw_of[5] = {8, 4, 4, 2, 8};
+  while (sp.num_kv_heads % nw_of[v] != 0) v = (v == 0 || v == 4) ? 1 : 3;
+#define BLK_CALL(ST, FP8V, NWV, SG, BP, MB)                                                     \
+  return launch_nhd_t<ST, FP8V, false, 128, NWV, SG, BP, XPV, MB>(p, workspace, workspace_bytes, \
+                                                                 num_sms, stream)
+#define BLK_BY_SHAPE(ST)                                                                        \
+  switch (v) {                                                                                  \
+    case 0: if (fp8) { BLK_CALL(ST, true, 8, 3, 2, 1); } else { BLK_CALL(ST, false, 8, 3, 1, 1); } \
+    case 2: if (fp8) { BLK_CALL(ST, true, 4, 3, 2, 2); } else { BLK_CALL(ST, false, 4, 3, 1, 2); } \
+    case 3: if (fp8) { BLK_CALL(ST, true, 2, 2, 2, 6); } else { BLK_CALL(ST, false, 2, 2, 1, 6); } \
+    case 4: if (fp8) { BLK_CALL(ST, true, 8, 2, 2, 1); } else { BLK_CALL(ST, false, 8, 2, 1, 1); } \
+    default: if (fp8) { BLK_CALL(ST, true, 4, 2, 2, 3); } else { BLK_CALL(ST, false, 4, 2, 1, 3); } \
   }
-  if (scalar_type == B200PA_BF16) { NHD_BY_HEADS(B200PA_BF16) }
-  else { NHD_BY_HEADS(B200PA_F16) }
-#undef NHD_BY_HEADS
-#undef NHD_CALL
+  if (scalar_type == B200PA_BF16) { BLK_BY_SHAPE(B200PA_BF16) }
+  else { BLK_BY_SHAPE(B200PA_F16) }
+#undef BLK_BY_SHAPE
+#undef BLK_CALL
 }
+#if STREAM_PART == 6
+int launch_stream_block_xp(const StreamParams& sp, bool fp8, int scalar_type, int head_size,
+    int tune, void* workspace, int64_t workspace_bytes, int num_sms, cudaStream_t stream) {
+  return launch_block_kernel(sp, fp8, scalar_type, head_size, tune, workspace, workspace_bytes,
+                             num_sms, stream);
+}
+#else
+int launch_stream_block_nhd(const StreamParams& sp, bool fp8, int scalar_type, int head_size,
+    int tune, void* workspace, int64_t workspace_bytes, int num_sms, cudaStream_t stream) {
+  return launch_block_kernel(sp, fp8, scalar_type, head_size, tune, workspace, workspace_bytes,
+                             num_sms, stream);
+}
+#endif
 #else
 // Upper bound of the workspace any stream launch on a device with `num_sms` SMs needs.
 int64_t stream_workspace_bytes(int num_sms, int head_size) {
@@ -1708,11 +1742,11 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
   if (flash_token_stride > 0) {
     // several kv heads per GPU in NHD order (a token's heads are adjacent, the tokens of one head
     // are not): whole-block stages through tensor-map TMA, one warp per head
-    // (paged_attention_nhd.cuh).  tune 99 (test hook) keeps the row copies of the FLASH path.
-    if (block_size == 16 && kv_head_stride < flash_token_stride && tune != 99 &&
+    // (paged_attention_nhd.cuh).  tune >= 100 (test hook) keeps the row copies of the FLASH path.
+    if (block_size == 16 && kv_head_stride < flash_token_stride && tune < 100 &&
         (kv_dtype == B200PA_KV_AUTO || kv_dtype == B200PA_KV_FP8_E4M3)) {
-      const int rc = launch_stream_nhd(p, fp8, scalar_type, head_size, workspace, workspace_bytes,
-                                       num_sms, stream);
+      const int rc = launch_stream_block_nhd(p, fp8, scalar_type, head_size, tune, workspace,
+                                             workspace_bytes, num_sms, stream);
       if (rc >= 0) return rc;
     }
     return launch_stream_flash(p, fp8, scalar_type, head_size, block_size, num_sms, workspace_bytes,
@@ -1720,6 +1754,15 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
   }
   if (block_size == 32)
     return launch_stream_bs32(p, fp8, scalar_type, head_size, num_sms, workspace_bytes, stream);
+  // all the kv heads of a block on this GPU and dense ([block][head] contiguous): whole-block
+  // stages, one warp per head (paged_attention_nhd.cuh with 1-D bulk copies of all heads' K / V).
+  // tune >= 100 (test hook) keeps the per-warp streams, launch shape tune - 100.
+  if (tune < 100 && kv_head_stride == (int64_t)head_size * block_size &&
+      (kv_dtype == B200PA_KV_AUTO || kv_dtype == B200PA_KV_FP8_E4M3)) {
+    const int rc = launch_stream_block_xp(p, fp8, scalar_type, head_size, tune, workspace,
+                                          workspace_bytes, num_sms, stream);
+    if (rc >= 0) return rc;
+  }
   // <ST, FP8, D, NW, STAGES, PPS, MINB>: fp8 stage = PPS x 4 KiB, 16-bit stage = PPS x 8 KiB (D=128).
   // Defaults (tune 0) by the SUSTAINED rate: seconds of back-to-back steps run under the 1 kW
   // power cap at 1.4-1.7 GHz, where 12 warps x 2 stages (fp8) hold 6.4-6.6 TB/s and the former
@@ -1761,6 +1804,7 @@ int launch_stream(void* out, float* lse, int64_t lse_seq_stride, int64_t lse_hea
     case 13: STREAM_CALL(ST, false, DV, 9, 2, 1, 1);                   \
     default: STREAM_CALL(ST, false, DV, 8, 2, 1, 1);                   \
   }
+  tune = tune >= 100 ? tune - 100 : 0;     // launch shapes of the per-warp kernel: 100 + i
   if (scalar_type == B200PA_BF16 && head_size == 128) {
     if (fp8) { STREAM_TUNE_FP8(B200PA_BF16, 128) } else { STREAM_TUNE_16(B200PA_BF16, 128) }
   }

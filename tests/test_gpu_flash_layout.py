@@ -96,10 +96,10 @@ CASES = [
 
 
 def _takes_block_kernel(layout, H, Hkv, D, kv, bs):
-    """2 / 4 / 8 kv heads, head size 128, 16-token blocks, group <= 8: the x-packed cache (the
+    """An even number of kv heads, head size 128, 16-token blocks, group <= 8: the x-packed cache (the
     comparison's other side) and the NHD cache take the whole-block kernel, the HND cache the
     per-warp kernel -- other span cuts, hence another merge order: no bitwise equality."""
-    return (D == 128 and bs == 16 and Hkv in (2, 4, 8) and H // Hkv <= 8
+    return (D == 128 and bs == 16 and Hkv % 2 == 0 and H // Hkv <= 8
             and kv in ("auto", "fp8"))
 
 

@@ -63,6 +63,9 @@ def main():
                                 w["Hkv"], w["scale"], w["bt"], w["sl"], bench.BS, w["max_len"],
                                 None, kv, w["ks"], w["vs"])
 
+        # the phase stamps live in the per-warp stream kernel (tune >= 100 selects it where the
+        # whole-block kernel would otherwise take the call)
+        _native.set_stream_tune(100)
         for _ in range(3):
             step()
         torch.cuda.synchronize()

@@ -37,7 +37,6 @@ int launch_stream(void*, float*, int64_t, int64_t, void*, int64_t, const void*, 
 bool stream_flash_supported(const void*, const void*, const void*, int, int, int, int, int64_t,
                             int64_t, int64_t, int64_t, int, int);
 bool stream_fused_supported(const FusedWrite&, int);
-bool stream_nhd_eligible(int, int, int, int, int64_t, int64_t, int);
 int64_t stream_workspace_bytes(int, int);
 int launch_merge_attn_states(void*, float*, const void*, const float*, const void*, const float*,
                              int64_t, int, int, int, cudaStream_t);

@@ -1539,7 +1539,7 @@ static int launch_block_kernel(const StreamParams& sp, bool fp8, int scalar_type
     int tune, void* workspace, int64_t workspace_bytes, int num_sms, cudaStream_t stream) {
   constexpr bool XPV = STREAM_PART == 6;
   if (head_size != 128 || sp.group > 8 || sp.h_tiles != 1) return -1;
-  if (sp.num_kv_heads != 2 && sp.num_kv_heads != 4 && sp.num_kv_heads != 8) return -1;
+  if (sp.num_kv_heads % 2 != 0) return -1;     // head groups of 2 / 4 / 8
   if (sp.bs_vert_stride > 1) return -1;
   NhdParams p;
   p.out = sp.out;
@@ -1574,7 +1574,10 @@ static int launch_block_kernel(const StreamParams& sp, bool fp8, int scalar_type
   // launch shapes (kv heads per CTA x stages x blocks per stage x CTAs per SM), tune 20 + i:
   //   0: 8 x 3 x (2 | 1) x 1    1: 4 x 2 x (2 | 1) x 3    2: 4 x 3 x (2 | 1) x 2
   //   3: 2 x 2 x (2 | 1) x 6    4: 8 x 2 x (2 | 1) x 1        (fp8 | 16-bit blocks per stage)
-  int v = (tune >= 20 && tune <= 24) ? tune - 20 : 1;
+  // Defaults by the sustained rate (profiles/r02m_kbench_block.jsonl, burst / last third of 3 s):
+  // fp8 shape 1 -- 12 warps -- 6666 / 6242 GB/s on cfg4 (shape 0: 6884 / 5767; the per-warp
+  // kernel 6387 / 6175); 16-bit shape 0, 6228 / 6460 on cfg2 (per-warp 6083 / 6292).
+  int v = (tune >= 20 && tune <= 24) ? tune - 20 : (fp8 ? 1 : 0);
   const int nw_of[5] = {8, 4, 4, 2, 8};
   while (sp.num_kv_heads % nw_of[v] != 0) v = (v == 0 || v == 4) ? 1 : 3;
 #define BLK_CALL(ST, FP8V, NWV, SG, BP, MB)                                                     \
@@ -1659,18 +1662,6 @@ bool stream_flash_supported(const void* query, const void* key_cache, const void
   if (token_stride <= 0 || head_stride < head_size) return false;
   if (q_stride % 4 != 0) return false;
   return true;
-}
-
-// Token-major caches the whole-block kernel (paged_attention_nhd.cuh) takes: NHD order with 2 / 4
-// / 8 kv heads, head size 128, 16-token blocks, group <= 8, auto / fp8_e4m3.  It has no fused
-// cache write: the entry point writes first (reshape_and_cache_flash) and attends second.
-bool stream_nhd_eligible(int num_heads, int num_kv_heads, int head_size, int block_size,
-                         int64_t token_stride, int64_t head_stride, int kv_dtype) {
-  if (head_size != 128 || block_size != 16) return false;
-  if (num_kv_heads != 2 && num_kv_heads != 4 && num_kv_heads != 8) return false;
-  if (num_heads % num_kv_heads != 0 || num_heads / num_kv_heads > 8) return false;
-  if (kv_dtype != B200PA_KV_AUTO && kv_dtype != B200PA_KV_FP8_E4M3) return false;
-  return head_stride < token_stride;
 }
 
 // The fused write reads the new key/value rows with 4-byte loads (pairs of 16-bit elements).

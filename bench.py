@@ -776,8 +776,10 @@ def run_ours(args):
                          "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic,
                          "traffic_source": "profiles/ncu_traffic.json (ncu --set full capture of "
                                            "this workload, committed; not measured in this run)",
-                         "kernel": "paged_attention_stream_kernel (CUDA events around the "
-                                   "attention op, in-loop"
+                         "kernel": ("paged_attention_nhd_kernel (whole-block decode kernel"
+                                    if world <= 4 else
+                                    "paged_attention_stream_kernel (per-warp decode kernel") +
+                                   "; CUDA events around the attention op, in-loop"
                                    + ("; includes the fused cache write)" if fused else ")"),
                          "kernel_ms": round(attn_ms, 4), "peak_source": peak_src,
                          "bytes": "sum(seq_len) * Hkv_local * D * 2 (K,V) * sizeof(cache_t)"},

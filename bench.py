@@ -557,8 +557,13 @@ def run_ours(args):
     my_bytes = kv_bytes(w["lens"], w["Hkv"], kv)
     sustained = None
     if args.sustain > 0:
+        # every rank must cut the leg into the SAME number of chunks (the per-chunk times are
+        # all-reduced below): the step-time hint is the maximum over ranks, not this rank's own
+        hint = torch.tensor([ms_total / K], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(hint, op=dist.ReduceOp.MAX)
         per, sus_ms, sus_steps, chunk, sens = sustained_leg(w, out, fused, args.sustain,
-                                                            ms_total / K, my_bytes, local_rank,
+                                                            float(hint[0]), my_bytes, local_rank,
                                                             barrier)
         sus = torch.tensor([sus_ms] + per, dtype=torch.float64, device=dev)
         if world > 1:

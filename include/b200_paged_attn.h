@@ -210,9 +210,12 @@ int b200pa_decode_step(
  * b200pa_reshape_and_cache_flash(key, value, ..., slot_mapping, num_tokens = num_seqs) BEFORE the
  * attention, in the same launch, under b200pa_decode_step's precondition (token b is position
  * seq_lens[b] - 1 of sequence b).  All three NULL: attention only.
- * Domain: head_size 32 / 64 / 96 / 128 / 192 / 256, block_size 16, f16 / bf16 query, auto /
- * fp8_e4m3 cache, 16-byte aligned rows; anything else is B200PA_ERR_UNSUPPORTED (there is no second kernel for this
- * layout).  A workspace (b200pa_paged_attention_workspace_bytes) is required.
+ * Domain: head_size 32 / 64 / 80 / 96 / 112 / 128 / 192 / 256, block_size 16 / 32, f16 / bf16
+ * query, auto / fp8_e4m3 / fp8_e5m2 cache, 16-byte aligned rows; anything else is
+ * B200PA_ERR_UNSUPPORTED (there is no second kernel for this layout).  A workspace
+ * (b200pa_paged_attention_workspace_bytes) is required.  NHD caches with an even number of kv
+ * heads, head size 128 and 16-token blocks are read a whole block (all heads) at a time through
+ * tensor-map TMA (csrc/paged_attention_nhd.cuh); everything else by rows.
  */
 int b200pa_paged_attention_flash(
     void* out, float* lse, int64_t lse_seq_stride, int64_t lse_head_stride, const void* query,

@@ -1,25 +1,32 @@
-// Decode attention over the token-major NHD cache with several kv heads per GPU -- included by
+// The whole-block decode kernel: paged decode attention when several kv heads live on the GPU,
+// for the x-packed cache and for the token-major NHD cache -- included by
 // paged_attention_stream.cu (inside its anonymous namespace: it shares the span arithmetic, the
-// PTX wrappers and the output helpers of the stream kernel).
+// PTX wrappers, the fragment conventions and the output helpers of the per-warp stream kernel).
 //
-// Why a second work decomposition: in the NHD layout [block][token][head][D] a
-// (block, head) is 16 rows of 128-256 bytes one `Hkv * D` apart.  The stream kernel gives every
-// WARP its own (sequence, head) stream, so the rows of the other heads of a block are fetched at
-// some other time by some other warp: 5.1 TB/s on cfg3 against 6.1 (HND) and 6.4 (x-packed).
-// Here the unit is the whole cache block:
-//  * a CTA has one warp per kv head; all of them walk the SAME span of (sequence, block) stages;
-//  * a stage (BPS blocks) arrives through tensor-map TMA (cp.async.bulk.tensor.4d, SASS UTMALDG):
-//    the box covers (128 bytes of D, 16 tokens, all heads) of one block -- one contiguous 16 KiB
-//    of global memory per box -- and the tensor map lists the dimensions as (D, token, head,
-//    block), so the box lands TRANSPOSED to [head][token][128 B]: every warp finds its head's 16
-//    rows contiguous, 128-byte swizzled (conflict-free ldmatrix, no padding);
+// Why a second work decomposition.  The stream kernel gives every WARP its own
+// (sequence, head) stream: 2-4 KiB bulk copies, and in the NHD layout [block][token][head][D] --
+// where a (block, head) is 16 rows of 128-256 bytes one `Hkv * D` apart -- 16-byte cp.async
+// granules, the rows of the other heads of a block being fetched at some other time by some other
+// warp (5.1 TB/s on cfg3 against 6.4 x-packed).  Here the unit is the cache block with ALL the
+// heads of a head group:
+//  * a CTA has one warp per kv head of a group of NW heads; an item is one (sequence, head group);
+//    all stages (BPS blocks each) are flattened and cut into one span per CTA, and the CTA's
+//    warps walk the span together, each computing its own head;
+//  * x-packed: K (and V) of one block, NW adjacent heads, is ONE contiguous run -- one 1-D bulk
+//    copy each (8-32 KiB), every warp finding its head's page at warp * PAGE_BYTES;
+//  * NHD: a stage arrives through tensor-map TMA (cp.async.bulk.tensor.4d, SASS UTMALDG): the box
+//    covers (128 bytes of D, 16 tokens, NW heads) of one block and the tensor map lists the
+//    dimensions as (D, token, head, block), so the box lands TRANSPOSED to [head][token][128 B]:
+//    every warp finds its head's 16 rows together, 128-byte swizzled (conflict-free ldmatrix, no
+//    padding, no per-row copies);
 //  * CTA-wide ring with full / empty mbarriers (warp 0 produces); a piece that does not cover
 //    its whole sequence leaves one partial per head in the CTA's workspace slots and the CTAs of
-//    a sequence elect the last one to arrive (ticket counter, as in the stream kernel) to merge
-//    them -- every warp merges its own head.
-// Scope: block size 16, group size <= 8, head rows of 128 or 256 bytes (fp8 D = 128 / 256, 16-bit
-// D = 64 / 128), 2 / 4 / 8 kv heads per GPU; no fused cache write (the entry point runs
-// reshape_and_cache_flash first).  Everything else stays on the stream kernel's FLASH path.
+//    an item elect the last one to arrive (ticket counter, as in the stream kernel) to merge them
+//    -- every warp merges its own head, pieces in CTA order;
+//  * the fused cache write of decode_step: the warp patches its head's row of the new token in
+//    shared memory and stores it to the cache.
+// Scope: block size 16, group size <= 8, head size 128 (NHD: head rows of 128 or 256 bytes), an
+// even number of kv heads per GPU, auto / fp8_e4m3.  Everything else stays on the stream kernel.
 #pragma once
 
 struct NhdParams {

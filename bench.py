@@ -416,10 +416,18 @@ def timed_steps(w, out, fused, K, barrier, native, graph=False):
     return ev0.elapsed_time(ev1), sum(a.elapsed_time(b) for a, b in a_ev) / K, launches
 
 
-def sustained_leg(w, out, fused, seconds, ms_step_hint, my_bytes, sampler_index, barrier):
-    """The same step back to back for >= `seconds`, an event every ~100 ms of work."""
+def sustained_plan(seconds, ms_step_hint):
+    """(steps per chunk, chunks) of the sustained leg: ~100 ms of work per chunk.  A pure function
+    of its arguments -- every rank must be given the SAME hint (the per-chunk times are
+    all-reduced as one tensor; see tests/test_bench_host.py)."""
     chunk = max(1, int(round(100.0 / max(ms_step_hint, 1e-3))))
     n_chunks = max(3, int(seconds * 1e3 / (chunk * ms_step_hint)) + 1)
+    return chunk, n_chunks
+
+
+def sustained_leg(w, out, fused, seconds, ms_step_hint, my_bytes, sampler_index, barrier):
+    """The same step back to back for >= `seconds`, an event every ~100 ms of work."""
+    chunk, n_chunks = sustained_plan(seconds, ms_step_hint)
     caches = w["kv_caches"]
     sampler = ClockSampler(sampler_index)
     sampler.start()

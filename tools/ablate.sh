@@ -2,7 +2,9 @@
 # Build copies of the package whose decode kernel lacks one ingredient of its main loop
 # (B200PA_ABLATE in csrc/paged_attention_stream.cu; head size 128 / bf16 query instantiations
 # only) into _ab/<label>/vllm_main_modify_b200, for tools/powerprobe.py and tools/kbench.py:
-#   B200PA_PKG_ROOT=_ab/no_cvt B200PA_AB_LABEL=no_cvt python tools/powerprobe.py
+#   B200PA_PKG_ROOT=_ab/no_cvt B200PA_AB_LABEL=no_cvt python tools/powerprobe.py --tune 100
+# (the ablation switches sit in the per-warp stream kernel: --tune 100 + i selects it with its
+# launch shape i; without it head size 128 with several kv heads takes the whole-block kernel)
 # Results of such a build are WRONG by construction; nothing but timing tools may load it.
 #   tools/ablate.sh no_cvt:1 no_mma:2 no_ldmatrix:4 no_exp:8 only_copy:15
 set -eu

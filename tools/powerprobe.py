@@ -29,7 +29,9 @@ def main():
     ap.add_argument("--config", default="cfg4")
     ap.add_argument("--tp", type=int, default=1)
     ap.add_argument("--seconds", type=float, default=4.0)
-    ap.add_argument("--tune", type=int, default=0)
+    ap.add_argument("--tune", type=int, default=0,
+                    help="test hook: 20-24 launch shapes of the whole-block kernel, 100 + i the "
+                         "per-warp stream kernel with its launch shape i")
     ap.add_argument("--unfused", action="store_true")
     args = ap.parse_args()
     import vllm_main_modify_b200

@@ -53,3 +53,25 @@ def test_oracle_lse_and_alibi_consistency():
     second = po.prefill_attention(qq[6:], kc, vc, bt, [0, 4], [50], 0.3, slopes)
     torch.testing.assert_close(torch.cat([first, second]), whole, atol=1e-6, rtol=1e-6)
     assert torch.isfinite(lse).all()
+
+
+@pytest.mark.parametrize("kv", ["fp8", "fp8_e5m2"])
+def test_oracle_fp8_dequant_agrees_with_the_pinned_decode_oracle(kv):
+    """Single-token chunks over an fp8 cache with k_scale / v_scale and ALiBi: the chunk oracle's
+    dequantisation and bias must agree with the C restatement of the reference's decode kernel
+    (oracle/paged_attn_oracle.c, itself pinned on the CUDA-toolkit fp8 goldens and on the
+    reference's CPU kernels)."""
+    from oracle import oracle as ora
+    B, H, Hkv, D, BS, NB = 4, 8, 2, 64, 16, 40
+    lens = [1, 16, 77, 300]
+    q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, NB, lens, torch.bfloat16, seed=9,
+                                             kv="fp8", permute=True)
+    if kv == "fp8_e5m2":
+        kc, vc = kc & 0xBB, vc & 0xBB      # finite e5m2 codes
+    slopes = torch.tensor([0.5 ** (i + 1) for i in range(H)])
+    ks, vs = 0.25, 0.5
+    want = torch.empty_like(q)
+    ora.paged_attention_v1(want, q, kc, vc, Hkv, 0.125, bt, sl, BS, max(lens), slopes, kv,
+                           torch.tensor(ks), torch.tensor(vs))
+    got = po.prefill_attention(q, kc, vc, bt, list(range(B + 1)), lens, 0.125, slopes, kv, ks, vs)
+    torch.testing.assert_close(got, want.float(), atol=2e-2, rtol=2e-2)

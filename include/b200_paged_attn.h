@@ -33,6 +33,9 @@
  *                                   AttentionImpl.can_return_lse_for_decode
  *                                   (vllm/attention/backends/abstract.py:115-138) asks of a
  *                                   backend for decode context parallelism
+ *   b200pa_paged_attention_v1_builtin_scratch
+ *                                   no counterpart in the reference: paged_attention_v1 with the
+ *                                   scratch inside the library, for callers that cannot allocate
  *
  * Conventions
  *   - All data pointers are DEVICE pointers on the current CUDA device; strides
@@ -126,6 +129,53 @@ int b200pa_paged_attention_v1(
     int tp_rank, int blocksparse_local_blocks, int blocksparse_vert_stride,
     int blocksparse_block_size, int blocksparse_head_sliding_step,
     void* workspace, int64_t workspace_bytes, void* stream);
+
+/*
+ * b200pa_paged_attention_v1 for a caller that cannot give it a workspace.  (No counterpart in the
+ * reference: its kernels take all scratch from torch's allocator, which such a caller does not
+ * have.)
+ *
+ * Who this is for.  The entry points above leave allocation to the caller: you size the workspace
+ * with b200pa_paged_attention_workspace_bytes, cudaMalloc it, zero its header, and pass it in.
+ * Some hosts of this ABI cannot do that --
+ *   - a plugin inside an engine that handed every free byte of HBM to its KV-cache pool at start-up
+ *     (the reference sizes the pool from what is left after profiling), where a cudaMalloc made
+ *     later may fail and all device memory is owned by the engine's arena;
+ *   - an FFI host (cgo, JNI, ctypes) that only ever receives device pointers from another
+ *     component and has no CUDA runtime binding to allocate with;
+ *   - a decode loop that must not run into cudaMalloc's device-wide synchronisation.
+ * For them the scratch is a static device array compiled into libb200pa.so.  It costs
+ * B200PA_BUILTIN_SCRATCH_BYTES (24 MiB) of device memory on EVERY GPU the library's code is loaded
+ * on, from load until the process exits, used or not.
+ *
+ * Arguments, domain, result and error codes: exactly b200pa_paged_attention_v1 without
+ * `workspace` / `workspace_bytes`; the same kernels run, so the output equals that entry point's.
+ * The call itself allocates nothing (no cudaMalloc / cudaFree, no allocating library routine).
+ *
+ * Limits and rules:
+ *   - The scratch the kernels need depends on head_size and the SM count only.  24 MiB covers
+ *     head_size <= 128 on a B200 (148 SMs).  A larger requirement (head_size 192 / 256, or a part
+ *     with more than 151 SMs) is refused with B200PA_ERR_UNSUPPORTED and a message that names both
+ *     sizes; use b200pa_paged_attention_v1 with your own workspace there.
+ *   - The FIRST call on each device looks the array's device address up (once per device, with that
+ *     device current -- make the call with the device you will run on selected).  Make that first
+ *     call during start-up, before any stream capture.
+ *   - One array per GPU, shared by every call of this entry point from every thread, and it keeps
+ *     whatever the last call left in it.  Each call clears the 4 KiB of ticket counters at its
+ *     front on `stream` before launching.  Two calls that can overlap on the GPU (different
+ *     streams without an event between them) RACE on it and produce wrong output: serialise them,
+ *     or give the concurrent ones their own workspace through b200pa_paged_attention_v1.
+ */
+#define B200PA_BUILTIN_SCRATCH_BYTES (24 * 1024 * 1024)
+int b200pa_paged_attention_v1_builtin_scratch(
+    void* out, const void* query, const void* key_cache, const void* value_cache,
+    int num_seqs, int num_heads, int num_kv_heads, int head_size, int block_size,
+    float scale, const int32_t* block_tables, int max_num_blocks_per_seq,
+    const int32_t* seq_lens, int max_seq_len, const float* alibi_slopes,
+    int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
+    int scalar_type, int kv_dtype, const float* k_scale, const float* v_scale,
+    int tp_rank, int blocksparse_local_blocks, int blocksparse_vert_stride,
+    int blocksparse_block_size, int blocksparse_head_sliding_step, void* stream);
 
 /*
  * Split-K variant.  Caller-provided scratch, reference shapes:

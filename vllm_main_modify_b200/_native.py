@@ -14,7 +14,8 @@ C_ABI_SYMBOLS = (
     "b200pa_abi_version", "b200pa_last_error", "b200pa_kv_dtype_from_string",
     "b200pa_launch_count",
     "b200pa_paged_attention_workspace_bytes",
-    "b200pa_paged_attention_v1", "b200pa_paged_attention_v2", "b200pa_paged_attention_lse",
+    "b200pa_paged_attention_v1", "b200pa_paged_attention_v1_builtin_scratch",
+    "b200pa_paged_attention_v2", "b200pa_paged_attention_lse",
     "b200pa_decode_step", "b200pa_paged_attention_flash", "b200pa_prefill_attention",
     "b200pa_merge_attn_states", "b200pa_correct_attn_out",
     "b200pa_swap_blocks", "b200pa_copy_blocks", "b200pa_gather_and_maybe_dequant_cache",

@@ -44,7 +44,8 @@ CU_SOURCES = [("c_abi.cu", [], "c_abi.o"), ("cache_kernels.cu", [], "cache_kerne
               ("paged_prefill.cu", ["-DPREFILL_PART=1"], "paged_prefill_small.o"),
               ("paged_prefill.cu", ["-DPREFILL_PART=2"], "paged_prefill_mid.o"),
               ("paged_prefill.cu", ["-DPREFILL_PART=3"], "paged_prefill_256.o"),
-              ("merge_attn_states.cu", [], "merge_attn_states.o"), ("block_ops.cu", [], "block_ops.o")]
+              ("merge_attn_states.cu", [], "merge_attn_states.o"), ("block_ops.cu", [], "block_ops.o"),
+              ("builtin_scratch.cu", [], "builtin_scratch.o")]
 # test hooks of include/b200_paged_attn_testing.h: compiled in unless B200PA_TESTING=0 is set
 TESTING = "-DB200PA_TESTING=" + ("0" if os.environ.get("B200PA_TESTING") == "0" else "1")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",

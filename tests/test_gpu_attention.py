@@ -498,6 +498,44 @@ def test_stream_graph_replay_follows_seq_lens(ops, native):
         assert not torch.isnan(out_g.float()).any()
 
 
+def test_first_use_of_a_stream_inside_a_capture_leaves_a_usable_workspace(ops):
+    """The shim's per-stream workspace is allocated and its ticket counters zeroed for real even
+    when the first call on a stream is made under CUDA-graph capture: the graph captured first is
+    NEVER replayed here, yet an eager call and a second graph on the same stream are correct
+    (sequences cut across CTAs go through the counters)."""
+    B, H, Hkv, D, BS = 6, 16, 2, 128, 16
+    s = D ** -0.5
+    lens = [4096, 9, 3000, 4095, 700, 2049]
+    q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, 6 * 256 + 1, lens, torch.bfloat16,
+                                             seed=8, kv="fp8", lo=-1.0, hi=1.0, permute=True)
+    qd, kcd, vcd, btd, sld = (t.to(DEV) for t in (q, kc, vc, bt, sl))
+    ks, vs = torch.tensor(0.5, device=DEV), torch.tensor(1.5, device=DEV)
+
+    def step(out):
+        ops.paged_attention_v1(out, qd, kcd, vcd, Hkv, s, btd, sld, BS, 4096, None, "fp8", ks, vs)
+
+    want = torch.empty_like(qd)
+    step(want)                                    # default stream: its own workspace
+    torch.cuda.synchronize()
+    stream = torch.cuda.Stream()                  # never used before
+    out1, out2, out3 = (torch.full_like(qd, float("nan")) for _ in range(3))
+    g1, g2 = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+    with torch.cuda.stream(stream):
+        with torch.cuda.graph(g1, stream=stream):
+            step(out1)                            # first use of `stream`: under capture
+        step(out2)                                # eager, g1 not replayed
+        stream.synchronize()
+        with torch.cuda.graph(g2, stream=stream):
+            step(out3)
+    g2.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out2, want)
+    assert torch.equal(out3, want)
+    g1.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out1, want)
+
+
 def test_c_abi_without_workspace_uses_generic_and_stream_needs_one(native):
     """Direct C-ABI calls (ctypes, raw device pointers): workspace == NULL is served by the
     generic kernel; forcing the stream kernel without a workspace is an error, not a fallback."""

@@ -16,6 +16,7 @@
 // `torch.ops._C.paged_attention_v1` etc. to this library.
 #include <cstdlib>
 #include <ATen/cuda/CUDAContext.h>
+#include <c10/cuda/CUDAGraphsC10Utils.h>
 #include <c10/cuda/CUDAGuard.h>
 #include <torch/all.h>
 #include <torch/library.h>
@@ -74,18 +75,36 @@ void check_cache_dtype(const torch::Tensor& cache, const torch::Tensor& ref, int
 // A call on another stream (a capture stream included) gets its own workspace, so concurrent
 // streams never share counters or slots.  Sized for the largest head size (256), so every shape
 // can use it.
+// The allocation and the zero fill always EXECUTE before this function returns the tensor's first
+// use: when the first use of a stream falls inside a CUDA-graph capture, they are made on a side
+// stream that is not capturing (ordinary allocator pool, not the graph's private one) and waited
+// for -- a memset merely recorded into that graph would leave the counters uninitialised for every
+// eager call and every other graph on the stream until that one graph is replayed.
+// The map is leaked on purpose: no tensor destructor may run after CUDA has been torn down at exit.
 torch::Tensor cached_workspace(const torch::Tensor& query) {
   static std::mutex mu;
-  static std::map<std::pair<int, cudaStream_t>, torch::Tensor> cache;
+  static auto* cache = new std::map<std::pair<int, cudaStream_t>, torch::Tensor>();
   const int dev = query.get_device();
   const cudaStream_t stream = at::cuda::getCurrentCUDAStream(dev);
   std::lock_guard<std::mutex> lock(mu);
-  auto it = cache.find({dev, stream});
-  if (it != cache.end()) return it->second;
+  auto it = cache->find({dev, stream});
+  if (it != cache->end()) return it->second;
   const at::cuda::OptionalCUDAGuard guard(device_of(query));
   const int64_t bytes = b200pa_paged_attention_workspace_bytes(256);
-  torch::Tensor ws = at::zeros({bytes}, query.options().dtype(at::kByte));
-  cache.emplace(std::make_pair(dev, stream), ws);
+  const auto opts = query.options().dtype(at::kByte);
+  torch::Tensor ws;
+  if (c10::cuda::currentStreamCaptureStatusMayInitCtx() != c10::cuda::CaptureStatus::None) {
+    const c10::cuda::CUDAStreamCaptureModeGuard relaxed(cudaStreamCaptureModeRelaxed);
+    const at::cuda::CUDAStream side = at::cuda::getStreamFromPool(false, dev);
+    {
+      const at::cuda::CUDAStreamGuard on_side(side);
+      ws = at::zeros({bytes}, opts);
+    }
+    side.synchronize();
+  } else {
+    ws = at::zeros({bytes}, opts);
+  }
+  cache->emplace(std::make_pair(dev, stream), ws);
   return ws;
 }
 

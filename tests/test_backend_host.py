@@ -155,6 +155,24 @@ def test_build_records_the_split():
     assert m.num_decode_tokens == 4 and m.num_decodes is None
 
 
+def test_build_ends_the_decode_run_at_a_zero_length_sequence():
+    """Sequence b of the decode call is token b, so a sequence without tokens cannot sit inside
+    the decode run: the run ends there and the chunk kernel takes the rest."""
+    c = _Common()
+    qsl = torch.tensor([0, 1, 1, 2, 7], dtype=torch.int32)        # q_len 1, 0, 1, 5
+    c.num_actual_tokens, c.max_query_len, c.num_reqs = 7, 5, 4
+    c.seq_lens = torch.tensor([10, 300, 20, 5], dtype=torch.int32)
+    c.seq_lens_cpu = c.seq_lens
+    c.max_seq_len = 300
+    c.block_table_tensor = torch.zeros(4, 20, dtype=torch.int32)
+    c.slot_mapping = torch.zeros(7, dtype=torch.int64)
+    c.query_start_loc = c.query_start_loc_cpu = qsl
+    m = be.B200PagedAttentionMetadataBuilder().build(0, c)
+    assert (m.num_decodes, m.num_prefills, m.num_prefill_tokens) == (1, 3, 6)
+    assert m.max_decode_seq_len == 10
+    assert int(qsl[m.num_decodes]) == m.num_decodes               # token b <-> sequence b holds
+
+
 def _reference_abstract_module():
     """The reference's vllm/attention/backends/abstract.py loaded on its own (its one vllm import,
     QuantKey, is a type annotation): only where /root/reference exists."""

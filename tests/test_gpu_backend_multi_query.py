@@ -109,8 +109,12 @@ class _Common:
     pass
 
 
+@pytest.mark.parametrize("qlens,split", [([1, 1, 1, 70, 20, 3], (3, 3)),
+                                         # a sequence without tokens inside the single-token run:
+                                         # the decode run ends before it
+                                         ([1, 0, 1, 70, 20, 3], (1, 5))])
 @pytest.mark.parametrize("kv", ["auto", "fp8"])
-def test_decode_first_batch_through_the_builder(kv):
+def test_decode_first_batch_through_the_builder(kv, qlens, split):
     """A batch as the runner hands it over after ``reorder_batch``: decodes first, then chunks;
     ``build`` records the split, ``forward`` runs the two kernels.  Checked against the chunk
     oracle on the cache as the backend itself wrote it (bit-exact bytes are the cache tests'
@@ -124,7 +128,6 @@ def test_decode_first_batch_through_the_builder(kv):
     dt = torch.bfloat16
     s = D ** -0.5
     hist = [300, 37, 1000, 0, 500, 16]
-    qlens = [1, 1, 1, 70, 20, 3]
     B, T = len(hist), sum(qlens)
     lens = [h + ql for h, ql in zip(hist, qlens)]
     NB = sum((L + BS - 1) // BS for L in lens) + 3
@@ -149,7 +152,7 @@ def test_decode_first_batch_through_the_builder(kv):
     c.query_start_loc_cpu = torch.tensor(qsl, dtype=torch.int32)
     c.query_start_loc = c.query_start_loc_cpu.to(DEV)
     meta = be.B200PagedAttentionMetadataBuilder().build(0, c)
-    assert (meta.num_decodes, meta.num_prefills) == (3, 3)
+    assert (meta.num_decodes, meta.num_prefills) == split
     backend = be.B200PagedAttentionBackend
     kv_cache = torch.empty(backend.get_kv_cache_shape(NB, BS, Hkv, D), dtype=kc.dtype, device=DEV)
     kv_cache[0] = kc.reshape(NB, -1).to(DEV)

@@ -148,10 +148,13 @@ class B200PagedAttentionMetadataBuilder:
         qsl_cpu = getattr(m, "query_start_loc_cpu", None)
         if meta.max_query_len > 1 and qsl_cpu is not None:
             # split_decodes_and_prefills (utils.py:721-771) on the host copy: the leading run of
-            # single-token sequences is the decode part
+            # single-token sequences is the decode part.  The decode call takes sequence b to be
+            # token b, so the run ends at the first sequence that does not have EXACTLY one token
+            # (a zero-length entry would shift every later token onto its neighbour's block
+            # table); the chunk kernel serves whatever follows, zero-length entries included.
             qlens = (qsl_cpu[1:] - qsl_cpu[:-1]).tolist()
             nd = 0
-            while nd < len(qlens) and qlens[nd] <= self.reorder_batch_threshold:
+            while nd < len(qlens) and qlens[nd] == 1:
                 nd += 1
             meta.num_decodes = nd
             meta.num_prefills = len(qlens) - nd
@@ -285,9 +288,10 @@ class B200PagedAttentionImpl:
     # shapes the chunk kernel (csrc/paged_prefill.cu) serves; others fall back to the expansion
     _PREFILL_HEAD_SIZES = (32, 64, 96, 128, 192, 256)
 
-    def _chunk_kernel_serves(self, query: torch.Tensor, block_size: int) -> bool:
+    def _chunk_kernel_serves(self, query: torch.Tensor, block_size: int, num_seqs: int = 0) -> bool:
+        # num_seqs: the chunk kernel puts the sequences on grid.z (at most 65535)
         return (self.head_size in self._PREFILL_HEAD_SIZES and block_size in (16, 32)
-                and query.dtype in (torch.float16, torch.bfloat16))
+                and query.dtype in (torch.float16, torch.bfloat16) and num_seqs <= 65535)
 
     def _forward_multi_query(self, layer, query, key, value, kv_cache, attn_metadata, output):
         """Batches with more than one query token per sequence (prefill, chunked prefill, mixed),
@@ -311,7 +315,7 @@ class B200PagedAttentionImpl:
             self.alibi_slopes = self.alibi_slopes.to(q.device)
         if m.query_start_loc is None:
             raise ValueError("batches with max_query_len > 1 need attn_metadata.query_start_loc")
-        if not self._chunk_kernel_serves(q, value_cache.shape[3]):
+        if not self._chunk_kernel_serves(q, value_cache.shape[3], m.query_start_loc.shape[0] - 1):
             bt_tok, sl_tok = expand_queries_to_sequences(m)
             PagedAttention.forward_decode(
                 q[:n], key_cache, value_cache, bt_tok, sl_tok, m.max_seq_len,

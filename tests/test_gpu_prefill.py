@@ -191,6 +191,51 @@ def test_long_chunk_with_context_and_empty_sequences():
     assert_close(got, want, "long chunk")
 
 
+@pytest.mark.parametrize("hpt", [0, 1])
+def test_sequence_shorter_than_its_chunk_gets_a_defined_result(hpt):
+    """seq_lens[b] < q_len (inconsistent metadata; the reference would index before the cache):
+    those rows come back as zeros with lse = -inf instead of stale memory, the other sequences
+    are unaffected; tensors on the wrong device are rejected by the shim."""
+    H, Hkv, D, BS = 8, 2, 128, 16
+    qlens, ctx = [70, 30, 5], [100, 20, 0]
+    q, kc, vc, bt, qsl, sl = make_inputs(qlens, ctx, H, Hkv, D, BS, torch.bfloat16, "auto", seed=4)
+    want, want_lse = po.prefill_attention(q, kc, vc, bt, qsl.tolist(), sl.tolist(), 0.09,
+                                          return_lse=True)
+    bad = sl.clone()
+    bad[1] = 12                                    # 30 query tokens, 12 tokens in the sequence
+    got, lse = run_op(q, kc, vc, bt, qsl, bad, 0.09, hpt=hpt, want_lse=True)
+    rows = slice(int(qsl[1]), int(qsl[2]))
+    assert float(got[rows].float().abs().max()) == 0.0
+    assert bool((lse[rows] == float("-inf")).all())
+    keep = torch.ones(q.shape[0], dtype=torch.bool)
+    keep[rows] = False
+    assert_close(got[keep], want[keep], "other sequences")
+    torch.testing.assert_close(lse[keep], want_lse[keep].float(), atol=1e-2, rtol=1e-2)
+    dev = "cuda:0"
+    one = torch.tensor(1.0, device=dev)
+    with pytest.raises(RuntimeError, match="CUDA device"):
+        ops().prefill_attention(torch.empty_like(q, device=dev), None, q.to(dev), kc.to(dev),
+                                vc.to(dev), 0.09, bt, qsl.to(dev), sl.to(dev), 70, None, "auto",
+                                one, one)
+
+
+def test_fp8_cache_with_large_bf16_queries_inside_the_f16_range():
+    """With an fp8 cache the chunk kernel computes in f16 (fp8 -> f16 is exact; a bf16 query is
+    converted, which is exact too while |q| <= 65504).  Documented limit: bf16 queries beyond the
+    f16 range overflow on this path (the reference dequantises to the query dtype instead).
+    Inside the range the result is the oracle's: queries of magnitude 300, far above anything
+    the other tests use, with a scale that keeps the logits moderate."""
+    H, Hkv, D, BS = 8, 2, 128, 16
+    qlens, ctx = [40, 3, 1], [200, 77, 500]
+    q, kc, vc, bt, qsl, sl = make_inputs(qlens, ctx, H, Hkv, D, BS, torch.bfloat16, "fp8", seed=13,
+                                         spread=300.0)
+    assert float(q.float().abs().max()) > 250
+    want = po.prefill_attention(q, kc, vc, bt, qsl.tolist(), sl.tolist(), 1e-3, None, "fp8",
+                                0.5, 0.25)
+    got = run_op(q, kc, vc, bt, qsl, sl, 1e-3, kv="fp8", ks=0.5, vs=0.25)
+    assert_close(got, want, "large bf16 queries, fp8 cache")
+
+
 def test_strided_query_and_out():
     """query / out as slices of a fused qkv buffer (token stride > H * D)."""
     H, Hkv, D, BS = 4, 2, 64, 16

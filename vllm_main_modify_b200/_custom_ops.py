@@ -77,6 +77,26 @@ def paged_attention_v2(
         blocksparse_block_size, blocksparse_head_sliding_step)
 
 
+def paged_attention_v2_partials(out, exp_sum, max_logits, tmp_out, query, key_cache, value_cache,
+                                num_kv_heads, scale, block_tables, seq_lens, block_size,
+                                max_seq_len, alibi_slopes, kv_cache_dtype, k_scale, v_scale,
+                                tp_rank: int = 0, blocksparse_local_blocks: int = 0,
+                                blocksparse_vert_stride: int = 0, blocksparse_block_size: int = 64,
+                                blocksparse_head_sliding_step: int = 0) -> None:
+    """``paged_attention_v2`` for a caller that READS the scratch: on return ``exp_sum`` /
+    ``max_logits`` / ``tmp_out`` hold the reference's per-partition partials
+    (``attention_kernels.cuh:345-351, 487``).  The plain op leaves them untouched on its fast path;
+    this per-call form (no reference counterpart) runs the slower generic kernel that fills them.
+    The environment variable ``B200PA_V2_REFERENCE_SCRATCH=1`` does the same process-wide for
+    callers that cannot be changed."""
+    _ops.paged_attention_v2_partials(
+        out, exp_sum, max_logits, tmp_out, query, key_cache, value_cache,
+        num_kv_heads, scale, block_tables, seq_lens, block_size, max_seq_len,
+        alibi_slopes, kv_cache_dtype, k_scale, v_scale, tp_rank,
+        blocksparse_local_blocks, blocksparse_vert_stride,
+        blocksparse_block_size, blocksparse_head_sliding_step)
+
+
 def merge_attn_states(output: torch.Tensor,
                       prefix_output: torch.Tensor,
                       prefix_lse: torch.Tensor,
@@ -198,7 +218,13 @@ def prefill_attention(
     ``flash_attn_varlen_func(..., block_table)`` for (``cpu_attn.py:584-612``).  ``query`` /
     ``out`` ``[num_tokens, num_heads, head_size]``, ``query_start_loc`` ``[num_seqs + 1]`` int32,
     ``seq_lens`` ``[num_seqs]`` int32 (context + new tokens), ``lse`` optional
-    ``[num_tokens, num_heads]`` fp32."""
+    ``[num_tokens, num_heads]`` fp32.
+
+    Limits: at most 65535 sequences per call.  With an fp8 cache the kernel computes in f16, so a
+    bf16 query must stay inside the f16 range (|q| <= 65504; larger values give inf / NaN, tiny
+    ones flush to zero) -- the reference dequantises to the query dtype instead.  A sequence whose
+    ``seq_lens`` entry is smaller than its number of query tokens (inconsistent metadata) gets
+    zero rows and ``lse = -inf``."""
     _ops.prefill_attention(out, lse, query, key_cache, value_cache, scale, block_tables,
                            query_start_loc, seq_lens, max_query_len, alibi_slopes,
                            kv_cache_dtype, k_scale, v_scale, heads_per_tile)

@@ -187,9 +187,25 @@ paged_prefill_kernel(const PrefillParams p) {
   const int tile = gridDim.x - 1 - blockIdx.x;      // long tiles first
   const int t0 = tile * p.tokens_per_tile;
   const int ctx = seq_len - q_len;                  // tokens before this chunk
-  if (t0 >= q_len || ctx < 0) return;
+  if (t0 >= q_len) return;
   const int hp = p.hpack;
   const int head0 = blockIdx.y * hp;
+  if (ctx < 0) {
+    // inconsistent metadata (fewer tokens in the sequence than in its chunk): nothing to attend
+    // to is defined.  Leave a defined result instead of stale memory: zero rows, lse = -inf.
+    using T0 = typename Scalar<ST>::type;
+    T0* const o = reinterpret_cast<T0*>(p.out);
+    const int nt = min(p.tokens_per_tile, q_len - t0);
+    for (int i = threadIdx.x; i < nt * hp * D; i += blockDim.x) {
+      const int tok = i / (hp * D), r = i % (hp * D);
+      o[(int64_t)(q_begin + t0 + tok) * p.out_stride + (int64_t)head0 * D + r] =
+          Scalar<ST>::from_float(0.f);
+    }
+    if (p.lse != nullptr)
+      for (int i = threadIdx.x; i < nt * hp; i += blockDim.x)
+        p.lse[(int64_t)(q_begin + t0 + i / hp) * p.num_heads + head0 + i % hp] = -INFINITY;
+    return;
+  }
   const int kvh = head0 / p.group;
   const int ntok = min(p.tokens_per_tile, q_len - t0);
   const int rows_valid = ntok * hp;

@@ -151,7 +151,8 @@ void paged_attention_v1(torch::Tensor& out, torch::Tensor& query, torch::Tensor&
       ws.defined() ? ws.numel() : 0, stream));
 }
 
-void paged_attention_v2(torch::Tensor& out, torch::Tensor& exp_sums, torch::Tensor& max_logits,
+void paged_attention_v2_impl(bool want_ref_scratch,
+                        torch::Tensor& out, torch::Tensor& exp_sums, torch::Tensor& max_logits,
                         torch::Tensor& tmp_out, torch::Tensor& query, torch::Tensor& key_cache,
                         torch::Tensor& value_cache, int64_t num_kv_heads, double scale,
                         torch::Tensor& block_tables, torch::Tensor& seq_lens, int64_t block_size,
@@ -181,16 +182,10 @@ void paged_attention_v2(torch::Tensor& out, torch::Tensor& exp_sums, torch::Tens
   const float* alibi = alibi_slopes ? reinterpret_cast<const float*>(alibi_slopes->data_ptr()) : nullptr;
   // The stream kernel splits the context by its own schedule and keeps its partials in the
   // workspace: exp_sums / max_logits / tmp_out stay untouched (the reference's callers treat them
-  // as scratch, paged_attn.py:163-173).  B200PA_V2_REFERENCE_SCRATCH=1 serves a caller that reads
-  // them: the call then takes the generic kernel, which leaves the reference's per-partition
-  // partials (attention_kernels.cuh:345-351, 487) in them.
-  const char* ref_scratch = std::getenv("B200PA_V2_REFERENCE_SCRATCH");
-  const bool want_ref_scratch = ref_scratch != nullptr && ref_scratch[0] == '1';
+  // as scratch, paged_attn.py:163-173).  want_ref_scratch serves a caller that reads them: the call
+  // then takes the generic kernel, which leaves the reference's per-partition partials
+  // (attention_kernels.cuh:345-351, 487) in them.
   const torch::Tensor ws = want_ref_scratch ? torch::Tensor() : attention_workspace(query);
-  if (ws.defined())
-    TORCH_WARN_ONCE("b200pa paged_attention_v2: exp_sums / max_logits / tmp_out are scratch and "
-                    "are left untouched by the stream kernel; set B200PA_V2_REFERENCE_SCRATCH=1 "
-                    "if a caller reads the reference's per-partition partials from them");
   check_status(b200pa_paged_attention_v2(
       out.data_ptr(), exp_sums.data_ptr<float>(), max_logits.data_ptr<float>(), tmp_out.data_ptr(),
       query.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(), (int)query.size(0),
@@ -203,6 +198,35 @@ void paged_attention_v2(torch::Tensor& out, torch::Tensor& exp_sums, torch::Tens
       (int)blocksparse_head_sliding_step, ws.defined() ? ws.data_ptr() : nullptr,
       ws.defined() ? ws.numel() : 0, stream));
 }
+
+#define B200PA_V2_ARGS                                                                             \
+  torch::Tensor &out, torch::Tensor &exp_sums, torch::Tensor &max_logits, torch::Tensor &tmp_out,  \
+      torch::Tensor &query, torch::Tensor &key_cache, torch::Tensor &value_cache,                  \
+      int64_t num_kv_heads, double scale, torch::Tensor &block_tables, torch::Tensor &seq_lens,    \
+      int64_t block_size, int64_t max_seq_len, const std::optional<torch::Tensor>&alibi_slopes,    \
+      const std::string &kv_cache_dtype, torch::Tensor &k_scale, torch::Tensor &v_scale,           \
+      const int64_t tp_rank, const int64_t blocksparse_local_blocks,                               \
+      const int64_t blocksparse_vert_stride, const int64_t blocksparse_block_size,                 \
+      const int64_t blocksparse_head_sliding_step
+#define B200PA_V2_PASS                                                                             \
+  out, exp_sums, max_logits, tmp_out, query, key_cache, value_cache, num_kv_heads, scale,          \
+      block_tables, seq_lens, block_size, max_seq_len, alibi_slopes, kv_cache_dtype, k_scale,      \
+      v_scale, tp_rank, blocksparse_local_blocks, blocksparse_vert_stride, blocksparse_block_size, \
+      blocksparse_head_sliding_step
+
+// The reference's op.  Process-wide switch for an UNMODIFIED caller that reads the partials:
+// B200PA_V2_REFERENCE_SCRATCH=1; a caller that can name the op it wants uses the per-call form
+// below instead.
+void paged_attention_v2(B200PA_V2_ARGS) {
+  const char* ref_scratch = std::getenv("B200PA_V2_REFERENCE_SCRATCH");
+  paged_attention_v2_impl(ref_scratch != nullptr && ref_scratch[0] == '1', B200PA_V2_PASS);
+}
+
+// b200pa::paged_attention_v2_partials -- same schema, and exp_sums / max_logits / tmp_out are
+// filled with the reference's per-partition partials on THIS call, whatever the environment says.
+void paged_attention_v2_partials(B200PA_V2_ARGS) { paged_attention_v2_impl(true, B200PA_V2_PASS); }
+#undef B200PA_V2_ARGS
+#undef B200PA_V2_PASS
 
 // Decode + log-sum-exp (b200pa namespace only; the reference has no such op -- it is what
 // AttentionImpl.can_return_lse_for_decode, abstract.py:115-138, asks of a backend).
@@ -391,6 +415,18 @@ void prefill_attention(torch::Tensor& out, const std::optional<torch::Tensor>& l
   const int kv = kv_code(kv_cache_dtype);
   const int st = scalar_code(query.scalar_type());
   check_cache_dtype(key_cache, query, kv, "key_cache");
+  check_cache_dtype(value_cache, query, kv, "value_cache");
+  for (const torch::Tensor* t : {&out, &key_cache, &value_cache, &block_tables, &query_start_loc,
+                                 &seq_lens, &k_scale, &v_scale})
+    TORCH_CHECK(t->is_cuda() && t->get_device() == query.get_device(),
+                "prefill_attention: every tensor must be on the query's CUDA device");
+  TORCH_CHECK(!alibi_slopes || (alibi_slopes->is_cuda() &&
+                                alibi_slopes->get_device() == query.get_device() &&
+                                alibi_slopes->scalar_type() == at::ScalarType::Float),
+              "alibi_slopes must be a float32 tensor on the query's device");
+  TORCH_CHECK(k_scale.scalar_type() == at::ScalarType::Float && k_scale.numel() >= 1 &&
+                  v_scale.scalar_type() == at::ScalarType::Float && v_scale.numel() >= 1,
+              "k_scale / v_scale must be float32 tensors");
   TORCH_CHECK(query.dim() == 3 && out.dim() == 3, "query / out must be [num_tokens, num_heads, head_size]");
   TORCH_CHECK(out.scalar_type() == query.scalar_type() && out.sizes() == query.sizes(),
               "out must have query's type and shape");
@@ -771,6 +807,12 @@ void define_attention(torch::Library& ops) {
   ops.impl("merge_attn_states", torch::kCUDA, &merge_attn_states);
 }
 void define_extras(torch::Library& ops) {
+  {
+    std::string schema(kSchemaV2);
+    schema.replace(0, std::string("paged_attention_v2").size(), "paged_attention_v2_partials");
+    ops.def(schema.c_str());
+    ops.impl("paged_attention_v2_partials", torch::kCUDA, &paged_attention_v2_partials);
+  }
   ops.def(kSchemaLse);
   ops.impl("paged_attention_lse", torch::kCUDA, &paged_attention_lse);
   ops.def(kSchemaStep);

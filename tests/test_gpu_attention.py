@@ -626,13 +626,14 @@ def test_strided_query_and_padded_cache(ops, ora, version, kv):
     _close(out.cpu(), want)
 
 
-@pytest.mark.parametrize("mode", ["generic", "env"])
+@pytest.mark.parametrize("mode", ["generic", "env", "op"])
 def test_v2_scratch_contract(ops, native, mode, monkeypatch):
     """After paged_attention_v2 through the generic kernel the scratch buffers hold the
     reference's partials: merging them with the reference's reduce formula
     (attention_kernels.cuh:560-664) reproduces `out`.  The default (stream) path keeps its
     partials in its own workspace and leaves the caller's scratch untouched; a caller that reads
-    the scratch sets B200PA_V2_REFERENCE_SCRATCH=1 (mode "env": no test hook involved)."""
+    the scratch sets B200PA_V2_REFERENCE_SCRATCH=1 (mode "env": no test hook involved) or calls
+    b200pa::paged_attention_v2_partials (mode "op": per call, no process-wide state)."""
     B, H, Hkv, D, BS, NB = 4, 16, 4, 128, 16, 600
     lens = [4096, 513, 100, 2049]
     s = D ** -0.5
@@ -640,6 +641,9 @@ def test_v2_scratch_contract(ops, native, mode, monkeypatch):
                                              lo=-s, hi=s)
     if mode == "env":
         monkeypatch.setenv("B200PA_V2_REFERENCE_SCRATCH", "1")
+    elif mode == "op":
+        # the per-call form: same schema, partials guaranteed on this call
+        monkeypatch.setattr(ops, "paged_attention_v2", ops.paged_attention_v2_partials)
     else:
         native.set_impl(GENERIC)
     try:
@@ -945,6 +949,44 @@ def test_backend_decode_step_matches_oracle(ora, kv):
     # and the cache bytes are the oracle's
     assert torch.equal(kv_cache[0].cpu().view(torch.uint8), kc_o.reshape(NB, -1).view(torch.uint8))
     assert torch.equal(kv_cache[1].cpu().view(torch.uint8), vc_o.reshape(NB, -1).view(torch.uint8))
+
+
+@pytest.mark.parametrize("head_size", [128, 120])
+def test_forward_decode_long_context_needs_no_scratch_on_the_one_launch_path(ops, head_size):
+    """PagedAttention.forward_decode beyond the reference's v1 limit (8192 tokens): where the
+    one-launch kernels serve the shape it allocates none of the reference's v2 scratch
+    ([seqs, heads, partitions, head_size] + two fp32 tensors) and returns what paged_attention_v2
+    returns; a shape left to the SIMT kernel (head size 120) keeps the reference's v1 / v2 choice."""
+    from vllm_main_modify_b200.paged_attn import PagedAttention
+    B, H, Hkv, D, BS = 2, 64, 8, head_size, 16
+    lens = [9000, 300]
+    s = D ** -0.5
+    q, kc, vc, bt, sl = hp.make_paged_inputs(B, H, Hkv, D, BS, 600, lens, torch.bfloat16, seed=12,
+                                             lo=-s, hi=s, permute=True)
+    qd, kcd, vcd, btd, sld = (t.to(DEV) for t in (q, kc, vc, bt, sl))
+    one = torch.tensor(1.0, device=DEV)
+    P = (9000 + 511) // 512
+    es = torch.empty(B, H, P, dtype=torch.float32, device=DEV)
+    ml = torch.empty_like(es)
+    tmp = torch.empty(B, H, P, D, dtype=qd.dtype, device=DEV)
+    want = torch.empty_like(qd)
+    ops.paged_attention_v2(want, es, ml, tmp, qd, kcd, vcd, Hkv, s, btd, sld, BS, 9000, None,
+                           "auto", one, one)
+    out = torch.empty_like(qd)
+    torch.cuda.synchronize()
+    torch.cuda.reset_peak_memory_stats()
+    base = torch.cuda.memory_allocated()
+    got = PagedAttention.forward_decode(qd, kcd, vcd, btd, sld, 9000, "auto", Hkv, s, None, one,
+                                        one, output=out)
+    torch.cuda.synchronize()
+    grew = torch.cuda.max_memory_allocated() - base
+    assert got is out
+    assert torch.equal(out, want)
+    scratch = tmp.numel() * tmp.element_size()
+    if head_size == 128:
+        assert grew < scratch // 8, grew
+    else:
+        assert grew >= scratch, grew
 
 
 # ------------------------------------------------- one launch per step, shared workspace

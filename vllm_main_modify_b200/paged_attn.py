@@ -10,6 +10,8 @@ from . import _custom_ops as ops
 
 # Same as PARTITION_SIZE of the split-K kernel (paged_attn.py:21 of the reference).
 _PARTITION_SIZE = 512
+# head sizes the one-launch decode kernels serve (csrc/paged_attention_stream.cu, stream_supported)
+_STREAM_HEAD_SIZES = (32, 64, 80, 96, 112, 128, 192, 256)
 
 
 @dataclass
@@ -90,8 +92,15 @@ class PagedAttention:
             output = torch.empty_like(query)
         block_size = value_cache.shape[3]
         num_seqs, num_heads, head_size = query.shape
-        max_num_partitions = (max_seq_len + _PARTITION_SIZE - 1) // _PARTITION_SIZE
-        if PagedAttention.use_v1(max_seq_len, num_seqs, num_heads):
+        # The decode kernels split long contexts by their own schedule inside ONE launch and keep
+        # their partials in the library's workspace, so where they serve the shape there is no
+        # v1 / v2 choice to make and no per-call scratch to allocate (the reference's
+        # [num_seqs, num_heads, partitions, head_size] tmp_output is 128 MiB for 128 x 64 heads at
+        # 32K context).  Only the shapes left to the SIMT kernel (head size 120, 8-token blocks,
+        # fp32) keep the reference's heuristic and its scratch.
+        one_launch = (block_size in (16, 32) and head_size in _STREAM_HEAD_SIZES
+                      and query.dtype in (torch.float16, torch.bfloat16))
+        if one_launch or PagedAttention.use_v1(max_seq_len, num_seqs, num_heads):
             ops.paged_attention_v1(
                 output, query, key_cache, value_cache, num_kv_heads, scale,
                 block_tables, seq_lens, block_size, max_seq_len, alibi_slopes,
@@ -100,6 +109,7 @@ class PagedAttention:
                 blocksparse_block_size, blocksparse_head_sliding_step)
         else:
             assert _PARTITION_SIZE % block_size == 0
+            max_num_partitions = (max_seq_len + _PARTITION_SIZE - 1) // _PARTITION_SIZE
             tmp_output = torch.empty(
                 size=(num_seqs, num_heads, max_num_partitions, head_size),
                 dtype=output.dtype, device=output.device)

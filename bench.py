@@ -290,6 +290,89 @@ def _diff(got, want):
     return ok, float(d.max()), max_rel
 
 
+def time_ref_cuda(ref, w, steps, graph):
+    """The kernel to beat, on the same box and the same tensors: the reference's own
+    reshape_and_cache + paged_attention_v2 (compiled unmodified for sm_100a) on a clone of the
+    cache, `steps` steps after one warm-up, CUDA events around them (one graph replay when our own
+    leg of this config is timed that way).  Scratch is allocated once, outside the timed steps --
+    kinder to the reference than its PagedAttention.forward_decode, which allocates per call
+    (paged_attn.py:163-173).  Harness shape: benchmarks/kernels/benchmark_paged_attention.py:
+    183-193 of the reference.  CHECKER-side only: never inside our timed region."""
+    from vllm_main_modify_b200.paged_attn import PagedAttention
+    cache = w["kv_caches"][0].clone()
+    kc, vc = PagedAttention.split_kv_cache(cache, w["Hkv"], D)
+    q = w["q"]
+    B, H, _ = q.shape
+    P = (w["max_len"] + 511) // 512
+    es = torch.empty(B, H, P, dtype=torch.float32, device=q.device)
+    ml = torch.empty_like(es)
+    tmp = torch.empty(B, H, P, D, dtype=q.dtype, device=q.device)
+    o = torch.empty_like(q)
+
+    def one():
+        ref.reshape_and_cache(w["k_new"], w["v_new"], kc, vc, w["slots"], w["kv"], w["ks"], w["vs"])
+        ref.paged_attention_v2(o, es, ml, tmp, q, kc, vc, w["Hkv"], w["scale"], w["bt"], w["sl"],
+                               BS, w["max_len"], None, w["kv"], w["ks"], w["vs"], 0, 0, 0, 64, 0)
+
+    one()
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if graph:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=side):
+                for _ in range(steps):
+                    one()
+        torch.cuda.current_stream().wait_stream(side)
+        g.replay()
+        torch.cuda.synchronize()
+        ev0.record()
+        g.replay()
+        ev1.record()
+    else:
+        ev0.record()
+        for _ in range(steps):
+            one()
+        ev1.record()
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1) / steps
+    del cache, kc, vc, es, ml, tmp, o
+    torch.cuda.empty_cache()
+    return ms
+
+
+def ref_cuda_entry(w, world, dev, our_ms_step, total_bytes, graph, steps=3):
+    """{"ms_per_step", "gbs", "speedup"} of the reference's CUDA kernels on this workload (max over
+    ranks), or why there is none."""
+    import torch.distributed as dist
+    try:
+        from oracle import ref_cuda as ref
+        if not os.path.exists(ref.LIB_PATH):
+            raise RuntimeError("oracle/_ref/libvllm_ref_cuda.so is not built")
+        ref.load()
+        ms = time_ref_cuda(ref, w, steps, graph)
+    except Exception as exc:   # every rank fails alike (same files): no collective to keep in step
+        return {"unavailable": str(exc)}
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t[0])
+    return {"ms_per_step": round(ms, 4), "gbs": round(total_bytes / (ms * 1e-3) / 1e9, 1),
+            "speedup": round(ms / our_ms_step, 2), "steps": steps,
+            "what": "reference CUDA reshape_and_cache + paged_attention_v2 (oracle/_ref/"
+                    "libvllm_ref_cuda.so, sm_100a build of the reference's own sources) on a clone "
+                    "of the timed tensors; speedup = its ms_per_step / ours (device-timed)"}
+
+
+def parity_status(parity):
+    """ "ok" | "failed" | "unchecked" -- an absent checker must not read as a pass."""
+    if not parity.get("checked"):
+        return "unchecked"
+    return "ok" if parity.get("ok") else "failed"
+
+
 def parity_check(cfg, w, out, fused, rank, world, dev):
     """Runs ONE step of the op that is about to be timed, on the tensors that are about to be
     timed, and compares output and cache bytes with the reference's CUDA kernels run on a clone
@@ -478,9 +561,12 @@ def run_side_config(cfg, rank, world, dev, fused, check, barrier, native, peak, 
     ms_step = float(st[0]) / steps
     gbs = float(tot[0]) / (ms_step * 1e-3) / 1e9
     op_gbs = float(tot[0]) / world / (float(st[1]) * 1e-3) / 1e9
+    ref_cuda = (ref_cuda_entry(w, world, dev, ms_step, float(tot[0]), graph) if check
+                else {"unavailable": "--no-check"})
     del w, out
     torch.cuda.empty_cache()
     return {"gbs": round(gbs, 1), "ms_per_step": round(ms_step, 4), "steps": steps,
+            "ref_cuda": ref_cuda, "parity_status": parity_status(par),
             "kv_bytes_total": int(tot[0]), "gbs_per_gpu": round(gbs / world, 1),
             "frac_of_measured_hbm": round(gbs / world / peak, 4),
             "pct_of_8TBps": round(100.0 * gbs / world / HBM_NOMINAL_GBPS, 2),
@@ -716,6 +802,10 @@ def run_ours(args):
     ms_total, ms_e2e, attn_ms, ms_e2e_graph = [float(x) for x in stats.tolist()]
     total_bytes, total_launches = tot.tolist()
 
+    # ---- the kernel to beat on this box: the reference's own CUDA kernels, same tensors -------
+    ref_cuda_main = (ref_cuda_entry(w, world, dev, ms_total / K, total_bytes, False)
+                     if args.check else {"unavailable": "--no-check"})
+
     # ---- the other BASELINE configs (driver-visible, 10 steps each) ---------
     del w, impl, meta, meta2, q2, k2, v2, dbuf, dq, dk, dv, dbt, dsl, dslots, e2e_caches
     torch.cuda.empty_cache()
@@ -772,6 +862,8 @@ def run_ours(args):
             "pct_of_8TBps": round(100.0 * value / world / HBM_NOMINAL_GBPS, 2),
             "pct_of_measured_hbm": round(100.0 * value / world / peak, 2),
             "parity": parity,
+            "parity_status": parity_status(parity),
+            "ref_cuda": ref_cuda_main,
             "e2e": {"value": round(e2e_val, 1), "unit": "GB/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "ms_per_step": round(ms_e2e / K, 4),
                     "tokens_per_s": round(B / (ms_e2e / K * 1e-3), 1),
@@ -824,11 +916,17 @@ def run_ours(args):
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)
     bad = parity.get("checked") and not parity.get("ok")
+    unchecked = args.check and not parity.get("checked")
     if world > 1:
         dist.destroy_process_group()
     if bad:
         raise SystemExit("bench.py: PARITY FAILED against the reference's CUDA kernels: "
                          + json.dumps(parity))
+    if unchecked:
+        # the line above carries "parity_status": "unchecked"; a run without its checker is not a
+        # pass (build oracle/_ref with __graft_entry__.build(), or say --no-check)
+        raise SystemExit("bench.py: PARITY UNCHECKED (" + str(parity.get("why")) + "); the number "
+                         "above was not compared with the reference's CUDA kernels")
 
 
 # ----------------------------------------------------------------------------
